@@ -1,0 +1,76 @@
+"""Pin the CPU oracle (oracle/sparse_chain.py) against fixtures produced by the reference's own
+golden functions (tests/golden/make_golden.py imports /root/reference/tests/utils.py)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import sparse_chain as oc
+
+CHAINS = ["chain_small", "chain_32k", "chain_ragged", "chain_randn"]
+
+
+def load(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, name + ".npz"))
+    return {k: (torch.from_numpy(z[k]) if z[k].ndim > 0 else z[k].item()) for k in z.files}
+
+
+def crop_pad(pos, width):
+    """The golden's width is max_b(pl) (utils.py:45-48), the op's is max_page_num: pad/crop with
+    INT32_MAX before comparing."""
+    B, H, W = pos.shape
+    out = torch.full((B, H, width), oc.INT32_MAX, dtype=torch.int32)
+    w = min(W, width)
+    out[:, :, :w] = pos[:, :, :w]
+    return out
+
+
+@pytest.mark.parametrize("name", CHAINS)
+def test_compute_cent_matches_reference_golden(golden_dir, name):
+    f = load(golden_dir, name)
+    got = oc.compute_cent(f["q"], f["l1"], k=64)
+    assert got.dtype == torch.int32
+    assert torch.equal(got, f["ref_indices"])          # order included (fixtures are tie-free)
+
+
+@pytest.mark.parametrize("name", CHAINS)
+def test_select_position_matches_reference_golden(golden_dir, name):
+    f = load(golden_dir, name)
+    Bs = f["seq_len"].shape[0]
+    pos, plen, gather = oc.select_position(f["block_ids"], f["block_table"], f["seq_len"],
+                                           f["ref_indices"][:Bs], f["block_size"], 256)
+    assert torch.equal(pos, crop_pad(f["ref_pos"], 256))
+    assert torch.equal(plen[:, :, 0], f["ref_len"])
+    assert bool((plen == plen[:, :, :1]).all())       # x8 replication
+    W = f["ref_cfull"].shape[2]
+    assert torch.equal(gather[:, :, :W], f["ref_cfull"])
+
+
+@pytest.mark.parametrize("name", CHAINS)
+def test_cent_select_chain_matches_reference_golden(golden_dir, name):
+    f = load(golden_dir, name)
+    pos, plen, mx = oc.cent_select(f["q"], f["l1"], f["block_ids"], f["block_table"], f["seq_len"],
+                                   k=64, block_size=f["block_size"], max_page_num=256)
+    assert torch.equal(pos, crop_pad(f["ref_pos"], 256))
+    # tests/cent_select.py:96-98
+    want = f["ref_len"].to(torch.int64).max(dim=1)[0] * f["block_size"]
+    assert mx.dtype == torch.int64 and mx.shape == (f["seq_len"].shape[0], 8)
+    assert torch.equal(mx[:, 0], want) and bool((mx == mx[:, :1]).all())
+
+
+def test_select_position_duplicate_indices(golden_dir):
+    f = load(golden_dir, "select_dupes")               # tests/select_position.py:42-45
+    pos, plen, gather = oc.select_position(f["block_ids"], f["block_table"], f["seq_len"],
+                                           f["indices"], f["block_size"], 256)
+    assert torch.equal(pos, crop_pad(f["ref_pos"], 256))
+    assert torch.equal(plen[:, :, 0], f["ref_len"])
+    W = f["ref_cfull"].shape[2]
+    assert torch.equal(gather[:, :, :W], f["ref_cfull"])
+
+
+def test_topk_tie_break_lowest_index():
+    s = np.zeros((1, 1, 16))
+    s[0, 0, [3, 7, 9]] = 1.0
+    got = oc.topk_indices(s, 6)
+    assert got.tolist() == [[[3, 7, 9, 0, 1, 2]]]
