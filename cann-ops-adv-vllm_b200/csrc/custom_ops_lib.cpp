@@ -1,0 +1,357 @@
+// PyTorch binding of the B200 sparse decode-attention chain: module `custom_ops_lib` and the
+// `myops` operator library, drop-in for the reference's extension/csrc/{add_custom.cpp,
+// registration.cpp, pytorch_npu_helper.hpp}.  It does what EXEC_NPU_CMD does there
+// (pytorch_npu_helper.hpp:721-800): convert at::Tensor -> C descriptors, call
+// <Op>GetWorkspaceSize, allocate the workspace from the caching allocator, launch on the current
+// stream -- but against the C ABI in include/spa_b200.h and CUDA streams.  No compute lives here.
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <torch/extension.h>
+#include <torch/library.h>
+
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/spa_b200.h"
+
+namespace {
+
+// Reference constants (add_custom.cpp:940,958,987; select_position.cpp:7); keyword-overridable
+// from Python, see custom_ops/add_custom.py.
+constexpr int64_t kDefaultK = 64;
+constexpr int64_t kDefaultMaxPageNum = 256;
+constexpr int64_t kDefaultBlockSize = 128;
+constexpr int64_t kPad = 8;
+
+int to_spa_dtype(at::ScalarType t) {
+    switch (t) {
+        case at::kHalf: return SPA_F16;
+        case at::kBFloat16: return SPA_BF16;
+        case at::kFloat: return SPA_F32;
+        case at::kChar: return SPA_I8;
+        case at::kInt: return SPA_I32;
+        case at::kLong: return SPA_I64;
+        default: TORCH_CHECK(false, "Unsupported tensor dtype");   // add_custom.cpp:69
+    }
+}
+
+// undefined or zero-element tensor => absent (add_custom.cpp:32-35)
+struct Desc {
+    spaTensor t;
+    bool present;
+    const spaTensor *ptr() const { return present ? &t : nullptr; }
+};
+
+Desc desc(const at::Tensor &x, const char *name, bool keep_empty = false) {
+    Desc d{};
+    d.present = false;
+    if (!x.defined()) return d;
+    if (x.numel() == 0 && !keep_empty) return d;
+    TORCH_CHECK(x.is_cuda(), name, ": expected a CUDA tensor");
+    TORCH_CHECK(x.dim() <= SPA_MAX_DIMS, name, ": too many dims");
+    d.t.data = x.numel() ? x.data_ptr() : nullptr;
+    d.t.dtype = to_spa_dtype(x.scalar_type());
+    d.t.ndim = (int32_t)x.dim();
+    for (int i = 0; i < x.dim(); ++i) { d.t.sizes[i] = x.size(i); d.t.strides[i] = x.stride(i); }
+    d.present = true;
+    return d;
+}
+
+void check(int rc, const char *what) {
+    TORCH_CHECK(rc == SPA_OK, what, " failed (", rc, "): ", spaGetLastError());
+}
+
+struct ExecGuard {
+    spaExecutor *e = nullptr;
+    ~ExecGuard() { if (e) spaDestroyExecutor(e); }
+};
+
+at::Tensor alloc_ws(uint64_t bytes, const at::Tensor &like) {
+    return at::empty({(int64_t)std::max<uint64_t>(bytes, 256)}, like.options().dtype(at::kByte));
+}
+
+at::Tensor seq_on_device(const at::Tensor &t, const at::Tensor &like) {
+    // the reference copies actual_seq_lengths to the HOST (add_custom.cpp:105-118); here the kernel
+    // reads it on device, so a host tensor is uploaded instead.
+    if (!t.defined() || t.numel() == 0) return t;
+    at::Tensor r = t.to(at::kLong);
+    if (!r.is_cuda()) r = r.to(like.device(), /*non_blocking=*/true);
+    return r.contiguous();
+}
+
+// ------------------------------------------------------------------------------------------
+at::Tensor compute_cent_k(const at::Tensor &query, const at::Tensor &l1_cent, int64_t k) {
+    TORCH_CHECK(query.is_cuda(), "compute_cent: the CUDA extension only runs on CUDA tensors");
+    c10::cuda::CUDAGuard guard(query.device());
+    at::Tensor result = at::empty({query.size(0), query.size(1), k}, query.options().dtype(at::kInt));
+    Desc q = desc(query, "query"), c = desc(l1_cent, "l1_cent"), r = desc(result, "indices", true);
+    uint64_t ws = 0; ExecGuard g;
+    check(spaComputeCentGetWorkspaceSize(q.ptr(), c.ptr(), r.ptr(), &ws, &g.e), "compute_cent");
+    check(spaComputeCent(nullptr, 0, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "compute_cent");
+    return result;
+}
+at::Tensor compute_cent(const at::Tensor &query, const at::Tensor &l1_cent) {
+    return compute_cent_k(query, l1_cent, kDefaultK);
+}
+
+std::tuple<at::Tensor, at::Tensor, at::Tensor> select_position_ex(
+    const at::Tensor &block_ids, const at::Tensor &block_table, const at::Tensor &seq_len,
+    const at::Tensor &indices, int64_t max_page_num, int64_t block_size) {
+    TORCH_CHECK(block_ids.is_cuda(), "select_position: the CUDA extension only runs on CUDA tensors");
+    c10::cuda::CUDAGuard guard(block_ids.device());
+    const int64_t B = indices.size(0), Nq = indices.size(1), maxP = block_table.size(1);
+    TORCH_CHECK(seq_len.dim() == 1 && seq_len.size(0) <= B, "select_position: seq_len must be [B]");
+    const int64_t Bs = seq_len.size(0);
+    auto opt = block_ids.options();
+    at::Tensor pp = at::empty({B, Nq, max_page_num}, opt);
+    at::Tensor ppl = at::empty({B, Nq, kPad}, opt);
+    at::Tensor gather = at::empty({B, Nq, maxP}, opt);
+    at::Tensor pp_v = pp.narrow(0, 0, Bs), ppl_v = ppl.narrow(0, 0, Bs), ga_v = gather.narrow(0, 0, Bs);
+    Desc a = desc(block_ids, "block_ids"), b = desc(block_table, "block_table"), c = desc(seq_len, "seq_len"),
+         d = desc(indices, "indices"), o1 = desc(pp_v, "page_position"), o2 = desc(ppl_v, "page_position_length"),
+         o3 = desc(ga_v, "block_table_gather");
+    uint64_t ws = 0; ExecGuard g;
+    check(spaSelectPositionGetWorkspaceSize(a.ptr(), b.ptr(), c.ptr(), d.ptr(), block_size, o1.ptr(), o2.ptr(),
+                                            o3.ptr(), &ws, &g.e), "select_position");
+    check(spaSelectPosition(nullptr, 0, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "select_position");
+    return std::make_tuple(pp, ppl, gather);
+}
+std::tuple<at::Tensor, at::Tensor, at::Tensor> select_position(const at::Tensor &block_ids,
+                                                               const at::Tensor &block_table,
+                                                               const at::Tensor &seq_len,
+                                                               const at::Tensor &indices) {
+    return select_position_ex(block_ids, block_table, seq_len, indices, kDefaultMaxPageNum, kDefaultBlockSize);
+}
+
+std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select_ex(
+    const at::Tensor &query, const at::Tensor &l1_cent, const at::Tensor &block_ids,
+    const at::Tensor &block_table, const at::Tensor &seq_len, int64_t k, int64_t max_page_num,
+    int64_t block_size) {
+    TORCH_CHECK(query.is_cuda(), "cent_select: the CUDA extension only runs on CUDA tensors");
+    c10::cuda::CUDAGuard guard(query.device());
+    const int64_t B = seq_len.size(0), Nq = query.size(1);          // add_custom.cpp:988
+    auto opt = block_ids.options();
+    at::Tensor pp = at::empty({B, Nq, max_page_num}, opt);
+    at::Tensor ppl = at::empty({B, Nq, kPad}, opt);
+    at::Tensor mppl = at::empty({B, kPad}, opt.dtype(at::kLong));
+    Desc q = desc(query, "query"), c = desc(l1_cent, "l1_cent"), a = desc(block_ids, "block_ids"),
+         b = desc(block_table, "block_table"), s = desc(seq_len, "seq_len"), o1 = desc(pp, "page_position", true),
+         o2 = desc(ppl, "page_position_length", true), o3 = desc(mppl, "max_page_position_length", true);
+    if (B == 0) return std::make_tuple(pp, ppl, mppl);
+    uint64_t ws = 0; ExecGuard g;
+    check(spaCentSelectGetWorkspaceSize(q.ptr(), c.ptr(), a.ptr(), b.ptr(), s.ptr(), k, block_size, o1.ptr(),
+                                        o2.ptr(), o3.ptr(), &ws, &g.e), "cent_select");
+    check(spaCentSelect(nullptr, 0, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "cent_select");
+    return std::make_tuple(pp, ppl, mppl);
+}
+std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select(const at::Tensor &query, const at::Tensor &l1_cent,
+                                                           const at::Tensor &block_ids,
+                                                           const at::Tensor &block_table,
+                                                           const at::Tensor &seq_len) {
+    return cent_select_ex(query, l1_cent, block_ids, block_table, seq_len, kDefaultK, kDefaultMaxPageNum,
+                          kDefaultBlockSize);
+}
+
+const at::Tensor &single(const std::vector<at::Tensor> &l, const char *name) {
+    TORCH_CHECK(l.size() == 1, name, ": expected a 1-element tensor list (add_custom.py:70-75)");
+    return l[0];
+}
+
+at::Tensor sparse_paged_attention(
+    const at::Tensor &query, const std::vector<at::Tensor> &key_list, const std::vector<at::Tensor> &value_list,
+    const at::Tensor &pse_shift, const at::Tensor &attention_mask, const at::Tensor &actual_seq_lengths,
+    const at::Tensor &dequant_scale1, const at::Tensor &quant_scale1, const at::Tensor &dequant_scale2,
+    const at::Tensor &quant_scale2, const at::Tensor &quant_offset2, const at::Tensor &antiquant_scale,
+    const at::Tensor &antiquant_offset, const at::Tensor &blocktable, const at::Tensor &kv_padding_size,
+    const at::Tensor &blockposition, int64_t num_heads, double scale_value, std::string input_layout,
+    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise) {
+    TORCH_CHECK(query.is_cuda(), "sparse_paged_attention: the CUDA extension only runs on CUDA tensors");
+    c10::cuda::CUDAGuard guard(query.device());
+    const at::Tensor &key = single(key_list, "key_list"), &value = single(value_list, "value_list");
+    at::Tensor out = at::empty(query.sizes(), query.options());                  // add_custom.cpp:559-560
+    at::Tensor asl = seq_on_device(actual_seq_lengths, query);
+    Desc q = desc(query, "query"), k = desc(key, "key"), v = desc(value, "value"), pse = desc(pse_shift, "pse_shift"),
+         am = desc(attention_mask, "attention_mask"), sl = desc(asl, "actual_seq_lengths"),
+         d1 = desc(dequant_scale1, "dequant_scale1"), q1 = desc(quant_scale1, "quant_scale1"),
+         d2 = desc(dequant_scale2, "dequant_scale2"), q2 = desc(quant_scale2, "quant_scale2"),
+         qo2 = desc(quant_offset2, "quant_offset2"), as = desc(antiquant_scale, "antiquant_scale"),
+         ao = desc(antiquant_offset, "antiquant_offset"), bt = desc(blocktable, "blocktable"),
+         kp = desc(kv_padding_size, "kv_padding_size"), bp = desc(blockposition, "blockposition"),
+         o = desc(out, "attention_out", true);
+    if (query.numel() == 0) return out;
+    uint64_t ws = 0; ExecGuard g;
+    check(spaSparsePagedAttentionGetWorkspaceSize(q.ptr(), k.ptr(), v.ptr(), pse.ptr(), am.ptr(), sl.ptr(), d1.ptr(),
+                                                  q1.ptr(), d2.ptr(), q2.ptr(), qo2.ptr(), as.ptr(), ao.ptr(), bt.ptr(),
+                                                  kp.ptr(), bp.ptr(), num_heads, scale_value, input_layout.c_str(),
+                                                  num_key_value_heads, block_size, inner_precise, o.ptr(), &ws, &g.e),
+          "sparse_paged_attention");
+    at::Tensor wsp = alloc_ws(ws, query);
+    check(spaSparsePagedAttention(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()),
+          "sparse_paged_attention");
+    return out;
+}
+
+// ---- fused op: plan object so callers can keep a launch-ready executor (CUDA graphs, serving) --
+struct FusionPlan {
+    spaExecutor *exec = nullptr;
+    uint64_t ws_bytes = 0;
+    at::Tensor workspace;
+    std::vector<at::Tensor> keep;     // keeps the planned tensors alive
+    ~FusionPlan() { if (exec) spaDestroyExecutor(exec); }
+};
+
+std::shared_ptr<FusionPlan> make_fusion_plan(
+    const at::Tensor &query, const at::Tensor &key, const at::Tensor &value, const at::Tensor &antiquant_scale,
+    const at::Tensor &antiquant_offset, const at::Tensor &blocktable, const at::Tensor &l1_cent,
+    const at::Tensor &block_ids, const at::Tensor &total_seq_len, const at::Tensor &block_position,
+    const at::Tensor &page_position_length, const at::Tensor &max_page_position_length,
+    const at::Tensor &attention_out, int64_t num_heads, double scale_value, const std::string &input_layout,
+    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k) {
+    TORCH_CHECK(query.is_cuda(), "sparse_paged_fusion_attention: the CUDA extension only runs on CUDA tensors");
+    c10::cuda::CUDAGuard guard(query.device());
+    auto plan = std::make_shared<FusionPlan>();
+    Desc q = desc(query, "query"), kk = desc(key, "key"), v = desc(value, "value"),
+         as = desc(antiquant_scale, "antiquant_scale"), ao = desc(antiquant_offset, "antiquant_offset"),
+         bt = desc(blocktable, "blocktable"), lc = desc(l1_cent, "l1_cent"), bi = desc(block_ids, "block_ids"),
+         ts = desc(total_seq_len, "total_seq_len"), bp = desc(block_position, "block_position", true),
+         pl = desc(page_position_length, "page_position_length", true),
+         mp = desc(max_page_position_length, "max_page_position_length", true),
+         o = desc(attention_out, "attention_out", true);
+    check(spaSparsePagedFusionAttentionGetWorkspaceSize(
+              q.ptr(), kk.ptr(), v.ptr(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+              as.ptr(), ao.ptr(), bt.ptr(), nullptr, lc.ptr(), bi.ptr(), ts.ptr(), num_heads, scale_value,
+              input_layout.c_str(), num_key_value_heads, block_size, inner_precise, k, bp.ptr(), pl.ptr(), mp.ptr(),
+              o.ptr(), &plan->ws_bytes, &plan->exec),
+          "sparse_paged_fusion_attention");
+    plan->workspace = alloc_ws(plan->ws_bytes, query);
+    plan->keep = {query, key, value, antiquant_scale, antiquant_offset, blocktable, l1_cent, block_ids,
+                  total_seq_len, block_position, page_position_length, max_page_position_length, attention_out};
+    return plan;
+}
+
+void launch_fusion_plan(const std::shared_ptr<FusionPlan> &plan) {
+    c10::cuda::CUDAGuard guard(plan->workspace.device());
+    check(spaSparsePagedFusionAttention(plan->workspace.data_ptr(), plan->ws_bytes, plan->exec,
+                                        (spaStream)at::cuda::getCurrentCUDAStream().stream()),
+          "sparse_paged_fusion_attention");
+}
+
+std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention_ex(
+    const at::Tensor &query, const std::vector<at::Tensor> &key_list, const std::vector<at::Tensor> &value_list,
+    const at::Tensor &pse_shift, const at::Tensor &attention_mask, const at::Tensor &actual_seq_lengths,
+    const at::Tensor &dequant_scale1, const at::Tensor &quant_scale1, const at::Tensor &dequant_scale2,
+    const at::Tensor &quant_scale2, const at::Tensor &quant_offset2, const at::Tensor &antiquant_scale,
+    const at::Tensor &antiquant_offset, const at::Tensor &blocktable, const at::Tensor &kv_padding_size,
+    const at::Tensor &l1_cent, const at::Tensor &block_ids, const at::Tensor &total_seq_len,
+    const at::Tensor &block_position, const at::Tensor &page_position_length,
+    const at::Tensor &max_page_position_length, int64_t num_heads, double scale_value, std::string input_layout,
+    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k) {
+    TORCH_CHECK(query.is_cuda(), "sparse_paged_fusion_attention: the CUDA extension only runs on CUDA tensors");
+    c10::cuda::CUDAGuard guard(query.device());
+    const at::Tensor &key = single(key_list, "key_list"), &value = single(value_list, "value_list");
+    (void)actual_seq_lengths;    // ignored by the fused kernel (sparse_paged_fusion_attention.cpp:68)
+    at::Tensor out = at::empty(query.sizes(), query.options());                  // add_custom.cpp:800-801
+    Desc q = desc(query, "query"), kk = desc(key, "key"), v = desc(value, "value"), pse = desc(pse_shift, "pse_shift"),
+         am = desc(attention_mask, "attention_mask"), d1 = desc(dequant_scale1, "dequant_scale1"),
+         q1 = desc(quant_scale1, "quant_scale1"), d2 = desc(dequant_scale2, "dequant_scale2"),
+         q2 = desc(quant_scale2, "quant_scale2"), qo2 = desc(quant_offset2, "quant_offset2"),
+         as = desc(antiquant_scale, "antiquant_scale"), ao = desc(antiquant_offset, "antiquant_offset"),
+         bt = desc(blocktable, "blocktable"), kp = desc(kv_padding_size, "kv_padding_size"),
+         lc = desc(l1_cent, "l1_cent"), bi = desc(block_ids, "block_ids"), ts = desc(total_seq_len, "total_seq_len"),
+         bp = desc(block_position, "block_position", true), pl = desc(page_position_length, "page_position_length", true),
+         mp = desc(max_page_position_length, "max_page_position_length", true), o = desc(out, "attention_out", true);
+    if (total_seq_len.numel() == 0) return std::make_tuple(out, block_position, max_page_position_length);
+    uint64_t ws = 0; ExecGuard g;
+    // C-level order: inputs, attrs, the three aux outputs, attention_out (add_custom.cpp:836-844)
+    check(spaSparsePagedFusionAttentionGetWorkspaceSize(
+              q.ptr(), kk.ptr(), v.ptr(), pse.ptr(), am.ptr(), nullptr, d1.ptr(), q1.ptr(), d2.ptr(), q2.ptr(), qo2.ptr(),
+              as.ptr(), ao.ptr(), bt.ptr(), kp.ptr(), lc.ptr(), bi.ptr(), ts.ptr(), num_heads, scale_value,
+              input_layout.c_str(), num_key_value_heads, block_size, inner_precise, k, bp.ptr(), pl.ptr(), mp.ptr(),
+              o.ptr(), &ws, &g.e),
+          "sparse_paged_fusion_attention");
+    at::Tensor wsp = alloc_ws(ws, query);
+    check(spaSparsePagedFusionAttention(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()),
+          "sparse_paged_fusion_attention");
+    return std::make_tuple(out, block_position, max_page_position_length);       // add_custom.cpp:931
+}
+
+std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention(
+    const at::Tensor &query, const std::vector<at::Tensor> &key_list, const std::vector<at::Tensor> &value_list,
+    const at::Tensor &pse_shift, const at::Tensor &attention_mask, const at::Tensor &actual_seq_lengths,
+    const at::Tensor &dequant_scale1, const at::Tensor &quant_scale1, const at::Tensor &dequant_scale2,
+    const at::Tensor &quant_scale2, const at::Tensor &quant_offset2, const at::Tensor &antiquant_scale,
+    const at::Tensor &antiquant_offset, const at::Tensor &blocktable, const at::Tensor &kv_padding_size,
+    const at::Tensor &l1_cent, const at::Tensor &block_ids, const at::Tensor &total_seq_len,
+    const at::Tensor &block_position, const at::Tensor &page_position_length,
+    const at::Tensor &max_page_position_length, int64_t num_heads, double scale_value, std::string input_layout,
+    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise) {
+    return sparse_paged_fusion_attention_ex(query, key_list, value_list, pse_shift, attention_mask,
+                                            actual_seq_lengths, dequant_scale1, quant_scale1, dequant_scale2,
+                                            quant_scale2, quant_offset2, antiquant_scale, antiquant_offset, blocktable,
+                                            kv_padding_size, l1_cent, block_ids, total_seq_len, block_position,
+                                            page_position_length, max_page_position_length, num_heads, scale_value,
+                                            input_layout, num_key_value_heads, block_size, inner_precise, kDefaultK);
+}
+
+at::Tensor incre_flash_attention_v4(
+    const at::Tensor &, const std::vector<at::Tensor> &, const std::vector<at::Tensor> &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &, int64_t, double, std::string, int64_t, int64_t, int64_t) {
+    // The reference routes this entry to the STOCK CANN IncreFlashAttention op (dense baseline, out
+    // of scope: SURVEY 2.2).  The dense comparison is obtained from sparse_paged_attention with an
+    // identity block_position.
+    TORCH_CHECK(false, "incre_flash_attention_v4 (stock dense IFA) is outside the sparse hot path; "
+                       "use sparse_paged_attention with an identity block_position");
+}
+
+}  // namespace
+
+// Schema strings identical to the reference's (extension/csrc/registration.cpp:43-57).
+TORCH_LIBRARY(myops, m) {
+    m.def("incre_flash_attention_v4(Tensor query, Tensor[] key_list, Tensor[] value_list, Tensor pse_shift, Tensor attention_mask, Tensor actual_seq_lengths, Tensor dequant_scale1, Tensor quant_scale1, Tensor dequant_scale2, Tensor quant_scale2, Tensor quant_offset2, Tensor antiquant_scale, Tensor antiquant_offset, Tensor blocktable, Tensor kv_padding_size, int num_heads, float scale_value, str input_layout, int num_key_value_heads, int block_size, int inner_precise) -> Tensor");
+    m.def("sparse_paged_attention(Tensor query, Tensor[] key_list, Tensor[] value_list, Tensor pse_shift, Tensor attention_mask,Tensor actual_seq_lengths, Tensor dequant_scale1, Tensor quant_scale1, Tensor dequant_scale2,Tensor quant_scale2, Tensor quant_offset2, Tensor antiquant_scale, Tensor antiquant_offset, Tensor blocktable,Tensor kv_padding_size, Tensor blockposition, int num_heads, float scale_value, str input_layout,int num_key_value_heads, int block_size, int inner_precise) ->Tensor");
+    m.def("compute_cent(Tensor query, Tensor l1_cent) -> Tensor");
+    m.def("select_position(Tensor block_ids, Tensor block_table, Tensor seq_len, Tensor indices) -> (Tensor, Tensor, Tensor)");
+    m.def("cent_select(Tensor query, Tensor l1_cent, Tensor block_ids, Tensor block_table, Tensor seq_len) -> (Tensor, Tensor, Tensor)");
+    m.def("sparse_paged_fusion_attention("
+          "Tensor query, Tensor[] key_list, Tensor[] value_list, Tensor pse_shift, Tensor attention_mask, Tensor actual_seq_lengths, "
+          "Tensor dequant_scale1, Tensor quant_scale1, Tensor dequant_scale2, Tensor quant_scale2, Tensor quant_offset2, "
+          "Tensor antiquant_scale, Tensor antiquant_offset, Tensor blocktable, Tensor kv_padding_size, "
+          "Tensor l1_cent, Tensor block_ids, Tensor total_seq_len, "
+          "Tensor block_position, Tensor page_position_length, Tensor max_page_position_length, "
+          "int num_heads, float scale_value, str input_layout, int num_key_value_heads, int block_size, int inner_precise) -> (Tensor, Tensor, Tensor)");
+}
+
+// The reference registers for PrivateUse1 (NPU), registration.cpp:60-68; here the CUDA key.
+TORCH_LIBRARY_IMPL(myops, CUDA, m) {
+    m.impl("incre_flash_attention_v4", &incre_flash_attention_v4);
+    m.impl("sparse_paged_attention", &sparse_paged_attention);
+    m.impl("compute_cent", &compute_cent);
+    m.impl("select_position", &select_position);
+    m.impl("cent_select", &cent_select);
+    m.impl("sparse_paged_fusion_attention", &sparse_paged_fusion_attention);
+}
+
+PYBIND11_MODULE(custom_ops_lib, m) {
+    // the six reference entry points (registration.cpp:71-79)
+    m.def("incre_flash_attention_v4", &incre_flash_attention_v4, "FlashAttention V4 (out of scope: raises)");
+    m.def("sparse_paged_attention", &sparse_paged_attention, "Sparse Paged Attention");
+    m.def("compute_cent", &compute_cent, "Compute Cent");
+    m.def("select_position", &select_position, "Select Position");
+    m.def("cent_select", &cent_select, "Cent Select");
+    m.def("sparse_paged_fusion_attention", &sparse_paged_fusion_attention, "Fused Sparse Paged Fusion Attention");
+    // keyword-extended variants used by custom_ops/add_custom.py (defaults == reference constants)
+    m.def("compute_cent_k", &compute_cent_k);
+    m.def("select_position_ex", &select_position_ex);
+    m.def("cent_select_ex", &cent_select_ex);
+    m.def("sparse_paged_fusion_attention_ex", &sparse_paged_fusion_attention_ex);
+    pybind11::class_<FusionPlan, std::shared_ptr<FusionPlan>>(m, "FusionPlan")
+        .def_property_readonly("workspace_bytes", [](const FusionPlan &p) { return p.ws_bytes; })
+        .def_property_readonly("num_launches", [](const FusionPlan &p) { return spaExecutorNumLaunches(p.exec); });
+    m.def("make_fusion_plan", &make_fusion_plan);
+    m.def("launch_fusion_plan", &launch_fusion_plan);
+    m.def("abi_version", []() { return spaGetVersion(); });
+    m.def("compiled_arch", []() { return spaGetCompiledArch(); });
+}

@@ -1,0 +1,248 @@
+// Common definitions for the sm_100a sparse decode-attention chain kernels.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace spa {
+
+constexpr int kD = 128;              // head dim (all reference sparse tests)
+constexpr int kBS = 128;             // tokens per KV page (PAGESIZE, select_position.cpp:7)
+constexpr int kConsumerWarps = 8;    // each owns 16 of the 128 tokens of a page
+constexpr int kThreads = (kConsumerWarps + 1) * 32;   // + 1 TMA producer warp
+constexpr int kSentinel = 0x7fffffff;
+constexpr int kPad = 8;              // x8 replication of the length outputs (add_custom.cpp:963,993)
+constexpr int kMaxGroup = 16;        // q heads per kv head handled by one CTA (2 n8 tiles)
+constexpr float kLog2e = 1.4426950408889634f;
+
+// One launch description, shared by every kernel of the chain.  Filled by the host plan.
+struct ChainParams {
+    // ---- problem dims
+    int B, Nq, Nkv, g;               // g = Nq / Nkv
+    int C, k;                        // clusters, top-k
+    int MP;                          // max_page_num = page_position.shape[2]
+    int maxP;                        // block_table.shape[1]
+    int kvPageLen;                   // block_ids.shape[1]
+    int bs;                          // block size (tokens per page) == kBS
+    int items;                       // B * Nkv work items (b, kv head)
+    // ---- selection inputs
+    const void *q;       long long q_sb, q_sh;          // element strides (batch, head); D contiguous
+    const void *cent;                                    // [Nkv, C, D] contiguous
+    const int *block_ids; long long bid_stride;
+    const int *block_table; long long bt_stride;
+    const int *seq_len;                                  // [B] int32 (total context length)
+    const int *indices_in; long long idx_sb, idx_sh;     // select_position: given indices [B,Nq,k]
+    // ---- selection outputs
+    int *indices_out;                                    // [B,Nq,k] (compute_cent) or null
+    int *page_position;                                  // [B,Nq,MP] or null
+    int *page_position_length;                           // [B,Nq,8] or null
+    long long *max_ppl;                                  // [B,8] or null
+    int *bt_gather;                                      // [B,Nq,maxP] or null
+    // ---- attention inputs
+    const long long *actual_seq; int actual_n;           // separate op: device int64 [B] or [1]
+    const int *bp_in; int bp_heads; long long bp_sb, bp_sh; int bp_len;   // block_position input
+    const void *aq_scale, *aq_offset;                    // int8 KV: [2, Nkv, D] in q dtype (or null)
+    int aq_per_tensor;
+    void *out; long long out_sb, out_sh;
+    float scale_log2;                                    // scale_value * log2(e)
+    int ax_row, ax_head, ax_blk;                         // TMA coordinate slots (1..3)
+    int num_blocks;
+    // ---- workspace
+    int *union_phys;                                     // [items, maxP]
+    unsigned *union_meta;                                // [items, maxP]  mask | tailmask << 16
+    int *union_len;                                      // [items]
+    int *tail_count;                                     // [items]
+    float *part_o;                                       // [slots, HP, D]
+    float *part_ml;                                      // [slots, HP, 2]
+    // ---- launch shape
+    int hb;                                              // heads scored per pass in phase A
+    int nbins;                                           // histogram bins (pow2)
+    int nstages;                                         // pipeline stages
+    int stage_bytes;
+    int smem_bytes;
+    int mode;                                            // see Mode
+};
+
+enum Mode : int {
+    kModeFused = 0,        // scores + topk + select + attention
+    kModeAttnOnly = 1,     // union from block_position + attention
+};
+
+// ------------------------------------------------------------------------------------------
+// small device helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ int warp_id() { return threadIdx.x >> 5; }
+
+template <typename T> struct QTraits;
+template <> struct QTraits<__half> {
+    static __device__ __forceinline__ double to_double(unsigned short bits) {
+        return static_cast<double>(__half2float(__ushort_as_half(bits)));
+    }
+    static __device__ __forceinline__ float to_float(unsigned short bits) {
+        return __half2float(__ushort_as_half(bits));
+    }
+    static __device__ __forceinline__ unsigned short from_float(float f) {
+        return __half_as_ushort(__float2half_rn(f));
+    }
+    static __device__ __forceinline__ uint32_t pack2(float a, float b) {
+        __half2 h = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&h);
+    }
+};
+template <> struct QTraits<__nv_bfloat16> {
+    static __device__ __forceinline__ double to_double(unsigned short bits) {
+        return static_cast<double>(__uint_as_float(static_cast<uint32_t>(bits) << 16));
+    }
+    static __device__ __forceinline__ float to_float(unsigned short bits) {
+        return __uint_as_float(static_cast<uint32_t>(bits) << 16);
+    }
+    static __device__ __forceinline__ unsigned short from_float(float f) {
+        return __bfloat16_as_ushort(__float2bfloat16_rn(f));
+    }
+    static __device__ __forceinline__ uint32_t pack2(float a, float b) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&h);
+    }
+};
+
+// ---- mbarrier / TMA (PTX ISA 8.x, sm_90+/sm_100a) -----------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 4-D tiled TMA load, completion on an mbarrier (SASS: UTMALDG)
+__device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0,
+                                            int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+
+// ---- warp-level matrix ops ------------------------------------------------------------------
+__device__ __forceinline__ void ldmatrix_x4(uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3,
+                                            uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"(addr));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t &r0, uint32_t &r1, uint32_t &r2,
+                                                  uint32_t &r3, uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"(addr));
+}
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
+    uint32_t d;
+    asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+    return d;
+}
+template <typename QT>
+__device__ __forceinline__ void mma_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                          uint32_t a3, uint32_t b0, uint32_t b1);
+template <>
+__device__ __forceinline__ void mma_16816<__half>(float (&c)[4], uint32_t a0, uint32_t a1,
+                                                  uint32_t a2, uint32_t a3, uint32_t b0,
+                                                  uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+        "{%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+template <>
+__device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&c)[4], uint32_t a0, uint32_t a1,
+                                                         uint32_t a2, uint32_t a3, uint32_t b0,
+                                                         uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+        "{%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// ---- int8 -> fp16/bf16 pairs (exact), for the fused KV antiquant ------------------------------
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+// Convert two signed bytes of r (byte indices I and J) to a packed pair {lo = byte I, hi = byte J}.
+template <typename QT, int I, int J> struct I8Pair;
+template <int I, int J> struct I8Pair<__half, I, J> {
+    // 0x6400 | (b + 128) is the half 1024 + (b + 128); subtracting 1152 leaves b exactly
+    static __device__ __forceinline__ uint32_t cvt(uint32_t r) {
+        const uint32_t x = r ^ 0x80808080u;
+        uint32_t h = prmt(x, 0x64646464u, 0x4040u | I | (J << 8));
+        const uint32_t magic = 0x64806480u;
+        __half2 v = __hsub2(*reinterpret_cast<__half2 *>(&h), *reinterpret_cast<const __half2 *>(&magic));
+        return *reinterpret_cast<uint32_t *>(&v);
+    }
+};
+template <int I, int J> struct I8Pair<__nv_bfloat16, I, J> {
+    // 0x4B000000 | (b + 128) is the float 2^23 + (b + 128); |b| <= 128 is exact in bf16
+    static __device__ __forceinline__ uint32_t cvt(uint32_t r) {
+        const uint32_t x = r ^ 0x80808080u;
+        const float fa = __uint_as_float(prmt(x, 0x4B000000u, 0x7440u | I)) - 8388736.f;
+        const float fb = __uint_as_float(prmt(x, 0x4B000000u, 0x7440u | J)) - 8388736.f;
+        return prmt(__float_as_uint(fa), __float_as_uint(fb), 0x7632u);
+    }
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ float fast_exp2(float x) {
+    float y;
+    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// order-preserving map float -> uint32 (larger float => larger key)
+__device__ __forceinline__ uint32_t float_key(float f) {
+    uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// (score desc, index asc) strict total order: does (sa, ia) come before (sb, ib)?
+__device__ __forceinline__ bool precedes(double sa, int ia, double sb, int ib) {
+    return (sa > sb) || (sa == sb && ia < ib);
+}
+
+}  // namespace spa

@@ -1,0 +1,699 @@
+// sm_100a kernels + C ABI (include/spa_b200.h) of the centroid-sparse paged decode-attention chain.
+//
+// Replaces, for this path only, the reference's device kernels
+//   src/transformer/{compute_cent,select_position,cent_select,sparse_paged_attention,
+//                    sparse_paged_fusion_attention}/*.cpp|*.h
+// and the host "ophost" layer (op defs, tiling, aclnn wrappers) under src/transformer/*/ophost/.
+#include <cooperative_groups.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+
+#include "../../include/spa_b200.h"
+#include "spa_attn.cuh"
+#include "spa_common.cuh"
+#include "spa_select.cuh"
+
+namespace cg = cooperative_groups;
+using namespace spa;
+
+// =============================================================================================
+// kernels
+// =============================================================================================
+__device__ __forceinline__ unsigned char *aligned_smem(unsigned char *raw) {
+    uintptr_t a = reinterpret_cast<uintptr_t>(raw);
+    return reinterpret_cast<unsigned char *>((a + 1023) & ~static_cast<uintptr_t>(1023));
+}
+
+// The whole chain in one persistent cooperative launch (SparsePagedFusionAttention,
+// sparse_paged_fusion_attention.cpp:56-76: InitCentSelect -> ProcessCentSelect -> SyncAll ->
+// Init/Process attention), or, with mode == kModeAttnOnly, SparsePagedAttention.
+template <typename QT, bool KVI8, int NT>
+__global__ void __launch_bounds__(kThreads, 1)
+spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = aligned_smem(smem_raw);
+    cg::grid_group grid = cg::this_grid();
+
+    // ---- phase A: selection (or union building) per (b, kv head)
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+        if (p.mode == kModeFused)
+            select_item<QT>(p, item, kSelScores | kSelSelect | kSelUnion, smem);
+        else
+            union_from_block_position(p, item, smem);
+    }
+    __threadfence();
+    grid.sync();
+    if (p.mode == kModeFused)
+        for (int b = blockIdx.x; b < p.B; b += gridDim.x) write_max_ppl(p, b);
+
+    // ---- phase B: stream the selected pages
+    attention_phase<QT, KVI8, NT>(p, &tmK, &tmV, smem);
+    __threadfence();
+    grid.sync();
+    // ---- phase C: combine
+    combine_phase<QT, KVI8, NT>(p, smem);
+}
+
+// Stand-alone selection ops (ComputeCent / SelectPosition / CentSelect share the device code).
+template <typename QT>
+__global__ void __launch_bounds__(kThreads, 1) spa_select_kernel(const __grid_constant__ ChainParams p,
+                                                                 int flags) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = aligned_smem(smem_raw);
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x) select_item<QT>(p, item, flags, smem);
+}
+
+__global__ void spa_max_ppl_kernel(const __grid_constant__ ChainParams p) {
+    for (int b = blockIdx.x; b < p.B; b += gridDim.x) write_max_ppl(p, b);
+}
+
+// =============================================================================================
+// host side: validation ("tiling checks"), plans, launches
+// =============================================================================================
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CUDA_TRY(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t e__ = (expr);                                                              \
+        if (e__ != cudaSuccess)                                                                \
+            return fail(SPA_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__));        \
+    } while (0)
+
+enum OpKind { OP_COMPUTE_CENT = 1, OP_SELECT_POSITION, OP_CENT_SELECT, OP_ATTENTION, OP_FUSION };
+
+struct spaExecutor {
+    int op;
+    ChainParams p;
+    CUtensorMap tmK, tmV;
+    int flags;            // selection flags
+    int grid;
+    int q_bf16, kv_i8, nt_tiles;
+    uint64_t ws_bytes;
+    // workspace offsets (bytes)
+    uint64_t off_uphys, off_umeta, off_ulen, off_tail, off_po, off_pml;
+    int launches;
+};
+
+static bool absent(const spaTensor *t) {
+    if (!t || !t->data) return true;
+    if (t->ndim <= 0) return false;
+    for (int i = 0; i < t->ndim; ++i)
+        if (t->sizes[i] == 0) return true;
+    return false;
+}
+static int64_t numel(const spaTensor *t) {
+    int64_t n = 1;
+    for (int i = 0; i < t->ndim; ++i) n *= t->sizes[i];
+    return n;
+}
+static bool contiguous(const spaTensor *t) {
+    int64_t s = 1;
+    for (int i = t->ndim - 1; i >= 0; --i) {
+        if (t->sizes[i] != 1 && t->strides[i] != s) return false;
+        s *= t->sizes[i];
+    }
+    return true;
+}
+static const char *dtype_name(int d) {
+    switch (d) {
+        case SPA_F16: return "float16"; case SPA_BF16: return "bfloat16"; case SPA_F32: return "float32";
+        case SPA_I8: return "int8"; case SPA_I32: return "int32"; case SPA_I64: return "int64";
+    }
+    return "?";
+}
+#define REQUIRE_PRESENT(t, name)                                                                \
+    if (absent(t)) return fail(SPA_ERR_ARG, "%s: required tensor is absent", name)
+#define REQUIRE_DTYPE(t, dt, name)                                                              \
+    if ((t)->dtype != (dt))                                                                     \
+    return fail(SPA_ERR_DTYPE, "%s: expected %s, got %s", name, dtype_name(dt), dtype_name((t)->dtype))
+#define REQUIRE_CONTIG(t, name)                                                                 \
+    if (!contiguous(t)) return fail(SPA_ERR_SHAPE, "%s: must be contiguous", name)
+
+struct DevInfo { int sms; int smem_optin; int coop; };
+static int dev_info(DevInfo *d) {
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&d->sms, cudaDevAttrMultiProcessorCount, dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&d->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&d->coop, cudaDevAttrCooperativeLaunch, dev));
+    return SPA_OK;
+}
+
+static int pow2_ceil(int x) { int p = 1; while (p < x) p <<= 1; return p; }
+
+// ---- query: [B,Nq,D] or [B,Nq,1,D]
+static int parse_query(const spaTensor *q, const char *name, int *B, int *Nq, long long *sb,
+                       long long *sh, int *is_bf16) {
+    REQUIRE_PRESENT(q, name);
+    if (q->dtype != SPA_F16 && q->dtype != SPA_BF16)
+        return fail(SPA_ERR_DTYPE, "%s: expected float16/bfloat16, got %s", name, dtype_name(q->dtype));
+    if (!(q->ndim == 3 || (q->ndim == 4 && q->sizes[2] == 1)))
+        return fail(SPA_ERR_SHAPE, "%s: expected [B,N,D] or [B,N,1,D]", name);
+    const int dl = q->ndim - 1;
+    if (q->sizes[dl] != kD) return fail(SPA_ERR_UNSUPPORTED, "%s: head dim %lld, this build supports D=%d", name, (long long)q->sizes[dl], kD);
+    if (q->strides[dl] != 1) return fail(SPA_ERR_SHAPE, "%s: last dim must be contiguous", name);
+    if ((q->strides[0] & 3) || (q->strides[1] & 3) || (reinterpret_cast<uintptr_t>(q->data) & 7))
+        return fail(SPA_ERR_SHAPE, "%s: rows must be 8-byte aligned", name);
+    *B = (int)q->sizes[0]; *Nq = (int)q->sizes[1]; *sb = q->strides[0]; *sh = q->strides[1];
+    *is_bf16 = q->dtype == SPA_BF16;
+    return SPA_OK;
+}
+
+static int parse_cent(const spaTensor *c, int qdtype, int *Nkv, int *C) {
+    REQUIRE_PRESENT(c, "l1_cent");
+    REQUIRE_DTYPE(c, qdtype, "l1_cent");
+    if (c->ndim != 3 || c->sizes[2] != kD) return fail(SPA_ERR_SHAPE, "l1_cent: expected [Nkv,C,%d]", kD);
+    REQUIRE_CONTIG(c, "l1_cent");
+    if (reinterpret_cast<uintptr_t>(c->data) & 15) return fail(SPA_ERR_SHAPE, "l1_cent: must be 16-byte aligned");
+    *Nkv = (int)c->sizes[0]; *C = (int)c->sizes[1];
+    if (*C > 65535) return fail(SPA_ERR_UNSUPPORTED, "l1_cent: C=%d > 65535", *C);
+    return SPA_OK;
+}
+
+static int parse_tables(const spaTensor *bid, const spaTensor *bt, const spaTensor *sl, ChainParams *p) {
+    REQUIRE_PRESENT(bid, "block_ids"); REQUIRE_DTYPE(bid, SPA_I32, "block_ids");
+    REQUIRE_PRESENT(bt, "block_table"); REQUIRE_DTYPE(bt, SPA_I32, "block_table");
+    REQUIRE_PRESENT(sl, "seq_len"); REQUIRE_DTYPE(sl, SPA_I32, "seq_len");
+    if (bid->ndim != 2 || bid->strides[1] != 1) return fail(SPA_ERR_SHAPE, "block_ids: expected [Nkv,kvPageLen], row-contiguous");
+    if (bt->ndim != 2 || bt->strides[1] != 1) return fail(SPA_ERR_SHAPE, "block_table: expected [maxB,maxP], row-contiguous");
+    if (sl->ndim != 1 || !contiguous(sl)) return fail(SPA_ERR_SHAPE, "seq_len: expected contiguous [B]");
+    p->block_ids = (const int *)bid->data; p->bid_stride = bid->strides[0]; p->kvPageLen = (int)bid->sizes[1];
+    p->block_table = (const int *)bt->data; p->bt_stride = bt->strides[0]; p->maxP = (int)bt->sizes[1];
+    p->seq_len = (const int *)sl->data;
+    if (sl->sizes[0] > bt->sizes[0]) return fail(SPA_ERR_SHAPE, "seq_len batch %lld exceeds block_table rows %lld", (long long)sl->sizes[0], (long long)bt->sizes[0]);
+    return SPA_OK;
+}
+
+// choose heads-per-pass / histogram bins for phase A so that its smem fits `budget`
+static int plan_select_smem(ChainParams *p, int budget, int *bytes) {
+    p->nbins = std::max(1024, pow2_ceil((p->C + 1) / 2));
+    const int Ceff = std::max(p->C, 1), keff = std::max(p->k, 1);
+    for (int hb = 8; hb >= 1; hb >>= 1) {
+        if (hb > pow2_ceil(p->g)) continue;
+        SelSmem L(p->g, Ceff, keff, hb, p->nbins, p->maxP);
+        if (L.total <= budget) { p->hb = hb; *bytes = L.total; return SPA_OK; }
+    }
+    return fail(SPA_ERR_UNSUPPORTED, "selection working set (g=%d, C=%d, k=%d, maxP=%d) exceeds shared memory", p->g, p->C, p->k, p->maxP);
+}
+
+// ---------------------------------------------------------------------------------------------
+// TMA tensor maps over the paged K / V pools
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+struct KvLayout { long long nblocks, s_blk, s_row, s_head; };   // strides in elements
+
+// Accepted pool layouts (tests/ifa_v5_case.py:408 vLLM [blocks,bs,Nkv,D]; :218 [blocks,bs,Nkv*D];
+// :36 BNSD-paged [blocks,Nkv,bs,D]).
+static int parse_kv(const spaTensor *t, const char *name, int Nkv, int bs, KvLayout *L) {
+    REQUIRE_PRESENT(t, name);
+    if (t->ndim == 3) {
+        if (t->sizes[1] != bs || t->sizes[2] != (int64_t)Nkv * kD || t->strides[2] != 1)
+            return fail(SPA_ERR_SHAPE, "%s: expected [blocks,%d,%d]", name, bs, Nkv * kD);
+        *L = {t->sizes[0], t->strides[0], t->strides[1], kD};
+    } else if (t->ndim == 4 && t->sizes[3] == kD && t->strides[3] == 1) {
+        if (t->sizes[1] == bs && t->sizes[2] == Nkv) *L = {t->sizes[0], t->strides[0], t->strides[1], t->strides[2]};
+        else if (t->sizes[1] == Nkv && t->sizes[2] == bs) *L = {t->sizes[0], t->strides[0], t->strides[2], t->strides[1]};
+        else return fail(SPA_ERR_SHAPE, "%s: expected [blocks,%d,%d,%d] or [blocks,%d,%d,%d]", name, bs, Nkv, kD, Nkv, bs, kD);
+    } else {
+        return fail(SPA_ERR_SHAPE, "%s: expected a 3-D or 4-D paged pool with head dim %d", name, kD);
+    }
+    return SPA_OK;
+}
+
+static int make_kv_map(CUtensorMap *map, const spaTensor *t, const KvLayout &L, int Nkv, int bs,
+                       int *ax_row, int *ax_head, int *ax_blk, const char *name) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return fail(SPA_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    const int esz = (t->dtype == SPA_I8) ? 1 : 2;
+    struct Ax { long long size, stride; int id; };
+    Ax ax[3] = {{bs, L.s_row * esz, 0}, {Nkv, L.s_head * esz, 1}, {L.nblocks, L.s_blk * esz, 2}};
+    // size-1 axes carry arbitrary strides: push them outermost and give them a consistent stride
+    std::stable_sort(ax, ax + 3, [](const Ax &a, const Ax &b) {
+        if ((a.size == 1) != (b.size == 1)) return b.size == 1;
+        return a.stride < b.stride;
+    });
+    long long prev_stride = (long long)kD * esz, prev_size = 1;
+    for (int i = 0; i < 3; ++i) {
+        if (ax[i].size == 1) ax[i].stride = prev_stride * prev_size;
+        prev_stride = ax[i].stride; prev_size = ax[i].size;
+    }
+    cuuint64_t gdim[4] = {(cuuint64_t)kD, (cuuint64_t)ax[0].size, (cuuint64_t)ax[1].size, (cuuint64_t)ax[2].size};
+    cuuint64_t gstr[3] = {(cuuint64_t)ax[0].stride, (cuuint64_t)ax[1].stride, (cuuint64_t)ax[2].stride};
+    cuuint32_t box[4] = {(cuuint32_t)(128 / esz), 1, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    for (int i = 0; i < 3; ++i) {
+        if (gstr[i] % 16) return fail(SPA_ERR_SHAPE, "%s: strides must be multiples of 16 bytes", name);
+        if (ax[i].id == 0) { box[i + 1] = (cuuint32_t)bs; *ax_row = i + 1; }
+        if (ax[i].id == 1) *ax_head = i + 1;
+        if (ax[i].id == 2) *ax_blk = i + 1;
+    }
+    if (reinterpret_cast<uintptr_t>(t->data) & 15) return fail(SPA_ERR_SHAPE, "%s: must be 16-byte aligned", name);
+    CUtensorMapDataType dt = t->dtype == SPA_I8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                             : t->dtype == SPA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                                    : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    CUresult r = enc(map, dt, 4, t->data, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(SPA_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%d)", name, (int)r);
+    return SPA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel dispatch tables
+// ---------------------------------------------------------------------------------------------
+typedef void (*ChainKernel)(const ChainParams, const CUtensorMap, const CUtensorMap);
+static ChainKernel chain_kernel_for(int bf16, int kvi8, int nt) {
+    if (!bf16 && !kvi8) return nt == 1 ? spa_chain_kernel<__half, false, 1> : spa_chain_kernel<__half, false, 2>;
+    if (bf16 && !kvi8) return nt == 1 ? spa_chain_kernel<__nv_bfloat16, false, 1> : spa_chain_kernel<__nv_bfloat16, false, 2>;
+    if (!bf16 && kvi8) return nt == 1 ? spa_chain_kernel<__half, true, 1> : spa_chain_kernel<__half, true, 2>;
+    return nt == 1 ? spa_chain_kernel<__nv_bfloat16, true, 1> : spa_chain_kernel<__nv_bfloat16, true, 2>;
+}
+typedef void (*SelectKernel)(const ChainParams, int);
+static SelectKernel select_kernel_for(int bf16) {
+    return bf16 ? spa_select_kernel<__nv_bfloat16> : spa_select_kernel<__half>;
+}
+
+static uint64_t align_up(uint64_t x, uint64_t a) { return (x + a - 1) / a * a; }
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+const char *spaGetLastError(void) { return g_err; }
+int spaGetVersion(void) { return 100; }
+int spaGetCompiledArch(void) { return 100; }
+int spaDestroyExecutor(spaExecutor *e) { delete e; return SPA_OK; }
+int spaExecutorNumLaunches(const spaExecutor *e) { return e ? e->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------
+// selection ops
+// ---------------------------------------------------------------------------------------------
+static int finish_select_plan(spaExecutor *e, uint64_t *ws, spaExecutor **out) {
+    DevInfo d;
+    int rc = dev_info(&d);
+    if (rc) { delete e; return rc; }
+    int bytes = 0;
+    rc = plan_select_smem(&e->p, d.smem_optin - 1024, &bytes);
+    if (rc) { delete e; return rc; }
+    e->p.smem_bytes = bytes + 1024;
+    e->grid = std::max(1, e->p.items);
+    e->ws_bytes = 0;
+    *ws = 0;
+    *out = e;
+    return SPA_OK;
+}
+
+static int launch_select(spaExecutor *e, cudaStream_t stream) {
+    if (e->p.items == 0) return SPA_OK;
+    SelectKernel k = select_kernel_for(e->q_bf16);
+    CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, e->p.smem_bytes));
+    k<<<e->grid, kThreads, e->p.smem_bytes, stream>>>(e->p, e->flags);
+    CUDA_TRY(cudaGetLastError());
+    if (e->op == OP_CENT_SELECT) {
+        spa_max_ppl_kernel<<<std::max(1, e->p.B), 32, 0, stream>>>(e->p);
+        CUDA_TRY(cudaGetLastError());
+    }
+    return SPA_OK;
+}
+
+int spaComputeCentGetWorkspaceSize(const spaTensor *query, const spaTensor *l1Cent,
+                                   const spaTensor *indicesOut, uint64_t *ws, spaExecutor **executor) {
+    if (!ws || !executor) return fail(SPA_ERR_ARG, "workspaceSize/executor must not be null");
+    spaExecutor *e = new (std::nothrow) spaExecutor();
+    if (!e) return fail(SPA_ERR_ARG, "out of host memory");
+    memset(e, 0, sizeof(*e));
+    ChainParams &p = e->p;
+    int rc;
+#define BAIL(x) do { rc = (x); if (rc) { delete e; return rc; } } while (0)
+    BAIL(parse_query(query, "query", &p.B, &p.Nq, &p.q_sb, &p.q_sh, &e->q_bf16));
+    BAIL(parse_cent(l1Cent, query->dtype, &p.Nkv, &p.C));
+    // k is read from the output's last dim (compute_cent_tiling.cpp:45-50); k == 0 => nothing to do
+    if (!indicesOut) { delete e; return fail(SPA_ERR_ARG, "indices: required [B,Nq,k] int32"); }
+    if (indicesOut->dtype != SPA_I32) { delete e; return fail(SPA_ERR_DTYPE, "indices: expected int32"); }
+    if (indicesOut->ndim != 3 || indicesOut->sizes[0] != p.B || indicesOut->sizes[1] != p.Nq || !contiguous(indicesOut)) {
+        delete e; return fail(SPA_ERR_SHAPE, "indices: expected contiguous [%d,%d,k]", p.B, p.Nq);
+    }
+    p.k = (int)indicesOut->sizes[2];
+    if (p.Nkv <= 0 || p.Nq % p.Nkv) { delete e; return fail(SPA_ERR_SHAPE, "num q heads %d not a multiple of kv heads %d", p.Nq, p.Nkv); }
+    p.g = p.Nq / p.Nkv;
+    if (p.g > kMaxGroup) { delete e; return fail(SPA_ERR_UNSUPPORTED, "group size %d > %d", p.g, kMaxGroup); }
+    if (p.k > p.C) { delete e; return fail(SPA_ERR_SHAPE, "k=%d exceeds cluster count C=%d", p.k, p.C); }
+    p.q = query->data; p.cent = l1Cent->data; p.indices_out = (int *)indicesOut->data;
+    p.items = (p.k == 0) ? 0 : p.B * p.Nkv; p.maxP = 1; p.bs = kBS; p.MP = 1;
+    e->op = OP_COMPUTE_CENT; e->flags = kSelScores | kSelWriteIndices; e->launches = 1;
+    return finish_select_plan(e, ws, executor);
+}
+
+int spaComputeCent(void *, uint64_t, spaExecutor *e, spaStream stream) {
+    if (!e || e->op != OP_COMPUTE_CENT) return fail(SPA_ERR_ARG, "bad executor");
+    return launch_select(e, (cudaStream_t)stream);
+}
+
+static int parse_select_outputs(ChainParams &p, const spaTensor *pp, const spaTensor *ppl) {
+    REQUIRE_PRESENT(pp, "page_position"); REQUIRE_DTYPE(pp, SPA_I32, "page_position");
+    REQUIRE_PRESENT(ppl, "page_position_length"); REQUIRE_DTYPE(ppl, SPA_I32, "page_position_length");
+    if (pp->ndim != 3 || pp->sizes[0] < p.B || pp->sizes[1] != p.Nq || !contiguous(pp))
+        return fail(SPA_ERR_SHAPE, "page_position: expected contiguous [%d,%d,max_page_num]", p.B, p.Nq);
+    if (ppl->ndim != 3 || ppl->sizes[0] < p.B || ppl->sizes[1] != p.Nq || ppl->sizes[2] != kPad || !contiguous(ppl))
+        return fail(SPA_ERR_SHAPE, "page_position_length: expected contiguous [%d,%d,%d]", p.B, p.Nq, kPad);
+    p.MP = (int)pp->sizes[2];
+    p.page_position = (int *)pp->data; p.page_position_length = (int *)ppl->data;
+    return SPA_OK;
+}
+
+int spaSelectPositionGetWorkspaceSize(const spaTensor *blockIds, const spaTensor *blockTable,
+                                      const spaTensor *seqLen, const spaTensor *indices, int64_t blockSize,
+                                      const spaTensor *pagePositionOut, const spaTensor *pagePositionLengthOut,
+                                      const spaTensor *blockTableGatherOut, uint64_t *ws, spaExecutor **executor) {
+    if (!ws || !executor) return fail(SPA_ERR_ARG, "workspaceSize/executor must not be null");
+    spaExecutor *e = new (std::nothrow) spaExecutor();
+    if (!e) return fail(SPA_ERR_ARG, "out of host memory");
+    memset(e, 0, sizeof(*e));
+    ChainParams &p = e->p;
+    int rc;
+    BAIL(parse_tables(blockIds, blockTable, seqLen, &p));
+    if (absent(indices)) { delete e; return fail(SPA_ERR_ARG, "indices: required tensor is absent"); }
+    if (indices->dtype != SPA_I32) { delete e; return fail(SPA_ERR_DTYPE, "indices: expected int32"); }
+    if (indices->ndim != 3 || indices->strides[2] != 1) { delete e; return fail(SPA_ERR_SHAPE, "indices: expected [B,Nq,k]"); }
+    if (blockSize <= 0) { delete e; return fail(SPA_ERR_SHAPE, "block_size must be positive"); }
+    p.B = (int)seqLen->sizes[0]; p.Nq = (int)indices->sizes[1]; p.Nkv = (int)blockIds->sizes[0];
+    if (indices->sizes[0] < p.B) { delete e; return fail(SPA_ERR_SHAPE, "indices batch smaller than seq_len batch"); }
+    if (p.Nkv <= 0 || p.Nq % p.Nkv) { delete e; return fail(SPA_ERR_SHAPE, "num q heads %d not a multiple of kv heads %d", p.Nq, p.Nkv); }
+    p.g = p.Nq / p.Nkv;
+    if (p.g > kMaxGroup) { delete e; return fail(SPA_ERR_UNSUPPORTED, "group size %d > %d", p.g, kMaxGroup); }
+    p.k = (int)indices->sizes[2]; p.C = 32;
+    p.indices_in = (const int *)indices->data; p.idx_sb = indices->strides[0]; p.idx_sh = indices->strides[1];
+    p.bs = (int)blockSize;
+    BAIL(parse_select_outputs(p, pagePositionOut, pagePositionLengthOut));
+    if (!absent(blockTableGatherOut)) {
+        if (blockTableGatherOut->dtype != SPA_I32 || blockTableGatherOut->ndim != 3 || blockTableGatherOut->sizes[0] != p.B ||
+            blockTableGatherOut->sizes[1] != p.Nq || blockTableGatherOut->sizes[2] != p.maxP || !contiguous(blockTableGatherOut)) {
+            delete e; return fail(SPA_ERR_SHAPE, "block_table_gather: expected contiguous int32 [%d,%d,%d]", p.B, p.Nq, p.maxP);
+        }
+        p.bt_gather = (int *)blockTableGatherOut->data;
+    }
+    p.items = p.B * p.Nkv;
+    e->op = OP_SELECT_POSITION; e->flags = kSelSelect | (p.bt_gather ? kSelGather : 0); e->launches = 1;
+    return finish_select_plan(e, ws, executor);
+}
+
+int spaSelectPosition(void *, uint64_t, spaExecutor *e, spaStream stream) {
+    if (!e || e->op != OP_SELECT_POSITION) return fail(SPA_ERR_ARG, "bad executor");
+    return launch_select(e, (cudaStream_t)stream);
+}
+
+static int parse_cent_select_common(spaExecutor *e, const spaTensor *query, const spaTensor *l1Cent,
+                                    const spaTensor *blockIds, const spaTensor *blockTable,
+                                    const spaTensor *seqLen, int64_t topK, int64_t blockSize,
+                                    const spaTensor *pp, const spaTensor *ppl, const spaTensor *mppl) {
+    ChainParams &p = e->p;
+    int rc, Bq = 0;
+    if ((rc = parse_query(query, "query", &Bq, &p.Nq, &p.q_sb, &p.q_sh, &e->q_bf16))) return rc;
+    if ((rc = parse_cent(l1Cent, query->dtype, &p.Nkv, &p.C))) return rc;
+    if ((rc = parse_tables(blockIds, blockTable, seqLen, &p))) return rc;
+    p.B = (int)seqLen->sizes[0];                                  // add_custom.cpp:988
+    if (p.B > Bq) return fail(SPA_ERR_SHAPE, "seq_len batch %d exceeds query batch %d", p.B, Bq);
+    if (p.Nkv <= 0 || p.Nq % p.Nkv) return fail(SPA_ERR_SHAPE, "num q heads %d not a multiple of kv heads %d", p.Nq, p.Nkv);
+    if (blockIds->sizes[0] != p.Nkv) return fail(SPA_ERR_SHAPE, "block_ids rows %lld != kv heads %d", (long long)blockIds->sizes[0], p.Nkv);
+    p.g = p.Nq / p.Nkv;
+    if (p.g > kMaxGroup) return fail(SPA_ERR_UNSUPPORTED, "group size %d > %d", p.g, kMaxGroup);
+    if (topK <= 0 || topK > p.C) return fail(SPA_ERR_SHAPE, "top-k %lld must be in [1, C=%d]", (long long)topK, p.C);
+    if (blockSize <= 0) return fail(SPA_ERR_SHAPE, "block_size must be positive");
+    p.k = (int)topK; p.bs = (int)blockSize;
+    if ((rc = parse_select_outputs(p, pp, ppl))) return rc;
+    REQUIRE_PRESENT(mppl, "max_page_position_length"); REQUIRE_DTYPE(mppl, SPA_I64, "max_page_position_length");
+    if (mppl->ndim != 2 || mppl->sizes[0] < p.B || mppl->sizes[1] != kPad || !contiguous(mppl))
+        return fail(SPA_ERR_SHAPE, "max_page_position_length: expected contiguous int64 [%d,%d]", p.B, kPad);
+    p.max_ppl = (long long *)mppl->data;
+    p.q = query->data; p.cent = l1Cent->data;
+    p.items = p.B * p.Nkv;
+    return SPA_OK;
+}
+
+int spaCentSelectGetWorkspaceSize(const spaTensor *query, const spaTensor *l1Cent, const spaTensor *blockIds,
+                                  const spaTensor *blockTable, const spaTensor *seqLen, int64_t topK,
+                                  int64_t blockSize, const spaTensor *pagePositionOut,
+                                  const spaTensor *pagePositionLengthOut, const spaTensor *maxPagePositionLengthOut,
+                                  uint64_t *ws, spaExecutor **executor) {
+    if (!ws || !executor) return fail(SPA_ERR_ARG, "workspaceSize/executor must not be null");
+    spaExecutor *e = new (std::nothrow) spaExecutor();
+    if (!e) return fail(SPA_ERR_ARG, "out of host memory");
+    memset(e, 0, sizeof(*e));
+    int rc;
+    BAIL(parse_cent_select_common(e, query, l1Cent, blockIds, blockTable, seqLen, topK, blockSize,
+                                  pagePositionOut, pagePositionLengthOut, maxPagePositionLengthOut));
+    e->op = OP_CENT_SELECT; e->flags = kSelScores | kSelSelect; e->launches = 2;
+    return finish_select_plan(e, ws, executor);
+}
+
+int spaCentSelect(void *, uint64_t, spaExecutor *e, spaStream stream) {
+    if (!e || e->op != OP_CENT_SELECT) return fail(SPA_ERR_ARG, "bad executor");
+    return launch_select(e, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// attention ops
+// ---------------------------------------------------------------------------------------------
+static int reject_unsupported(const spaTensor *pse, const spaTensor *mask, const spaTensor *dq1,
+                              const spaTensor *q1, const spaTensor *dq2, const spaTensor *q2,
+                              const spaTensor *qo2, const spaTensor *kvpad) {
+    // Never non-empty in any reference sparse test (tests/ifa_v5_case.py:133-146)
+    if (!absent(pse)) return fail(SPA_ERR_UNSUPPORTED, "pse_shift is not supported in the sparse path");
+    if (!absent(mask)) return fail(SPA_ERR_UNSUPPORTED, "attention_mask is not supported in the sparse path");
+    if (!absent(dq1) || !absent(q1) || !absent(dq2) || !absent(q2) || !absent(qo2))
+        return fail(SPA_ERR_UNSUPPORTED, "quant/dequant scales (int8 in/out) are not supported in the sparse path");
+    if (!absent(kvpad)) return fail(SPA_ERR_UNSUPPORTED, "kv_padding_size is not supported in the sparse path");
+    return SPA_OK;
+}
+
+static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTensor *key, const spaTensor *value,
+                          const spaTensor *aqs, const spaTensor *aqo, const spaTensor *blocktable,
+                          int64_t numHeads, double scaleValue, const char *inputLayout, int64_t numKV,
+                          int64_t blockSize, const spaTensor *out, uint64_t *ws) {
+    ChainParams &p = e->p;
+    int rc;
+    if (inputLayout && strcmp(inputLayout, "BNSD") && strcmp(inputLayout, "BSH") && strcmp(inputLayout, "BSND"))
+        return fail(SPA_ERR_ARG, "input_layout '%s' not one of BNSD/BSH/BSND", inputLayout);
+    if (p.Nq != numHeads) return fail(SPA_ERR_SHAPE, "num_heads=%lld disagrees with query heads %d", (long long)numHeads, p.Nq);
+    if (numKV <= 0) numKV = numHeads;                    // reference default: 0 => MHA
+    if (p.Nq % numKV) return fail(SPA_ERR_SHAPE, "num_heads %d not a multiple of num_key_value_heads %lld", p.Nq, (long long)numKV);
+    p.Nkv = (int)numKV; p.g = p.Nq / p.Nkv;
+    if (p.g > kMaxGroup) return fail(SPA_ERR_UNSUPPORTED, "group size %d > %d", p.g, kMaxGroup);
+    if (blockSize != kBS) return fail(SPA_ERR_UNSUPPORTED, "block_size %lld: this build supports %d", (long long)blockSize, kBS);
+    p.bs = kBS;
+    REQUIRE_PRESENT(key, "key"); REQUIRE_PRESENT(value, "value");
+    if (key->dtype != value->dtype) return fail(SPA_ERR_DTYPE, "key/value dtypes differ");
+    e->kv_i8 = key->dtype == SPA_I8;
+    if (!e->kv_i8 && key->dtype != query->dtype)
+        return fail(SPA_ERR_DTYPE, "key dtype %s must equal query dtype %s or int8", dtype_name(key->dtype), dtype_name(query->dtype));
+    KvLayout LK, LV;
+    if ((rc = parse_kv(key, "key", p.Nkv, p.bs, &LK))) return rc;
+    if ((rc = parse_kv(value, "value", p.Nkv, p.bs, &LV))) return rc;
+    p.num_blocks = (int)LK.nblocks;
+    int ar, ah, ab, vr, vh, vb;
+    if ((rc = make_kv_map(&e->tmK, key, LK, p.Nkv, p.bs, &ar, &ah, &ab, "key"))) return rc;
+    if ((rc = make_kv_map(&e->tmV, value, LV, p.Nkv, p.bs, &vr, &vh, &vb, "value"))) return rc;
+    if (ar != vr || ah != vh || ab != vb) return fail(SPA_ERR_SHAPE, "key and value pools must share a layout");
+    p.ax_row = ar; p.ax_head = ah; p.ax_blk = ab;
+    // antiquant: non-empty <=> int8 KV
+    if (e->kv_i8) {
+        if (absent(aqs)) return fail(SPA_ERR_ARG, "int8 KV requires antiquant_scale");
+        if (aqs->dtype != query->dtype) return fail(SPA_ERR_DTYPE, "antiquant_scale dtype must equal query dtype");
+        const int64_t n = numel(aqs);
+        if (n == 2) p.aq_per_tensor = 1;
+        else if (n == 2LL * p.Nkv * kD && aqs->sizes[0] == 2) p.aq_per_tensor = 0;
+        else return fail(SPA_ERR_SHAPE, "antiquant_scale: expected [2] or [2,Nkv,(1,)D]");
+        REQUIRE_CONTIG(aqs, "antiquant_scale");
+        p.aq_scale = aqs->data;
+        if (!absent(aqo)) {
+            if (aqo->dtype != query->dtype || numel(aqo) != n) return fail(SPA_ERR_SHAPE, "antiquant_offset must match antiquant_scale");
+            REQUIRE_CONTIG(aqo, "antiquant_offset");
+            p.aq_offset = aqo->data;
+        }
+    } else if (!absent(aqs) || !absent(aqo)) {
+        return fail(SPA_ERR_ARG, "antiquant_scale/offset given but KV is not int8");
+    }
+    REQUIRE_PRESENT(blocktable, "blocktable"); REQUIRE_DTYPE(blocktable, SPA_I32, "blocktable");
+    if (blocktable->ndim != 2 || blocktable->strides[1] != 1) return fail(SPA_ERR_SHAPE, "blocktable: expected [maxB,maxP]");
+    if (blocktable->sizes[0] < p.B) return fail(SPA_ERR_SHAPE, "blocktable rows %lld < batch %d", (long long)blocktable->sizes[0], p.B);
+    p.block_table = (const int *)blocktable->data; p.bt_stride = blocktable->strides[0]; p.maxP = (int)blocktable->sizes[1];
+    // output: same shape/dtype as query (add_custom.cpp:559-560)
+    REQUIRE_PRESENT(out, "attention_out"); REQUIRE_DTYPE(out, query->dtype, "attention_out");
+    if (out->ndim != query->ndim) return fail(SPA_ERR_SHAPE, "attention_out must have the query's shape");
+    for (int i = 0; i < out->ndim; ++i)
+        if (out->sizes[i] != query->sizes[i] && !(i == 0 && out->sizes[0] >= p.B))
+            return fail(SPA_ERR_SHAPE, "attention_out must have the query's shape");
+    if (out->strides[out->ndim - 1] != 1 || (out->strides[0] & 3) || (out->strides[1] & 3) ||
+        (reinterpret_cast<uintptr_t>(out->data) & 7))
+        return fail(SPA_ERR_SHAPE, "attention_out rows must be contiguous and 8-byte aligned");
+    p.out = out->data; p.out_sb = out->strides[0]; p.out_sh = out->strides[1];
+    p.q = query->data;
+    p.scale_log2 = (float)scaleValue * kLog2e;
+    p.items = p.B * p.Nkv;
+    if (p.items > 8192) return fail(SPA_ERR_UNSUPPORTED, "B*Nkv = %d > 8192 work items", p.items);
+
+    // ---- launch shape
+    DevInfo d;
+    if ((rc = dev_info(&d))) return rc;
+    if (!d.coop) return fail(SPA_ERR_CUDA, "device lacks cooperative launch");
+    e->nt_tiles = (p.g + 7) / 8;
+    p.stage_bytes = e->kv_i8 ? 16384 : 32768;
+    const int budget = d.smem_optin - 1024;
+    int nst = e->kv_i8 ? 12 : 6;
+    for (; nst >= 2; --nst)
+        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.items).total <= budget) break;
+    if (nst < 2) return fail(SPA_ERR_UNSUPPORTED, "attention working set exceeds shared memory");
+    p.nstages = nst;
+    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.items).total;
+    int sel_bytes = p.maxP * 4;
+    if (p.mode == kModeFused) { if ((rc = plan_select_smem(&p, budget, &sel_bytes))) return rc; }
+    p.smem_bytes = std::max(attn_bytes, sel_bytes) + 1024;
+    if (p.smem_bytes > d.smem_optin) return fail(SPA_ERR_UNSUPPORTED, "shared memory need %d > %d", p.smem_bytes, d.smem_optin);
+    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
+    int occ = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, p.smem_bytes));
+    if (occ < 1) return fail(SPA_ERR_CUDA, "chain kernel does not fit on an SM (smem %d)", p.smem_bytes);
+    e->grid = d.sms;                                     // one persistent CTA per SM
+    // ---- workspace
+    const int HP = e->nt_tiles * 8;
+    uint64_t o = 0;
+    e->off_uphys = o; o = align_up(o + (uint64_t)p.items * p.maxP * 4, 256);
+    e->off_umeta = o; o = align_up(o + (uint64_t)p.items * p.maxP * 4, 256);
+    e->off_ulen = o;  o = align_up(o + (uint64_t)p.items * 4, 256);
+    e->off_tail = o;  o = align_up(o + (uint64_t)p.items * 4, 256);
+    const uint64_t slots = (uint64_t)p.items + e->grid;
+    e->off_po = o;    o = align_up(o + slots * HP * kD * 4, 256);
+    e->off_pml = o;   o = align_up(o + slots * HP * 2 * 4, 256);
+    e->ws_bytes = o;
+    *ws = o;
+    e->launches = 1;
+    return SPA_OK;
+}
+
+static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaStream_t stream) {
+    if (e->p.items == 0) return SPA_OK;
+    if (!workspace || wsSize < e->ws_bytes)
+        return fail(SPA_ERR_WORKSPACE, "workspace %llu bytes < required %llu", (unsigned long long)wsSize, (unsigned long long)e->ws_bytes);
+    if (reinterpret_cast<uintptr_t>(workspace) & 255) return fail(SPA_ERR_WORKSPACE, "workspace must be 256-byte aligned");
+    ChainParams p = e->p;
+    char *w = (char *)workspace;
+    p.union_phys = (int *)(w + e->off_uphys); p.union_meta = (unsigned *)(w + e->off_umeta);
+    p.union_len = (int *)(w + e->off_ulen); p.tail_count = (int *)(w + e->off_tail);
+    p.part_o = (float *)(w + e->off_po); p.part_ml = (float *)(w + e->off_pml);
+    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
+    void *args[] = {(void *)&p, (void *)&e->tmK, (void *)&e->tmV};
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void *)kern, dim3(e->grid), dim3(kThreads), args,
+                                         (size_t)p.smem_bytes, stream));
+    return SPA_OK;
+}
+
+int spaSparsePagedAttentionGetWorkspaceSize(
+    const spaTensor *query, const spaTensor *key, const spaTensor *value, const spaTensor *pseShift,
+    const spaTensor *attenMask, const spaTensor *actualSeqLengths, const spaTensor *dequantScale1,
+    const spaTensor *quantScale1, const spaTensor *dequantScale2, const spaTensor *quantScale2,
+    const spaTensor *quantOffset2, const spaTensor *antiquantScale, const spaTensor *antiquantOffset,
+    const spaTensor *blocktable, const spaTensor *kvPaddingSize, const spaTensor *blockPosition,
+    int64_t numHeads, double scaleValue, const char *inputLayout, int64_t numKeyValueHeads,
+    int64_t blockSize, int64_t innerPrecise, const spaTensor *attentionOut, uint64_t *ws,
+    spaExecutor **executor) {
+    (void)innerPrecise;   // accepted and ignored: the intermediate type is always float (…_Us2.h:69-70)
+    if (!ws || !executor) return fail(SPA_ERR_ARG, "workspaceSize/executor must not be null");
+    spaExecutor *e = new (std::nothrow) spaExecutor();
+    if (!e) return fail(SPA_ERR_ARG, "out of host memory");
+    memset(e, 0, sizeof(*e));
+    ChainParams &p = e->p;
+    int rc;
+    BAIL(reject_unsupported(pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize));
+    BAIL(parse_query(query, "query", &p.B, &p.Nq, &p.q_sb, &p.q_sh, &e->q_bf16));
+    p.mode = kModeAttnOnly;
+    if (absent(blockPosition)) { delete e; return fail(SPA_ERR_ARG, "blockposition: required tensor is absent"); }
+    if (blockPosition->dtype != SPA_I32) { delete e; return fail(SPA_ERR_DTYPE, "blockposition: expected int32"); }
+    if (absent(actualSeqLengths)) { delete e; return fail(SPA_ERR_ARG, "actual_seq_lengths: required tensor is absent"); }
+    if (actualSeqLengths->dtype != SPA_I64) { delete e; return fail(SPA_ERR_DTYPE, "actual_seq_lengths: expected int64"); }
+    BAIL(plan_attention(e, query, key, value, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
+                        inputLayout, numKeyValueHeads, blockSize, attentionOut, ws));
+    if (blockPosition->ndim != 3 || blockPosition->sizes[0] < p.B || blockPosition->strides[2] != 1 ||
+        (blockPosition->sizes[1] != p.Nkv && blockPosition->sizes[1] != p.Nq)) {
+        delete e; return fail(SPA_ERR_SHAPE, "blockposition: expected [B, Nkv or Nq, max_page_num]");
+    }
+    p.bp_in = (const int *)blockPosition->data; p.bp_heads = (int)blockPosition->sizes[1];
+    p.bp_sb = blockPosition->strides[0]; p.bp_sh = blockPosition->strides[1]; p.bp_len = (int)blockPosition->sizes[2];
+    const int64_t na = numel(actualSeqLengths);
+    if (!(na == 1 || na >= p.B) || !contiguous(actualSeqLengths)) { delete e; return fail(SPA_ERR_SHAPE, "actual_seq_lengths: expected int64 [B] or [1]"); }
+    p.actual_seq = (const long long *)actualSeqLengths->data; p.actual_n = (int)na;
+    e->op = OP_ATTENTION;
+    *executor = e;
+    return SPA_OK;
+}
+
+int spaSparsePagedAttention(void *workspace, uint64_t wsSize, spaExecutor *e, spaStream stream) {
+    if (!e || e->op != OP_ATTENTION) return fail(SPA_ERR_ARG, "bad executor");
+    return launch_chain(workspace, wsSize, e, (cudaStream_t)stream);
+}
+
+int spaSparsePagedFusionAttentionGetWorkspaceSize(
+    const spaTensor *query, const spaTensor *key, const spaTensor *value, const spaTensor *pseShift,
+    const spaTensor *attenMask, const spaTensor *actualSeqLengths, const spaTensor *dequantScale1,
+    const spaTensor *quantScale1, const spaTensor *dequantScale2, const spaTensor *quantScale2,
+    const spaTensor *quantOffset2, const spaTensor *antiquantScale, const spaTensor *antiquantOffset,
+    const spaTensor *blocktable, const spaTensor *kvPaddingSize, const spaTensor *l1Cent,
+    const spaTensor *blockIds, const spaTensor *totalSeqLen, int64_t numHeads, double scaleValue,
+    const char *inputLayout, int64_t numKeyValueHeads, int64_t blockSize, int64_t innerPrecise,
+    int64_t topK, const spaTensor *blockPosition, const spaTensor *pagePositionLength,
+    const spaTensor *maxPagePositionLength, const spaTensor *attentionOut, uint64_t *ws,
+    spaExecutor **executor) {
+    (void)innerPrecise; (void)actualSeqLengths;
+    if (!ws || !executor) return fail(SPA_ERR_ARG, "workspaceSize/executor must not be null");
+    spaExecutor *e = new (std::nothrow) spaExecutor();
+    if (!e) return fail(SPA_ERR_ARG, "out of host memory");
+    memset(e, 0, sizeof(*e));
+    ChainParams &p = e->p;
+    int rc;
+    BAIL(reject_unsupported(pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize));
+    p.mode = kModeFused;
+    BAIL(parse_cent_select_common(e, query, l1Cent, blockIds, blocktable, totalSeqLen, topK, blockSize,
+                                  blockPosition, pagePositionLength, maxPagePositionLength));
+    if (numKeyValueHeads > 0 && numKeyValueHeads != p.Nkv) { delete e; return fail(SPA_ERR_SHAPE, "num_key_value_heads=%lld disagrees with l1_cent heads %d", (long long)numKeyValueHeads, p.Nkv); }
+    BAIL(plan_attention(e, query, key, value, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
+                        inputLayout, p.Nkv, blockSize, attentionOut, ws));
+    e->op = OP_FUSION;
+    *executor = e;
+    return SPA_OK;
+}
+
+int spaSparsePagedFusionAttention(void *workspace, uint64_t wsSize, spaExecutor *e, spaStream stream) {
+    if (!e || e->op != OP_FUSION) return fail(SPA_ERR_ARG, "bad executor");
+    return launch_chain(workspace, wsSize, e, (cudaStream_t)stream);
+}
+
+}  // extern "C"

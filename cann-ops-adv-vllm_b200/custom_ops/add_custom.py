@@ -1,0 +1,189 @@
+"""Python operator API of the sparse decode-attention chain.
+
+Positional signatures, return arity, dtypes and shapes are those of the reference's
+extension/custom_ops/add_custom.py:10-135.  Keyword-only extensions (`k`, `max_page_num`,
+`block_size`) default to the constants the reference hard-codes in its binding/tiling
+(add_custom.cpp:940,958,987; select_position.cpp:7) so BASELINE configs with k in {8,128} or more
+than 256 selected pages are reachable without changing any existing call site.
+
+All compute happens in `custom_ops_lib` (C++ binding -> C ABI -> CUDA kernels).  There is no CPU or
+eager fallback: importing this module without the built extension raises ImportError.
+"""
+from typing import List, Tuple
+
+import torch
+
+try:
+    import custom_ops_lib
+except ImportError as exc:  # fail loudly: the product has no fallback path
+    raise ImportError(
+        "custom_ops_lib (the sm_100a CUDA extension) is not built; run "
+        "`python cann-ops-adv-vllm_b200/build.py` or `__graft_entry__.build()`") from exc
+
+
+def _tensor(x, dtype, device):
+    if torch.is_tensor(x):
+        return x
+    # fused_ifa_v5_case.py:92 passes actual_seq_lengths as a python list
+    return torch.as_tensor(x, dtype=dtype, device=device)
+
+
+def incre_flash_attention_v4(query: torch.Tensor,
+                             key_list: List[torch.Tensor],
+                             value_list: List[torch.Tensor],
+                             pse_shift: torch.Tensor,
+                             attention_mask: torch.Tensor,
+                             actual_seq_lengths: torch.Tensor,
+                             dequant_scale1: torch.Tensor,
+                             quant_scale1: torch.Tensor,
+                             dequant_scale2: torch.Tensor,
+                             quant_scale2: torch.Tensor,
+                             quant_offset2: torch.Tensor,
+                             antiquant_scale: torch.Tensor,
+                             antiquant_offset: torch.Tensor,
+                             blocktable: torch.Tensor,
+                             kv_padding_size: torch.Tensor,
+                             num_heads: int,
+                             scale_value: float,
+                             input_layout: str,
+                             num_key_value_heads: int,
+                             block_size: int,
+                             inner_precise: int) -> torch.Tensor:
+    """Stock dense IFA entry (add_custom.py:10-40): outside the sparse hot path, raises."""
+    return custom_ops_lib.incre_flash_attention_v4(
+        query, key_list, value_list, pse_shift, attention_mask, actual_seq_lengths,
+        dequant_scale1, quant_scale1, dequant_scale2, quant_scale2, quant_offset2,
+        antiquant_scale, antiquant_offset, blocktable, kv_padding_size,
+        num_heads, scale_value, input_layout, num_key_value_heads, block_size, inner_precise)
+
+
+def sparse_paged_attention(query: torch.Tensor,
+                           key: torch.Tensor,
+                           value: torch.Tensor,
+                           pse_shift: torch.Tensor,
+                           attention_mask: torch.Tensor,
+                           actual_seq_lengths: torch.Tensor,
+                           dequant_scale1: torch.Tensor,
+                           quant_scale1: torch.Tensor,
+                           dequant_scale2: torch.Tensor,
+                           quant_scale2: torch.Tensor,
+                           quant_offset2: torch.Tensor,
+                           antiquant_scale: torch.Tensor,
+                           antiquant_offset: torch.Tensor,
+                           blocktable: torch.Tensor,
+                           kv_padding_size: torch.Tensor,
+                           blockposition: torch.Tensor,
+                           num_heads: int,
+                           scale_value: float,
+                           input_layout: str,
+                           num_key_value_heads: int,
+                           block_size: int,
+                           inner_precise: int) -> torch.Tensor:
+    """Paged flash-decode over the pages listed in `blockposition` (add_custom.py:41-75)."""
+    actual_seq_lengths = _tensor(actual_seq_lengths, torch.int64, query.device)
+    return custom_ops_lib.sparse_paged_attention(
+        query, [key], [value], pse_shift, attention_mask, actual_seq_lengths,
+        dequant_scale1, quant_scale1, dequant_scale2, quant_scale2, quant_offset2,
+        antiquant_scale, antiquant_offset, blocktable, kv_padding_size,
+        blockposition, int(num_heads), float(scale_value), input_layout, int(num_key_value_heads),
+        int(block_size), int(inner_precise))
+
+
+def compute_cent(query: torch.Tensor, l1_cent: torch.Tensor, *, k: int = 64) -> torch.Tensor:
+    """query . l1_cent^T + TopK over clusters -> int32 [B, Nq, k] (add_custom.py:77-81)."""
+    return custom_ops_lib.compute_cent_k(query, l1_cent, int(k))
+
+
+def select_position(block_ids: torch.Tensor, block_table: torch.Tensor, seq_len: torch.Tensor,
+                    indices: torch.Tensor, *, max_page_num: int = 256,
+                    block_size: int = 128) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """-> (page_position, page_position_length, block_table_gather) (add_custom.py:83-87)."""
+    return custom_ops_lib.select_position_ex(block_ids, block_table, seq_len, indices,
+                                             int(max_page_num), int(block_size))
+
+
+def cent_select(query: torch.Tensor, l1_cent: torch.Tensor, block_ids: torch.Tensor,
+                block_table: torch.Tensor, seq_len: torch.Tensor, *, k: int = 64,
+                max_page_num: int = 256,
+                block_size: int = 128) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """-> (page_position, page_position_length, max_page_position_length) (add_custom.py:89-93)."""
+    return custom_ops_lib.cent_select_ex(query, l1_cent, block_ids, block_table, seq_len, int(k),
+                                         int(max_page_num), int(block_size))
+
+
+def sparse_paged_fusion_attention(query: torch.Tensor,
+                                  key: torch.Tensor,
+                                  value: torch.Tensor,
+                                  pse_shift: torch.Tensor,
+                                  attention_mask: torch.Tensor,
+                                  actual_seq_lengths: torch.Tensor,
+                                  dequant_scale1: torch.Tensor,
+                                  quant_scale1: torch.Tensor,
+                                  dequant_scale2: torch.Tensor,
+                                  quant_scale2: torch.Tensor,
+                                  quant_offset2: torch.Tensor,
+                                  antiquant_scale: torch.Tensor,
+                                  antiquant_offset: torch.Tensor,
+                                  blocktable: torch.Tensor,
+                                  kv_padding_size: torch.Tensor,
+                                  l1_cent: torch.Tensor,
+                                  block_ids: torch.Tensor,
+                                  total_seq_len: torch.Tensor,
+                                  block_position: torch.Tensor,
+                                  page_position_length: torch.Tensor,
+                                  max_page_position_length: torch.Tensor,
+                                  num_heads: int,
+                                  scale_value: float,
+                                  input_layout: str,
+                                  num_key_value_heads: int,
+                                  block_size: int,
+                                  inner_precise: int,
+                                  *, k: int = 64) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """CentSelect + sparse paged attention in ONE launch (add_custom.py:96-135).
+
+    `block_position`, `page_position_length`, `max_page_position_length` are caller-allocated and
+    written in place; returns (attention_out, block_position, max_page_position_length) exactly as
+    the reference binding does (add_custom.cpp:931).  max_page_num is `block_position.shape[2]`
+    (sparse_paged_fusion_attention_tiling.cc:1606).
+    """
+    actual_seq_lengths = _tensor(actual_seq_lengths, torch.int64, query.device)
+    return custom_ops_lib.sparse_paged_fusion_attention_ex(
+        query, [key], [value], pse_shift, attention_mask, actual_seq_lengths,
+        dequant_scale1, quant_scale1, dequant_scale2, quant_scale2, quant_offset2,
+        antiquant_scale, antiquant_offset, blocktable, kv_padding_size,
+        l1_cent, block_ids, total_seq_len,
+        block_position, page_position_length, max_page_position_length,
+        int(num_heads), float(scale_value), input_layout, int(num_key_value_heads), int(block_size),
+        int(inner_precise), int(k))
+
+
+class FusedDecodePlan:
+    """Launch-ready fused executor bound to fixed tensors (extension; the reference keeps its aclnn
+    executor repeatable the same way, add_custom.cpp:847).  `launch()` performs no host-side
+    validation or allocation, so it is CUDA-graph capturable and is what bench.py times as the
+    device-resident number."""
+
+    def __init__(self, query, key, value, blocktable, l1_cent, block_ids, total_seq_len,
+                 block_position, page_position_length, max_page_position_length, attention_out,
+                 num_heads, scale_value, num_key_value_heads, block_size=128, *, k=64,
+                 antiquant_scale=None, antiquant_offset=None, input_layout="BNSD", inner_precise=1):
+        empty = torch.empty(0, dtype=query.dtype, device=query.device)
+        self.attention_out = attention_out
+        self._plan = custom_ops_lib.make_fusion_plan(
+            query, key, value, empty if antiquant_scale is None else antiquant_scale,
+            empty if antiquant_offset is None else antiquant_offset, blocktable, l1_cent, block_ids,
+            total_seq_len, block_position, page_position_length, max_page_position_length,
+            attention_out, int(num_heads), float(scale_value), input_layout,
+            int(num_key_value_heads), int(block_size), int(inner_precise), int(k))
+
+    @property
+    def workspace_bytes(self) -> int:
+        return self._plan.workspace_bytes
+
+    @property
+    def num_launches(self) -> int:
+        return self._plan.num_launches
+
+    def launch(self) -> torch.Tensor:
+        custom_ops_lib.launch_fusion_plan(self._plan)
+        return self.attention_out

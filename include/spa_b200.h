@@ -1,0 +1,163 @@
+/*
+ * spa_b200.h -- C ABI of the B200-native centroid-sparse paged decode-attention chain.
+ *
+ * This is the drop-in boundary: it replaces the reference's aclnn two-phase C interface
+ *   aclnn<Op>GetWorkspaceSize(tensors..., attrs..., outputs..., uint64_t *workspaceSize, aclOpExecutor **executor)
+ *   aclnn<Op>(void *workspace, uint64_t workspaceSize, aclOpExecutor *executor, aclrtStream stream)
+ * (reference: README.md:125-181, misc/aclnn_compute_cent.h, misc/aclnn_select_position.h,
+ *  misc/aclnn_cent_select.h:27-51, src/transformer/sparse_paged_attention/ophost/aclnn_sparse_paged_attention.h,
+ *  src/transformer/sparse_paged_fusion_attention/ophost/aclnn_sparse_paged_fusion_attention.h:60-81)
+ * which the reference's PyTorch binding resolves with dlsym from libcust_opapi.so
+ * (extension/csrc/pytorch_npu_helper.hpp:225-260).  Same shape here: plain C types only, no torch
+ * types, no exceptions; phase 1 validates (where the reference's tiling checks live) and returns a
+ * workspace size plus an executor ("plan"), phase 2 launches asynchronously on the given stream.
+ *
+ * Ownership (as in the reference, extension/csrc/add_custom.cpp:153,278-280,866-873): the caller
+ * allocates every output and the workspace; kernels never allocate.  An executor stays valid (and
+ * re-launchable, e.g. under CUDA-graph capture) as long as the tensors it was planned for live;
+ * release it with spaDestroyExecutor.
+ *
+ * Optional tensors: pass NULL, or a descriptor with data == NULL / zero elements
+ * (the reference maps empty at::Tensor to a null aclTensor, add_custom.cpp:32-35).
+ */
+#ifndef SPA_B200_H_
+#define SPA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPA_API __attribute__((visibility("default")))
+
+typedef enum {
+    SPA_OK = 0,
+    SPA_ERR_ARG = -1,          /* null pointer / malformed descriptor            */
+    SPA_ERR_SHAPE = -2,        /* shapes inconsistent with each other or attrs   */
+    SPA_ERR_DTYPE = -3,        /* unsupported dtype combination                  */
+    SPA_ERR_UNSUPPORTED = -4,  /* legal in the reference op, not in this build   */
+    SPA_ERR_CUDA = -5,         /* CUDA runtime / driver error                    */
+    SPA_ERR_WORKSPACE = -6     /* workspace pointer null or too small            */
+} spaStatus;
+
+/* dtype codes (subset the reference binding converts, add_custom.cpp:43-70) */
+typedef enum {
+    SPA_F16 = 0, SPA_BF16 = 1, SPA_F32 = 2, SPA_I8 = 3, SPA_I32 = 4, SPA_I64 = 5
+} spaDtype;
+
+#define SPA_MAX_DIMS 8
+typedef struct {
+    void *data;                    /* device pointer                                 */
+    int32_t dtype;                 /* spaDtype                                       */
+    int32_t ndim;
+    int64_t sizes[SPA_MAX_DIMS];
+    int64_t strides[SPA_MAX_DIMS]; /* in ELEMENTS                                    */
+} spaTensor;
+
+typedef struct spaExecutor spaExecutor;     /* replaces aclOpExecutor  */
+typedef struct CUstream_st *spaStream;      /* == cudaStream_t         */
+
+/* Thread-local text of the last error on this thread (replaces aclGetRecentErrMsg,
+ * add_custom.cpp:263-265). */
+SPA_API const char *spaGetLastError(void);
+SPA_API int spaDestroyExecutor(spaExecutor *executor);
+/* Library/ABI version, and the SM architecture the kernels were compiled for (100 => sm_100a). */
+SPA_API int spaGetVersion(void);
+SPA_API int spaGetCompiledArch(void);
+/* Number of kernel launches an executor performs per spa<Op>() call (for bench accounting). */
+SPA_API int spaExecutorNumLaunches(const spaExecutor *executor);
+
+/* ---- ComputeCent: replaces aclnnComputeCentGetWorkspaceSize / aclnnComputeCent
+ *      (misc/aclnn_compute_cent.h; kernel compute_cent/compute_cent.cpp:345).
+ * query [B,Nq,D] (or [B,Nq,1,D]) f16/bf16, l1Cent [Nkv,C,D] same dtype,
+ * indicesOut [B,Nq,k] int32 -- k is read from the OUTPUT's last dim exactly as the reference
+ * tiling does (compute_cent_tiling.cpp:45-50).  Result: k largest q.cent scores per (b,head),
+ * sorted descending, ties -> lowest index.                                                     */
+SPA_API int spaComputeCentGetWorkspaceSize(const spaTensor *query, const spaTensor *l1Cent,
+                                           const spaTensor *indicesOut,
+                                           uint64_t *workspaceSize, spaExecutor **executor);
+SPA_API int spaComputeCent(void *workspace, uint64_t workspaceSize, spaExecutor *executor,
+                           spaStream stream);
+
+/* ---- SelectPosition: replaces aclnnSelectPosition* (misc/aclnn_select_position.h; kernel
+ *      select_position/select_position.cpp:242).  All int32.
+ * blockIds [Nkv,kvPageLen], blockTable [maxB,maxP], seqLen [B], indices [B,Nq,k];
+ * pagePositionOut [B,Nq,MP] (pad 0x7fffffff), pagePositionLengthOut [B,Nq,8],
+ * blockTableGatherOut [B,Nq,maxP].  blockSize: tokens per page (reference constant 128,
+ * select_position.cpp:7).                                                                      */
+SPA_API int spaSelectPositionGetWorkspaceSize(const spaTensor *blockIds, const spaTensor *blockTable,
+                                              const spaTensor *seqLen, const spaTensor *indices,
+                                              int64_t blockSize,
+                                              const spaTensor *pagePositionOut,
+                                              const spaTensor *pagePositionLengthOut,
+                                              const spaTensor *blockTableGatherOut,
+                                              uint64_t *workspaceSize, spaExecutor **executor);
+SPA_API int spaSelectPosition(void *workspace, uint64_t workspaceSize, spaExecutor *executor,
+                              spaStream stream);
+
+/* ---- CentSelect: replaces aclnnCentSelect* (misc/aclnn_cent_select.h:27-51; kernel
+ *      cent_select/cent_select.cpp:538).  topK: reference constant 64 (cent_select_tiling.cpp:58).
+ * maxPagePositionLengthOut [B,8] int64 = blockSize * max over heads of the count.
+ * Batch is seqLen's (add_custom.cpp:988).                                                      */
+SPA_API int spaCentSelectGetWorkspaceSize(const spaTensor *query, const spaTensor *l1Cent,
+                                          const spaTensor *blockIds, const spaTensor *blockTable,
+                                          const spaTensor *seqLen, int64_t topK, int64_t blockSize,
+                                          const spaTensor *pagePositionOut,
+                                          const spaTensor *pagePositionLengthOut,
+                                          const spaTensor *maxPagePositionLengthOut,
+                                          uint64_t *workspaceSize, spaExecutor **executor);
+SPA_API int spaCentSelect(void *workspace, uint64_t workspaceSize, spaExecutor *executor,
+                          spaStream stream);
+
+/* ---- SparsePagedAttention: replaces aclnnSparsePagedAttention* (ophost/aclnn_sparse_paged_attention.h;
+ *      kernel sparse_paged_attention/sparse_paged_attention.cpp:135).  Argument order follows the
+ *      aclnn prototype: inputs, attrs, output.  key/value are single tensors (the reference passes
+ *      1-element tensor lists, add_custom.py:70-75).
+ * actualSeqLengths: DEVICE int64 [B] or [1] (the reference copies it to the host,
+ *      add_custom.cpp:105-118; here it is read on device, no sync).
+ * blockPosition [B, Nkv or Nq, MP] int32, 0x7fffffff-terminated.
+ * pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2,
+ * kvPaddingSize must be absent (SPA_ERR_UNSUPPORTED otherwise).                                 */
+SPA_API int spaSparsePagedAttentionGetWorkspaceSize(
+    const spaTensor *query, const spaTensor *key, const spaTensor *value,
+    const spaTensor *pseShift, const spaTensor *attenMask, const spaTensor *actualSeqLengths,
+    const spaTensor *dequantScale1, const spaTensor *quantScale1, const spaTensor *dequantScale2,
+    const spaTensor *quantScale2, const spaTensor *quantOffset2,
+    const spaTensor *antiquantScale, const spaTensor *antiquantOffset,
+    const spaTensor *blocktable, const spaTensor *kvPaddingSize, const spaTensor *blockPosition,
+    int64_t numHeads, double scaleValue, const char *inputLayout, int64_t numKeyValueHeads,
+    int64_t blockSize, int64_t innerPrecise,
+    const spaTensor *attentionOut, uint64_t *workspaceSize, spaExecutor **executor);
+SPA_API int spaSparsePagedAttention(void *workspace, uint64_t workspaceSize, spaExecutor *executor,
+                                    spaStream stream);
+
+/* ---- SparsePagedFusionAttention: replaces aclnnSparsePagedFusionAttention*
+ *      (ophost/aclnn_sparse_paged_fusion_attention.h:60-81; kernel
+ *      sparse_paged_fusion_attention/sparse_paged_fusion_attention.cpp:156).  Argument order as in
+ *      the aclnn prototype: inputs, attrs, the three aux outputs, attentionOut.
+ * One launch: CentSelect (writes blockPosition [B,Nq,MP], pagePositionLength [B,Nq,8],
+ * maxPagePositionLength [B,8] in place) then attention over the selected pages.
+ * topK: reference tiling constant (cent_select: 64).  actualSeqLengths is accepted and ignored
+ * (the reference kernel substitutes the on-device maxPagePositionLength,
+ * sparse_paged_fusion_attention.cpp:68).                                                        */
+SPA_API int spaSparsePagedFusionAttentionGetWorkspaceSize(
+    const spaTensor *query, const spaTensor *key, const spaTensor *value,
+    const spaTensor *pseShift, const spaTensor *attenMask, const spaTensor *actualSeqLengths,
+    const spaTensor *dequantScale1, const spaTensor *quantScale1, const spaTensor *dequantScale2,
+    const spaTensor *quantScale2, const spaTensor *quantOffset2,
+    const spaTensor *antiquantScale, const spaTensor *antiquantOffset,
+    const spaTensor *blocktable, const spaTensor *kvPaddingSize,
+    const spaTensor *l1Cent, const spaTensor *blockIds, const spaTensor *totalSeqLen,
+    int64_t numHeads, double scaleValue, const char *inputLayout, int64_t numKeyValueHeads,
+    int64_t blockSize, int64_t innerPrecise, int64_t topK,
+    const spaTensor *blockPosition, const spaTensor *pagePositionLength,
+    const spaTensor *maxPagePositionLength,
+    const spaTensor *attentionOut, uint64_t *workspaceSize, spaExecutor **executor);
+SPA_API int spaSparsePagedFusionAttention(void *workspace, uint64_t workspaceSize,
+                                          spaExecutor *executor, spaStream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPA_B200_H_ */
