@@ -39,7 +39,7 @@ def report(name, got, want, exact=True):
 def main():
     dev = "cuda"
     torch.manual_seed(0)
-    for (B, Nq, Nkv, C, S, k) in [(2, 8, 2, 128, 4096, 8), (2, 32, 8, 512, 32768, 64), (1, 16, 2, 256, 8192 - 77, 16)]:
+    for (B, Nq, Nkv, C, S, k) in [(2, 8, 2, 128, 4096, 8), (2, 32, 8, 512, 32768, 64), (1, 16, 2, 256, 8192 - 77, 16), (1, 32, 2, 128, 8192 - 3, 16)]:
         print(f"== case B={B} Nq={Nq} Nkv={Nkv} C={C} S={S} k={k}", flush=True)
         c = make_case(100 + B + Nq, B, Nq, Nkv, C, S, kv_pages=max(64, 2 * ((S + 127) // 128)), ragged=(S % 128 != 0))
         g = to_device(c, dev)

@@ -1,0 +1,384 @@
+"""GPU parity tests (run on the B200 box: `pytest -m gpu`).
+
+Every test calls the product through its public surface -- `custom_ops.*` -> `custom_ops_lib`
+(C++ binding) -> C ABI (`libspa_b200.so`) -> sm_100a kernels -- and compares with the CPU oracle
+(`oracle/sparse_chain.py`) or the committed reference-generated fixtures (`tests/golden/*.npz`).
+Bars: indices / page_position / lengths bit-exact; attention_out atol=rtol=1e-3 (fp16),
+2e-2 (bf16 or int8 KV)  -- BASELINE.json north_star.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from cases import attn_call, fused_call, make_case, to_device
+from oracle import sparse_chain as oc
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    import custom_ops
+    return custom_ops
+
+
+def load(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, name + ".npz"))
+    return {k: (torch.from_numpy(z[k]) if z[k].ndim > 0 else z[k].item()) for k in z.files}
+
+
+def crop_pad(pos, width):
+    B, H, W = pos.shape
+    out = torch.full((B, H, width), oc.INT32_MAX, dtype=torch.int32)
+    w = min(W, width)
+    out[:, :, :w] = pos[:, :, :w]
+    return out
+
+
+def assert_close(got, want, tol, what=""):
+    got = got.float().cpu()
+    want = want.float().cpu()
+    assert not torch.isnan(got).any(), f"{what}: NaN in output"
+    err = (got - want).abs()
+    bound = tol + tol * want.abs()
+    bad = err > bound
+    assert not bad.any(), (f"{what}: {int(bad.sum())} elements outside atol=rtol={tol}; "
+                           f"max_abs={err.max().item():.3e}")
+
+
+# ------------------------------------------------------------------------------------------
+# selection ops against the reference-generated fixtures (k = 64, the reference constant)
+# ------------------------------------------------------------------------------------------
+CHAINS = ["chain_small", "chain_32k", "chain_ragged", "chain_randn"]
+
+
+@pytest.mark.parametrize("name", CHAINS)
+def test_compute_cent_golden(ops, golden_dir, name):
+    f = load(golden_dir, name)
+    got = ops.compute_cent(f["q"].to(DEV), f["l1"].to(DEV))
+    assert got.dtype == torch.int32 and tuple(got.shape) == tuple(f["ref_indices"].shape)
+    assert torch.equal(got.cpu(), f["ref_indices"])
+
+
+@pytest.mark.parametrize("name", CHAINS + ["select_dupes"])
+def test_select_position_golden(ops, golden_dir, name):
+    f = load(golden_dir, name)
+    Bs = f["seq_len"].shape[0]
+    idx = (f["indices"] if "indices" in f else f["ref_indices"][:Bs]).to(DEV)
+    pp, ppl, gather = ops.select_position(f["block_ids"].to(DEV), f["block_table"].to(DEV),
+                                          f["seq_len"].to(DEV), idx)
+    assert tuple(pp.shape) == (Bs, idx.shape[1], 256) and tuple(ppl.shape) == (Bs, idx.shape[1], 8)
+    assert torch.equal(pp.cpu(), crop_pad(f["ref_pos"], 256))
+    assert torch.equal(ppl.cpu()[:, :, 0], f["ref_len"])
+    assert bool((ppl == ppl[:, :, :1]).all())
+    W = f["ref_cfull"].shape[2]
+    assert torch.equal(gather.cpu()[:, :, :W], f["ref_cfull"])
+
+
+@pytest.mark.parametrize("name", CHAINS)
+def test_cent_select_golden(ops, golden_dir, name):
+    f = load(golden_dir, name)
+    pp, ppl, mppl = ops.cent_select(f["q"].to(DEV), f["l1"].to(DEV), f["block_ids"].to(DEV),
+                                    f["block_table"].to(DEV), f["seq_len"].to(DEV))
+    assert torch.equal(pp.cpu(), crop_pad(f["ref_pos"], 256))
+    assert torch.equal(ppl.cpu()[:, :, 0], f["ref_len"])
+    want = f["ref_len"].to(torch.int64).max(dim=1)[0] * f["block_size"]        # tests/cent_select.py:96-98
+    assert mppl.dtype == torch.int64 and torch.equal(mppl.cpu()[:, 0], want)
+    assert bool((mppl == mppl[:, :1]).all())
+
+
+# ------------------------------------------------------------------------------------------
+# selection ops against the oracle on seeded cases (other k, C, group sizes, bf16)
+# ------------------------------------------------------------------------------------------
+SEL_CASES = [
+    # B, Nq, Nkv, C, S, k, qdtype, cent_dist
+    (1, 32, 8, 64, 4096, 8, torch.float16, "rand"),          # BASELINE configs[0]
+    (4, 32, 8, 512, 32768, 64, torch.float16, "rand"),       # configs[1] shape, reduced batch
+    (2, 64, 8, 2048, 131072, 128, torch.float16, "rand"),    # configs[3] shape, reduced batch
+    (3, 32, 8, 512, 32768 - 1000, 64, torch.bfloat16, "randn"),
+    (2, 8, 8, 100, 5000, 100, torch.float16, "rand"),        # g=1, k == C, C not a power of two
+    (2, 16, 1, 256, 2048, 1, torch.float16, "randn"),        # g=16, k=1
+]
+
+
+@pytest.mark.parametrize("B,Nq,Nkv,C,S,k,qdtype,dist", SEL_CASES)
+def test_selection_chain_oracle(ops, B, Nq, Nkv, C, S, k, qdtype, dist):
+    P = (S + 127) // 128
+    c = make_case(7 + C + k, B, Nq, Nkv, C, S, kv_pages=max(P + 7, 64), qdtype=qdtype, cent_dist=dist,
+                  ragged=True, MP=max(256, P))
+    g = to_device(c, DEV)
+    MP = c["MP"]
+    want_idx = oc.compute_cent(c["q"], c["l1"], k)
+    got_idx = ops.compute_cent(g["q"], g["l1"], k=k)
+    assert torch.equal(got_idx.cpu(), want_idx)
+    wp, wl, wg = oc.select_position(c["block_ids"], c["block_table"], c["seq"], want_idx, 128, MP)
+    gp, gl, gg = ops.select_position(g["block_ids"], g["block_table"], g["seq"], got_idx, max_page_num=MP)
+    assert torch.equal(gp.cpu(), wp) and torch.equal(gl.cpu(), wl) and torch.equal(gg.cpu(), wg)
+    wp2, wl2, wm2 = oc.cent_select(c["q"], c["l1"], c["block_ids"], c["block_table"], c["seq"], k, 128, MP)
+    gp2, gl2, gm2 = ops.cent_select(g["q"], g["l1"], g["block_ids"], g["block_table"], g["seq"], k=k,
+                                    max_page_num=MP)
+    assert torch.equal(gp2.cpu(), wp2) and torch.equal(gl2.cpu(), wl2) and torch.equal(gm2.cpu(), wm2)
+
+
+def test_topk_ties_lowest_index_first(ops):
+    """All-equal scores: the k lowest cluster ids must be chosen, in ascending order."""
+    q = torch.full((1, 4, 128), 0.5, dtype=torch.float16, device=DEV)
+    l1 = torch.full((2, 300, 128), 0.25, dtype=torch.float16, device=DEV)
+    got = ops.compute_cent(q, l1, k=37).cpu()
+    assert torch.equal(got, torch.arange(37, dtype=torch.int32).expand(1, 4, 37))
+    l1[:, 100:120] = 0.5                                           # two tied plateaus
+    got = ops.compute_cent(q, l1, k=30).cpu()
+    want = torch.cat([torch.arange(100, 120), torch.arange(0, 10)]).to(torch.int32).expand(1, 4, 30)
+    assert torch.equal(got, want)
+
+
+def test_select_truncates_at_max_page_num(ops):
+    """More selected pages than max_page_num: list is cut, length is the kept count."""
+    c = make_case(11, 1, 4, 2, 16, 64 * 128, kv_pages=80)
+    g = to_device(c, DEV)
+    idx = torch.arange(16, dtype=torch.int32).expand(1, 4, 16).contiguous()       # every cluster selected
+    wp, wl, _ = oc.select_position(c["block_ids"], c["block_table"], c["seq"], idx, 128, 32)
+    gp, gl, _ = ops.select_position(g["block_ids"], g["block_table"], g["seq"], idx.to(DEV), max_page_num=32)
+    assert torch.equal(gp.cpu(), wp) and torch.equal(gl.cpu(), wl) and int(gl.max()) == 32
+
+
+# ------------------------------------------------------------------------------------------
+# attention: known-answer vectors restated from the reference tests
+# ------------------------------------------------------------------------------------------
+def build_kat(num_heads, block_size, total_kv, sel_tokens, layout, batch=1, head_delta=0.0):
+    """tests/ifa_v5_case.py:584-765 (vLLM layout) / :12-191 (BNSD-paged): selected pages hold
+    0.1 (+ h*head_delta), every other page 9.9, q = 0.1.  Head h uses physical blocks
+    (3h + 2i) mod block_num; block_table packs the heads one after another and
+    block_position[b,h,i] is the running index.  Expected output: the per-head constant."""
+    D = 128
+    block_num = total_kv // block_size
+    per_head = sel_tokens // block_size
+    q = torch.full((batch, num_heads, D), 0.1, dtype=torch.float16)
+    shape = (block_num, block_size, num_heads, D) if layout == "vllm" else (block_num, num_heads, block_size, D)
+    key = torch.full(shape, 9.9, dtype=torch.float16)
+    value = torch.full(shape, 9.9, dtype=torch.float16)
+    bt = torch.full((batch, num_heads * per_head), 0x7FFFFFFF, dtype=torch.int32)
+    bp = torch.full((batch, num_heads, per_head), 0x7FFFFFFF, dtype=torch.int32)
+    run = 0
+    for h in range(num_heads):
+        val = 0.1 + h * head_delta
+        for i in range(per_head):
+            blk = (3 * h + 2 * i) % block_num
+            bt[:, run] = blk
+            bp[:, h, i] = run
+            run += 1
+            if layout == "vllm":
+                key[blk, :, h, :] = val
+                value[blk, :, h, :] = val
+            else:
+                key[blk, h, :, :] = val
+                value[blk, h, :, :] = val
+    asl = torch.tensor([per_head * block_size] * batch, dtype=torch.int64)
+    expect = torch.tensor([0.1 + h * head_delta for h in range(num_heads)]).to(torch.float16)
+    return q, key, value, bt, bp, asl, expect
+
+
+@pytest.mark.parametrize("layout,delta", [("vllm", 0.0), ("vllm", 0.001), ("bnsd", 0.001)])
+def test_attention_known_answer(ops, layout, delta):
+    H = 32
+    q, key, value, bt, bp, asl, expect = build_kat(H, 128, 32 * 1024, 10 * 1024, layout, head_delta=delta)
+    e = torch.empty(0, device=DEV)
+    out = ops.sparse_paged_attention(q.to(DEV), key.to(DEV), value.to(DEV), e, e, asl.to(DEV), e, e, e, e, e, e, e,
+                                     bt.to(DEV), e, bp.to(DEV), H, np.float32(1.0), "BNSD", H, 128, 1)
+    out = out.cpu()
+    assert out.shape == q.shape and out.dtype == torch.float16
+    assert not ((out.float() - 9.9).abs() < 1.0).any()            # ifa_v5_case.py:176-178 pass criterion
+    want = expect.view(1, H, 1).expand_as(out)
+    assert_close(out, want, 1e-3, "KAT")
+
+
+# ------------------------------------------------------------------------------------------
+# attention against the oracle
+# ------------------------------------------------------------------------------------------
+ATTN_CASES = [
+    # B, Nq, Nkv, C, S, k, qdtype, int8, tol
+    (1, 32, 8, 64, 4096, 8, torch.float16, False, 1e-3),         # configs[0]
+    (3, 32, 8, 512, 32768, 64, torch.float16, False, 1e-3),      # configs[1] shape
+    (2, 32, 8, 512, 32768 - 555, 64, torch.bfloat16, False, 2e-2),
+    (3, 32, 8, 512, 32768, 64, torch.bfloat16, True, 2e-2),      # configs[2] shape: int8 KV, bf16 q
+    (2, 32, 8, 256, 16384 - 77, 32, torch.float16, True, 2e-2),
+    (1, 64, 8, 2048, 131072, 128, torch.float16, False, 1e-3),   # configs[3] shape
+    (2, 8, 8, 128, 8192, 16, torch.float16, False, 1e-3),        # g = 1 (MHA)
+    (1, 32, 2, 128, 8192 - 3, 16, torch.float16, False, 1e-3),   # g = 16 (two head tiles)
+]
+
+
+@pytest.mark.parametrize("B,Nq,Nkv,C,S,k,qdtype,int8,tol", ATTN_CASES)
+def test_fused_vs_oracle(ops, B, Nq, Nkv, C, S, k, qdtype, int8, tol):
+    P = (S + 127) // 128
+    c = make_case(31 + C + k + B, B, Nq, Nkv, C, S, kv_pages=max(2 * P, 64), qdtype=qdtype, kv_int8=int8,
+                  ragged=(S % 128 != 0), MP=max(256, P))
+    g = to_device(c, DEV)
+    aqs = c["aq_scale"] if int8 else None
+    aqo = c["aq_offset"] if int8 else None
+    wout, wpos, wlen, wmx = oc.sparse_paged_fusion_attention(
+        c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"], c["seq"], Nq, c["scale"], Nkv,
+        128, k, c["MP"], aqs, aqo)
+    out, bp, ppl, mppl, ret = fused_call(ops, g, k)
+    assert torch.equal(bp.cpu(), wpos) and torch.equal(ppl.cpu(), wlen) and torch.equal(mppl.cpu(), wmx)
+    assert ret[0].data_ptr() == bp.data_ptr() and ret[1].data_ptr() == mppl.data_ptr()   # written in place
+    assert out.dtype == qdtype and out.shape == c["q"].shape
+    assert_close(out, wout, tol, "fused attention_out")
+
+
+@pytest.mark.parametrize("B,Nq,Nkv,C,S,k,qdtype,int8,tol", ATTN_CASES[:5])
+def test_separate_chain_matches_fused_and_oracle(ops, B, Nq, Nkv, C, S, k, qdtype, int8, tol):
+    """cent_select -> sparse_paged_attention (fused_ifa_v5_case.py:228-252) must agree with the
+    fused op: block_position exactly, attention_out within tolerance (S a multiple of the block
+    size, otherwise the separate op cannot know the context's last partial page)."""
+    S = (S + 127) // 128 * 128
+    P = S // 128
+    c = make_case(57 + C + k, B, Nq, Nkv, C, S, kv_pages=max(2 * P, 64), qdtype=qdtype, kv_int8=int8, MP=max(256, P))
+    g = to_device(c, DEV)
+    out_f, bp_f, ppl_f, mppl_f, _ = fused_call(ops, g, k)
+    pp, ppl, mppl = ops.cent_select(g["q"], g["l1"], g["block_ids"], g["block_table"], g["seq"], k=k,
+                                    max_page_num=c["MP"])
+    assert torch.equal(pp, bp_f) and torch.equal(mppl, mppl_f)
+    out_s = attn_call(ops, g, pp, mppl[:, 0].contiguous())
+    assert_close(out_s, out_f, tol, "separate vs fused")
+    want = oc.sparse_paged_attention(c["q"], c["key"], c["value"], mppl[:, 0].cpu(), c["block_table"], pp.cpu(),
+                                     Nq, c["scale"], Nkv, 128, c["aq_scale"] if int8 else None,
+                                     c["aq_offset"] if int8 else None)
+    assert_close(out_s, want, tol, "separate vs oracle")
+
+
+def test_attention_block_position_per_kv_head_and_partial_tail(ops):
+    """block_position given per KV head (kernel indexing, ..._Us2.h:258) with actual_seq_lengths not
+    a multiple of the block size: the last slot is clipped."""
+    B, Nq, Nkv, S = 2, 16, 4, 8192
+    c = make_case(91, B, Nq, Nkv, 64, S, kv_pages=128)
+    g = to_device(c, DEV)
+    gen = torch.Generator().manual_seed(5)
+    bp = torch.full((B, Nkv, 256), oc.INT32_MAX, dtype=torch.int32)
+    n = 11
+    for b in range(B):
+        for h in range(Nkv):
+            bp[b, h, :n] = torch.randperm(S // 128, generator=gen)[:n].to(torch.int32)   # unsorted on purpose
+    asl = torch.tensor([n * 128 - 50, (n - 3) * 128 + 1], dtype=torch.int64)
+    want = oc.sparse_paged_attention(c["q"], c["key"], c["value"], asl, c["block_table"], bp, Nq, c["scale"], Nkv, 128)
+    got = attn_call(ops, g, bp.to(DEV), asl.to(DEV))
+    assert_close(got, want, 1e-3, "per-kv-head block_position")
+
+
+def test_dense_mode_identity_block_position(ops):
+    """BASELINE configs[4]: the dense comparison runs the same kernel with an identity block_position."""
+    B, Nq, Nkv, S = 2, 32, 8, 4096
+    P = S // 128
+    c = make_case(93, B, Nq, Nkv, 64, S, kv_pages=2 * B * P, permute_table=True)
+    g = to_device(c, DEV)
+    bp = torch.arange(P, dtype=torch.int32).expand(B, Nkv, P).contiguous()
+    asl = torch.full((B,), S, dtype=torch.int64)
+    want = oc.sparse_paged_attention(c["q"], c["key"], c["value"], asl, c["block_table"], bp, Nq, c["scale"], Nkv, 128)
+    got = attn_call(ops, g, bp.to(DEV), asl.to(DEV))
+    assert_close(got, want, 1e-3, "dense mode")
+    # cross-check against torch SDPA on the gathered dense KV (independent of the oracle)
+    bt = c["block_table"].long()
+    K = c["key"][bt[:B, :P]].reshape(B, S, Nkv, 128).permute(0, 2, 1, 3).float()
+    V = c["value"][bt[:B, :P]].reshape(B, S, Nkv, 128).permute(0, 2, 1, 3).float()
+    qf = c["q"].float().view(B, Nkv, Nq // Nkv, 128)
+    ref = torch.nn.functional.scaled_dot_product_attention(qf, K, V, scale=c["scale"]).reshape(B, Nq, 128)
+    assert_close(got, ref, 2e-3, "dense mode vs SDPA")
+
+
+def test_empty_and_degenerate_inputs(ops):
+    B, Nq, Nkv = 2, 8, 2
+    c = make_case(95, B, Nq, Nkv, 64, 1024, kv_pages=64)
+    g = to_device(c, DEV)
+    # a sequence of length 0 selects nothing: lengths 0, padding everywhere, zero output
+    g["seq"] = torch.tensor([0, 1024], dtype=torch.int32, device=DEV)
+    c["seq"] = g["seq"].cpu()
+    wout, wpos, wlen, wmx = oc.sparse_paged_fusion_attention(
+        c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"], c["seq"], Nq, c["scale"], Nkv, 128, 8, 256)
+    out, bp, ppl, mppl, _ = fused_call(ops, g, 8)
+    assert torch.equal(bp.cpu(), wpos) and torch.equal(ppl.cpu(), wlen) and torch.equal(mppl.cpu(), wmx)
+    assert bool((out[0] == 0).all())
+    assert_close(out, wout, 1e-3, "seq_len 0")
+    # all-sentinel block_position -> zeros
+    bp0 = torch.full((B, Nkv, 256), oc.INT32_MAX, dtype=torch.int32, device=DEV)
+    got = attn_call(ops, g, bp0, torch.tensor([1024, 1024], device=DEV))
+    assert bool((got == 0).all())
+
+
+def test_query_4d_and_noncontiguous(ops):
+    B, Nq, Nkv, S, k = 2, 32, 8, 8192, 16
+    c = make_case(97, B, Nq, Nkv, 128, S, kv_pages=256)
+    g = to_device(c, DEV)
+    wout, *_ = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"],
+                                                c["block_ids"], c["seq"], Nq, c["scale"], Nkv, 128, k, 256)
+    big = torch.zeros(B, Nq, 3, 128, dtype=torch.float16, device=DEV)
+    big[:, :, 1] = g["q"]
+    g4 = dict(g)
+    g4["q"] = big[:, :, 1:2, :]                                   # [B,Nq,1,D], strided
+    out, *_ = fused_call(ops, g4, k)
+    assert out.shape == (B, Nq, 1, 128)
+    assert_close(out.view(B, Nq, 128), wout, 1e-3, "4-D strided query")
+
+
+def test_unsupported_arguments_raise(ops):
+    c = make_case(99, 1, 8, 2, 64, 1024, kv_pages=64)
+    g = to_device(c, DEV)
+    e = torch.empty(0, device=DEV)
+    bp = torch.zeros(1, 2, 256, dtype=torch.int32, device=DEV)
+    asl = torch.tensor([128], device=DEV)
+
+    def call(pse=e, mask=e, heads=8, bs=128):
+        return ops.sparse_paged_attention(g["q"], g["key"], g["value"], pse, mask, asl, e, e, e, e, e, e, e,
+                                          g["block_table"], e, bp, heads, 1.0, "BNSD", 2, bs, 1)
+
+    with pytest.raises(RuntimeError, match="pse_shift"):
+        call(pse=torch.zeros(1, device=DEV))
+    with pytest.raises(RuntimeError, match="attention_mask"):
+        call(mask=torch.zeros(1, device=DEV))
+    with pytest.raises(RuntimeError, match="num_heads"):
+        call(heads=16)
+    with pytest.raises(RuntimeError, match="block_size"):
+        call(bs=64)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        ops.compute_cent(c["q"], c["l1"])
+    with pytest.raises(RuntimeError, match="exceeds cluster count"):
+        ops.compute_cent(g["q"], g["l1"], k=65)
+    with pytest.raises(RuntimeError):
+        ops.incre_flash_attention_v4(g["q"], [g["key"]], [g["value"]], e, e, asl, e, e, e, e, e, e, e,
+                                     g["block_table"], e, 8, 1.0, "BNSD", 2, 128, 1)
+
+
+def test_torch_ops_namespace_and_plan(ops):
+    """torch.ops.myops.* keeps the reference schema (registration.cpp:43-57); FusedDecodePlan replays."""
+    c = make_case(101, 2, 32, 8, 128, 8192, kv_pages=256)
+    g = to_device(c, DEV)
+    a = torch.ops.myops.compute_cent(g["q"], g["l1"])
+    b = ops.compute_cent(g["q"], g["l1"])
+    assert torch.equal(a, b)
+    out, bp, ppl, mppl, _ = fused_call(ops, g, 64)
+    bp2, ppl2, mppl2 = torch.empty_like(bp), torch.empty_like(ppl), torch.empty_like(mppl)
+    out2 = torch.empty_like(out)
+    plan = ops.FusedDecodePlan(g["q"], g["key"], g["value"], g["block_table"], g["l1"], g["block_ids"], g["seq"],
+                               bp2, ppl2, mppl2, out2, 32, c["scale"], 8, 128, k=64)
+    assert plan.num_launches == 1
+    for _ in range(3):
+        plan.launch()
+    torch.cuda.synchronize()
+    assert torch.equal(bp2, bp) and torch.equal(mppl2, mppl) and torch.equal(out2, out)
+    # CUDA-graph capture of the fused launch
+    gr = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        plan.launch()
+    torch.cuda.current_stream().wait_stream(s)
+    with torch.cuda.graph(gr):
+        plan.launch()
+    out2.zero_()
+    gr.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out2, out)
