@@ -1,0 +1,470 @@
+#!/usr/bin/env python
+"""Benchmark of the fused centroid-sparse paged decode-attention step (SparsePagedFusionAttention).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c2]
+
+One "step" = one fused decode-attention call for one layer: ComputeCent + SelectPosition + sparse
+paged flash-decode for B sequences (BASELINE.json metric: decode attn tokens/s + achieved HBM GB/s
+on the selected-KV bytes).  Prints ONE JSON line on rank 0.
+
+  value     tokens/s with every input resident in HBM, launch-ready executor (FusedDecodePlan),
+            CUDA events on the launching stream, L2 flushed before every timed step.
+  e2e       same metric through `custom_ops.sparse_paged_fusion_attention` (the reference-facing
+            plugin call: validation, descriptors, workspace allocation) with the step's inputs
+            (query, block_table, total_seq_len) copied from pinned host memory and attention_out
+            copied back to pinned host memory inside the timed region.  The paged KV pool, the
+            centroids and block_ids are the resident cache state of the serving engine (they live
+            in device memory in the reference too) and are not per-step inputs.
+  roofline  algorithmic bytes of one launch (union-of-group selected K+V page slices +
+            centroids + index tensors + q/out, computed from the selection the kernel produced)
+            / CUDA-event duration of that launch, against MEASURED_PEAKS.json hbm_gbs.
+  cpu_baseline  the CPU oracle (port of the reference golden chain + attention restatement) timed
+            on this box's host cores on a bounded sample (first sequences of the same workload).
+
+Multi-GPU (torchrun, one rank per GPU): KV-head tensor parallelism -- rank r owns KV heads
+[r*Nkv/N, (r+1)*Nkv/N) with their query heads, centroids, block_ids and a rank-local KV pool; the
+only collective is the NCCL all-gather of attention_out.  Default scaling is "weak": the batch
+grows with N (B = 16*N) so the bytes streamed per GPU stay fixed; `--scaling strong` keeps the
+global workload fixed (BASELINE configs[3]: c4 on 2/4/8 GPUs).
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "cann-ops-adv-vllm_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+BS = 128
+D = 128
+WORKLOADS = {
+    # BASELINE.json configs[0..3]
+    "c1": dict(B=1, Nq=32, Nkv=8, S=4096, C=64, k=8, q="f16", kv="f16",
+               desc="CPU golden case: B=1 32Q/8KV D=128 seq 4096 C=64 top-k=8 fp16"),
+    "c2": dict(B=16, Nq=32, Nkv=8, S=32768, C=512, k=64, q="f16", kv="f16",
+               desc="Llama-3-8B decode: B=16 32Q/8KV D=128 seq 32k C=512 top-k=64 fp16 KV, fused"),
+    "c3": dict(B=64, Nq=32, Nkv=8, S=32768, C=512, k=64, q="bf16", kv="i8",
+               desc="Llama-3-8B decode, int8 KV (antiquant), bf16 query: B=64 seq 32k C=512 top-k=64, fused"),
+    "c4": dict(B=32, Nq=64, Nkv=8, S=131072, C=2048, k=128, q="f16", kv="f16",
+               desc="Llama-3-70B decode: B=32 64Q/8KV D=128 seq 128k C=2048 top-k=128 fp16 KV, fused"),
+}
+METRIC = "decode_attn_tokens_per_s"
+UNIT = "tokens/s"
+
+
+def qdtype(w):
+    return torch.float16 if w["q"] == "f16" else torch.bfloat16
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic inputs: generated on the device, seeded; block_table is a per-sequence
+# permutation of distinct physical pages so aliasing does not inflate L2 hits
+# ------------------------------------------------------------------------------------------------
+def make_inputs(w, B, rank, world, device, seed=1234):
+    Nq, Nkv, S, C = w["Nq"], w["Nkv"], w["S"], w["C"]
+    assert Nkv % world == 0, "KV heads must divide across ranks"
+    nkv = Nkv // world
+    nq = Nq // world
+    P = (S + BS - 1) // BS
+    pages = B * P
+    qd = qdtype(w)
+    g_common = torch.Generator(device=device).manual_seed(seed)
+    g_rank = torch.Generator(device=device).manual_seed(seed + 1000 * (rank + 1))
+    block_table = torch.randperm(pages, generator=g_common, device=device).to(torch.int32).view(B, P)
+    seq = torch.full((B,), S, dtype=torch.int32, device=device)
+    q = torch.rand(B, nq, D, generator=g_rank, device=device).to(qd)
+    l1 = torch.rand(nkv, C, D, generator=g_rank, device=device).to(qd)
+    block_ids = torch.randint(0, C, (nkv, pages), generator=g_rank, device=device, dtype=torch.int32)
+    if w["kv"] == "i8":
+        key = torch.empty(pages, BS, nkv, D, dtype=torch.int8, device=device)
+        value = torch.empty_like(key)
+        aq_scale = (torch.rand(2, nkv, D, generator=g_rank, device=device) * 0.02 + 0.005).to(qd)
+        aq_offset = torch.randn(2, nkv, D, generator=g_rank, device=device).to(qd)
+    else:
+        key = torch.empty(pages, BS, nkv, D, dtype=qd, device=device)
+        value = torch.empty_like(key)
+        aq_scale = torch.empty(0, dtype=qd, device=device)
+        aq_offset = torch.empty(0, dtype=qd, device=device)
+    chunk = max(1, (64 << 20) // (BS * nkv * D))              # ~64 Mi elements per chunk
+    for t in (key, value):
+        for p0 in range(0, pages, chunk):
+            n = min(chunk, pages - p0)
+            if w["kv"] == "i8":
+                t[p0:p0 + n] = torch.randint(-128, 128, (n, BS, nkv, D), generator=g_rank, device=device,
+                                             dtype=torch.int8)
+            else:
+                t[p0:p0 + n] = (torch.rand(n, BS, nkv, D, generator=g_rank, device=device) * (1 - 1e-3) + 1e-3).to(qd)
+    return dict(q=q, l1=l1, block_ids=block_ids, block_table=block_table, seq=seq, key=key, value=value,
+                aq_scale=aq_scale, aq_offset=aq_offset, B=B, Nq=nq, Nkv=nkv, C=C, S=S, P=P, k=w["k"],
+                scale=1.0 / math.sqrt(D), MP=256, qd=qd)
+
+
+def algorithmic_bytes(inp, page_position, page_position_length):
+    """compulsory bytes of one fused launch, from the selection actually produced."""
+    B, nq, nkv, P, MP = inp["B"], inp["Nq"], inp["Nkv"], inp["P"], inp["MP"]
+    g = nq // nkv
+    ln = page_position_length[:, :, 0].long()
+    valid = torch.arange(MP, device=ln.device).view(1, 1, MP) < ln.unsqueeze(-1)
+    pp = page_position.long().clamp(0, P - 1)
+    onehot = torch.zeros(B, nq, P, dtype=torch.bool, device=ln.device)
+    onehot.scatter_(2, pp, valid)
+    union_pages = int(onehot.view(B, nkv, g, P).any(dim=2).sum().item())
+    selected = int(ln.sum().item())
+    kv_elem = inp["key"].element_size()
+    q_elem = inp["q"].element_size()
+    page_bytes = BS * D * 2 * kv_elem                        # K + V slice of one page for one kv head
+    bytes_kv = union_pages * page_bytes
+    bytes_sel = (nkv * inp["C"] * D * q_elem + nkv * B * P * 4 + B * P * 4 + B * nq * (MP + 8) * 4 + B * 8 * 8)
+    bytes_io = 2 * B * nq * D * q_elem
+    if kv_elem == 1:
+        bytes_sel += 2 * 2 * nkv * D * q_elem
+    return dict(bytes_alg=bytes_kv + bytes_sel + bytes_io, bytes_kv_union=bytes_kv,
+                bytes_logical=selected * page_bytes, union_pages=union_pages, selected_pages=selected,
+                bytes_dense=B * nkv * P * page_bytes)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md "clocks DURING the timed region")
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline (oracle port) on a bounded sample
+# ------------------------------------------------------------------------------------------------
+def cpu_sample(inp, nseq):
+    """First `nseq` sequences of the workload, their pages compacted into a small CPU pool."""
+    bt = inp["block_table"][:nseq].long()                          # [nseq, P]
+    flat = bt.reshape(-1)
+    c = dict(q=inp["q"][:nseq].cpu(), l1=inp["l1"].cpu(), seq=inp["seq"][:nseq].cpu(),
+             key=inp["key"][flat].cpu(), value=inp["value"][flat].cpu(),
+             block_ids=inp["block_ids"][:, flat].cpu().contiguous(),
+             block_table=torch.arange(flat.numel(), dtype=torch.int32).view(nseq, -1),
+             aq_scale=inp["aq_scale"].cpu(), aq_offset=inp["aq_offset"].cpu())
+    return c
+
+
+def run_oracle(c, inp):
+    from oracle import sparse_chain as oc
+    i8 = c["key"].dtype == torch.int8
+    return oc.sparse_paged_fusion_attention(
+        c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"], c["seq"], inp["Nq"],
+        inp["scale"], inp["Nkv"], BS, inp["k"], inp["MP"], c["aq_scale"] if i8 else None,
+        c["aq_offset"] if i8 else None)
+
+
+def time_cpu_baseline(inp, budget_s=15.0, nseq=1):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    c = cpu_sample(inp, nseq)
+    best = float("inf")
+    t_all = time.perf_counter()
+    reps = 0
+    while reps < 3 or (time.perf_counter() - t_all < budget_s and reps < 10):
+        t0 = time.perf_counter()
+        run_oracle(c, inp)
+        best = min(best, time.perf_counter() - t0)
+        reps += 1
+        if time.perf_counter() - t_all > 2 * budget_s:
+            break
+    return {"value": nseq / best, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"first {nseq} of {inp['B']} sequences of the workload (all {inp['Nq']} q heads), "
+                      f"oracle/sparse_chain.py fused chain, best of {reps}, torch threads={cores}"}, c
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="replay the step from a CUDA graph")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    w = WORKLOADS[args.workload]
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        return reference_arm(args, w)
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback exists)"
+    import custom_ops
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    B = w["B"] * world if args.scaling == "weak" else w["B"]
+    inp = make_inputs(w, B, rank, world, dev)
+    nq, nkv = inp["Nq"], inp["Nkv"]
+    qd = inp["qd"]
+
+    bp = torch.empty(B, nq, inp["MP"], dtype=torch.int32, device=dev)
+    ppl = torch.empty(B, nq, 8, dtype=torch.int32, device=dev)
+    mppl = torch.empty(B, 8, dtype=torch.int64, device=dev)
+    out = torch.empty(B, nq, D, dtype=qd, device=dev)
+    out_all = torch.empty(world, B, nq, D, dtype=qd, device=dev) if world > 1 else None
+    i8 = w["kv"] == "i8"
+    plan = custom_ops.FusedDecodePlan(
+        inp["q"], inp["key"], inp["value"], inp["block_table"], inp["l1"], inp["block_ids"], inp["seq"],
+        bp, ppl, mppl, out, nq, inp["scale"], nkv, BS, k=inp["k"],
+        antiquant_scale=inp["aq_scale"] if i8 else None, antiquant_offset=inp["aq_offset"] if i8 else None)
+    launches_per_step = plan.num_launches
+    flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step():
+        plan.launch()
+        if world > 1:
+            dist.all_gather_into_tensor(out_all, out)
+
+    graph = None
+    if args.graph:
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            step()
+        torch.cuda.current_stream().wait_stream(s)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            step()
+
+    def run_step():
+        if graph is not None:
+            graph.replay()
+        else:
+            step()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---------------- device-resident timing ----------------
+    for _ in range(args.warmup):
+        if flush is not None:
+            flush.zero_()
+        run_step()
+    barrier()
+    ab = algorithmic_bytes(inp, bp, ppl)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for s0, s1 in ev:
+        if flush is not None:
+            flush.zero_()
+        s0.record()
+        run_step()
+        s1.record()
+    barrier()
+    times = [a.elapsed_time(b) for a, b in ev]                      # ms
+    total_ms = torch.tensor([sum(times)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    ms_per_step = total_ms.item() / args.steps
+    st = sorted(times)
+
+    # ---------------- end-to-end through the reference-facing call ----------------
+    hq = inp["q"].cpu().pin_memory()
+    hbt = inp["block_table"].cpu().pin_memory()
+    hseq = inp["seq"].cpu().pin_memory()
+    hout = torch.empty(B, nq * world, D, dtype=qd).pin_memory() if world > 1 else torch.empty(B, nq, D, dtype=qd).pin_memory()
+    e = torch.empty(0, dtype=qd, device=dev)
+    e64 = torch.empty(0, dtype=torch.int64, device=dev)
+    h2d = hq.numel() * hq.element_size() + hbt.numel() * 4 + hseq.numel() * 4
+    d2h = hout.numel() * hout.element_size()
+
+    def e2e_step():
+        dq = hq.to(dev, non_blocking=True)
+        dbt = hbt.to(dev, non_blocking=True)
+        dseq = hseq.to(dev, non_blocking=True)
+        o, _, _ = custom_ops.sparse_paged_fusion_attention(
+            dq, inp["key"], inp["value"], e, e, e64, e, e, e, e, e, inp["aq_scale"], inp["aq_offset"], dbt, e64,
+            inp["l1"], inp["block_ids"], dseq, bp, ppl, mppl, nq, inp["scale"], "BNSD", nkv, BS, 1, k=inp["k"])
+        if world > 1:
+            dist.all_gather_into_tensor(out_all, o)
+            hout.copy_(out_all.permute(1, 0, 2, 3).reshape(B, nq * world, D), non_blocking=True)
+        else:
+            hout.copy_(o, non_blocking=True)
+
+    for _ in range(args.warmup):
+        e2e_step()
+    barrier()
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for s0, s1 in ev2:
+        if flush is not None:
+            flush.zero_()
+        s0.record()
+        e2e_step()
+        s1.record()
+        s1.synchronize()                                            # the caller consumes hout every step
+    barrier()
+    t2 = [a.elapsed_time(b) for a, b in ev2]
+    tot2 = torch.tensor([sum(t2)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot2, op=dist.ReduceOp.MAX)
+    e2e_ms = tot2.item() / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+
+    # sum the per-rank algorithmic bytes (whole job)
+    agg = torch.tensor([ab["bytes_alg"], ab["bytes_kv_union"], ab["bytes_logical"], ab["bytes_dense"]],
+                       dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            cpu, _ = time_cpu_baseline(inp)
+        tokens_per_s = B / (ms_per_step * 1e-3)
+        achieved = ab["bytes_alg"] / (ms_per_step * 1e-3) / 1e9      # per-GPU kernel (rank 0's launch)
+        line = {
+            "metric": METRIC, "value": tokens_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f16" if w["q"] == "f16" else "bf16",
+            "data": "synthetic (seeded torch.rand/randint on device; block_table = random permutation of distinct pages)",
+            "config": {"workload": f"{args.workload}: {w['desc']}", "global_batch": B, "q_heads": w["Nq"],
+                       "kv_heads": w["Nkv"], "head_dim": D, "seq_len": w["S"], "block_size": BS, "clusters": w["C"],
+                       "top_k": w["k"], "kv_dtype": w["kv"], "q_dtype": w["q"],
+                       "parallelism": f"kv-head tp{world}" if world > 1 else "single gpu",
+                       "l2": ("flushed before every timed step (256 MiB memset); " if flush is not None else "not flushed; ") +
+                             f"per-step read set {ab['bytes_kv_union'] / 2**20:.0f} MiB > 126 MB L2",
+                       "launch": "cuda graph replay" if graph is not None else "FusedDecodePlan.launch()"},
+            "achieved_hbm_gbs_selected_kv": agg[1].item() / (ms_per_step * 1e-3) / 1e9,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "spa_chain_kernel (fused: select + flash-decode + combine)",
+                         "bytes_alg_per_launch": ab["bytes_alg"], "bytes_kv_union": ab["bytes_kv_union"],
+                         "bytes_logical_per_q_head": ab["bytes_logical"], "bytes_dense": ab["bytes_dense"],
+                         "union_pages": ab["union_pages"], "selected_pages": ab["selected_pages"]},
+            "timing": {"min_ms": st[0], "median_ms": st[len(st) // 2], "p90_ms": st[int(len(st) * 0.9)],
+                       "max_ms": st[-1]},
+            "e2e": {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
+                    "api": "custom_ops.sparse_paged_fusion_attention"},
+            "gpu_launches": launches_per_step * args.steps,
+            "clocks": clocks,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def reference_arm(args, w):
+    """The reference's CPU implementation of the path (its torch golden for the selection + the CPU
+    restatement of the attention kernel), i.e. the oracle port, on this box's host cores."""
+    dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    nseq = 1
+    # inputs: same generator as the b200 arm when a GPU is present, else a CPU-generated sample
+    if dev.type == "cuda":
+        inp = make_inputs(w, w["B"], 0, 1, dev)
+        c = cpu_sample(inp, nseq)
+    else:
+        small = dict(w); small["B"] = nseq
+        inp = make_inputs(small, nseq, 0, 1, dev)
+        c = cpu_sample(inp, nseq)
+    for _ in range(min(args.warmup, 3)):
+        run_oracle(c, inp)
+    steps = max(1, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        run_oracle(c, inp)
+    dt = (time.perf_counter() - t0) / steps
+    v = nseq / dt
+    sample = (f"each step = first {nseq} of {w['B']} sequences of the workload (all {w['Nq']} q heads); "
+              f"oracle/sparse_chain.py fused chain; torch threads={cores}")
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": min(args.warmup, 3), "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f16" if w["q"] == "f16" else "bf16",
+            "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {w['desc']}", "sample": sample},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
