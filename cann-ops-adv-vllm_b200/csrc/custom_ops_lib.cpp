@@ -88,7 +88,8 @@ at::Tensor compute_cent_k(const at::Tensor &query, const at::Tensor &l1_cent, in
     Desc q = desc(query, "query"), c = desc(l1_cent, "l1_cent"), r = desc(result, "indices", true);
     uint64_t ws = 0; ExecGuard g;
     check(spaComputeCentGetWorkspaceSize(q.ptr(), c.ptr(), r.ptr(), &ws, &g.e), "compute_cent");
-    check(spaComputeCent(nullptr, 0, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "compute_cent");
+    at::Tensor wsp = alloc_ws(ws, query);
+    check(spaComputeCent(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "compute_cent");
     return result;
 }
 at::Tensor compute_cent(const at::Tensor &query, const at::Tensor &l1_cent) {
@@ -114,7 +115,8 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> select_position_ex(
     uint64_t ws = 0; ExecGuard g;
     check(spaSelectPositionGetWorkspaceSize(a.ptr(), b.ptr(), c.ptr(), d.ptr(), block_size, o1.ptr(), o2.ptr(),
                                             o3.ptr(), &ws, &g.e), "select_position");
-    check(spaSelectPosition(nullptr, 0, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "select_position");
+    at::Tensor wsp = alloc_ws(ws, block_ids);
+    check(spaSelectPosition(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "select_position");
     return std::make_tuple(pp, ppl, gather);
 }
 std::tuple<at::Tensor, at::Tensor, at::Tensor> select_position(const at::Tensor &block_ids,
@@ -142,7 +144,8 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select_ex(
     uint64_t ws = 0; ExecGuard g;
     check(spaCentSelectGetWorkspaceSize(q.ptr(), c.ptr(), a.ptr(), b.ptr(), s.ptr(), k, block_size, o1.ptr(),
                                         o2.ptr(), o3.ptr(), &ws, &g.e), "cent_select");
-    check(spaCentSelect(nullptr, 0, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "cent_select");
+    at::Tensor wsp = alloc_ws(ws, query);
+    check(spaCentSelect(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "cent_select");
     return std::make_tuple(pp, ppl, mppl);
 }
 std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select(const at::Tensor &query, const at::Tensor &l1_cent,
@@ -349,7 +352,15 @@ PYBIND11_MODULE(custom_ops_lib, m) {
     m.def("sparse_paged_fusion_attention_ex", &sparse_paged_fusion_attention_ex);
     pybind11::class_<FusionPlan, std::shared_ptr<FusionPlan>>(m, "FusionPlan")
         .def_property_readonly("workspace_bytes", [](const FusionPlan &p) { return p.ws_bytes; })
-        .def_property_readonly("num_launches", [](const FusionPlan &p) { return spaExecutorNumLaunches(p.exec); });
+        .def_property_readonly("num_launches", [](const FusionPlan &p) { return spaExecutorNumLaunches(p.exec); })
+        .def_property_readonly("grid_size", [](const FusionPlan &p) { return spaExecutorGridSize(p.exec); })
+        .def("set_trace", [](FusionPlan &p, const at::Tensor &buf) {
+            if (!buf.defined() || buf.numel() == 0) { spaExecutorSetTrace(p.exec, nullptr); return; }
+            TORCH_CHECK(buf.is_cuda() && buf.scalar_type() == at::kLong && buf.is_contiguous() &&
+                        buf.numel() >= (int64_t)spaExecutorGridSize(p.exec) * 16, "trace: need int64 CUDA [grid,16]");
+            p.keep.push_back(buf);
+            spaExecutorSetTrace(p.exec, buf.data_ptr());
+        });
     m.def("make_fusion_plan", &make_fusion_plan);
     m.def("launch_fusion_plan", &launch_fusion_plan);
     m.def("abi_version", []() { return spaGetVersion(); });

@@ -56,14 +56,18 @@ struct ChainParams {
     int *tail_count;                                     // [items]
     float *part_o;                                       // [slots, HP, D]
     float *part_ml;                                      // [slots, HP, 2]
+    double *exact_scratch;                               // [grid, kConsumerWarps, C] (rare: > 512 near-ties)
     // ---- launch shape
-    int hb;                                              // heads scored per pass in phase A
-    int nbins;                                           // histogram bins (pow2)
+    int sel_gw;                                          // warps per selection group (4 or 8)
+    int sel_group_bytes;                                 // smem bytes of one selection group
     int nstages;                                         // pipeline stages
     int stage_bytes;
     int smem_bytes;
     int mode;                                            // see Mode
+    // ---- optional phase trace: [gridDim.x, kTraceSlots] globaltimer ns (null = off)
+    unsigned long long *trace;
 };
+constexpr int kTraceSlots = 16;
 
 enum Mode : int {
     kModeFused = 0,        // scores + topk + select + attention
@@ -226,6 +230,15 @@ template <int I, int J> struct I8Pair<__nv_bfloat16, I, J> {
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void trace_mark(const ChainParams &p, int slot) {
+    if (p.trace != nullptr && threadIdx.x == 0) p.trace[(size_t)blockIdx.x * kTraceSlots + slot] = globaltimer_ns();
 }
 
 __device__ __forceinline__ float fast_exp2(float x) {

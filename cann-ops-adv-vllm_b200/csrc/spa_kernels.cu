@@ -39,24 +39,28 @@ spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ 
     unsigned char *smem = aligned_smem(smem_raw);
     cg::grid_group grid = cg::this_grid();
 
+    trace_mark(p, 0);
     // ---- phase A: selection (or union building) per (b, kv head)
-    for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
-        if (p.mode == kModeFused)
-            select_item<QT>(p, item, kSelScores | kSelSelect | kSelUnion, smem);
-        else
-            union_from_block_position(p, item, smem);
-    }
+    if (p.mode == kModeFused)
+        select_phase<QT>(p, kSelScores | kSelSelect | kSelUnion, smem);
+    else
+        for (int item = blockIdx.x; item < p.items; item += gridDim.x) union_from_block_position(p, item, smem);
+    trace_mark(p, 1);
     __threadfence();
     grid.sync();
+    trace_mark(p, 2);
     if (p.mode == kModeFused)
         for (int b = blockIdx.x; b < p.B; b += gridDim.x) write_max_ppl(p, b);
 
     // ---- phase B: stream the selected pages
     attention_phase<QT, KVI8, NT>(p, &tmK, &tmV, smem);
+    trace_mark(p, 3);
     __threadfence();
     grid.sync();
+    trace_mark(p, 4);
     // ---- phase C: combine
     combine_phase<QT, KVI8, NT>(p, smem);
+    trace_mark(p, 5);
 }
 
 // Stand-alone selection ops (ComputeCent / SelectPosition / CentSelect share the device code).
@@ -65,7 +69,7 @@ __global__ void __launch_bounds__(kThreads, 1) spa_select_kernel(const __grid_co
                                                                  int flags) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = aligned_smem(smem_raw);
-    for (int item = blockIdx.x; item < p.items; item += gridDim.x) select_item<QT>(p, item, flags, smem);
+    select_phase<QT>(p, flags, smem);
 }
 
 __global__ void spa_max_ppl_kernel(const __grid_constant__ ChainParams p) {
@@ -102,7 +106,7 @@ struct spaExecutor {
     int q_bf16, kv_i8, nt_tiles;
     uint64_t ws_bytes;
     // workspace offsets (bytes)
-    uint64_t off_uphys, off_umeta, off_ulen, off_tail, off_po, off_pml;
+    uint64_t off_uphys, off_umeta, off_ulen, off_tail, off_po, off_pml, off_xs;
     int launches;
 };
 
@@ -141,6 +145,8 @@ static const char *dtype_name(int d) {
 #define REQUIRE_CONTIG(t, name)                                                                 \
     if (!contiguous(t)) return fail(SPA_ERR_SHAPE, "%s: must be contiguous", name)
 
+static uint64_t align_up(uint64_t x, uint64_t a) { return (x + a - 1) / a * a; }
+
 struct DevInfo { int sms; int smem_optin; int coop; };
 static int dev_info(DevInfo *d) {
     int dev = 0;
@@ -151,7 +157,6 @@ static int dev_info(DevInfo *d) {
     return SPA_OK;
 }
 
-static int pow2_ceil(int x) { int p = 1; while (p < x) p <<= 1; return p; }
 
 // ---- query: [B,Nq,D] or [B,Nq,1,D]
 static int parse_query(const spaTensor *q, const char *name, int *B, int *Nq, long long *sb,
@@ -196,14 +201,17 @@ static int parse_tables(const spaTensor *bid, const spaTensor *bt, const spaTens
     return SPA_OK;
 }
 
-// choose heads-per-pass / histogram bins for phase A so that its smem fits `budget`
-static int plan_select_smem(ChainParams *p, int budget, int *bytes) {
-    p->nbins = std::max(1024, pow2_ceil((p->C + 1) / 2));
+// choose the selection group width (4 or 8 warps per item) so that phase A's smem fits `budget`
+static int plan_select_smem(ChainParams *p, int flags, int grid, int budget, int *bytes) {
     const int Ceff = std::max(p->C, 1), keff = std::max(p->k, 1);
-    for (int hb = 8; hb >= 1; hb >>= 1) {
-        if (hb > pow2_ceil(p->g)) continue;
-        SelSmem L(p->g, Ceff, keff, hb, p->nbins, p->maxP);
-        if (L.total <= budget) { p->hb = hb; *bytes = L.total; return SPA_OK; }
+    int gw = (p->g > 4 || p->items <= grid) ? 8 : 4;
+    for (; gw <= 8; gw *= 2) {
+        SelSmem L(p->g, Ceff, keff, p->maxP, gw, flags);
+        const long long total = (long long)L.total * (kConsumerWarps / gw);
+        if (total <= budget) {
+            p->sel_gw = gw; p->sel_group_bytes = L.total; *bytes = (int)total;
+            return SPA_OK;
+        }
     }
     return fail(SPA_ERR_UNSUPPORTED, "selection working set (g=%d, C=%d, k=%d, maxP=%d) exceeds shared memory", p->g, p->C, p->k, p->maxP);
 }
@@ -300,7 +308,6 @@ static SelectKernel select_kernel_for(int bf16) {
     return bf16 ? spa_select_kernel<__nv_bfloat16> : spa_select_kernel<__half>;
 }
 
-static uint64_t align_up(uint64_t x, uint64_t a) { return (x + a - 1) / a * a; }
 
 // =============================================================================================
 // C ABI
@@ -312,6 +319,12 @@ int spaGetVersion(void) { return 100; }
 int spaGetCompiledArch(void) { return 100; }
 int spaDestroyExecutor(spaExecutor *e) { delete e; return SPA_OK; }
 int spaExecutorNumLaunches(const spaExecutor *e) { return e ? e->launches : 0; }
+int spaExecutorGridSize(const spaExecutor *e) { return e ? e->grid : 0; }
+int spaExecutorSetTrace(spaExecutor *e, void *deviceBuffer) {
+    if (!e) return fail(SPA_ERR_ARG, "bad executor");
+    e->p.trace = (unsigned long long *)deviceBuffer;
+    return SPA_OK;
+}
 
 // ---------------------------------------------------------------------------------------------
 // selection ops
@@ -321,24 +334,32 @@ static int finish_select_plan(spaExecutor *e, uint64_t *ws, spaExecutor **out) {
     int rc = dev_info(&d);
     if (rc) { delete e; return rc; }
     int bytes = 0;
-    rc = plan_select_smem(&e->p, d.smem_optin - 1024, &bytes);
+    // stand-alone ops: enough CTAs for one item per group, capped at a few waves
+    rc = plan_select_smem(&e->p, e->flags, 0, d.smem_optin - 1024, &bytes);
     if (rc) { delete e; return rc; }
     e->p.smem_bytes = bytes + 1024;
-    e->grid = std::max(1, e->p.items);
-    e->ws_bytes = 0;
-    *ws = 0;
+    const int ngroups = kConsumerWarps / e->p.sel_gw;
+    e->grid = std::max(1, std::min((e->p.items + ngroups - 1) / ngroups, 8 * d.sms));
+    // exact-score scratch for the rare case of more than kXCap near-ties around the k-th score
+    e->off_xs = 0;
+    e->ws_bytes = (e->flags & kSelScores) ? align_up((uint64_t)e->grid * kConsumerWarps * std::max(e->p.C, 1) * 8, 256) : 0;
+    *ws = e->ws_bytes;
     *out = e;
     return SPA_OK;
 }
 
-static int launch_select(spaExecutor *e, cudaStream_t stream) {
+static int launch_select(void *workspace, uint64_t wsSize, spaExecutor *e, cudaStream_t stream) {
     if (e->p.items == 0) return SPA_OK;
+    if (e->ws_bytes && (!workspace || wsSize < e->ws_bytes))
+        return fail(SPA_ERR_WORKSPACE, "workspace %llu bytes < required %llu", (unsigned long long)wsSize, (unsigned long long)e->ws_bytes);
+    ChainParams p = e->p;
+    p.exact_scratch = (double *)workspace;
     SelectKernel k = select_kernel_for(e->q_bf16);
-    CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, e->p.smem_bytes));
-    k<<<e->grid, kThreads, e->p.smem_bytes, stream>>>(e->p, e->flags);
+    CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
+    k<<<e->grid, kThreads, p.smem_bytes, stream>>>(p, e->flags);
     CUDA_TRY(cudaGetLastError());
     if (e->op == OP_CENT_SELECT) {
-        spa_max_ppl_kernel<<<std::max(1, e->p.B), 32, 0, stream>>>(e->p);
+        spa_max_ppl_kernel<<<std::max(1, p.B), 32, 0, stream>>>(p);
         CUDA_TRY(cudaGetLastError());
     }
     return SPA_OK;
@@ -372,9 +393,9 @@ int spaComputeCentGetWorkspaceSize(const spaTensor *query, const spaTensor *l1Ce
     return finish_select_plan(e, ws, executor);
 }
 
-int spaComputeCent(void *, uint64_t, spaExecutor *e, spaStream stream) {
+int spaComputeCent(void *workspace, uint64_t wsSize, spaExecutor *e, spaStream stream) {
     if (!e || e->op != OP_COMPUTE_CENT) return fail(SPA_ERR_ARG, "bad executor");
-    return launch_select(e, (cudaStream_t)stream);
+    return launch_select(workspace, wsSize, e, (cudaStream_t)stream);
 }
 
 static int parse_select_outputs(ChainParams &p, const spaTensor *pp, const spaTensor *ppl) {
@@ -425,9 +446,9 @@ int spaSelectPositionGetWorkspaceSize(const spaTensor *blockIds, const spaTensor
     return finish_select_plan(e, ws, executor);
 }
 
-int spaSelectPosition(void *, uint64_t, spaExecutor *e, spaStream stream) {
+int spaSelectPosition(void *workspace, uint64_t wsSize, spaExecutor *e, spaStream stream) {
     if (!e || e->op != OP_SELECT_POSITION) return fail(SPA_ERR_ARG, "bad executor");
-    return launch_select(e, (cudaStream_t)stream);
+    return launch_select(workspace, wsSize, e, (cudaStream_t)stream);
 }
 
 static int parse_cent_select_common(spaExecutor *e, const spaTensor *query, const spaTensor *l1Cent,
@@ -474,9 +495,9 @@ int spaCentSelectGetWorkspaceSize(const spaTensor *query, const spaTensor *l1Cen
     return finish_select_plan(e, ws, executor);
 }
 
-int spaCentSelect(void *, uint64_t, spaExecutor *e, spaStream stream) {
+int spaCentSelect(void *workspace, uint64_t wsSize, spaExecutor *e, spaStream stream) {
     if (!e || e->op != OP_CENT_SELECT) return fail(SPA_ERR_ARG, "bad executor");
-    return launch_select(e, (cudaStream_t)stream);
+    return launch_select(workspace, wsSize, e, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -574,7 +595,9 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     p.nstages = nst;
     int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.items).total;
     int sel_bytes = p.maxP * 4;
-    if (p.mode == kModeFused) { if ((rc = plan_select_smem(&p, budget, &sel_bytes))) return rc; }
+    if (p.mode == kModeFused) {
+        if ((rc = plan_select_smem(&p, kSelScores | kSelSelect | kSelUnion, d.sms, budget, &sel_bytes))) return rc;
+    }
     p.smem_bytes = std::max(attn_bytes, sel_bytes) + 1024;
     if (p.smem_bytes > d.smem_optin) return fail(SPA_ERR_UNSUPPORTED, "shared memory need %d > %d", p.smem_bytes, d.smem_optin);
     ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
@@ -593,6 +616,8 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     const uint64_t slots = (uint64_t)p.items + e->grid;
     e->off_po = o;    o = align_up(o + slots * HP * kD * 4, 256);
     e->off_pml = o;   o = align_up(o + slots * HP * 2 * 4, 256);
+    e->off_xs = o;
+    if (p.mode == kModeFused) o = align_up(o + (uint64_t)e->grid * kConsumerWarps * std::max(p.C, 1) * 8, 256);
     e->ws_bytes = o;
     *ws = o;
     e->launches = 1;
@@ -609,6 +634,7 @@ static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaSt
     p.union_phys = (int *)(w + e->off_uphys); p.union_meta = (unsigned *)(w + e->off_umeta);
     p.union_len = (int *)(w + e->off_ulen); p.tail_count = (int *)(w + e->off_tail);
     p.part_o = (float *)(w + e->off_po); p.part_ml = (float *)(w + e->off_pml);
+    p.exact_scratch = (double *)(w + e->off_xs);
     ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
     void *args[] = {(void *)&p, (void *)&e->tmK, (void *)&e->tmV};

@@ -184,6 +184,22 @@ class FusedDecodePlan:
     def num_launches(self) -> int:
         return self._plan.num_launches
 
+    @property
+    def grid_size(self) -> int:
+        return self._plan.grid_size
+
+    def trace_phases(self) -> torch.Tensor:
+        """Run one traced launch; returns int64 [grid, 16] of per-CTA %globaltimer ns at the phase
+        boundaries (include/spa_b200.h: spaExecutorSetTrace)."""
+        buf = torch.zeros(self.grid_size, 16, dtype=torch.int64, device=self.attention_out.device)
+        self._plan.set_trace(buf)
+        try:
+            custom_ops_lib.launch_fusion_plan(self._plan)
+            torch.cuda.synchronize()
+        finally:
+            self._plan.set_trace(torch.empty(0, dtype=torch.int64, device=buf.device))
+        return buf
+
     def launch(self) -> torch.Tensor:
         custom_ops_lib.launch_fusion_plan(self._plan)
         return self.attention_out

@@ -67,6 +67,14 @@ SPA_API int spaGetVersion(void);
 SPA_API int spaGetCompiledArch(void);
 /* Number of kernel launches an executor performs per spa<Op>() call (for bench accounting). */
 SPA_API int spaExecutorNumLaunches(const spaExecutor *executor);
+/* Profiling hook (the reference has device printf macros gated by V5_SPARSE_DEBUG_ENABLE,
+ * sparse_paged_attention_split_Bbn2s2_Us2.h:28-36): when set, every CTA of the chain kernel stores
+ * %globaltimer (ns) at its phase boundaries into deviceBuffer[grid][16] (uint64; 8..15 = stages of
+ * the CTA's last selection item):
+ * 0 start, 1 selection done, 2 past grid sync, 3 page stream done, 4 past grid sync, 5 combine done.
+ * NULL switches it off (default).                                                              */
+SPA_API int spaExecutorGridSize(const spaExecutor *executor);
+SPA_API int spaExecutorSetTrace(spaExecutor *executor, void *deviceBuffer);
 
 /* ---- ComputeCent: replaces aclnnComputeCentGetWorkspaceSize / aclnnComputeCent
  *      (misc/aclnn_compute_cent.h; kernel compute_cent/compute_cent.cpp:345).

@@ -1,0 +1,160 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads without a GPU, exports every
+symbol `include/spa_b200.h` declares, and its phase-1 ("GetWorkspaceSize") validation -- the place
+the reference keeps its tiling checks (sparse_paged_attention_tiling_check.cc) -- rejects malformed
+descriptors with the documented status codes before touching CUDA.  No compute is launched."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "spa_b200.h")
+LIB = os.path.join(ROOT, "cann-ops-adv-vllm_b200", "libspa_b200.so")
+
+SPA_OK, SPA_ERR_ARG, SPA_ERR_SHAPE, SPA_ERR_DTYPE, SPA_ERR_UNSUPPORTED = 0, -1, -2, -3, -4
+SPA_F16, SPA_BF16, SPA_F32, SPA_I8, SPA_I32, SPA_I64 = range(6)
+
+
+class SpaTensor(ctypes.Structure):
+    _fields_ = [("data", ctypes.c_void_p), ("dtype", ctypes.c_int32), ("ndim", ctypes.c_int32),
+                ("sizes", ctypes.c_int64 * 8), ("strides", ctypes.c_int64 * 8)]
+
+
+def tensor(sizes, dtype, data=0x1000):
+    t = SpaTensor()
+    t.data = data
+    t.dtype = dtype
+    t.ndim = len(sizes)
+    s = 1
+    for i in reversed(range(len(sizes))):
+        t.sizes[i] = sizes[i]
+        t.strides[i] = s
+        s *= sizes[i]
+    return t
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(LIB):
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("spa_build", os.path.join(ROOT, "cann-ops-adv-vllm_b200", "build.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        mod.build_kernels()
+    L = ctypes.CDLL(LIB)
+    L.spaGetLastError.restype = ctypes.c_char_p
+    return L
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"SPA_API\s+[\w\s\*]+?\b(spa\w+)\s*\(", text)))
+
+
+def test_header_declares_the_five_ops_two_phase():
+    syms = declared_symbols()
+    for op in ("ComputeCent", "SelectPosition", "CentSelect", "SparsePagedAttention", "SparsePagedFusionAttention"):
+        assert f"spa{op}GetWorkspaceSize" in syms and f"spa{op}" in syms      # aclnn two-phase shape
+    assert {"spaGetLastError", "spaDestroyExecutor", "spaGetVersion", "spaGetCompiledArch"} <= set(syms)
+
+
+def test_library_exports_every_declared_symbol(lib):
+    for s in declared_symbols():
+        assert hasattr(lib, s), f"{s} declared in include/spa_b200.h but not exported"
+
+
+def test_version_and_arch(lib):
+    assert lib.spaGetVersion() >= 100
+    assert lib.spaGetCompiledArch() == 100                        # sm_100a
+
+
+def test_compute_cent_validation_needs_no_gpu(lib):
+    ws = ctypes.c_uint64(0)
+    ex = ctypes.c_void_p(0)
+    q = tensor([2, 32, 128], SPA_F16)
+    cent = tensor([8, 512, 128], SPA_F16)
+    idx = tensor([2, 32, 64], SPA_I32)
+    f = lib.spaComputeCentGetWorkspaceSize
+    # absent query
+    assert f(None, ctypes.byref(cent), ctypes.byref(idx), ctypes.byref(ws), ctypes.byref(ex)) == SPA_ERR_ARG
+    assert b"query" in lib.spaGetLastError()
+    # wrong dtype
+    qf = tensor([2, 32, 128], SPA_F32)
+    assert f(ctypes.byref(qf), ctypes.byref(cent), ctypes.byref(idx), ctypes.byref(ws), ctypes.byref(ex)) == SPA_ERR_DTYPE
+    # head dim other than 128
+    q64 = tensor([2, 32, 64], SPA_F16)
+    assert f(ctypes.byref(q64), ctypes.byref(cent), ctypes.byref(idx), ctypes.byref(ws), ctypes.byref(ex)) == SPA_ERR_UNSUPPORTED
+    # centroid dtype must equal the query's (cent_select_def.cpp:12-21 is fp16-only)
+    cb = tensor([8, 512, 128], SPA_BF16)
+    assert f(ctypes.byref(q), ctypes.byref(cb), ctypes.byref(idx), ctypes.byref(ws), ctypes.byref(ex)) == SPA_ERR_DTYPE
+    # k (= indices.shape[2], compute_cent_tiling.cpp:45-50) larger than C
+    big = tensor([2, 32, 513], SPA_I32)
+    assert f(ctypes.byref(q), ctypes.byref(cent), ctypes.byref(big), ctypes.byref(ws), ctypes.byref(ex)) == SPA_ERR_SHAPE
+    assert b"exceeds cluster count" in lib.spaGetLastError()
+    # q heads not a multiple of kv heads
+    q30 = tensor([2, 30, 128], SPA_F16)
+    i30 = tensor([2, 30, 64], SPA_I32)
+    assert f(ctypes.byref(q30), ctypes.byref(cent), ctypes.byref(i30), ctypes.byref(ws), ctypes.byref(ex)) == SPA_ERR_SHAPE
+    # null out-pointers
+    assert f(ctypes.byref(q), ctypes.byref(cent), ctypes.byref(idx), None, ctypes.byref(ex)) == SPA_ERR_ARG
+
+
+def test_select_position_validation_needs_no_gpu(lib):
+    ws = ctypes.c_uint64(0)
+    ex = ctypes.c_void_p(0)
+    bid = tensor([8, 1280], SPA_I32)
+    bt = tensor([4, 1024], SPA_I32)
+    sl = tensor([4], SPA_I32)
+    idx = tensor([4, 32, 64], SPA_I32)
+    pp = tensor([4, 32, 256], SPA_I32)
+    ppl = tensor([4, 32, 8], SPA_I32)
+    f = lib.spaSelectPositionGetWorkspaceSize
+    args = lambda **kw: [ctypes.byref(kw.get("bid", bid)), ctypes.byref(kw.get("bt", bt)), ctypes.byref(kw.get("sl", sl)),
+                         ctypes.byref(kw.get("idx", idx)), ctypes.c_int64(kw.get("bs", 128)),
+                         ctypes.byref(kw.get("pp", pp)), ctypes.byref(kw.get("ppl", ppl)), None,
+                         ctypes.byref(ws), ctypes.byref(ex)]
+    assert f(*args(bid=tensor([8, 1280], SPA_I64))) == SPA_ERR_DTYPE
+    assert f(*args(sl=tensor([9], SPA_I32))) == SPA_ERR_SHAPE           # more sequences than block_table rows
+    assert f(*args(bs=0)) == SPA_ERR_SHAPE
+    assert f(*args(ppl=tensor([4, 32, 4], SPA_I32))) == SPA_ERR_SHAPE   # x8 padding is part of the contract
+    assert f(*args(idx=tensor([4, 30, 64], SPA_I32))) == SPA_ERR_SHAPE
+
+
+def test_attention_rejects_unsupported_ifa_features_without_gpu(lib):
+    """pse_shift / attention_mask / quant scales / kv_padding are never non-empty in any reference
+    sparse test (tests/ifa_v5_case.py:133-146): the boundary refuses them instead of ignoring them."""
+    ws = ctypes.c_uint64(0)
+    ex = ctypes.c_void_p(0)
+    q = tensor([2, 32, 128], SPA_F16)
+    kv = tensor([64, 128, 8, 128], SPA_F16)
+    asl = tensor([2], SPA_I64)
+    bt = tensor([2, 32], SPA_I32)
+    bp = tensor([2, 8, 256], SPA_I32)
+    out = tensor([2, 32, 128], SPA_F16)
+    extra = tensor([1], SPA_F16)
+    f = lib.spaSparsePagedAttentionGetWorkspaceSize
+    f.argtypes = [ctypes.c_void_p] * 16 + [ctypes.c_int64, ctypes.c_double, ctypes.c_char_p, ctypes.c_int64,
+                                           ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p,
+                                           ctypes.c_void_p]
+
+    def call(pse=None, mask=None, dq1=None, kvpad=None, heads=32, layout=b"BNSD", bs=128, kvh=8):
+        p = lambda t: ctypes.cast(ctypes.pointer(t), ctypes.c_void_p) if t is not None else None
+        return f(p(q), p(kv), p(kv), p(pse), p(mask), p(asl), p(dq1), None, None, None, None, None, None, p(bt),
+                 p(kvpad), p(bp), heads, 0.088, layout, kvh, bs, 1, p(out), ctypes.addressof(ws),
+                 ctypes.addressof(ex))
+
+    assert call(pse=extra) == SPA_ERR_UNSUPPORTED and b"pse_shift" in lib.spaGetLastError()
+    assert call(mask=extra) == SPA_ERR_UNSUPPORTED and b"attention_mask" in lib.spaGetLastError()
+    assert call(dq1=extra) == SPA_ERR_UNSUPPORTED
+    assert call(kvpad=extra) == SPA_ERR_UNSUPPORTED
+    assert call(heads=16) == SPA_ERR_SHAPE and b"num_heads" in lib.spaGetLastError()
+    assert call(layout=b"XYZ") == SPA_ERR_ARG
+    assert call(bs=64) == SPA_ERR_UNSUPPORTED
+    assert call(kvh=5) == SPA_ERR_SHAPE
+
+
+def test_destroy_null_executor_is_ok(lib):
+    assert lib.spaDestroyExecutor(None) == SPA_OK
+    assert lib.spaExecutorNumLaunches(None) == 0

@@ -137,6 +137,52 @@ def test_topk_ties_lowest_index_first(ops):
     assert torch.equal(got, want)
 
 
+@pytest.mark.parametrize("qdtype", [torch.float16, torch.bfloat16])
+def test_topk_near_ties_resolved_exactly(ops, qdtype):
+    """Half of the clusters are copies of one centroid perturbed by single ulps in a dimension where q
+    is tiny: their scores differ by ~5e-7, far below fp32 resolution at the score magnitude (ulp(32) =
+    3.8e-6), and the k-th boundary is placed inside that group.  Tensor-core fp32 scores cannot order
+    them; the selection must still equal the exact-arithmetic oracle (order included)."""
+    gen = torch.Generator().manual_seed(77)
+    B, Nq, Nkv, C, D = 2, 8, 2, 512, 128
+    q = torch.rand(B, Nq, D, generator=gen)
+    q[:, :, 5] = 2.0 ** -10
+    q = q.to(qdtype)
+    l1 = torch.rand(Nkv, C, D, generator=gen)
+    ulp = 2.0 ** -11 if qdtype == torch.float16 else 2.0 ** -8          # ulp at 0.5
+    for n in range(Nkv):
+        base = l1[n, 0].clone()
+        base[5] = 0.5
+        steps = torch.randperm(C // 2, generator=gen).float()
+        tie = base.unsqueeze(0).repeat(C // 2, 1)
+        tie[:, 5] = 0.5 + steps * ulp
+        where = torch.randperm(C, generator=gen)[: C // 2]
+        l1[n, where] = tie
+        l1[n, where[:7]] = tie[0]                                          # a few exact duplicates too
+    l1 = l1.to(qdtype)
+    exact = oc.cent_scores(q, l1)                                          # [B, Nq, C] float64
+    # k such that the boundary falls inside the near-tie group for head (0, 0)
+    tied_score = exact[0, 0][((l1[0, :, 5].float() >= 0.5) & (l1[0, :, 5].float() < 0.5 + C * ulp)).numpy()].mean()
+    k = int((exact[0, 0] > tied_score + 1e-2).sum()) + 100
+    assert 100 < k < C
+    want = oc.compute_cent(q, l1, k)
+    got = ops.compute_cent(q.to(DEV), l1.to(DEV), k=k)
+    assert torch.equal(got.cpu(), want)
+
+
+def test_topk_huge_plateau_uses_scratch(ops):
+    """More than 512 exact ties around the boundary (e.g. a zero-initialised centroid table): the
+    exact-score scratch in the workspace takes over; lowest indices win."""
+    q = torch.rand(2, 8, 128, dtype=torch.float16, device=DEV)
+    l1 = torch.zeros(2, 2048, 128, dtype=torch.float16, device=DEV)
+    got = ops.compute_cent(q, l1, k=128).cpu()
+    assert torch.equal(got, torch.arange(128, dtype=torch.int32).expand(2, 8, 128))
+    l1[:, 1500:1540] = 1.0
+    got = ops.compute_cent(q, l1, k=64).cpu()
+    want = torch.cat([torch.arange(1500, 1540), torch.arange(0, 24)]).to(torch.int32)
+    assert torch.equal(got, want.expand(2, 8, 64))
+
+
 def test_select_truncates_at_max_page_num(ops):
     """More selected pages than max_page_num: list is cut, length is the kept count."""
     c = make_case(11, 1, 4, 2, 16, 64 * 128, kv_pages=80)
