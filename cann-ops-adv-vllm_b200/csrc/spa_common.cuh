@@ -60,6 +60,7 @@ struct ChainParams {
     // ---- launch shape
     int sel_gw;                                          // warps per selection group (4 or 8)
     int sel_group_bytes;                                 // smem bytes of one selection group
+    int sel_ns;                                          // centroid-tile stages per selection group
     int nstages;                                         // pipeline stages
     int stage_bytes;
     int smem_bytes;
@@ -153,6 +154,21 @@ __device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *map, u
         " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
         "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
+}
+// 2-D tiled TMA load (centroid table tiles)
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+// 4-byte asynchronous global -> shared copy (SASS: LDGSTS): gathers that must not hold registers
+__device__ __forceinline__ void cp_async_4(void *dst, const void *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");

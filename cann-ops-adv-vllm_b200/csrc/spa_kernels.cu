@@ -34,7 +34,7 @@ __device__ __forceinline__ unsigned char *aligned_smem(unsigned char *raw) {
 template <typename QT, bool KVI8, int NT>
 __global__ void __launch_bounds__(kThreads, 1)
 spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ CUtensorMap tmK,
-                 const __grid_constant__ CUtensorMap tmV) {
+                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmC) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = aligned_smem(smem_raw);
     cg::grid_group grid = cg::this_grid();
@@ -42,7 +42,7 @@ spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ 
     trace_mark(p, 0);
     // ---- phase A: selection (or union building) per (b, kv head)
     if (p.mode == kModeFused)
-        select_phase<QT>(p, kSelScores | kSelSelect | kSelUnion, smem);
+        select_phase<QT, kSelScores | kSelSelect | kSelUnion>(p, &tmC, smem);
     else
         for (int item = blockIdx.x; item < p.items; item += gridDim.x) union_from_block_position(p, item, smem);
     trace_mark(p, 1);
@@ -64,12 +64,12 @@ spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ 
 }
 
 // Stand-alone selection ops (ComputeCent / SelectPosition / CentSelect share the device code).
-template <typename QT>
+template <typename QT, int FLAGS>
 __global__ void __launch_bounds__(kThreads, 1) spa_select_kernel(const __grid_constant__ ChainParams p,
-                                                                 int flags) {
+                                                                 const __grid_constant__ CUtensorMap tmC) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = aligned_smem(smem_raw);
-    select_phase<QT>(p, flags, smem);
+    select_phase<QT, FLAGS>(p, &tmC, smem);
 }
 
 __global__ void spa_max_ppl_kernel(const __grid_constant__ ChainParams p) {
@@ -100,7 +100,7 @@ enum OpKind { OP_COMPUTE_CENT = 1, OP_SELECT_POSITION, OP_CENT_SELECT, OP_ATTENT
 struct spaExecutor {
     int op;
     ChainParams p;
-    CUtensorMap tmK, tmV;
+    CUtensorMap tmK, tmV, tmC;
     int flags;            // selection flags
     int grid;
     int q_bf16, kv_i8, nt_tiles;
@@ -201,17 +201,25 @@ static int parse_tables(const spaTensor *bid, const spaTensor *bt, const spaTens
     return SPA_OK;
 }
 
-// choose the selection group width (4 or 8 warps per item) so that phase A's smem fits `budget`
+// Phase A shared memory: [ngroups x sel_ns centroid-tile stages][ngroups x group state].  Chooses the
+// group width (two 4-warp groups when g <= 4 and there are more items than CTAs) and the stage count.
 static int plan_select_smem(ChainParams *p, int flags, int grid, int budget, int *bytes) {
     const int Ceff = std::max(p->C, 1), keff = std::max(p->k, 1);
+    const bool scores = (flags & kSelScores) != 0;
+    const int ntiles = (Ceff + kCentTileRows - 1) / kCentTileRows;
+    SelSmem L(p->g, Ceff, keff, p->maxP, flags);
     int gw = (p->g > 4 || p->items <= grid) ? 8 : 4;
     for (; gw <= 8; gw *= 2) {
-        SelSmem L(p->g, Ceff, keff, p->maxP, gw, flags);
-        const long long total = (long long)L.total * (kConsumerWarps / gw);
-        if (total <= budget) {
-            p->sel_gw = gw; p->sel_group_bytes = L.total; *bytes = (int)total;
-            return SPA_OK;
-        }
+        const int ngroups = kConsumerWarps / gw;
+        const long long state = (long long)L.total * ngroups;
+        int ns = 0;
+        if (scores) {
+            ns = (int)std::min<long long>(std::min(ntiles, 4), (budget - state) / ((long long)ngroups * kCentTileBytes));
+            if (ns < 1) continue;
+        } else if (state > budget) continue;
+        p->sel_gw = gw; p->sel_group_bytes = L.total; p->sel_ns = ns;
+        *bytes = (int)(state + (long long)ngroups * ns * kCentTileBytes);
+        return SPA_OK;
     }
     return fail(SPA_ERR_UNSUPPORTED, "selection working set (g=%d, C=%d, k=%d, maxP=%d) exceeds shared memory", p->g, p->C, p->k, p->maxP);
 }
@@ -293,21 +301,46 @@ static int make_kv_map(CUtensorMap *map, const spaTensor *t, const KvLayout &L, 
     return SPA_OK;
 }
 
+// 2-D map over the centroid table [Nkv*C, 128]; box = 64 columns x 128 rows, 128B swizzle (the same
+// smem image as one half of a K page, so phase A reuses the ldmatrix addressing of phase B).
+static int make_cent_map(CUtensorMap *map, const void *cent, int rows, int bf16) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return fail(SPA_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t gdim[2] = {(cuuint64_t)kD, (cuuint64_t)std::max(rows, 1)};
+    cuuint64_t gstr[1] = {(cuuint64_t)kD * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)kCentTileRows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                     const_cast<void *>(cent), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(SPA_ERR_CUDA, "l1_cent: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return SPA_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // kernel dispatch tables
 // ---------------------------------------------------------------------------------------------
-typedef void (*ChainKernel)(const ChainParams, const CUtensorMap, const CUtensorMap);
+typedef void (*ChainKernel)(const ChainParams, const CUtensorMap, const CUtensorMap, const CUtensorMap);
 static ChainKernel chain_kernel_for(int bf16, int kvi8, int nt) {
     if (!bf16 && !kvi8) return nt == 1 ? spa_chain_kernel<__half, false, 1> : spa_chain_kernel<__half, false, 2>;
     if (bf16 && !kvi8) return nt == 1 ? spa_chain_kernel<__nv_bfloat16, false, 1> : spa_chain_kernel<__nv_bfloat16, false, 2>;
     if (!bf16 && kvi8) return nt == 1 ? spa_chain_kernel<__half, true, 1> : spa_chain_kernel<__half, true, 2>;
     return nt == 1 ? spa_chain_kernel<__nv_bfloat16, true, 1> : spa_chain_kernel<__nv_bfloat16, true, 2>;
 }
-typedef void (*SelectKernel)(const ChainParams, int);
-static SelectKernel select_kernel_for(int bf16) {
-    return bf16 ? spa_select_kernel<__nv_bfloat16> : spa_select_kernel<__half>;
+typedef void (*SelectKernel)(const ChainParams, const CUtensorMap);
+static SelectKernel select_kernel_for(int bf16, int flags) {
+    switch (flags) {
+        case kSelScores | kSelWriteIndices:
+            return bf16 ? spa_select_kernel<__nv_bfloat16, kSelScores | kSelWriteIndices> : spa_select_kernel<__half, kSelScores | kSelWriteIndices>;
+        case kSelScores | kSelSelect:
+            return bf16 ? spa_select_kernel<__nv_bfloat16, kSelScores | kSelSelect> : spa_select_kernel<__half, kSelScores | kSelSelect>;
+        case kSelSelect:
+            return spa_select_kernel<__half, kSelSelect>;
+        case kSelSelect | kSelGather:
+            return spa_select_kernel<__half, kSelSelect | kSelGather>;
+    }
+    return nullptr;
 }
-
 
 // =============================================================================================
 // C ABI
@@ -335,8 +368,13 @@ static int finish_select_plan(spaExecutor *e, uint64_t *ws, spaExecutor **out) {
     if (rc) { delete e; return rc; }
     int bytes = 0;
     // stand-alone ops: enough CTAs for one item per group, capped at a few waves
-    rc = plan_select_smem(&e->p, e->flags, 0, d.smem_optin - 1024, &bytes);
+    rc = plan_select_smem(&e->p, e->flags, 0, d.smem_optin - 2048, &bytes);
     if (rc) { delete e; return rc; }
+    memset(&e->tmC, 0, sizeof(e->tmC));
+    if (e->flags & kSelScores) {
+        rc = make_cent_map(&e->tmC, e->p.cent, e->p.Nkv * e->p.C, e->q_bf16);
+        if (rc) { delete e; return rc; }
+    }
     e->p.smem_bytes = bytes + 1024;
     const int ngroups = kConsumerWarps / e->p.sel_gw;
     e->grid = std::max(1, std::min((e->p.items + ngroups - 1) / ngroups, 8 * d.sms));
@@ -354,9 +392,10 @@ static int launch_select(void *workspace, uint64_t wsSize, spaExecutor *e, cudaS
         return fail(SPA_ERR_WORKSPACE, "workspace %llu bytes < required %llu", (unsigned long long)wsSize, (unsigned long long)e->ws_bytes);
     ChainParams p = e->p;
     p.exact_scratch = (double *)workspace;
-    SelectKernel k = select_kernel_for(e->q_bf16);
+    SelectKernel k = select_kernel_for(e->q_bf16, e->flags);
+    if (!k) return fail(SPA_ERR_ARG, "no selection kernel for flags %d", e->flags);
     CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
-    k<<<e->grid, kThreads, p.smem_bytes, stream>>>(p, e->flags);
+    k<<<e->grid, kThreads, p.smem_bytes, stream>>>(p, e->tmC);
     CUDA_TRY(cudaGetLastError());
     if (e->op == OP_CENT_SELECT) {
         spa_max_ppl_kernel<<<std::max(1, p.B), 32, 0, stream>>>(p);
@@ -596,7 +635,8 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.items).total;
     int sel_bytes = p.maxP * 4;
     if (p.mode == kModeFused) {
-        if ((rc = plan_select_smem(&p, kSelScores | kSelSelect | kSelUnion, d.sms, budget, &sel_bytes))) return rc;
+        if ((rc = plan_select_smem(&p, kSelScores | kSelSelect | kSelUnion, d.sms, budget - 1024, &sel_bytes))) return rc;
+        if ((rc = make_cent_map(&e->tmC, p.cent, p.Nkv * p.C, e->q_bf16))) return rc;
     }
     p.smem_bytes = std::max(attn_bytes, sel_bytes) + 1024;
     if (p.smem_bytes > d.smem_optin) return fail(SPA_ERR_UNSUPPORTED, "shared memory need %d > %d", p.smem_bytes, d.smem_optin);
@@ -637,7 +677,7 @@ static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaSt
     p.exact_scratch = (double *)(w + e->off_xs);
     ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
-    void *args[] = {(void *)&p, (void *)&e->tmK, (void *)&e->tmV};
+    void *args[] = {(void *)&p, (void *)&e->tmK, (void *)&e->tmV, (void *)&e->tmC};
     CUDA_TRY(cudaLaunchCooperativeKernel((const void *)kern, dim3(e->grid), dim3(kThreads), args,
                                          (size_t)p.smem_bytes, stream));
     return SPA_OK;

@@ -7,28 +7,33 @@
 // there are more items than CTAs); groups synchronise with their own named barrier.
 //
 // Scores and TopK -- how bit-exact selection is obtained from tensor-core arithmetic:
-//   1. approximate scores a[h][c] = q[h] . cent[c] on the tensor cores (mma.sync m16n8k16, fp16/bf16
-//      operands, fp32 accumulate; M = 16 clusters, N = the group's heads, K = head dim);
+//   1. approximate scores a[h][c] = q[h] . cent[c] on the tensor cores: the kv head's centroid
+//      table arrives as 128-row tiles by TMA (128B-swizzled, same shape as a K page), ldmatrix +
+//      mma.sync m16n8k16 with fp32 accumulate (M = 16 clusters, N = the group's heads, K = head dim);
 //   2. |a - e| <= eps[h] for the exact score e, with eps = 2^-16 * ||q_h||_1 * max|cent| (the
-//      products are exact in fp32; the bound covers 128 accumulation roundings with a 2^9 margin);
-//   3. one 1024-bin histogram of order-preserving keys locates the bin holding the k-th largest a;
-//      elements more than 2*eps above the bin are certainly selected, elements more than 2*eps
-//      below it certainly not; only the few in between ("candidates") get their EXACT score
-//      (float64 sum of exact products, order-independent) and are ranked by (score desc, index asc).
+//      products are exact in fp32; the bound covers 128 truncating accumulation steps);
+//   3. one 1024-bin histogram of order-preserving keys per head locates the bin holding the k-th
+//      largest a; elements more than 2*eps above the bin are certainly selected, elements more
+//      than 2*eps below it certainly not; the few in between ("candidates") are ranked by their
+//      approximate score, and only those within 2*eps of the cut get their EXACT score (float64 sum
+//      of exact products, order-independent), ranked by (score desc, index asc).
 // The result equals the exact-arithmetic TopK of the oracle (oracle/sparse_chain.py:cent_scores,
 // topk_indices), which is the tie-free centre of every fp32 evaluation order of the reference
 // (compute_cent.cpp:277-343 VMLA + pair-add + BlockReduceSum; tests/utils.py:117 torch.matmul).
+//
+// The code is deliberately compact (little unrolling): it runs once per CTA from a cold
+// instruction cache, where straight-line code costs more than loops.
 #pragma once
 #include "spa_common.cuh"
 
 namespace spa {
 
 constexpr int kSelBins = 1024;            // histogram bins per head (power of two, multiple of 32)
-constexpr int kXCap = kSelBins / 2;       // exact scores per warp kept in smem (aliases the histogram)
-constexpr int kPG = 8;                    // logical pages per thread whose cluster id is held in registers
-constexpr int kScoreTiles = 2;            // 16-cluster tiles loaded per batch by one warp
+constexpr int kXCap = 256;                // exact scores per head kept in smem (more -> workspace)
+constexpr int kCentTileRows = 128;        // centroid rows per TMA tile
+constexpr int kCentTileBytes = kCentTileRows * kD * 2;
 
-// flags
+// flags (compile-time per kernel instantiation)
 enum : int { kSelScores = 1, kSelWriteIndices = 2, kSelSelect = 4, kSelUnion = 8, kSelGather = 16 };
 
 // ---- a group of warps working on one item ----------------------------------------------------
@@ -50,28 +55,43 @@ __device__ __forceinline__ Grp make_group(int gw) {
 }
 __device__ __forceinline__ void grp_sync(const Grp &G) { named_bar_sync(G.bar, G.gt); }
 
-// ---- shared-memory carve-up of ONE group (host + device) ---------------------------------------
+// per-head record in shared memory
+struct HeadRec {
+    unsigned kmin, kmax;                 // key range of the approximate scores
+    int ncand;                           // candidates collected
+    float l1;                            // ||q_h||_1
+    float lo_val, hi_val, band;          // edges of the bin of the k-th largest, 2*eps
+    int total;                           // selected pages (compaction)
+};
+
+// ---- shared-memory carve-up of ONE group (host + device), offsets from the group base ---------
 struct SelSmem {
-    int scs, bw;                         // score row stride (floats), bitmap words per head
-    int sc, wreg, cand, sel, bitmap, pm, phys, srt, misc, total;
+    int scs, bw, nch;                    // score row stride (floats), bitmap words per head, 32-page chunks
+    int sc, hist, cand, xs, sel, bitmap, pm, phys, cval, cnt, srt, hd, misc, total;
     __host__ __device__ static inline int al(int x) { return (x + 15) & ~15; }
-    __host__ __device__ SelSmem(int g, int C, int k, int maxP, int gw, int flags) {
+    __host__ __device__ SelSmem(int g, int C, int k, int maxP, int flags) {
         const bool scores = (flags & kSelScores) != 0;
         scs = ((C + 3) & ~3) + 4;        // +4: the 4 lanes of a quad (heads 2t) hit distinct banks
         bw = (C + 31) / 32;
+        nch = (maxP + 31) / 32;
         int o = 0;
         sc = o;      o = al(o + (scores ? g * scs * 4 : 0));
-        wreg = o;    o = al(o + (scores ? gw * kSelBins * 4 : 0));
-        cand = o;    o = al(o + (scores ? gw * C * 2 : 0));
-        sel = o;     o = al(o + ((scores && (flags & kSelWriteIndices)) ? gw * k * 4 : 0));
+        hist = o;    o = al(o + (scores ? g * kSelBins * 4 : 0));
+        cand = o;    o = al(o + (scores ? g * C * 2 : 0));
+        xs = o;      o = al(o + (scores ? g * kXCap * 8 : 0));
+        sel = o;     o = al(o + ((scores && (flags & kSelWriteIndices)) ? g * k * 4 : 0));
         bitmap = o;  o = al(o + (scores ? g * bw * 4 : 0));
         pm = o;      o = al(o + maxP * 4);
         phys = o;    o = al(o + maxP * 4);
+        cval = o;    o = al(o + maxP * 4);
+        cnt = o;     o = al(o + nch * (kMaxGroup + 1) * 4);
         srt = o;     o = al(o + (scores ? 0 : g * k * 4));      // given indices (select_position)
+        hd = o;      o = al(o + kMaxGroup * (int)sizeof(HeadRec));
         misc = o;    o = al(o + 16 * 4);
         total = (o + 127) & ~127;
     }
 };
+// misc words: [0..7] per-warp max|cent|, [8] truncation flag, [9] union total
 
 __device__ __forceinline__ float key_float(uint32_t key) {      // inverse of float_key()
     return __uint_as_float((key & 0x80000000u) ? (key & 0x7fffffffu) : ~key);
@@ -87,85 +107,129 @@ template <> __device__ __forceinline__ uint32_t absmax2<__nv_bfloat16>(uint32_t 
     return *reinterpret_cast<uint32_t *>(&r);
 }
 
+// ---- per-group TMA ring of centroid tiles -------------------------------------------------------
+struct CentRing {
+    unsigned char *base;                 // ns stages of kCentTileBytes (aliases the attention ring)
+    uint64_t *full, *empty;              // [ns] each
+    int ns;
+};
+__device__ __forceinline__ void issue_cent_tile(const CUtensorMap *tmC, const CentRing &R, int stage, int row0) {
+    unsigned char *dst = R.base + (size_t)stage * kCentTileBytes;
+    mbar_expect_tx(&R.full[stage], (uint32_t)kCentTileBytes);
+    tma_load_2d(dst, tmC, &R.full[stage], 0, row0);
+    tma_load_2d(dst + kCentTileBytes / 2, tmC, &R.full[stage], 64, row0);
+}
+
 // ---- approximate scores on the tensor cores ----------------------------------------------------
-// S^T[c][h] = cent[c][:] . q[h][:]  : A = 16 clusters x 16 d (row major), B = 16 d x 8 heads.
-// The contraction index is order-free, so each thread of a quad owns a contiguous 64-byte quarter
-// of a centroid row (4 x 128-bit loads, a quad covers the whole 256-byte row): k-slot (2t+e) of
-// k-step s is d = 32t + 4s + e and slot (2t+8+e) is d = 32t + 4s + 2 + e, for A and B alike.
+// S^T[c][h] = cent[c][:] . q[h][:]  per 128-row tile: A = 16 clusters x 16 d via ldmatrix from the
+// swizzled tile, B = 16 d x 8 heads from registers.  Also gathers, per head, the key range of the
+// scores and ||q_h||_1, and max|cent| (for the error band).
 template <typename QT>
-__device__ __forceinline__ float score_tiles(const ChainParams &p, int b, int n2, float *sc, int scs,
-                                             const Grp &G) {
+__device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorMap *tmC, int b, int n2, float *sc,
+                                           int scs, HeadRec *hd, float *misc, const CentRing &R, unsigned &tcount,
+                                           const Grp &G) {
     const int lane = lane_id(), gid = lane >> 2, tig = lane & 3;
     const int g = p.g, C = p.C;
     const int ntl = (g + 7) >> 3;                      // head tiles (1 or 2)
     const unsigned short *q = reinterpret_cast<const unsigned short *>(p.q);
     uint32_t qf[2][8][2];
+    float l1[2] = {0.f, 0.f};
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
         const int h = nt * 8 + gid;
-        if (nt < ntl && h < g) {
-            const uint2 *qp = reinterpret_cast<const uint2 *>(q + (size_t)b * p.q_sb + (size_t)(n2 * g + h) * p.q_sh + tig * 32);
+        const bool on = nt < ntl && h < g;
+        const unsigned short *qrow = q + (size_t)b * p.q_sb + (size_t)(n2 * g + (on ? h : 0)) * p.q_sh;
 #pragma unroll
-            for (int s = 0; s < 8; ++s) { uint2 v = __ldg(qp + s); qf[nt][s][0] = v.x; qf[nt][s][1] = v.y; }
-        } else {
-#pragma unroll
-            for (int s = 0; s < 8; ++s) { qf[nt][s][0] = 0u; qf[nt][s][1] = 0u; }
-        }
-    }
-    const uint4 *cent = reinterpret_cast<const uint4 *>(p.cent) + (size_t)n2 * C * (kD / 8);
-    const int ntiles = (C + 15) >> 4;
-    uint32_t mx = 0u;
-    for (int t0 = G.warp; t0 < ntiles; t0 += G.gw * kScoreTiles) {
-        uint4 a[kScoreTiles][8];
-#pragma unroll
-        for (int u = 0; u < kScoreTiles; ++u) {
-            const int mt = t0 + u * G.gw;
-            const int r0 = mt * 16 + gid, r1 = r0 + 8;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                a[u][j] = (mt < ntiles && r0 < C) ? __ldg(cent + (size_t)r0 * 16 + tig * 4 + j) : make_uint4(0, 0, 0, 0);
-                a[u][4 + j] = (mt < ntiles && r1 < C) ? __ldg(cent + (size_t)r1 * 16 + tig * 4 + j) : make_uint4(0, 0, 0, 0);
+        for (int ks = 0; ks < 8; ++ks) {
+            uint32_t v0 = 0u, v1 = 0u;
+            if (on) {
+                v0 = *reinterpret_cast<const uint32_t *>(qrow + ks * 16 + tig * 2);
+                v1 = *reinterpret_cast<const uint32_t *>(qrow + ks * 16 + tig * 2 + 8);
             }
+            qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
+            l1[nt] += fabsf(QTraits<QT>::to_float((unsigned short)(v0 & 0xffffu))) + fabsf(QTraits<QT>::to_float((unsigned short)(v0 >> 16))) +
+                      fabsf(QTraits<QT>::to_float((unsigned short)(v1 & 0xffffu))) + fabsf(QTraits<QT>::to_float((unsigned short)(v1 >> 16)));
         }
-#pragma unroll
-        for (int u = 0; u < kScoreTiles; ++u) {
-            const int mt = t0 + u * G.gw;
-            if (mt >= ntiles) break;
+        l1[nt] += __shfl_xor_sync(0xffffffffu, l1[nt], 1);
+        l1[nt] += __shfl_xor_sync(0xffffffffu, l1[nt], 2);
+        if (G.warp == 0 && tig == 0 && on) hd[h].l1 = l1[nt];
+    }
+    const int ntiles = (C + kCentTileRows - 1) / kCentTileRows;
+    const int sub = kConsumerWarps / G.gw;             // 16-row slabs per warp per tile
+    unsigned kmn[2][2] = {{0xffffffffu, 0xffffffffu}, {0xffffffffu, 0xffffffffu}}, kmx[2][2] = {{0u, 0u}, {0u, 0u}};
+    uint32_t mx = 0u;
+    const uint32_t ring_u32 = smem_u32(R.base);
+    const int a_chk = lane >> 4;
+#pragma unroll 1
+    for (int t = 0; t < ntiles; ++t) {
+        const unsigned tc = tcount + (unsigned)t;
+        const int s = (int)(tc % (unsigned)R.ns);
+        const unsigned par = (tc / (unsigned)R.ns) & 1u;
+        mbar_wait(&R.full[s], par);
+#pragma unroll 1
+        for (int mi = 0; mi < sub; ++mi) {
+            const int t0 = (G.warp + mi * G.gw) * 16;
+            const int a_row = t0 + (lane & 15);
             float acc[2][4];
 #pragma unroll
             for (int nt = 0; nt < 2; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+            const uint32_t rowaddr = ring_u32 + (uint32_t)s * kCentTileBytes + a_row * 128;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const uint4 v0 = a[u][j], v1 = a[u][4 + j];
-                mx = absmax2<QT>(mx, v0.x); mx = absmax2<QT>(mx, v0.y); mx = absmax2<QT>(mx, v0.z); mx = absmax2<QT>(mx, v0.w);
-                mx = absmax2<QT>(mx, v1.x); mx = absmax2<QT>(mx, v1.y); mx = absmax2<QT>(mx, v1.z); mx = absmax2<QT>(mx, v1.w);
-#pragma unroll
-                for (int nt = 0; nt < 2; ++nt) {
-                    if (nt < ntl) {
-                        mma_16816<QT>(acc[nt], v0.x, v1.x, v0.y, v1.y, qf[nt][2 * j][0], qf[nt][2 * j][1]);
-                        mma_16816<QT>(acc[nt], v0.z, v1.z, v0.w, v1.w, qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
-                    }
-                }
+            for (int ks = 0; ks < 8; ++ks) {
+                const int chunk = (ks & 3) * 2 + a_chk;
+                uint32_t a0, a1, a2, a3;
+                ldmatrix_x4(a0, a1, a2, a3, rowaddr + (ks >> 2) * (kCentTileRows * 128) + ((chunk ^ (a_row & 7)) << 4));
+                mx = absmax2<QT>(absmax2<QT>(absmax2<QT>(absmax2<QT>(mx, a0), a1), a2), a3);
+                mma_16816<QT>(acc[0], a0, a1, a2, a3, qf[0][ks][0], qf[0][ks][1]);
+                if (ntl > 1) mma_16816<QT>(acc[1], a0, a1, a2, a3, qf[1][ks][0], qf[1][ks][1]);
             }
-            const int r0 = mt * 16 + gid, r1 = r0 + 8;
+            const int r0 = t * kCentTileRows + t0 + gid, r1 = r0 + 8;
 #pragma unroll
             for (int nt = 0; nt < 2; ++nt) {
-                const int h0 = nt * 8 + tig * 2;
-                if (nt < ntl && h0 < g) {
-                    if (r0 < C) sc[h0 * scs + r0] = acc[nt][0];
-                    if (r1 < C) sc[h0 * scs + r1] = acc[nt][2];
-                    if (h0 + 1 < g) {
-                        if (r0 < C) sc[(h0 + 1) * scs + r0] = acc[nt][1];
-                        if (r1 < C) sc[(h0 + 1) * scs + r1] = acc[nt][3];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int h = nt * 8 + tig * 2 + e;
+                    if (nt < ntl && h < g) {
+                        if (r0 < C) {
+                            sc[h * scs + r0] = acc[nt][e];
+                            const unsigned key = float_key(acc[nt][e]);
+                            kmn[nt][e] = min(kmn[nt][e], key); kmx[nt][e] = max(kmx[nt][e], key);
+                        }
+                        if (r1 < C) {
+                            sc[h * scs + r1] = acc[nt][2 + e];
+                            const unsigned key = float_key(acc[nt][2 + e]);
+                            kmn[nt][e] = min(kmn[nt][e], key); kmx[nt][e] = max(kmx[nt][e], key);
+                        }
                     }
                 }
             }
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&R.empty[s]);
+        if (G.tid == 0 && t + R.ns < ntiles) {
+            mbar_wait(&R.empty[s], par);
+            issue_cent_tile(tmC, R, s, n2 * C + (t + R.ns) * kCentTileRows);
+        }
     }
+    tcount += (unsigned)ntiles;
+    // key range per head: reduce over the 8 row-lanes, one shared atomic per (warp, head)
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            unsigned lo = kmn[nt][e], hi = kmx[nt][e];
+#pragma unroll
+            for (int o = 4; o < 32; o <<= 1) {
+                lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+                hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+            }
+            const int h = nt * 8 + tig * 2 + e;
+            if (gid == 0 && nt < ntl && h < g && lo <= hi) { atomicMin(&hd[h].kmin, lo); atomicMax(&hd[h].kmax, hi); }
+        }
     float m = fmaxf(QTraits<QT>::to_float((unsigned short)(mx & 0xffffu)), QTraits<QT>::to_float((unsigned short)(mx >> 16)));
 #pragma unroll
     for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    return m;
+    if (lane == 0) misc[G.warp] = m;
 }
 
 // exact partial dot of this lane's 4 head-dim elements (d = 4*lane .. 4*lane+3)
@@ -177,17 +241,19 @@ __device__ __forceinline__ double exact_partial(uint2 v, const double (&qd)[4]) 
     s = fma(QTraits<QT>::to_double((unsigned short)(v.y >> 16)), qd[3], s);
     return s;
 }
-__device__ __forceinline__ double warp_sum_double(double s) {
-#pragma unroll
-    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    return s;
-}
 
 // exact scores of list[0..n) -> xs[0..n)   (one warp; rows come from L2, 4 in flight)
 template <typename QT>
-__device__ __forceinline__ void exact_scores(const uint2 *cent_rows, const double (&qd)[4], const int *list32,
-                                             const unsigned short *list16, int n, double *xs) {
+__device__ __noinline__ void exact_scores(const uint2 *cent_rows, const unsigned short *qrow, const int *list32,
+                                          const unsigned short *list16, int n, double *xs) {
     const int lane = lane_id();
+    double qd[4];
+    {
+        const uint2 qv = *reinterpret_cast<const uint2 *>(qrow + 4 * lane);
+        qd[0] = QTraits<QT>::to_double((unsigned short)(qv.x & 0xffffu)); qd[1] = QTraits<QT>::to_double((unsigned short)(qv.x >> 16));
+        qd[2] = QTraits<QT>::to_double((unsigned short)(qv.y & 0xffffu)); qd[3] = QTraits<QT>::to_double((unsigned short)(qv.y >> 16));
+    }
+#pragma unroll 1
     for (int i0 = 0; i0 < n; i0 += 4) {
         uint2 v[4];
 #pragma unroll
@@ -198,133 +264,170 @@ __device__ __forceinline__ void exact_scores(const uint2 *cent_rows, const doubl
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const double s = warp_sum_double(exact_partial<QT>(v[u], qd));
+            double s = exact_partial<QT>(v[u], qd);
+#pragma unroll
+            for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
             if (lane == 0 && i0 + u < n) xs[i0 + u] = s;
         }
     }
     __syncwarp();
 }
 
-// ---- TopK of one head by one warp ------------------------------------------------------------------
-// row[0..C): approximate scores.  Writes bitmap_h[0..bw) (membership of the k selected clusters) and,
-// if sel != nullptr, sel[0..k) (unordered).  wreg: kSelBins words of warp-private smem.
-template <typename QT>
-__device__ void topk_head(const ChainParams &p, const unsigned short *qrow, const uint2 *cent_rows,
-                          const float *row, float maxabs, unsigned *wreg, unsigned short *cand, int *sel,
-                          unsigned *bitmap_h, double *gscratch, double (&qd)[4]) {
-    const int lane = lane_id();
-    const int C = p.C, k = p.k;
-    const unsigned lt = (1u << lane) - 1u;
-    // q_h as doubles (4 per lane) and its L1 norm
-    float l1 = 0.f;
-    {
-        const uint2 qv = *reinterpret_cast<const uint2 *>(qrow + 4 * lane);
-        const unsigned short e[4] = {(unsigned short)(qv.x & 0xffffu), (unsigned short)(qv.x >> 16),
-                                     (unsigned short)(qv.y & 0xffffu), (unsigned short)(qv.y >> 16)};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { qd[i] = QTraits<QT>::to_double(e[i]); l1 += fabsf(QTraits<QT>::to_float(e[i])); }
+// ---- TopK, step 1 (group): histogram of the order-preserving keys of every head ----------------
+__device__ __forceinline__ int key_shift(unsigned kmin, unsigned kmax) {
+    const int bits = 32 - __clz(kmax - kmin);                     // kmax - kmin < 2^bits
+    return max(0, bits - 10);                                     // 10 = log2(kSelBins)
+}
+__device__ __forceinline__ void topk_hist(const ChainParams &p, const float *sc, int scs, unsigned *hist,
+                                          const HeadRec *hd, const Grp &G) {
+#pragma unroll 1
+    for (int h = 0; h < p.g; ++h) {
+        const unsigned lo = hd[h].kmin;
+        const int shift = key_shift(lo, hd[h].kmax);
+        const float *row = sc + h * scs;
+        unsigned *hh = hist + h * kSelBins;
+#pragma unroll 2
+        for (int c = G.tid; c < p.C; c += G.gt) atomicAdd(&hh[(float_key(row[c]) - lo) >> shift], 1u);
     }
-#pragma unroll
-    for (int o = 16; o; o >>= 1) l1 += __shfl_xor_sync(0xffffffffu, l1, o);
-    const float band = ldexpf(l1 * maxabs, -15) * 1.0625f;        // 2 * eps, eps = 2^-16 ||q||_1 max|cent|
+}
 
-    // key range
-    uint32_t lo = 0xffffffffu, hi = 0u;
-    for (int c = lane; c < C; c += 32) {
-        const uint32_t key = float_key(row[c]);
-        lo = min(lo, key); hi = max(hi, key);
-    }
-#pragma unroll
-    for (int o = 16; o; o >>= 1) {
-        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-    }
-    const int bits = 32 - __clz(hi - lo);                         // hi - lo < 2^bits
-    const int shift = max(0, bits - 10);                          // 10 = log2(kSelBins)
-    for (int i = lane; i < kSelBins; i += 32) wreg[i] = 0u;
-    __syncwarp();
-    for (int c = lane; c < C; c += 32) atomicAdd(&wreg[(float_key(row[c]) - lo) >> shift], 1u);
-    __syncwarp();
-    // bin holding the k-th largest: lane covers bins [32 lane, 32 lane + 32); suffix sums from the top
-    int bstar, above;
+// ---- TopK, step 2 (one warp per head): the bin holding the k-th largest score ------------------
+__device__ __forceinline__ void topk_bin(const ChainParams &p, const unsigned *hh, HeadRec *r, float maxabs) {
+    const int lane = lane_id(), k = p.k;
+    // level 1: lane covers bins [32 lane, 32 lane + 32); suffix sums from the top
+    int s = 0;
     {
-        const uint4 *hv = reinterpret_cast<const uint4 *>(wreg + lane * 32);
-        int s = 0;
+        const uint4 *hv = reinterpret_cast<const uint4 *>(hh + lane * 32);
 #pragma unroll
         for (int i = 0; i < 8; ++i) { const uint4 v = hv[i]; s += v.x + v.y + v.z + v.w; }
-        int suf = s;
+    }
+    int suf = s;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_down_sync(0xffffffffu, suf, o);
-            if (lane + o < 32) suf += t;
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, suf >= k);
-        const int ls = 31 - __clz(bal);                           // highest lane whose suffix reaches k
-        int b_ = 0, cum = 0;
-        if (lane == ls) {
-            cum = suf - s;                                        // elements in lanes above
-            for (b_ = lane * 32 + 31; b_ > lane * 32; --b_) {
-                const int hb = wreg[b_];
-                if (cum + hb >= k) break;
-                cum += hb;
-            }
-        }
-        bstar = __shfl_sync(0xffffffffu, b_, ls);
-        above = __shfl_sync(0xffffffffu, cum, ls);
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_down_sync(0xffffffffu, suf, o);
+        if (lane + o < 32) suf += t;
     }
-    (void)above;
-    __syncwarp();                                                 // histogram is dead from here on
-    const unsigned long long lo_key = (unsigned long long)lo + ((unsigned long long)bstar << shift);
-    const unsigned long long hi_key = lo_key + (1ull << shift);
-    const float lo_val = key_float((uint32_t)lo_key);
-    const float hi_val = (hi_key >= 0xFF800000ull) ? INFINITY : key_float((uint32_t)hi_key);
+    const int ls = 31 - __clz(__ballot_sync(0xffffffffu, suf >= k));       // highest block whose suffix reaches k
+    const int above_blk = __shfl_sync(0xffffffffu, suf - s, ls);           // elements in blocks above
+    // level 2: lane = bin within block ls
+    const int v = hh[ls * 32 + lane];
+    int suf2 = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_down_sync(0xffffffffu, suf2, o);
+        if (lane + o < 32) suf2 += t;
+    }
+    const int lb = 31 - __clz(__ballot_sync(0xffffffffu, above_blk + suf2 >= k));
+    const int bstar = ls * 32 + lb;
+    if (lane == 0) {
+        const unsigned lo = r->kmin;
+        const int shift = key_shift(lo, r->kmax);
+        const unsigned long long lo_key = (unsigned long long)lo + ((unsigned long long)bstar << shift);
+        const unsigned long long hi_key = lo_key + (1ull << shift);
+        r->lo_val = key_float((uint32_t)lo_key);
+        r->hi_val = (hi_key >= 0xFF800000ull) ? INFINITY : key_float((uint32_t)hi_key);
+        r->band = ldexpf(r->l1 * maxabs, -15) * 1.0625f;                   // 2 * eps
+    }
+}
 
-    // classify: certainly selected / candidate / certainly not
-    int nsel = 0, ncand = 0;
-    for (int c0 = 0; c0 < C; c0 += 32) {
-        const int c = c0 + lane;
-        const bool valid = c < C;
-        const float a = valid ? row[c] : 0.f;
-        const bool in = valid && (a - band >= hi_val);
-        const bool cd = valid && !in && (a + band >= lo_val);
-        const unsigned bi = __ballot_sync(0xffffffffu, in), bc = __ballot_sync(0xffffffffu, cd);
-        if (lane == 0) bitmap_h[c0 >> 5] = bi;
-        if (sel != nullptr && in) sel[nsel + __popc(bi & lt)] = c;
-        if (cd) cand[ncand + __popc(bc & lt)] = (unsigned short)c;
-        nsel += __popc(bi); ncand += __popc(bc);
+// ---- TopK, step 3 (group): certainly selected -> bitmap, near the cut -> candidate list ----------
+__device__ __forceinline__ void topk_classify(const ChainParams &p, const float *sc, int scs, HeadRec *hd,
+                                              unsigned *bitmap, int bw, unsigned short *cand, const Grp &G) {
+#pragma unroll 1
+    for (int h = 0; h < p.g; ++h) {
+        const float lo_val = hd[h].lo_val, hi_val = hd[h].hi_val, band = hd[h].band;
+        const float *row = sc + h * scs;
+#pragma unroll 2
+        for (int c = G.tid; c < p.C; c += G.gt) {
+            const float a = row[c];
+            if (a - band >= hi_val) atomicOr(&bitmap[h * bw + (c >> 5)], 1u << (c & 31));
+            else if (a + band >= lo_val) cand[(size_t)h * p.C + atomicAdd(&hd[h].ncand, 1)] = (unsigned short)c;
+        }
     }
-    const int need = k - nsel;
-    __syncwarp();
-    if (ncand == need) {
-        for (int i = lane; i < ncand; i += 32) {
+}
+
+// ---- TopK, step 4 (one warp per head): settle the candidates ------------------------------------
+template <typename QT>
+__device__ __forceinline__ void topk_resolve(const ChainParams &p, const unsigned short *qrow, const uint2 *cent_rows,
+                                             const float *row, const HeadRec *r, unsigned short *cand,
+                                             unsigned *bitmap_h, int bw, double *xs_smem, double *gscratch) {
+    const int lane = lane_id();
+    const unsigned lt = (1u << lane) - 1u;
+    int nsel = 0;
+    for (int w = lane; w < bw; w += 32) nsel += __popc(bitmap_h[w]);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) nsel += __shfl_xor_sync(0xffffffffu, nsel, o);
+    int need = p.k - nsel;
+    int n = r->ncand;
+    if (n != need && n <= 32) {
+        // rank the candidates by approximate score; only those within the band of the cut stay open
+        const float band = r->band;
+        const int ci = (lane < n) ? (int)cand[lane] : 0x7fffffff;
+        const float ai = (lane < n) ? row[ci] : -INFINITY;
+        int rank = 0;
+        for (int j = 0; j < n; ++j) {
+            const float aj = __shfl_sync(0xffffffffu, ai, j);
+            const int cj = __shfl_sync(0xffffffffu, ci, j);
+            rank += (aj > ai || (aj == ai && cj < ci)) ? 1 : 0;
+        }
+        const unsigned bcut = __ballot_sync(0xffffffffu, lane < n && rank == need - 1);
+        const float astar = __shfl_sync(0xffffffffu, ai, __ffs(bcut) - 1);
+        const bool in = lane < n && (ai - band > astar);
+        const bool amb = lane < n && !in && (ai + band >= astar);
+        if (in) atomicOr(&bitmap_h[ci >> 5], 1u << (ci & 31));
+        const unsigned bamb = __ballot_sync(0xffffffffu, amb);
+        need -= __popc(__ballot_sync(0xffffffffu, in));
+        n = __popc(bamb);
+        __syncwarp();
+        if (amb) cand[__popc(bamb & lt)] = (unsigned short)ci;
+        __syncwarp();
+    }
+    if (n == need) {
+        for (int i = lane; i < n; i += 32) {
             const int c = cand[i];
             atomicOr(&bitmap_h[c >> 5], 1u << (c & 31));
-            if (sel != nullptr) sel[nsel + i] = c;
         }
     } else {
-        double *xs = (ncand <= kXCap) ? reinterpret_cast<double *>(wreg) : gscratch;
-        exact_scores<QT>(cent_rows, qd, nullptr, cand, ncand, xs);
-        for (int i = lane; i < ncand; i += 32) {
+        double *xs = (n <= kXCap) ? xs_smem : gscratch;
+        exact_scores<QT>(cent_rows, qrow, nullptr, cand, n, xs);
+        for (int i = lane; i < n; i += 32) {
             const int e = cand[i];
             const double se = xs[i];
             int rank = 0;
-            for (int j = 0; j < ncand; ++j) rank += precedes(xs[j], (int)cand[j], se, e) ? 1 : 0;
-            if (rank < need) {
-                atomicOr(&bitmap_h[e >> 5], 1u << (e & 31));
-                if (sel != nullptr) sel[nsel + rank] = e;
-            }
+            for (int j = 0; j < n; ++j) rank += precedes(xs[j], (int)cand[j], se, e) ? 1 : 0;
+            if (rank < need) atomicOr(&bitmap_h[e >> 5], 1u << (e & 31));
         }
     }
     __syncwarp();
 }
 
-// sel[0..k) -> out[0..k) in (exact score desc, index asc) order   (compute_cent op output)
+// compute_cent op output: the k selected clusters in (exact score desc, index asc) order  (one warp)
 template <typename QT>
-__device__ void sort_selected(const ChainParams &p, const uint2 *cent_rows, const double (&qd)[4], const int *sel,
-                              unsigned *wreg, double *gscratch, int *out) {
-    const int k = p.k, lane = lane_id();
-    double *xs = (k <= kXCap) ? reinterpret_cast<double *>(wreg) : gscratch;
-    exact_scores<QT>(cent_rows, qd, sel, nullptr, k, xs);
+__device__ __forceinline__ void emit_sorted(const ChainParams &p, const unsigned short *qrow, const uint2 *cent_rows,
+                                            const unsigned *bitmap_h, int bw, int *sel, double *xs_smem,
+                                            double *gscratch, int *out) {
+    const int lane = lane_id(), k = p.k;
+    int base = 0;
+    for (int w0 = 0; w0 < bw; w0 += 32) {
+        unsigned word = (w0 + lane < bw) ? bitmap_h[w0 + lane] : 0u;
+        int inc = __popc(word);
+        const int mine = inc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        int pos = base + inc - mine;
+        while (word) {
+            const int bit = __ffs(word) - 1;
+            sel[pos++] = (w0 + lane) * 32 + bit;
+            word &= word - 1;
+        }
+        base += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    __syncwarp();
+    double *xs = (k <= kXCap) ? xs_smem : gscratch;
+    exact_scores<QT>(cent_rows, qrow, sel, nullptr, k, xs);
     for (int i = lane; i < k; i += 32) {
         const int e = sel[i];
         const double se = xs[i];
@@ -335,11 +438,11 @@ __device__ void sort_selected(const ChainParams &p, const uint2 *cent_rows, cons
     __syncwarp();
 }
 
-// ---- compaction of one bit-plane of pm[] into an ascending page list -------------------------
+// ---- slow path (a head selected more pages than max_page_num): serial compaction ---------------
 // One warp.  Writes out[0..min(count, cap)) = ascending i with (pm[i] >> bit) & 1, pads with the
-// sentinel up to cap, clears the bit of entries beyond cap (so later consumers agree with the
+// sentinel up to cap, clears the bit of entries beyond cap (so the union agrees with the
 // truncated list), returns the kept count.
-__device__ inline int warp_compact_bit(unsigned *pm, int pl, int bit, int *out, int cap) {
+__device__ __noinline__ int warp_compact_bit(unsigned *pm, int pl, int bit, int *out, int cap) {
     const int lane = lane_id();
     int base = 0;
     for (int i0 = 0; i0 < pl; i0 += 32) {
@@ -358,11 +461,9 @@ __device__ inline int warp_compact_bit(unsigned *pm, int pl, int bit, int *out, 
     return cnt;
 }
 
-// ---- union list of one item ------------------------------------------------------------------
-// pm[i] = head mask | tail mask << 16 for logical page i.  Emits the ascending list of pages with
-// a non-zero mask: physical block id (block_table value) + meta word, and the item's length.
-// phys: block_table row, either staged in smem or the global row itself.
-__device__ inline void warp_emit_union(const ChainParams &p, int item, const int *phys, const unsigned *pm, int pl) {
+// Union list of one item (one warp, serial over chunks).  pm[i] = head mask | tail mask << 16 for
+// logical page i; emits the ascending pages with a non-zero mask: physical block id + meta word.
+__device__ __noinline__ void warp_emit_union(const ChainParams &p, int item, const int *phys, const unsigned *pm, int pl) {
     const int lane = lane_id();
     int *uphys = p.union_phys + (size_t)item * p.maxP;
     unsigned *umeta = p.union_meta + (size_t)item * p.maxP;
@@ -382,94 +483,126 @@ __device__ inline void warp_emit_union(const ChainParams &p, int item, const int
     if (lane == 0) p.union_len[item] = base;
 }
 
-// ---- phase A for the fused op / cent_select / compute_cent / select_position ------------------
-template <typename QT>
-__device__ void select_item(const ChainParams &p, int item, int flags, unsigned char *smem, const Grp &G) {
+// ---- phase A for one item: fused op / cent_select / compute_cent / select_position ------------
+template <typename QT, int FLAGS>
+__device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int item, unsigned char *smem,
+                            const CentRing &R, unsigned &tcount, const Grp &G) {
+    constexpr bool DS = (FLAGS & kSelScores) != 0, DP = (FLAGS & kSelSelect) != 0;
+    constexpr int KG1 = kMaxGroup + 1;
     const int b = item / p.Nkv, n2 = item % p.Nkv;
-    const int g = p.g, C = p.C, k = p.k;
-    const int lane = lane_id();
-    SelSmem L(g, C, k, p.maxP, G.gw, flags);
+    const int g = p.g, C = p.C, k = p.k, lane = lane_id();
+    const int hq0 = n2 * g;
+    const SelSmem L(g, C, k, p.maxP, FLAGS);
     float *sc = reinterpret_cast<float *>(smem + L.sc);
-    unsigned *wreg = reinterpret_cast<unsigned *>(smem + L.wreg) + G.warp * kSelBins;
-    unsigned short *cand = reinterpret_cast<unsigned short *>(smem + L.cand) + (size_t)G.warp * C;
-    int *selw = (flags & kSelWriteIndices) ? reinterpret_cast<int *>(smem + L.sel) + G.warp * k : nullptr;
+    unsigned *hist = reinterpret_cast<unsigned *>(smem + L.hist);
+    unsigned short *cand = reinterpret_cast<unsigned short *>(smem + L.cand);
+    double *xs = reinterpret_cast<double *>(smem + L.xs);
+    int *selS = reinterpret_cast<int *>(smem + L.sel);
     unsigned *bitmap = reinterpret_cast<unsigned *>(smem + L.bitmap);
     unsigned *pm = reinterpret_cast<unsigned *>(smem + L.pm);
     int *physS = reinterpret_cast<int *>(smem + L.phys);
+    int *cS = reinterpret_cast<int *>(smem + L.cval);
+    int *cnt = reinterpret_cast<int *>(smem + L.cnt);
     int *srt = reinterpret_cast<int *>(smem + L.srt);
+    HeadRec *hd = reinterpret_cast<HeadRec *>(smem + L.hd);
     float *misc = reinterpret_cast<float *>(smem + L.misc);
-    const bool do_scores = (flags & kSelScores) != 0, do_select = (flags & kSelSelect) != 0;
+    int *miscI = reinterpret_cast<int *>(smem + L.misc);
 
-    // ---- page-table gathers first: c[i] = block_ids[n2, block_table[b, i]] stays in registers
-    //      until the selection is known (select_position.cpp:97-115 CopyIn/Gather)
+    // ---- S0: start everything asynchronous, initialise the per-item state
     int seq = 0, pl = 0, rem = 0;
     bool has_tail = false;
-    int creg[kPG];
-    const int *bt = nullptr, *bid = nullptr;
-    if (do_select) {
+    const int *bid = nullptr;
+    if (DP) {
         seq = p.seq_len[b];
         pl = max(0, min((seq + p.bs - 1) / p.bs, p.maxP));
         rem = (pl > 0) ? seq - (pl - 1) * p.bs : 0;               // tokens on the last page
         has_tail = (pl > 0) && (rem < p.bs);
-        bt = p.block_table + (size_t)b * p.bt_stride;
+        const int *bt = p.block_table + (size_t)b * p.bt_stride;
         bid = p.block_ids + (size_t)n2 * p.bid_stride;
-        int btv[kPG];
-#pragma unroll
-        for (int j = 0; j < kPG; ++j) {
-            const int i = G.tid + j * G.gt;
-            btv[j] = (i < pl) ? __ldg(bt + i) : 0;
+        for (int i = G.tid; i < pl; i += G.gt) cp_async_4(&physS[i], bt + i);     // block_table row -> smem
+    }
+    if (DS) {
+        if (G.tid == 0) {
+            const int nt = min((C + kCentTileRows - 1) / kCentTileRows, R.ns);
+            for (int t = 0; t < nt; ++t)
+                issue_cent_tile(tmC, R, (int)((tcount + (unsigned)t) % (unsigned)R.ns), n2 * C + t * kCentTileRows);
         }
-#pragma unroll
-        for (int j = 0; j < kPG; ++j) {
-            const int i = G.tid + j * G.gt;
-            creg[j] = 0;
-            if (i < pl) {
-                physS[i] = btv[j];
-                creg[j] = __ldg(bid + max(0, min(btv[j], p.kvPageLen - 1)));   // clamp: utils.py:62
-            }
+        if (G.tid < g) { hd[G.tid].kmin = 0xffffffffu; hd[G.tid].kmax = 0u; hd[G.tid].ncand = 0; }
+        uint4 *hz = reinterpret_cast<uint4 *>(hist);
+        for (int i = G.tid; i < g * (kSelBins / 4); i += G.gt) hz[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = G.tid; i < g * L.bw; i += G.gt) bitmap[i] = 0u;
+    }
+    if (G.tid == 0) { miscI[8] = 0; miscI[9] = 0; }
+    if (DP && p.page_position != nullptr) {
+        // pad first: the real positions overwrite the head of each row later (ordered by the barriers)
+        int *base = p.page_position + ((size_t)b * p.Nq + hq0) * p.MP;
+        const int total = g * p.MP;
+        if ((total & 3) == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0) {
+            int4 *b4 = reinterpret_cast<int4 *>(base);
+            for (int i = G.tid; i < total / 4; i += G.gt) b4[i] = make_int4(kSentinel, kSentinel, kSentinel, kSentinel);
+        } else {
+            for (int i = G.tid; i < total; i += G.gt) base[i] = kSentinel;
         }
     }
-
+    if (DP) cp_async_wait_all();
+    grp_sync(G);
+    if (DP) {
+        // c[i] = block_ids[n2, block_table[b, i]] (select_position.cpp:97-115), asynchronously into smem;
+        // the table value is clamped as the golden does (tests/utils.py:62)
+        for (int i = G.tid; i < pl; i += G.gt) cp_async_4(&cS[i], bid + max(0, min(physS[i], p.kvPageLen - 1)));
+    }
     trace_mark(p, 8);
-    if (do_scores) {
-        const float wmax = score_tiles<QT>(p, b, n2, sc, L.scs, G);
-        if (lane == 0) misc[G.warp] = wmax;
-        trace_mark(p, 9);
+
+    const unsigned short *q = reinterpret_cast<const unsigned short *>(p.q);
+    if (DS) {
+        score_item<QT>(p, tmC, b, n2, sc, L.scs, hd, misc, R, tcount, G);
         grp_sync(G);
-        trace_mark(p, 10);
+        trace_mark(p, 9);
         float maxabs = 0.f;
         for (int w = 0; w < G.gw; ++w) maxabs = fmaxf(maxabs, misc[w]);
-        const unsigned short *q = reinterpret_cast<const unsigned short *>(p.q);
+        topk_hist(p, sc, L.scs, hist, hd, G);
+        grp_sync(G);
+        trace_mark(p, 10);
+        for (int h = G.warp; h < g; h += G.gw) topk_bin(p, hist + h * kSelBins, &hd[h], maxabs);
+        grp_sync(G);
+        trace_mark(p, 11);
+        topk_classify(p, sc, L.scs, hd, bitmap, L.bw, cand, G);
+        grp_sync(G);
+        trace_mark(p, 12);
         const uint2 *cent_rows = reinterpret_cast<const uint2 *>(p.cent) + (size_t)n2 * C * (kD / 4);
         double *gscratch = p.exact_scratch + ((size_t)blockIdx.x * kConsumerWarps + warp_id()) * C;
+#pragma unroll 1
         for (int h = G.warp; h < g; h += G.gw) {
-            const int hq = n2 * g + h;
-            double qd[4];
-            topk_head<QT>(p, q + (size_t)b * p.q_sb + (size_t)hq * p.q_sh, cent_rows, sc + h * L.scs, maxabs, wreg,
-                          cand, selw, bitmap + h * L.bw, gscratch, qd);
-            if (flags & kSelWriteIndices)
-                sort_selected<QT>(p, cent_rows, qd, selw, wreg, gscratch, p.indices_out + ((size_t)b * p.Nq + hq) * k);
+            const unsigned short *qrow = q + (size_t)b * p.q_sb + (size_t)(hq0 + h) * p.q_sh;
+            topk_resolve<QT>(p, qrow, cent_rows, sc + h * L.scs, &hd[h], cand + (size_t)h * C, bitmap + h * L.bw, L.bw,
+                             xs + h * kXCap, gscratch);
+            if (FLAGS & kSelWriteIndices)
+                emit_sorted<QT>(p, qrow, cent_rows, bitmap + h * L.bw, L.bw, selS + h * k, xs + h * kXCap, gscratch,
+                                p.indices_out + ((size_t)b * p.Nq + hq0 + h) * k);
         }
-    } else if (do_select) {
+        trace_mark(p, 13);
+    } else if (DP) {
         // indices are given (select_position op): arbitrary values, duplicates allowed
         // (tests/select_position.py:45) -> direct comparison against the k entries per head.
-        for (int i = G.tid; i < g * k; i += G.gt) {
-            const int h = i / k;
-            srt[i] = p.indices_in[(size_t)b * p.idx_sb + (size_t)(n2 * g + h) * p.idx_sh + (i % k)];
-        }
+        for (int i = G.tid; i < g * k; i += G.gt)
+            srt[i] = p.indices_in[(size_t)b * p.idx_sb + (size_t)(hq0 + i / k) * p.idx_sh + (i % k)];
     }
-    if (!do_select) { grp_sync(G); return; }
-    trace_mark(p, 11);
+    if (!DP) { grp_sync(G); return; }
+    cp_async_wait_all();
     grp_sync(G);
-    trace_mark(p, 12);
 
     // ---- membership mask per logical page (select_position.cpp:122-183; tests/utils.py:57-80)
-    auto page_mask = [&](int i, int c) {
+#pragma unroll 1
+    for (int i = G.tid; i < pl; i += G.gt) {
+        const int c = cS[i];
         unsigned m = 0u;
-        if (do_scores) {
-            if (c >= 0 && c < C)
+        if (DS) {
+            if (c >= 0 && c < C) {
+#pragma unroll 1
                 for (int h = 0; h < g; ++h) m |= ((bitmap[h * L.bw + (c >> 5)] >> (c & 31)) & 1u) << h;
+            }
         } else {
+#pragma unroll 1
             for (int h = 0; h < g; ++h) {
                 bool hit = false;
                 for (int j = 0; j < k; ++j) hit |= (srt[h * k + j] == c);
@@ -478,38 +611,102 @@ __device__ void select_item(const ChainParams &p, int item, int flags, unsigned 
         }
         if (has_tail && i == pl - 1) m |= m << 16;
         pm[i] = m;
-        if (flags & kSelGather)
-            for (int h = 0; h < g; ++h) p.bt_gather[((size_t)b * p.Nq + n2 * g + h) * p.maxP + i] = c;
-    };
-#pragma unroll
-    for (int j = 0; j < kPG; ++j) {
-        const int i = G.tid + j * G.gt;
-        if (i < pl) page_mask(i, creg[j]);
+        if (FLAGS & kSelGather)
+            for (int h = 0; h < g; ++h) p.bt_gather[((size_t)b * p.Nq + hq0 + h) * p.maxP + i] = c;
     }
-    for (int i = G.tid + kPG * G.gt; i < pl; i += G.gt) {          // very long block tables
-        const int ph = __ldg(bt + i);
-        physS[i] = ph;
-        page_mask(i, __ldg(bid + max(0, min(ph, p.kvPageLen - 1))));
-    }
-    if (flags & kSelGather)
+    if (FLAGS & kSelGather)
         for (int i = pl + G.tid; i < p.maxP; i += G.gt)
-            for (int h = 0; h < g; ++h) p.bt_gather[((size_t)b * p.Nq + n2 * g + h) * p.maxP + i] = 0;
+            for (int h = 0; h < g; ++h) p.bt_gather[((size_t)b * p.Nq + hq0 + h) * p.maxP + i] = 0;
     grp_sync(G);
-    trace_mark(p, 13);
-    // ---- per-head ascending compaction -> page_position / page_position_length
-    for (int h = G.warp; h < g; h += G.gw) {
-        const int hq = n2 * g + h;
-        int *pp = p.page_position ? p.page_position + ((size_t)b * p.Nq + hq) * p.MP : nullptr;
-        const int cnt = warp_compact_bit(pm, pl, h, pp, p.MP);
-        if (p.page_position_length && lane < kPad)
-            p.page_position_length[((size_t)b * p.Nq + hq) * kPad + lane] = cnt;
-    }
     trace_mark(p, 14);
-    if (flags & kSelUnion) {
-        grp_sync(G);
-        if (G.warp == 0) {
-            warp_emit_union(p, item, physS, pm, pl);
-            if (lane == 0) p.tail_count[item] = has_tail ? rem : p.bs;
+
+    // ---- compaction: per-head ascending page lists + the group's union list, all warps in parallel.
+    // pass 1: per 32-page chunk, the number of set bits of every head plane (and of the union)
+    const int nch = (pl + 31) >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll 1
+    for (int ch = G.warp; ch < nch; ch += G.gw) {
+        const int i = ch * 32 + lane;
+        const unsigned m = (i < pl) ? pm[i] : 0u;
+        int mine = 0;
+#pragma unroll 1
+        for (int h = 0; h <= g; ++h) {
+            const bool on = (h < g) ? ((m >> h) & 1u) : ((m & 0xffffu) != 0u);
+            const int c = __popc(__ballot_sync(0xffffffffu, on));
+            if (lane == h) mine = c;
+        }
+        if (lane <= g) cnt[ch * KG1 + lane] = mine;
+    }
+    grp_sync(G);
+    // exclusive prefix over chunks, one column (head / union) at a time; lanes = chunks
+    if (G.warp == 0) {
+#pragma unroll 1
+        for (int col = 0; col <= g; ++col) {
+            int run = 0;
+            for (int c0 = 0; c0 < nch; c0 += 32) {
+                const int ch = c0 + lane;
+                const int v = (ch < nch) ? cnt[ch * KG1 + col] : 0;
+                int inc = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += t;
+                }
+                if (ch < nch) cnt[ch * KG1 + col] = run + inc - v;
+                run += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            if (lane == 0) {
+                if (col < g) { hd[col].total = min(run, p.MP); if (run > p.MP) miscI[8] = 1; }
+                else miscI[9] = run;
+            }
+        }
+    }
+    grp_sync(G);
+    int *pp0 = p.page_position ? p.page_position + ((size_t)b * p.Nq + hq0) * p.MP : nullptr;
+    if (miscI[8] == 0) {
+        // pass 2: scatter
+        int *uphys = p.union_phys + (size_t)item * p.maxP;
+        unsigned *umeta = p.union_meta + (size_t)item * p.maxP;
+#pragma unroll 1
+        for (int ch = G.warp; ch < nch; ch += G.gw) {
+            const int i = ch * 32 + lane;
+            const unsigned m = (i < pl) ? pm[i] : 0u;
+#pragma unroll 1
+            for (int h = 0; h < g; ++h) {
+                const bool on = (m >> h) & 1u;
+                const unsigned bal = __ballot_sync(0xffffffffu, on);
+                if (on && pp0) pp0[(size_t)h * p.MP + cnt[ch * KG1 + h] + __popc(bal & lt)] = i;
+            }
+            if (FLAGS & kSelUnion) {
+                const bool on = (m & 0xffffu) != 0u;
+                const unsigned bal = __ballot_sync(0xffffffffu, on);
+                if (on) {
+                    const int pos = cnt[ch * KG1 + g] + __popc(bal & lt);
+                    uphys[pos] = physS[i];
+                    umeta[pos] = m;
+                }
+            }
+        }
+        if (p.page_position_length)
+            for (int i = G.tid; i < g * kPad; i += G.gt)
+                p.page_position_length[((size_t)b * p.Nq + hq0) * kPad + i] = hd[i / kPad].total;
+        if ((FLAGS & kSelUnion) && G.tid == 0) {
+            p.union_len[item] = miscI[9];
+            p.tail_count[item] = has_tail ? rem : p.bs;
+        }
+    } else {
+        // a head selected more than max_page_num pages: serial path that truncates consistently
+        for (int h = G.warp; h < g; h += G.gw) {
+            const int c = warp_compact_bit(pm, pl, h, pp0 ? pp0 + (size_t)h * p.MP : nullptr, p.MP);
+            if (p.page_position_length && lane < kPad)
+                p.page_position_length[((size_t)b * p.Nq + hq0 + h) * kPad + lane] = c;
+        }
+        if (FLAGS & kSelUnion) {
+            grp_sync(G);
+            if (G.warp == 0) {
+                warp_emit_union(p, item, physS, pm, pl);
+                if (lane == 0) p.tail_count[item] = has_tail ? rem : p.bs;
+            }
         }
     }
     trace_mark(p, 15);
@@ -559,15 +756,29 @@ __device__ inline void union_from_block_position(const ChainParams &p, int item,
     __syncthreads();
 }
 
-// all items of phase A handled by this CTA's worker groups (warps 0..kConsumerWarps-1)
-template <typename QT>
-__device__ __forceinline__ void select_phase(const ChainParams &p, int flags, unsigned char *smem) {
+// ---- all items of phase A handled by this CTA's worker groups (warps 0..kConsumerWarps-1) --------
+// smem: [ngroups x sel_ns centroid-tile stages][ngroups x group state]
+template <typename QT, int FLAGS>
+__device__ __forceinline__ void select_phase(const ChainParams &p, const CUtensorMap *tmC, unsigned char *smem) {
+    __shared__ uint64_t sel_bars[2][16];               // per group: full[0..8), empty[8..16)
+    const int ngroups = kConsumerWarps / p.sel_gw;
+    if ((FLAGS & kSelScores) && threadIdx.x == 0) {
+        for (int gi = 0; gi < ngroups; ++gi)
+            for (int s = 0; s < p.sel_ns; ++s) { mbar_init(&sel_bars[gi][s], 1); mbar_init(&sel_bars[gi][8 + s], p.sel_gw); }
+        fence_barrier_init();
+        fence_proxy_async();
+        tma_prefetch_desc(tmC);
+    }
+    __syncthreads();
     if (warp_id() >= kConsumerWarps) return;
     const Grp G = make_group(p.sel_gw);
-    const int ngroups = kConsumerWarps / p.sel_gw;
-    unsigned char *gs = smem + (size_t)G.id * p.sel_group_bytes;
+    CentRing R;
+    R.base = smem + (size_t)G.id * p.sel_ns * kCentTileBytes;
+    R.full = &sel_bars[G.id][0]; R.empty = &sel_bars[G.id][8]; R.ns = p.sel_ns;
+    unsigned char *gs = smem + (size_t)ngroups * p.sel_ns * kCentTileBytes + (size_t)G.id * p.sel_group_bytes;
+    unsigned tcount = 0;
     for (int item = blockIdx.x + G.id * gridDim.x; item < p.items; item += gridDim.x * ngroups)
-        select_item<QT>(p, item, flags, gs, G);
+        select_item<QT, FLAGS>(p, tmC, item, gs, R, tcount, G);
 }
 
 // max_page_position_length[b, 0..7] = bs * max_h count   (cent_select.cpp:123-160)

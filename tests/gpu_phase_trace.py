@@ -33,7 +33,8 @@ def main():
     torch.cuda.synchronize()
     names = ["A select", "sync1", "B stream", "sync2", "C combine"]
     for rep in range(3):
-        flush()
+        if not os.environ.get('NOFLUSH'):
+            flush()
         t = plan.trace_phases().cpu().double()
         t0 = t[:, 0].min()
         rel = (t - t0) / 1e3                                     # us
