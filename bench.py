@@ -292,7 +292,11 @@ def main():
     ppl = torch.empty(B, nq, 8, dtype=torch.int32, device=dev)
     mppl = torch.empty(B, 8, dtype=torch.int64, device=dev)
     out = torch.empty(B, nq, D, dtype=qd, device=dev)
-    out_all = torch.empty(world, B, nq, D, dtype=qd, device=dev) if world > 1 else None
+    gather = out_full = None
+    if world > 1:
+        from kvhead_tp import HeadGather
+        gather = HeadGather(out.shape, qd, dev)                      # NCCL all-gather of the output shards
+        out_full = torch.empty(B, nq * world, D, dtype=qd, device=dev)
     i8 = w["kv"] == "i8"
     plan = custom_ops.FusedDecodePlan(
         inp["q"], inp["key"], inp["value"], inp["block_table"], inp["l1"], inp["block_ids"], inp["seq"],
@@ -304,7 +308,7 @@ def main():
     def step():
         plan.launch()
         if world > 1:
-            dist.all_gather_into_tensor(out_all, out)
+            gather(out, out_full)
 
     graph = None
     if args.graph:
@@ -373,8 +377,7 @@ def main():
             dq, inp["key"], inp["value"], e, e, e64, e, e, e, e, e, inp["aq_scale"], inp["aq_offset"], dbt, e64,
             inp["l1"], inp["block_ids"], dseq, bp, ppl, mppl, nq, inp["scale"], "BNSD", nkv, BS, 1, k=inp["k"])
         if world > 1:
-            dist.all_gather_into_tensor(out_all, o)
-            hout.copy_(out_all.permute(1, 0, 2, 3).reshape(B, nq * world, D), non_blocking=True)
+            hout.copy_(gather(o, out_full), non_blocking=True)
         else:
             hout.copy_(o, non_blocking=True)
 
