@@ -228,6 +228,8 @@ std::shared_ptr<FusionPlan> make_fusion_plan(
               o.ptr(), &plan->ws_bytes, &plan->exec),
           "sparse_paged_fusion_attention");
     plan->workspace = alloc_ws(plan->ws_bytes, query);
+    // the plan owns its workspace and nothing else writes to it: the queue words need clearing only once
+    check(spaExecutorSetPersistentWorkspace(plan->exec, 1), "spaExecutorSetPersistentWorkspace");
     plan->keep = {query, key, value, antiquant_scale, antiquant_offset, blocktable, l1_cent, block_ids,
                   total_seq_len, block_position, page_position_length, max_page_position_length, attention_out};
     return plan;
@@ -357,7 +359,7 @@ PYBIND11_MODULE(custom_ops_lib, m) {
         .def("set_trace", [](FusionPlan &p, const at::Tensor &buf) {
             if (!buf.defined() || buf.numel() == 0) { spaExecutorSetTrace(p.exec, nullptr); return; }
             TORCH_CHECK(buf.is_cuda() && buf.scalar_type() == at::kLong && buf.is_contiguous() &&
-                        buf.numel() >= (int64_t)spaExecutorGridSize(p.exec) * 16, "trace: need int64 CUDA [grid,16]");
+                        buf.numel() >= (int64_t)spaExecutorGridSize(p.exec) * 32, "trace: need int64 CUDA [grid,32]");
             p.keep.push_back(buf);
             spaExecutorSetTrace(p.exec, buf.data_ptr());
         });

@@ -1,31 +1,43 @@
-// Phase B (paged flash-decode over the union of the selected pages) and phase C (split combine).
+// Phase B (paged flash-decode over the union of the selected pages) with the split combine folded in.
 //
 // Work item = (b, kv head).  All g query heads of the GQA group are processed together, so every
 // selected K/V page slice is fetched from HBM once per group (the compulsory traffic)
 // even though each query head has its own page set: per-page head masks switch heads off.
-// The flattened list of all items' union pages is cut into gridDim.x equal contiguous ranges
-// (the scheme the reference authors prototyped in tests/test_block_lookup.py:22-48); a CTA
-// streams its range through a TMA -> shared-memory ring and leaves one partial (O, m, l) per
-// item it touched; phase C merges the partials of each item (flash-decode combine,
-// sparse_paged_attention_split_Bbn2s2_Us2.h:2392-2495).
+//
+// Scheduling: phase A publishes each item's union pages into one global page queue (spa_select.cuh,
+// queue_commit).  A CTA claims runs of consecutive queue entries with one atomicAdd; run lengths
+// shrink with the remaining work (guided self-scheduling), so all SMs drain HBM until the very end
+// and no grid-wide barrier separates selection, streaming and combine.  (The reference authors
+// prototyped equal static ranges in tests/test_block_lookup.py:22-48; the dynamic queue also
+// absorbs the spread of phase A and of the HBM channels.)  A run is streamed through a
+// TMA -> shared-memory ring; whenever the item changes the CTA leaves one partial (O, m, l), and
+// the CTA that completes an item's page count merges that item's partials (flash-decode combine,
+// sparse_paged_attention_split_Bbn2s2_Us2.h:2392-2495) and writes attention_out.
 #pragma once
 #include "spa_common.cuh"
 
 namespace spa {
 
-constexpr int kMergeHeadStride = 132;   // floats; +4 padding keeps the 4 lanes of a quad on distinct banks
+constexpr int kMergeHalf = 64;                          // head dims merged per round
+constexpr int kMergeHeadStride = kMergeHalf + 4;        // floats; +4 padding keeps the 4 lanes of a quad on distinct banks
+constexpr int kMergeWarpFloats = 8 * kMergeHeadStride;
+constexpr int kMailSlots = 4;                           // flush -> post-warp messages in flight
+constexpr int kPostWarp = kConsumerWarps + 1;           // warp 8: TMA producer, warps 9..11: partial bookkeeping + combine
 
 struct AttnSmem {
-    int stages, scratch, wml, meta, bars, prefix, total;
+    int stages, mbuf, wml, meta, bars, mail, list, total;
+    int list_cap;
     __host__ __device__ static inline int align(int x, int a) { return (x + a - 1) / a * a; }
-    __host__ __device__ AttnSmem(int nstages, int stage_bytes, int nt_tiles, int items) {
+    __host__ __device__ AttnSmem(int nstages, int stage_bytes, int nt_tiles, int max_partials) {
         int o = 0;
         stages = o;   o = align(o + nstages * stage_bytes, 1024);
-        scratch = o;  o = align(o + 4 * nt_tiles * 8 * kMergeHeadStride * 4, 16);
-        wml = o;      o = align(o + kConsumerWarps * nt_tiles * 8 * 2 * 4, 16);
-        meta = o;     o = align(o + nstages * 4, 16);
-        bars = o;     o = align(o + nstages * 2 * 8, 16);
-        prefix = o;   o = align(o + (items + 2) * 4, 16);
+        mbuf = o;     o = align(o + kConsumerWarps * kMergeWarpFloats * 4, 16);   // 8 heads x 64 dims per warp
+        wml = o;      o = align(o + kConsumerWarps * nt_tiles * 8 * 2 * 4 + 16, 16);   // + the flush's slot word
+        meta = o;     o = align(o + nstages * 16, 16);
+        bars = o;     o = align(o + (nstages * 2 + kPostWarps * kMailSlots * 2) * 8, 16);
+        mail = o;     o = align(o + kPostWarps * kMailSlots * 32, 16);
+        list_cap = max_partials;
+        list = o;     o = align(o + kPostWarps * max_partials * 4, 16);
         total = o;
     }
 };
@@ -36,122 +48,435 @@ __device__ __forceinline__ int o_dim(int mt, int gid, int r) {
     return KVI8 ? mt * 16 + 2 * gid + (r >> 1) : mt * 16 + gid + (r >> 1) * 8;
 }
 
-__device__ __forceinline__ int upper_item(const int *prefix, int items, int pos) {
-    // largest item with prefix[item] <= pos  (prefix is non-decreasing, prefix[items] = T > pos)
-    int lo = 0, hi = items;          // invariant: prefix[lo] <= pos < prefix[hi]
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (prefix[mid] <= pos) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
-// exclusive prefix sums of union_len into smem; prefix[items] = total
-__device__ inline void build_prefix(const ChainParams &p, int *prefix) {
-    const int tid = threadIdx.x, nt = blockDim.x;
-    for (int i = tid; i < p.items; i += nt) prefix[i + 1] = p.union_len[i];
-    if (tid == 0) prefix[0] = 0;
-    __syncthreads();
-    if (warp_id() == 0) {
-        const int lane = lane_id();
-        int base = 0;
-        for (int i0 = 0; i0 < p.items; i0 += 32) {
-            int i = i0 + lane;
-            int v = (i < p.items) ? prefix[i + 1] : 0;
-            int inc = v;
-            for (int o = 1; o < 32; o <<= 1) {
-                int t = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += t;
-            }
-            if (i < p.items) prefix[i + 1] = base + inc;
-            base += __shfl_sync(0xffffffffu, inc, 31);
+// normalise NV consecutive head dims d0.. of one output row, V antiquant, store
+template <typename QT, bool KVI8, int NV>
+__device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int n2, int h, int d0, const float (&acc)[NV],
+                                               float Lsum) {
+    const float inv = (Lsum > 0.f) ? 1.f / Lsum : 0.f;
+    float r[NV];
+#pragma unroll
+    for (int e = 0; e < NV; ++e) r[e] = acc[e] * inv;
+    if (KVI8 && Lsum > 0.f) {
+        // V dequant applied once to the normalised sum: (O + offset_v) * scale_v (…_Us2.h:3655-3670)
+        const unsigned short *sv = reinterpret_cast<const unsigned short *>(p.aq_scale) +
+                                   (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD);
+        const unsigned short *ov = p.aq_offset ? reinterpret_cast<const unsigned short *>(p.aq_offset) +
+                                   (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD) : nullptr;
+#pragma unroll
+        for (int e = 0; e < NV; ++e) {
+            const int d = p.aq_per_tensor ? 0 : d0 + e;
+            const float off = ov ? QTraits<QT>::to_float(ov[d]) : 0.f;
+            r[e] = (r[e] + off) * QTraits<QT>::to_float(sv[d]);
         }
     }
-    __syncthreads();
+    unsigned short *op = reinterpret_cast<unsigned short *>(p.out) + (size_t)b * p.out_sb +
+                         (size_t)(n2 * p.g + h) * p.out_sh + d0;
+#pragma unroll
+    for (int e = 0; e < NV; e += 2) *reinterpret_cast<uint32_t *>(op + e) = QTraits<QT>::pack2(r[e], r[e + 1]);
+}
+
+// ---- combine (post warp): the CTA whose partial completed the item's page count merges all partials ----
+// A CTA that left a partial for a segment starting at queue index i wrote (slot + 1) into flat[i]
+// (the entry itself was consumed and zeroed before); the item's range is scanned for those marks.
+// Latency-bound (everything sits in L2): marks, then (m, l) of every partial and head, then the O rows
+// of two heads x eight partials per round trip.
+template <typename QT, bool KVI8, int NT>
+__device__ void combine_item_warp(const ChainParams &p, int item, int base, int len, int *list, int list_cap) {
+    constexpr int HP = NT * 8;
+    const int lane = lane_id();
+    const unsigned lt = (1u << lane) - 1u;
+    const int b = item / p.Nkv, n2 = item % p.Nkv, g = p.g;
+    unsigned long long *marks = p.flat + base;
+    int n = 0;
+    for (int j0 = 0; j0 < len; j0 += 128) {
+        unsigned long long mk[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int j = j0 + u * 32 + lane;
+            mk[u] = (j < len) ? ld_relaxed_u64(marks + j) : 0ull;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const bool ok = mk[u] != 0ull && !(mk[u] >> 63);
+            const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            if (ok) {
+                const int at = n + __popc(bal & lt);
+                if (at < list_cap) list[at] = (int)(mk[u] - 1);
+                st_relaxed_u64(marks + j0 + u * 32 + lane, 0ull);       // leave the queue words as found
+            }
+            n += __popc(bal);
+        }
+    }
+    if (n > list_cap) __trap();                                          // more partials than runs exist: unreachable
+    __syncwarp();
+#pragma unroll 1
+    for (int h0 = 0; h0 < g; h0 += 2) {
+        const int nh = min(2, g - h0);
+        float M[2] = {-INFINITY, -INFINITY}, Ls[2] = {0.f, 0.f};
+        float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll 1
+        for (int c0 = 0; c0 < n; c0 += 32) {
+            const int slot = (c0 + lane < n) ? list[c0 + lane] : -1;
+            float w[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                float2 ml = make_float2(-INFINITY, 0.f);
+                if (slot >= 0 && e < nh) ml = __ldcg(reinterpret_cast<const float2 *>(p.part_ml + ((size_t)slot * HP + h0 + e) * 2));
+                float cm = ml.x;
+#pragma unroll
+                for (int o = 16; o; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+                const float newM = fmaxf(M[e], cm);
+                const float r = (M[e] == -INFINITY) ? 0.f : fast_exp2(M[e] - newM);
+                acc[e][0] *= r; acc[e][1] *= r; acc[e][2] *= r; acc[e][3] *= r;
+                Ls[e] *= r;
+                M[e] = newM;
+                w[e] = (ml.x == -INFINITY) ? 0.f : fast_exp2(ml.x - newM);
+                Ls[e] += ml.y * w[e];
+            }
+            const int nn = min(32, n - c0);
+#pragma unroll 1
+            for (int j0 = 0; j0 < nn; j0 += 8) {
+                float4 v[2][8];
+                float wj[2][8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int jj = min(j0 + u, nn - 1);
+                    const int sj = __shfl_sync(0xffffffffu, slot, jj);
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float we = __shfl_sync(0xffffffffu, w[e], jj);
+                        wj[e][u] = (j0 + u < nn && e < nh) ? we : 0.f;
+                        v[e][u] = __ldcg(reinterpret_cast<const float4 *>(p.part_o + ((size_t)sj * HP + h0 + min(e, nh - 1)) * kD) + lane);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        acc[e][0] += v[e][u].x * wj[e][u]; acc[e][1] += v[e][u].y * wj[e][u];
+                        acc[e][2] += v[e][u].z * wj[e][u]; acc[e][3] += v[e][u].w * wj[e][u];
+                    }
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            float L = Ls[e];
+#pragma unroll
+            for (int o = 16; o; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
+            if (e < nh) write_out_vals<QT, KVI8, 4>(p, b, n2, h0 + e, lane * 4, acc[e], L);
+        }
+    }
+    if (lane == 0) { p.item_info[item] = 0ull; p.ctrl[Ctrl::pages_done(p.B, item)] = 0; }
+}
+
+// ---- post warp: takes the flush messages of this CTA's consumers; publishes each partial (mark in the
+// queue, fence, page count) and combines the items this CTA completed.  Keeps every global round trip
+// of the bookkeeping off the consumers' path: under a saturated HBM each one costs microseconds.
+template <typename QT, bool KVI8, int NT>
+__device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t *mfull, uint64_t *mempty, int *list,
+                               int list_cap) {
+    const int lane = lane_id();
+    int mi = 0;
+    uint32_t mph = 0;
+    for (;;) {
+        mbar_wait(&mfull[mi], mph);
+        const int4 m0 = mail[mi * 2], m1 = mail[mi * 2 + 1];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&mempty[mi]);
+        if (++mi == kMailSlots) { mi = 0; mph ^= 1u; }
+        const int item = m0.x, first_idx = m0.y, cnt = m0.z, slot = m0.w;
+        if (item < 0) break;
+        const int base = m1.x, len = m1.y;
+        int old = 0;
+        if (lane == 0) {
+            st_relaxed_u64(p.flat + first_idx, (unsigned long long)slot + 1ull);
+            __threadfence();
+            old = atomicAdd(p.ctrl + Ctrl::pages_done(p.B, item), cnt);
+        }
+        old = __shfl_sync(0xffffffffu, old, 0);
+        if (old == len - cnt) {
+            __threadfence();
+            const unsigned long long tc0 = (p.dbg && lane == 0) ? globaltimer_ns() : 0ull;
+            combine_item_warp<QT, KVI8, NT>(p, item, base, len, list, list_cap);
+            if (p.dbg && lane == 0 && p.trace) {
+                p.trace[(size_t)blockIdx.x * kTraceSlots + 10] += 1;
+                p.trace[(size_t)blockIdx.x * kTraceSlots + 11] += globaltimer_ns() - tc0;
+            }
+        }
+    }
+}
+
+// consumers' thread 0: hand a message to the post warp
+// mi counts messages: message k goes to post warp k % kPostWarps, slot (k / kPostWarps) % kMailSlots
+__device__ __forceinline__ void post_message(int4 *mail, uint64_t *mfull, uint64_t *mempty, int &mi, uint32_t &mph,
+                                             int4 m0, int4 m1) {
+    const int w = mi % kPostWarps, r = mi / kPostWarps;
+    const int sl = w * kMailSlots + (r % kMailSlots);
+    const uint32_t ph = (uint32_t)(r / kMailSlots) & 1u;
+    mbar_wait(&mempty[sl], ph ^ 1u);
+    mail[sl * 2] = m0; mail[sl * 2 + 1] = m1;
+    mbar_arrive(&mfull[sl]);
+    ++mi;
+    (void)mph;
+}
+
+// ---- segment flush: merge the 8 warps' running states of `item`; either finish the item (all of its
+// pages were in this segment) or leave a partial and tell the post warp.  All consumers.
+template <typename QT, bool KVI8, int NT>
+__device__ __forceinline__ void flush_segment(const ChainParams &p, int item, int first_idx, int cnt,
+                                              unsigned long long rec, int slot_t0, float (&o)[NT][8][4],
+                                              float (&m_run)[NT][2], float (&l_run)[NT][2], float *mbuf,
+                                              float *wml, int4 *mail, uint64_t *mfull, uint64_t *mempty, int &mi,
+                                              uint32_t &mph) {
+    constexpr int HP = NT * 8;
+    constexpr int kAll = kConsumerWarps * 32;
+    const int lane = lane_id(), warp = warp_id(), gid = lane >> 2, tig = lane & 3;
+    const int b = item / p.Nkv, n2 = item % p.Nkv;
+    // l: reduce the thread-partials over the 8 token rows held by different lanes
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            float l = l_run[nt][e];
+            l += __shfl_xor_sync(0xffffffffu, l, 4);
+            l += __shfl_xor_sync(0xffffffffu, l, 8);
+            l += __shfl_xor_sync(0xffffffffu, l, 16);
+            if (gid == 0) {
+                const int h = nt * 8 + tig * 2 + e;
+                wml[(warp * HP + h) * 2 + 0] = m_run[nt][e];
+                wml[(warp * HP + h) * 2 + 1] = l;
+            }
+        }
+    while (!(rec >> 63)) rec = ld_relaxed_u64(p.item_info + item);     // published before the entries; normally valid at once
+    const int len = record_len(rec);
+    const bool whole = (cnt == len);                                    // uniform over the CTA
+    int slot = __shfl_sync(0xffffffffu, slot_t0, 0);                    // thread 0's reservation ...
+    if (lane == 0 && warp == 0) reinterpret_cast<int *>(wml)[kConsumerWarps * HP * 2] = slot;
+    named_bar_sync(1, kAll);
+    slot = reinterpret_cast<const int *>(wml)[kConsumerWarps * HP * 2];  // ... for everyone
+    if (!whole && slot >= p.pool_cap) __trap();                          // cannot happen: see plan_attention
+    // bring every warp's accumulators to the common max of the head
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int h = nt * 8 + tig * 2 + e;
+            float M = -INFINITY;
+#pragma unroll
+            for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, wml[(w * HP + h) * 2]);
+            const float sc = (m_run[nt][e] == -INFINITY) ? 0.f : fast_exp2(m_run[nt][e] - M);
+#pragma unroll
+            for (int mt = 0; mt < 8; ++mt) { o[nt][mt][e] *= sc; o[nt][mt][2 + e] *= sc; }
+        }
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        // thread (warp, lane) owns head nt*8 + warp: its max and sum over the 8 warps
+        const int h = nt * 8 + warp;
+        float M = -INFINITY, Ls = 0.f;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, wml[(w * HP + h) * 2]);
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) {
+            const float mw = wml[(w * HP + h) * 2];
+            Ls += (mw == -INFINITY) ? 0.f : wml[(w * HP + h) * 2 + 1] * fast_exp2(mw - M);
+        }
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            if (nt + half > 0) named_bar_sync(1, kAll);               // merge buffers are reused per round
+            float *mine = mbuf + warp * kMergeWarpFloats;
+#pragma unroll
+            for (int mt = half * 4; mt < half * 4 + 4; ++mt)
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                    mine[(tig * 2 + (r & 1)) * kMergeHeadStride + o_dim<KVI8>(mt, gid, r) - half * kMergeHalf] = o[nt][mt][r];
+            named_bar_sync(1, kAll);
+            // dims half*64 + 2*lane, +1 of head h: sum over the 8 warps
+            float acc[2] = {0.f, 0.f};
+#pragma unroll
+            for (int w = 0; w < kConsumerWarps; ++w) {
+                const float2 v = *reinterpret_cast<const float2 *>(mbuf + w * kMergeWarpFloats + warp * kMergeHeadStride + lane * 2);
+                acc[0] += v.x; acc[1] += v.y;
+            }
+            const int d0 = half * kMergeHalf + lane * 2;
+            if (whole) {
+                if (h < p.g) write_out_vals<QT, KVI8, 2>(p, b, n2, h, d0, acc, Ls);
+            } else {
+                *reinterpret_cast<float2 *>(p.part_o + ((size_t)slot * HP + h) * kD + d0) = make_float2(acc[0], acc[1]);
+            }
+        }
+        if (!whole && lane == 0) *reinterpret_cast<float2 *>(p.part_ml + ((size_t)slot * HP + h) * 2) = make_float2(M, Ls);
+    }
+    named_bar_sync(1, kAll);      // every thread's partial stores precede the message; smem free for the next flush
+    if (threadIdx.x == 0) {
+        if (whole) p.item_info[item] = 0ull;                          // consumed: nobody else holds pages of it
+        else post_message(mail, mfull, mempty, mi, mph, make_int4(item, first_idx, cnt, slot),
+                          make_int4(record_base(rec), len, 0, 0));
+    }
+}
+
+// ---- producer side ------------------------------------------------------------------------------------
+// One queue entry (any lane).  The producer only reads entries after it has seen "all items done"
+// (acquire), so the first read normally succeeds; the loop covers the memory model.
+// A consumed entry is returned to zero, so the queue is clean for the next launch.
+__device__ __forceinline__ unsigned long long take_entry(const ChainParams &p, int idx, unsigned long long v) {
+    unsigned long long *e = p.flat + idx;
+    while (!(v >> 63)) { __nanosleep(32); v = ld_relaxed_u64(e); }
+    st_relaxed_u64(e, 0ull);
+    return v;
 }
 
 template <typename QT, bool KVI8, int NT>
 __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, const CUtensorMap *tmV,
                                 unsigned char *smem) {
-    constexpr int HP = NT * 8;
-    AttnSmem L(p.nstages, p.stage_bytes, NT, p.items);
+    AttnSmem L(p.nstages, p.stage_bytes, NT, p.list_cap);
     unsigned char *stage_base = smem + L.stages;
-    float *scratch = reinterpret_cast<float *>(smem + L.scratch);
+    float *mbuf = reinterpret_cast<float *>(smem + L.mbuf);
     float *wml = reinterpret_cast<float *>(smem + L.wml);
-    unsigned *metaS = reinterpret_cast<unsigned *>(smem + L.meta);
+    int4 *metaS = reinterpret_cast<int4 *>(smem + L.meta);
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + L.bars);
     uint64_t *empty = full + p.nstages;
-    int *prefix = reinterpret_cast<int *>(smem + L.prefix);
+    uint64_t *mfull = empty + p.nstages;
+    uint64_t *mempty = mfull + kPostWarps * kMailSlots;
+    int4 *mail = reinterpret_cast<int4 *>(smem + L.mail);
+    int *list = reinterpret_cast<int *>(smem + L.list);
 
     const int tid = threadIdx.x, lane = lane_id(), warp = warp_id();
     const int nstages = p.nstages;
-    const int G = gridDim.x, cta = blockIdx.x;
 
-    build_prefix(p, prefix);
-    const int T = prefix[p.items];
-    const int start = (int)(((long long)cta * T) / G);
-    const int end = (int)(((long long)(cta + 1) * T) / G);
-
+    __syncthreads();                                  // phase A of every warp group is done with the shared memory
     if (tid == 0) {
         for (int s = 0; s < nstages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kConsumerWarps); }
+        for (int s = 0; s < kPostWarps * kMailSlots; ++s) { mbar_init(&mfull[s], 1); mbar_init(&mempty[s], 1); }
         fence_barrier_init();
         fence_proxy_async();
     }
     __syncthreads();
-    if (start >= end) return;
 
     int stage = 0;
     uint32_t phase = 0;
-    int pos = start;
-    int item = upper_item(prefix, p.items, start);
 
+    if (warp >= kPostWarp) {
+        const int pw = warp - kPostWarp;
+        post_warp_loop<QT, KVI8, NT>(p, mail + pw * kMailSlots * 2, mfull + pw * kMailSlots, mempty + pw * kMailSlots,
+                                     list + pw * L.list_cap, L.list_cap);
+        return;
+    }
     if (warp == kConsumerWarps) {
         // =============================== TMA producer ===============================
         if (lane == 0) { tma_prefetch_desc(tmK); tma_prefetch_desc(tmV); }
-        while (pos < end) {
-            const int seg_end = min(end, prefix[item + 1]);
-            const int n2 = item % p.Nkv;
-            const int *uphys = p.union_phys + (size_t)item * p.maxP - prefix[item];
-            const unsigned *umeta = p.union_meta + (size_t)item * p.maxP - prefix[item];
-            for (int base = pos; base < seg_end; base += 32) {
-                const int idx = base + lane;
-                int phys = 0; unsigned meta = 0;
-                if (idx < seg_end) { phys = uphys[idx]; meta = umeta[idx]; }
-                const int n = min(32, seg_end - base);
-                for (int j = 0; j < n; ++j) {
-                    const int ph = __shfl_sync(0xffffffffu, phys, j);
-                    const unsigned mt = __shfl_sync(0xffffffffu, meta, j);
-                    if (lane == 0) {
-                        int c[4];
-                        c[1] = (p.ax_head == 1) ? n2 : (p.ax_blk == 1 ? ph : 0);
-                        c[2] = (p.ax_head == 2) ? n2 : (p.ax_blk == 2 ? ph : 0);
-                        c[3] = (p.ax_head == 3) ? n2 : (p.ax_blk == 3 ? ph : 0);
+        // The queue is final once every item has reported.  Most of it is cut statically (no traffic on
+        // the critical path: every control access costs microseconds while HBM is saturated); the rest
+        // is handed out in short runs, one claim always in flight, which evens out the SMs' speeds.
+        int T = 0;
+        if (lane == 0) {
+            while (ld_acquire(p.ctrl + Ctrl::kItemsDone) != p.items) __nanosleep(64);
+            T = ld_relaxed(p.ctrl + Ctrl::kTail);
+        }
+        T = __shfl_sync(0xffffffffu, T, 0);
+        const int G = gridDim.x;
+        const int S = (int)((long long)T * p.static_pct / 100 / G);        // static pages per CTA
+        const int dyn0 = G * S;
+        const int Rd = max(1, (T - dyn0 + p.dyn_runs * G - 1) / (p.dyn_runs * G));
+        // Static share [s0, e0).  An item cut by a range boundary is finished by two CTAs; if each CTA
+        // walked its range front to back, every such item would complete at the very end (this CTA's last
+        // pages, the neighbour's first) and all combines would pile up after the stream.  So the part of
+        // the last item is streamed right after the first item: cut items complete early, their combine
+        // hides under the stream, and the range ends with whole items (no partial, no combine).
+        const int s0 = blockIdx.x * S, e0 = s0 + S;
+        int srun[3][2] = {{s0, S}, {0, 0}, {0, 0}};
+        int nsr = (S > 0) ? 1 : 0;
+        if (S > 0) {
+            unsigned long long pr = 0ull;
+            if (lane < 2) {
+                const unsigned long long *pe = p.flat + (lane == 0 ? s0 : e0 - 1);
+                unsigned long long ev;
+                do { ev = ld_relaxed_u64(pe); } while (!(ev >> 63));
+                const unsigned long long *pi = p.item_info + (int)((ev >> 48) & (kMaxItems - 1));
+                do { pr = ld_relaxed_u64(pi); } while (!(pr >> 63));
+            }
+            const unsigned long long ra = __shfl_sync(0xffffffffu, pr, 0), rb = __shfl_sync(0xffffffffu, pr, 1);
+            const int b1 = min(e0, record_base(ra) + record_len(ra));       // end of the first item
+            const int bb = max(s0, record_base(rb));                        // start of the last item
+            if (bb > b1 && record_base(rb) + record_len(rb) > e0) {
+                srun[0][1] = b1 - s0;
+                srun[1][0] = bb; srun[1][1] = e0 - bb;
+                srun[2][0] = b1; srun[2][1] = bb - b1;
+                nsr = 3;
+            }
+        }
+        int sri = 0;                                                       // next static run
+        int rf = 0, rn = 0;                                                // current run: [rf, rf + rn)
+        int nf = 0;                                                        // next claim, in flight (lane 0)
+        if (lane == 0) nf = atomicAdd(p.ctrl + Ctrl::kHead, Rd);
+        unsigned long long t_runs = 1, t_pages = 0;
+        bool more = true;
+        // next chunk (<= 32 entries of one run) -> cf, cn; false when the queue is exhausted
+        auto next_chunk = [&](int &cf, int &cn) -> bool {
+            while (rn == 0 && sri < nsr) { rf = srun[sri][0]; rn = srun[sri][1]; ++sri; }
+            if (rn == 0) {
+                if (!more) return false;
+                const int f = dyn0 + __shfl_sync(0xffffffffu, nf, 0);
+                const int n = min(Rd, T - f);
+                if (n <= 0) { more = false; return false; }
+                rf = f; rn = n; ++t_runs;
+                if (lane == 0) { nf = atomicAdd(p.ctrl + Ctrl::kHead, Rd); trace_put(p, 2, globaltimer_ns()); }
+            }
+            cf = rf; cn = min(32, rn);
+            rf += cn; rn -= cn;
+            return true;
+        };
+        int cf = 0, cn = 0;
+        bool ok = next_chunk(cf, cn);
+        unsigned long long ent = (ok && lane < cn) ? ld_relaxed_u64(p.flat + cf + lane) : 0ull;
+        while (ok) {
+            // entries of the following chunk travel while this chunk is issued
+            int cf2 = 0, cn2 = 0;
+            const bool ok2 = next_chunk(cf2, cn2);
+            const unsigned long long ent2 = (ok2 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
+            if (lane < cn) ent = take_entry(p, cf + lane, ent);
+            t_pages += cn;
+            for (int j = 0; j < cn; ++j) {
+                const unsigned long long e = __shfl_sync(0xffffffffu, ent, j);
+                if (lane == 0) {
+                    const unsigned hi = (unsigned)(e >> 32), lo = (unsigned)e;
+                    const int ph = (int)(lo & 0xffffffu), item = (int)((hi >> 16) & (kMaxItems - 1));
+                    const int n2 = item % p.Nkv;
+                    // stage header: head mask | tail flag << 16, item, queue index, tokens on a tail page
+                    const int4 md = make_int4((int)(hi & 0xffffu) | (int)(((hi >> 30) & 1u) << 16), item, cf + j,
+                                              (int)((lo >> 24) & 0x7fu) + 1);
+                    int c[4];
+                    c[1] = (p.ax_head == 1) ? n2 : (p.ax_blk == 1 ? ph : 0);
+                    c[2] = (p.ax_head == 2) ? n2 : (p.ax_blk == 2 ? ph : 0);
+                    c[3] = (p.ax_head == 3) ? n2 : (p.ax_blk == 3 ? ph : 0);
 #pragma unroll
-                        for (int kv = 0; kv < 2; ++kv) {
-                            mbar_wait(&empty[stage], phase ^ 1u);
-                            metaS[stage] = mt;
-                            mbar_expect_tx(&full[stage], (uint32_t)p.stage_bytes);
-                            unsigned char *dst = stage_base + (size_t)stage * p.stage_bytes;
-                            const CUtensorMap *tm = kv ? tmV : tmK;
-                            if (KVI8) {
-                                tma_load_4d(dst, tm, &full[stage], 0, c[1], c[2], c[3]);
-                            } else {
-                                tma_load_4d(dst, tm, &full[stage], 0, c[1], c[2], c[3]);
-                                tma_load_4d(dst + p.stage_bytes / 2, tm, &full[stage], 64, c[1], c[2], c[3]);
-                            }
-                            if (++stage == nstages) { stage = 0; phase ^= 1u; }
+                    for (int kv = 0; kv < 2; ++kv) {
+                        mbar_wait(&empty[stage], phase ^ 1u);
+                        metaS[stage] = md;
+                        mbar_expect_tx(&full[stage], (uint32_t)p.stage_bytes);
+                        unsigned char *dst = stage_base + (size_t)stage * p.stage_bytes;
+                        const CUtensorMap *tm = kv ? tmV : tmK;
+                        if (KVI8) {
+                            tma_load_4d(dst, tm, &full[stage], 0, c[1], c[2], c[3]);
+                        } else {
+                            tma_load_4d(dst, tm, &full[stage], 0, c[1], c[2], c[3]);
+                            tma_load_4d(dst + p.stage_bytes / 2, tm, &full[stage], 64, c[1], c[2], c[3]);
                         }
+                        if (++stage == nstages) { stage = 0; phase ^= 1u; }
                     }
                 }
-                __syncwarp();
             }
-            pos = seg_end;
-            ++item;
-            while (item < p.items && prefix[item + 1] == prefix[item]) ++item;
+            __syncwarp();
+            ok = ok2; cf = cf2; cn = cn2; ent = ent2;
+        }
+        if (lane == 0) { unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid)); trace_put(p, 12, smid); }
+        if (lane == 0) { trace_put(p, 4, t_pages); trace_put(p, 6, t_runs); trace_put(p, 7, globaltimer_ns()); }
+        if (lane == 0) {                                  // end marker: a stage without data
+            mbar_wait(&empty[stage], phase ^ 1u);
+            metaS[stage] = make_int4(0, -2, 0, 0);       // item -2: never equals a consumer's current item
+            mbar_arrive(&full[stage]);
         }
         return;
     }
-
     // ================================= consumers =================================
     const int gid = lane >> 2, tig = lane & 3;
     const int t0 = warp * 16;                       // this warp's 16 tokens of every page
@@ -163,343 +488,198 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     const int v_row = t0 + (lane & 7) + ((lane >> 4) & 1) * 8;   // V tile as A^T operand (.trans)
     const int v_chk = (lane >> 3) & 1;
 
-    while (pos < end) {
-        const int seg_end = min(end, prefix[item + 1]);
-        const int b = item / p.Nkv, n2 = item % p.Nkv;
-        const int tail_cnt = p.tail_count[item];
-
-        // ---- Q fragments (B operand of S^T = K Q^T): b0 = Q[head][d0,d0+1], b1 = Q[head][d0+8,+9]
-        uint32_t qf[NT][8][2];
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-            const int h = nt * 8 + gid;
-            const unsigned short *qrow = qg + (size_t)b * p.q_sb + (size_t)(n2 * p.g + h) * p.q_sh;
-#pragma unroll
-            for (int ks = 0; ks < 8; ++ks) {
-                // fp16/bf16 KV: k-slots of the mma map to d in natural order.  int8 KV: one
-                // ldmatrix row-quad holds 4 consecutive d, so slot (2*tig+e) <-> d = 16ks+4tig+e and
-                // slot (2*tig+8+e) <-> d = 16ks+4tig+2+e (same permutation on both operands).
-                const int d0 = KVI8 ? ks * 16 + tig * 4 : ks * 16 + tig * 2;
-                const int dstep = KVI8 ? 2 : 8;
-                uint32_t v0 = 0, v1 = 0;
-                if (h < p.g) {
-                    v0 = *reinterpret_cast<const uint32_t *>(qrow + d0);
-                    v1 = *reinterpret_cast<const uint32_t *>(qrow + d0 + dstep);
-                    if (KVI8) {
-                        // fold the per-channel K scale into Q (…_Us2.h:2142); the K offset adds a
-                        // per-head constant to every logit and cancels in the softmax (:2146-2155)
-                        const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) +
-                                                   (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
-                        float s0 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0]);
-                        float s1 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + 1]);
-                        float s8 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + dstep]);
-                        float s9 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + dstep + 1]);
-                        v0 = QTraits<QT>::pack2(QTraits<QT>::to_float(v0 & 0xffff) * s0,
-                                                QTraits<QT>::to_float(v0 >> 16) * s1);
-                        v1 = QTraits<QT>::pack2(QTraits<QT>::to_float(v1 & 0xffff) * s8,
-                                                QTraits<QT>::to_float(v1 >> 16) * s9);
-                    }
-                }
-                qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
-            }
-        }
-        // ---- running state: O^T[d][head] fragments, m (log2 domain), l (thread-partial)
-        float o[NT][8][4];
-        float m_run[NT][2], l_run[NT][2];
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-#pragma unroll
-            for (int mt = 0; mt < 8; ++mt)
-#pragma unroll
-                for (int r = 0; r < 4; ++r) o[nt][mt][r] = 0.f;
-            m_run[nt][0] = m_run[nt][1] = -INFINITY;
-            l_run[nt][0] = l_run[nt][1] = 0.f;
-        }
-
-        for (; pos < seg_end; ++pos) {
-            // ------------------------------ K: S^T = K Q^T ------------------------------
-            mbar_wait(&full[stage], phase);
-            const unsigned meta = metaS[stage];
-            float s[NT][4];
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-            {
-                const uint32_t kb = stage_u32 + (uint32_t)stage * p.stage_bytes;
-                if (!KVI8) {
-#pragma unroll
-                    for (int ks = 0; ks < 8; ++ks) {
-                        const int chunk = (ks & 3) * 2 + a_chk;
-                        const uint32_t addr = kb + (ks >> 2) * (kBS * 128) + a_row * 128 +
-                                              ((chunk ^ (a_row & 7)) << 4);
-                        uint32_t a0, a1, a2, a3;
-                        ldmatrix_x4(a0, a1, a2, a3, addr);
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt)
-                            mma_16816<QT>(s[nt], a0, a1, a2, a3, qf[nt][ks][0], qf[nt][ks][1]);
-                    }
-                } else {
-                    // int8 page: [128 tokens][128 B]; one ldmatrix.x4 covers 16 tokens x 32 d
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int chunk = j * 2 + a_chk;
-                        const uint32_t addr = kb + a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
-                        uint32_t r0, r1, r2, r3;
-                        ldmatrix_x4(r0, r1, r2, r3, addr);
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt) {
-                            mma_16816<QT>(s[nt], I8Pair<QT, 0, 1>::cvt(r0), I8Pair<QT, 0, 1>::cvt(r1),
-                                          I8Pair<QT, 2, 3>::cvt(r0), I8Pair<QT, 2, 3>::cvt(r1),
-                                          qf[nt][2 * j][0], qf[nt][2 * j][1]);
-                            mma_16816<QT>(s[nt], I8Pair<QT, 0, 1>::cvt(r2), I8Pair<QT, 0, 1>::cvt(r3),
-                                          I8Pair<QT, 2, 3>::cvt(r2), I8Pair<QT, 2, 3>::cvt(r3),
-                                          qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
-                        }
-                    }
-                }
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[stage]);
-            if (++stage == nstages) { stage = 0; phase ^= 1u; }
-
-            // ------------------------------ online softmax ------------------------------
-            uint32_t pb[NT][2];                      // P^T as B fragments (after transpose)
+    // running state of the current segment: O^T[d][head] fragments, m (log2 domain), l (thread-partial)
+    uint32_t qf[NT][8][2];
+    float o[NT][8][4];
+    float m_run[NT][2], l_run[NT][2];
+    int cur = -1, cnt = 0, first_idx = 0, slot_t0 = 0;
+    unsigned long long rec = 0ull;
+    int mi = 0;
+    uint32_t mph = 0;
+    for (;;) {
+        mbar_wait(&full[stage], phase);
+        const int4 md = metaS[stage];
+        const unsigned meta = (unsigned)md.x & 0xffffu;      // head mask of the page
+        const bool tail_page = (md.x >> 16) & 1;
+        const int tail_cnt = md.w;
+        if (md.y != cur) {
+            if (p.dbg && tid == 0 && md.y < 0) { trace_put(p, 10, 0); trace_put(p, 11, 0); trace_put(p, 8, globaltimer_ns()); }
+            if (cur >= 0) flush_segment<QT, KVI8, NT>(p, cur, first_idx, cnt, rec, slot_t0, o, m_run, l_run, mbuf, wml, mail, mfull, mempty, mi, mph);
+            if (p.dbg && tid == 0 && md.y < 0) trace_put(p, 9, globaltimer_ns());
+            if (md.y < 0) break;
+            cur = md.y; cnt = 0; first_idx = md.z;
+            rec = ld_relaxed_u64(p.item_info + cur);             // first used at the flush
+            // partial slot for this segment: the atomic's result is first used at the flush
+            if (tid == 0) slot_t0 = atomicAdd(p.ctrl + Ctrl::kPool, 1);
+            const int b = cur / p.Nkv, n2 = cur % p.Nkv;
+            // ---- Q fragments (B operand of S^T = K Q^T): b0 = Q[head][d0,d0+1], b1 = Q[head][d0+8,+9]
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
-                float pr[4];
-                float alpha[2];
+                const int h = nt * 8 + gid;
+                const unsigned short *qrow = qg + (size_t)b * p.q_sb + (size_t)(n2 * p.g + h) * p.q_sh;
 #pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int h = nt * 8 + tig * 2 + e;
-                    const bool member = (meta >> h) & 1u;
-                    const bool tail = (meta >> (16 + h)) & 1u;
-                    const int ntok = member ? (tail ? tail_cnt : kBS) : 0;
-                    float x0 = (t0 + gid < ntok) ? s[nt][e] * p.scale_log2 : -INFINITY;
-                    float x1 = (t0 + gid + 8 < ntok) ? s[nt][2 + e] * p.scale_log2 : -INFINITY;
-                    float mx = fmaxf(x0, x1);
-                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
-                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
-                    const float m_new = fmaxf(m_run[nt][e], mx);
-                    const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-                    alpha[e] = fast_exp2(m_run[nt][e] - m_use);
-                    const float p0 = fast_exp2(x0 - m_use);
-                    const float p1 = fast_exp2(x1 - m_use);
-                    l_run[nt][e] = l_run[nt][e] * alpha[e] + p0 + p1;
-                    m_run[nt][e] = m_new;
-                    pr[e] = p0; pr[2 + e] = p1;
-                }
-#pragma unroll
-                for (int mt = 0; mt < 8; ++mt) {
-                    o[nt][mt][0] *= alpha[0]; o[nt][mt][1] *= alpha[1];
-                    o[nt][mt][2] *= alpha[0]; o[nt][mt][3] *= alpha[1];
-                }
-                // P rounded to the matmul dtype before PV (…_Us2.h:3062-3063); 8x8 transposes turn
-                // the accumulator layout [tok][head] into the B-operand layout [k=tok][n=head]
-                pb[nt][0] = movmatrix_trans(QTraits<QT>::pack2(pr[0], pr[1]));
-                pb[nt][1] = movmatrix_trans(QTraits<QT>::pack2(pr[2], pr[3]));
-            }
-
-            // ------------------------------ V: O^T += V^T P^T ------------------------------
-            mbar_wait(&full[stage], phase);
-            {
-                const uint32_t vb = stage_u32 + (uint32_t)stage * p.stage_bytes;
-                if (!KVI8) {
-#pragma unroll
-                    for (int mt = 0; mt < 8; ++mt) {
-                        const int chunk = (mt & 3) * 2 + v_chk;
-                        const uint32_t addr = vb + (mt >> 2) * (kBS * 128) + v_row * 128 +
-                                              ((chunk ^ (v_row & 7)) << 4);
-                        uint32_t a0, a1, a2, a3;
-                        ldmatrix_x4_trans(a0, a1, a2, a3, addr);
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt)
-                            mma_16816<QT>(o[nt][mt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
-                    }
-                } else {
-                    // int8 page, transposed 8x8 b16 loads: a register holds V[tok 2tig][d,d+1] and
-                    // V[tok 2tig+1][d,d+1] with d = 16*chunk + 2*gid; m-tile row gid <-> d, row
-                    // gid+8 <-> d+1 (see o_dim()).
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int chunk = j * 2 + a_chk;
-                        const uint32_t addr = vb + a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
-                        uint32_t r0, r1, r2, r3;
-                        ldmatrix_x4_trans(r0, r1, r2, r3, addr);
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt) {
-                            mma_16816<QT>(o[nt][2 * j], I8Pair<QT, 0, 2>::cvt(r0), I8Pair<QT, 1, 3>::cvt(r0),
-                                          I8Pair<QT, 0, 2>::cvt(r1), I8Pair<QT, 1, 3>::cvt(r1), pb[nt][0], pb[nt][1]);
-                            mma_16816<QT>(o[nt][2 * j + 1], I8Pair<QT, 0, 2>::cvt(r2), I8Pair<QT, 1, 3>::cvt(r2),
-                                          I8Pair<QT, 0, 2>::cvt(r3), I8Pair<QT, 1, 3>::cvt(r3), pb[nt][0], pb[nt][1]);
+                for (int ks = 0; ks < 8; ++ks) {
+                    // fp16/bf16 KV: k-slots of the mma map to d in natural order.  int8 KV: one
+                    // ldmatrix row-quad holds 4 consecutive d, so slot (2*tig+e) <-> d = 16ks+4tig+e and
+                    // slot (2*tig+8+e) <-> d = 16ks+4tig+2+e (same permutation on both operands).
+                    const int d0 = KVI8 ? ks * 16 + tig * 4 : ks * 16 + tig * 2;
+                    const int dstep = KVI8 ? 2 : 8;
+                    uint32_t v0 = 0, v1 = 0;
+                    if (h < p.g) {
+                        v0 = *reinterpret_cast<const uint32_t *>(qrow + d0);
+                        v1 = *reinterpret_cast<const uint32_t *>(qrow + d0 + dstep);
+                        if (KVI8) {
+                            // fold the per-channel K scale into Q (…_Us2.h:2142); the K offset adds a
+                            // per-head constant to every logit and cancels in the softmax (:2146-2155)
+                            const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) +
+                                                       (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
+                            float s0 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0]);
+                            float s1 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + 1]);
+                            float s8 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + dstep]);
+                            float s9 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + dstep + 1]);
+                            v0 = QTraits<QT>::pack2(QTraits<QT>::to_float(v0 & 0xffff) * s0,
+                                                    QTraits<QT>::to_float(v0 >> 16) * s1);
+                            v1 = QTraits<QT>::pack2(QTraits<QT>::to_float(v1 & 0xffff) * s8,
+                                                    QTraits<QT>::to_float(v1 >> 16) * s9);
                         }
                     }
+                    qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
                 }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[stage]);
-            if (++stage == nstages) { stage = 0; phase ^= 1u; }
-        }
-
-        // ---------------- segment flush: merge the 8 warps, write one partial ----------------
-        // l: reduce the thread-partials over the 8 token rows held by different lanes
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                float l = l_run[nt][e];
-                l += __shfl_xor_sync(0xffffffffu, l, 4);
-                l += __shfl_xor_sync(0xffffffffu, l, 8);
-                l += __shfl_xor_sync(0xffffffffu, l, 16);
-                l_run[nt][e] = l;
-                if (gid == 0) {
-                    const int h = nt * 8 + tig * 2 + e;
-                    wml[(warp * HP + h) * 2 + 0] = m_run[nt][e];
-                    wml[(warp * HP + h) * 2 + 1] = l;
-                }
-            }
-        named_bar_sync(1, kConsumerWarps * 32);
-        float Mh[NT][2], Lh[NT][2];
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int h = nt * 8 + tig * 2 + e;
-                float M = -INFINITY;
-#pragma unroll
-                for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, wml[(w * HP + h) * 2]);
-                float Ls = 0.f;
-#pragma unroll
-                for (int w = 0; w < kConsumerWarps; ++w) {
-                    const float mw = wml[(w * HP + h) * 2];
-                    Ls += (mw == -INFINITY) ? 0.f : wml[(w * HP + h) * 2 + 1] * fast_exp2(mw - M);
-                }
-                const float sc = (m_run[nt][e] == -INFINITY) ? 0.f : fast_exp2(m_run[nt][e] - M);
-#pragma unroll
-                for (int mt = 0; mt < 8; ++mt) { o[nt][mt][e] *= sc; o[nt][mt][2 + e] *= sc; }
-                Mh[nt][e] = M; Lh[nt][e] = Ls;
-            }
-        // pairwise tree over warps through 4 scratch buffers
-#pragma unroll
-        for (int half = kConsumerWarps / 2; half >= 1; half >>= 1) {
-            if (warp >= half && warp < 2 * half) {
-                float *buf = scratch + (size_t)(warp - half) * HP * kMergeHeadStride;
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-                    for (int mt = 0; mt < 8; ++mt)
-#pragma unroll
-                        for (int r = 0; r < 4; ++r) {
-                            const int h = nt * 8 + tig * 2 + (r & 1);
-                            const int d = o_dim<KVI8>(mt, gid, r);
-                            buf[h * kMergeHeadStride + d] = o[nt][mt][r];
-                        }
-            }
-            named_bar_sync(1, kConsumerWarps * 32);
-            if (warp < half) {
-                const float *buf = scratch + (size_t)warp * HP * kMergeHeadStride;
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-                    for (int mt = 0; mt < 8; ++mt)
-#pragma unroll
-                        for (int r = 0; r < 4; ++r) {
-                            const int h = nt * 8 + tig * 2 + (r & 1);
-                            const int d = o_dim<KVI8>(mt, gid, r);
-                            o[nt][mt][r] += buf[h * kMergeHeadStride + d];
-                        }
-            }
-            named_bar_sync(1, kConsumerWarps * 32);
-        }
-        if (warp == 0) {
-            const size_t slot = (size_t)item + cta;
-            float *po = p.part_o + slot * HP * kD;
-            float *pml = p.part_ml + slot * HP * 2;
+            // ---- running state: O^T[d][head] fragments, m (log2 domain), l (thread-partial)
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
                 for (int mt = 0; mt < 8; ++mt)
 #pragma unroll
-                    for (int r = 0; r < 4; ++r) {
-                        const int h = nt * 8 + tig * 2 + (r & 1);
-                        const int d = o_dim<KVI8>(mt, gid, r);
-                        po[h * kD + d] = o[nt][mt][r];
-                    }
-                if (gid == 0) {
+                    for (int r = 0; r < 4; ++r) o[nt][mt][r] = 0.f;
+                m_run[nt][0] = m_run[nt][1] = -INFINITY;
+                l_run[nt][0] = l_run[nt][1] = 0.f;
+            }
+
+        }
+        ++cnt;
+        // ------------------------------ K: S^T = K Q^T ------------------------------
+        float s[NT][4];
 #pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int h = nt * 8 + tig * 2 + e;
-                        pml[h * 2 + 0] = Mh[nt][e];
-                        pml[h * 2 + 1] = Lh[nt][e];
+        for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        {
+            const uint32_t kb = stage_u32 + (uint32_t)stage * p.stage_bytes;
+            if (!KVI8) {
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    const int chunk = (ks & 3) * 2 + a_chk;
+                    const uint32_t addr = kb + (ks >> 2) * (kBS * 128) + a_row * 128 +
+                                          ((chunk ^ (a_row & 7)) << 4);
+                    uint32_t a0, a1, a2, a3;
+                    ldmatrix_x4(a0, a1, a2, a3, addr);
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt)
+                        mma_16816<QT>(s[nt], a0, a1, a2, a3, qf[nt][ks][0], qf[nt][ks][1]);
+                }
+            } else {
+                // int8 page: [128 tokens][128 B]; one ldmatrix.x4 covers 16 tokens x 32 d
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int chunk = j * 2 + a_chk;
+                    const uint32_t addr = kb + a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
+                    uint32_t r0, r1, r2, r3;
+                    ldmatrix_x4(r0, r1, r2, r3, addr);
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        mma_16816<QT>(s[nt], I8Pair<QT, 0, 1>::cvt(r0), I8Pair<QT, 0, 1>::cvt(r1),
+                                      I8Pair<QT, 2, 3>::cvt(r0), I8Pair<QT, 2, 3>::cvt(r1),
+                                      qf[nt][2 * j][0], qf[nt][2 * j][1]);
+                        mma_16816<QT>(s[nt], I8Pair<QT, 0, 1>::cvt(r2), I8Pair<QT, 0, 1>::cvt(r3),
+                                      I8Pair<QT, 2, 3>::cvt(r2), I8Pair<QT, 2, 3>::cvt(r3),
+                                      qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
                     }
                 }
             }
         }
-        ++item;
-        while (item < p.items && prefix[item + 1] == prefix[item]) ++item;
-    }
-}
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[stage]);
+        if (++stage == nstages) { stage = 0; phase ^= 1u; }
 
-// ---- phase C: merge the partials of every (item, head) and write attention_out ---------------
-template <typename QT, bool KVI8, int NT>
-__device__ void combine_phase(const ChainParams &p, unsigned char *smem) {
-    constexpr int HP = NT * 8;
-    AttnSmem L(p.nstages, p.stage_bytes, NT, p.items);
-    const int *prefix = reinterpret_cast<const int *>(smem + L.prefix);
-    const int lane = lane_id();
-    const int G = gridDim.x;
-    const long long T = prefix[p.items];
-    const int nwarps = blockDim.x / 32;
-    const int units = p.items * p.g;
-    for (int u = blockIdx.x * nwarps + warp_id(); u < units; u += G * nwarps) {
-        const int item = u / p.g, h = u % p.g;
-        const int b = item / p.Nkv, n2 = item % p.Nkv;
-        const long long P0 = prefix[item], P1 = prefix[item + 1];
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        float Lsum = 0.f;
-        if (P1 > P0) {
-            const int c0 = (int)(((P0 + 1) * G + T - 1) / T) - 1;
-            const int c1 = (int)((P1 * G + T - 1) / T) - 1;
-            // CTAs whose page range is empty (T < gridDim.x) never wrote their slot: skip them
-            float M = -INFINITY;
-            for (int c = c0; c <= c1; ++c) {
-                if ((long long)c * T / G == (long long)(c + 1) * T / G) continue;
-                M = fmaxf(M, p.part_ml[((size_t)(item + c) * HP + h) * 2]);
+        // ------------------------------ online softmax ------------------------------
+        uint32_t pb[NT][2];                      // P^T as B fragments (after transpose)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            float pr[4];
+            float alpha[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int h = nt * 8 + tig * 2 + e;
+                const bool member = (meta >> h) & 1u;
+                const int ntok = member ? (tail_page ? tail_cnt : kBS) : 0;
+                float x0 = (t0 + gid < ntok) ? s[nt][e] * p.scale_log2 : -INFINITY;
+                float x1 = (t0 + gid + 8 < ntok) ? s[nt][2 + e] * p.scale_log2 : -INFINITY;
+                float mx = fmaxf(x0, x1);
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+                const float m_new = fmaxf(m_run[nt][e], mx);
+                const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+                alpha[e] = fast_exp2(m_run[nt][e] - m_use);
+                const float p0 = fast_exp2(x0 - m_use);
+                const float p1 = fast_exp2(x1 - m_use);
+                l_run[nt][e] = l_run[nt][e] * alpha[e] + p0 + p1;
+                m_run[nt][e] = m_new;
+                pr[e] = p0; pr[2 + e] = p1;
             }
-            for (int c = c0; c <= c1; ++c) {
-                if ((long long)c * T / G == (long long)(c + 1) * T / G) continue;
-                const size_t slot = (size_t)item + c;
-                const float m = p.part_ml[(slot * HP + h) * 2];
-                const float l = p.part_ml[(slot * HP + h) * 2 + 1];
-                const float w = (m == -INFINITY) ? 0.f : fast_exp2(m - M);
-                Lsum += l * w;
-                const float4 v = *reinterpret_cast<const float4 *>(p.part_o + (slot * HP + h) * kD + lane * 4);
-                acc[0] += v.x * w; acc[1] += v.y * w; acc[2] += v.z * w; acc[3] += v.w * w;
+#pragma unroll
+            for (int mt = 0; mt < 8; ++mt) {
+                o[nt][mt][0] *= alpha[0]; o[nt][mt][1] *= alpha[1];
+                o[nt][mt][2] *= alpha[0]; o[nt][mt][3] *= alpha[1];
+            }
+            // P rounded to the matmul dtype before PV (…_Us2.h:3062-3063); 8x8 transposes turn
+            // the accumulator layout [tok][head] into the B-operand layout [k=tok][n=head]
+            pb[nt][0] = movmatrix_trans(QTraits<QT>::pack2(pr[0], pr[1]));
+            pb[nt][1] = movmatrix_trans(QTraits<QT>::pack2(pr[2], pr[3]));
+        }
+
+        // ------------------------------ V: O^T += V^T P^T ------------------------------
+        mbar_wait(&full[stage], phase);
+        {
+            const uint32_t vb = stage_u32 + (uint32_t)stage * p.stage_bytes;
+            if (!KVI8) {
+#pragma unroll
+                for (int mt = 0; mt < 8; ++mt) {
+                    const int chunk = (mt & 3) * 2 + v_chk;
+                    const uint32_t addr = vb + (mt >> 2) * (kBS * 128) + v_row * 128 +
+                                          ((chunk ^ (v_row & 7)) << 4);
+                    uint32_t a0, a1, a2, a3;
+                    ldmatrix_x4_trans(a0, a1, a2, a3, addr);
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt)
+                        mma_16816<QT>(o[nt][mt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
+                }
+            } else {
+                // int8 page, transposed 8x8 b16 loads: a register holds V[tok 2tig][d,d+1] and
+                // V[tok 2tig+1][d,d+1] with d = 16*chunk + 2*gid; m-tile row gid <-> d, row
+                // gid+8 <-> d+1 (see o_dim()).
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int chunk = j * 2 + a_chk;
+                    const uint32_t addr = vb + a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
+                    uint32_t r0, r1, r2, r3;
+                    ldmatrix_x4_trans(r0, r1, r2, r3, addr);
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        mma_16816<QT>(o[nt][2 * j], I8Pair<QT, 0, 2>::cvt(r0), I8Pair<QT, 1, 3>::cvt(r0),
+                                      I8Pair<QT, 0, 2>::cvt(r1), I8Pair<QT, 1, 3>::cvt(r1), pb[nt][0], pb[nt][1]);
+                        mma_16816<QT>(o[nt][2 * j + 1], I8Pair<QT, 0, 2>::cvt(r2), I8Pair<QT, 1, 3>::cvt(r2),
+                                      I8Pair<QT, 0, 2>::cvt(r3), I8Pair<QT, 1, 3>::cvt(r3), pb[nt][0], pb[nt][1]);
+                    }
+                }
             }
         }
-        const float inv = (Lsum > 0.f) ? 1.f / Lsum : 0.f;
-        float r[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) r[e] = acc[e] * inv;
-        if (KVI8 && Lsum > 0.f) {
-            // V dequant applied once to the normalised sum: (O + offset_v) * scale_v (…_Us2.h:3655-3670)
-            const unsigned short *sv = reinterpret_cast<const unsigned short *>(p.aq_scale) +
-                                       (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD);
-            const unsigned short *ov = p.aq_offset ? reinterpret_cast<const unsigned short *>(p.aq_offset) +
-                                       (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD) : nullptr;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int d = p.aq_per_tensor ? 0 : lane * 4 + e;
-                const float off = ov ? QTraits<QT>::to_float(ov[d]) : 0.f;
-                r[e] = (r[e] + off) * QTraits<QT>::to_float(sv[d]);
-            }
-        }
-        unsigned short *op = reinterpret_cast<unsigned short *>(p.out) + (size_t)b * p.out_sb +
-                             (size_t)(n2 * p.g + h) * p.out_sh + lane * 4;
-        uint2 pk;
-        pk.x = QTraits<QT>::pack2(r[0], r[1]);
-        pk.y = QTraits<QT>::pack2(r[2], r[3]);
-        *reinterpret_cast<uint2 *>(op) = pk;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[stage]);
+        if (++stage == nstages) { stage = 0; phase ^= 1u; }
     }
+    if (tid == 0)                                                    // post warps: done
+        for (int w = 0; w < kPostWarps; ++w) post_message(mail, mfull, mempty, mi, mph, make_int4(-1, 0, 0, 0), make_int4(0, 0, 0, 0));
 }
 
 }  // namespace spa

@@ -11,7 +11,8 @@ namespace spa {
 constexpr int kD = 128;              // head dim (all reference sparse tests)
 constexpr int kBS = 128;             // tokens per KV page (PAGESIZE, select_position.cpp:7)
 constexpr int kConsumerWarps = 8;    // each owns 16 of the 128 tokens of a page
-constexpr int kThreads = (kConsumerWarps + 1) * 32;   // + 1 TMA producer warp
+constexpr int kPostWarps = 3;         // bookkeeping of partials + combine, off the consumers' path
+constexpr int kThreads = (kConsumerWarps + 1 + kPostWarps) * 32;   // + TMA producer warp + post warps
 constexpr int kSentinel = 0x7fffffff;
 constexpr int kPad = 8;              // x8 replication of the length outputs (add_custom.cpp:963,993)
 constexpr int kMaxGroup = 16;        // q heads per kv head handled by one CTA (2 n8 tiles)
@@ -50,12 +51,13 @@ struct ChainParams {
     int ax_row, ax_head, ax_blk;                         // TMA coordinate slots (1..3)
     int num_blocks;
     // ---- workspace
-    int *union_phys;                                     // [items, maxP]
-    unsigned *union_meta;                                // [items, maxP]  mask | tailmask << 16
-    int *union_len;                                      // [items]
-    int *tail_count;                                     // [items]
-    float *part_o;                                       // [slots, HP, D]
-    float *part_ml;                                      // [slots, HP, 2]
+    unsigned long long *flat;                            // page queue, see queue_entry(); zero = not published
+    unsigned long long *item_info;                       // [items] see item_record(); zero = not published
+    int *item_ppl;                                       // [items] max selected pages over the item's heads
+    int *ctrl;                                           // queue counters, see Ctrl (all zero between launches)
+    int pool_cap;                                        // partial slots available
+    float *part_o;                                       // [pool_cap, HP, D]
+    float *part_ml;                                      // [pool_cap, HP, 2]
     double *exact_scratch;                               // [grid, kConsumerWarps, C] (rare: > 512 near-ties)
     // ---- launch shape
     int sel_gw;                                          // warps per selection group (4 or 8)
@@ -65,19 +67,79 @@ struct ChainParams {
     int stage_bytes;
     int smem_bytes;
     int mode;                                            // see Mode
+    int static_pct;                                      // share of the page queue cut statically, percent
+    int dyn_runs;                                        // the rest is claimed in about this many runs per CTA
+    int list_cap;                                        // partial slots the post warp can list for one item
     // ---- optional phase trace: [gridDim.x, kTraceSlots] globaltimer ns (null = off)
     unsigned long long *trace;
+    int dbg;                                             // trace-only experiments (env SPA_DBG_REPEAT)
 };
-constexpr int kTraceSlots = 16;
+constexpr int kTraceSlots = 32;
 
 enum Mode : int {
     kModeFused = 0,        // scores + topk + select + attention
     kModeAttnOnly = 1,     // union from block_position + attention
 };
 
+// Queue control block (ints).  Every word is zero when a launch starts and is returned to zero by
+// the launch itself (per-item words by the item's combiner, the globals by the last CTA to leave).
+struct Ctrl {
+    enum { kHead = 0, kTail = 1, kItemsDone = 3, kPool = 4, kFinished = 5, kError = 6, kGlobals = 16 };
+    __host__ __device__ static inline int b_done(int b) { return kGlobals + b; }
+    __host__ __device__ static inline int pages_done(int B, int item) { return kGlobals + B + item; }
+    __host__ __device__ static inline int words(int B, int items) { return kGlobals + B + items; }
+};
+
 // ------------------------------------------------------------------------------------------
 // small device helpers
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int ld_acquire(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int *p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Page-queue entry: physical block id in the low word; high word = valid | tail page | item | head mask.
+// Low word: physical block id (24 bits) | (tokens on the page if it is a tail page) - 1 (7 bits).
+constexpr int kMaxBlocks = 1 << 24;
+__host__ __device__ __forceinline__ unsigned long long queue_entry(int phys, unsigned mask16, bool tail, int item, int tail_cnt) {
+    const unsigned hi = 0x80000000u | (tail ? 0x40000000u : 0u) | ((unsigned)item << 16) | (mask16 & 0xffffu);
+    const unsigned lo = ((unsigned)phys & 0xffffffu) | (((unsigned)(tail_cnt - 1) & 0x7fu) << 24);
+    return ((unsigned long long)hi << 32) | lo;
+}
+constexpr int kMaxItems = 1 << 14;
+// Per-item record: valid | tail tokens (8 bits, 1..128) | union pages (24 bits) | queue base (28 bits)
+constexpr int kMaxQueue = 1 << 28;
+__host__ __device__ __forceinline__ unsigned long long item_record(int base, int len, int tail_cnt) {
+    return (1ull << 63) | ((unsigned long long)(tail_cnt & 0xff) << 52) | ((unsigned long long)(len & 0xffffff) << 28) |
+           (unsigned long long)(base & (kMaxQueue - 1));
+}
+__host__ __device__ __forceinline__ int record_base(unsigned long long r) { return (int)(r & (kMaxQueue - 1)); }
+__host__ __device__ __forceinline__ int record_len(unsigned long long r) { return (int)((r >> 28) & 0xffffff); }
+__host__ __device__ __forceinline__ int record_tail(unsigned long long r) { return (int)((r >> 52) & 0xff); }
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ int ld_relaxed(const int *p) {
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
@@ -255,6 +317,20 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 __device__ __forceinline__ void trace_mark(const ChainParams &p, int slot) {
     if (p.trace != nullptr && threadIdx.x == 0) p.trace[(size_t)blockIdx.x * kTraceSlots + slot] = globaltimer_ns();
+}
+
+// any single thread: raw value into a slot of this CTA's trace row
+__device__ __forceinline__ void trace_put(const ChainParams &p, int slot, unsigned long long v) {
+    if (p.trace != nullptr) p.trace[(size_t)blockIdx.x * kTraceSlots + slot] = v;
+}
+
+// fine-grained probe: SM clock of thread 0 (slots 16..31)
+__device__ __forceinline__ void trace_clk(const ChainParams &p, int slot) {
+    if (p.trace != nullptr && threadIdx.x == 0) {
+        long long c;
+        asm volatile("mov.u64 %0, %%clock64;" : "=l"(c));
+        p.trace[(size_t)blockIdx.x * kTraceSlots + slot] = (unsigned long long)c;
+    }
 }
 
 __device__ __forceinline__ float fast_exp2(float x) {

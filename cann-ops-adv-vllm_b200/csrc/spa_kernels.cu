@@ -5,8 +5,10 @@
 //                    sparse_paged_fusion_attention}/*.cpp|*.h
 // and the host "ophost" layer (op defs, tiling, aclnn wrappers) under src/transformer/*/ophost/.
 #include <cooperative_groups.h>
+#include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -28,38 +30,39 @@ __device__ __forceinline__ unsigned char *aligned_smem(unsigned char *raw) {
     return reinterpret_cast<unsigned char *>((a + 1023) & ~static_cast<uintptr_t>(1023));
 }
 
-// The whole chain in one persistent cooperative launch (SparsePagedFusionAttention,
+// The whole chain in one persistent launch (SparsePagedFusionAttention,
 // sparse_paged_fusion_attention.cpp:56-76: InitCentSelect -> ProcessCentSelect -> SyncAll ->
-// Init/Process attention), or, with mode == kModeAttnOnly, SparsePagedAttention.
+// Init/Process attention), or, with mode == kModeAttnOnly, SparsePagedAttention.  The reference's
+// SyncAll between selection and attention becomes a producer/consumer page queue: CTAs only wait
+// for entries that are not published yet, so the launch is cooperative (co-residency) but has no
+// grid-wide barrier.
 template <typename QT, bool KVI8, int NT>
 __global__ void __launch_bounds__(kThreads, 1)
 spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmC) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = aligned_smem(smem_raw);
-    cg::grid_group grid = cg::this_grid();
 
     trace_mark(p, 0);
-    // ---- phase A: selection (or union building) per (b, kv head)
+    // ---- phase A: selection (or union building) per (b, kv head); every item ends by publishing its
+    // pages into the queue
     if (p.mode == kModeFused)
         select_phase<QT, kSelScores | kSelSelect | kSelUnion>(p, &tmC, smem);
     else
         for (int item = blockIdx.x; item < p.items; item += gridDim.x) union_from_block_position(p, item, smem);
     trace_mark(p, 1);
-    __threadfence();
-    grid.sync();
-    trace_mark(p, 2);
-    if (p.mode == kModeFused)
-        for (int b = blockIdx.x; b < p.B; b += gridDim.x) write_max_ppl(p, b);
-
-    // ---- phase B: stream the selected pages
+    // ---- phase B + C: stream queue runs; the CTA completing an item combines it
     attention_phase<QT, KVI8, NT>(p, &tmK, &tmV, smem);
     trace_mark(p, 3);
-    __threadfence();
-    grid.sync();
-    trace_mark(p, 4);
-    // ---- phase C: combine
-    combine_phase<QT, KVI8, NT>(p, smem);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // the last CTA to leave returns the queue counters to zero for the next launch
+        __threadfence();
+        if (atomicAdd(p.ctrl + Ctrl::kFinished, 1) == (int)gridDim.x - 1) {
+            p.ctrl[Ctrl::kHead] = 0; p.ctrl[Ctrl::kTail] = 0;
+            p.ctrl[Ctrl::kItemsDone] = 0; p.ctrl[Ctrl::kPool] = 0; p.ctrl[Ctrl::kFinished] = 0;
+        }
+    }
     trace_mark(p, 5);
 }
 
@@ -106,7 +109,10 @@ struct spaExecutor {
     int q_bf16, kv_i8, nt_tiles;
     uint64_t ws_bytes;
     // workspace offsets (bytes)
-    uint64_t off_uphys, off_umeta, off_ulen, off_tail, off_po, off_pml, off_xs;
+    uint64_t off_ctrl, off_flat, off_info, off_ippl, off_po, off_pml, off_xs;
+    uint64_t ctrl_bytes;
+    int persistent_ws;     // see spaExecutorSetPersistentWorkspace
+    void *clean_ws;        // workspace whose queue words are known to be zero
     int launches;
 };
 
@@ -353,9 +359,16 @@ int spaGetCompiledArch(void) { return 100; }
 int spaDestroyExecutor(spaExecutor *e) { delete e; return SPA_OK; }
 int spaExecutorNumLaunches(const spaExecutor *e) { return e ? e->launches : 0; }
 int spaExecutorGridSize(const spaExecutor *e) { return e ? e->grid : 0; }
+int spaExecutorSetPersistentWorkspace(spaExecutor *e, int enable) {
+    if (!e) return fail(SPA_ERR_ARG, "bad executor");
+    e->persistent_ws = enable ? 1 : 0;
+    e->clean_ws = nullptr;
+    return SPA_OK;
+}
 int spaExecutorSetTrace(spaExecutor *e, void *deviceBuffer) {
     if (!e) return fail(SPA_ERR_ARG, "bad executor");
     e->p.trace = (unsigned long long *)deviceBuffer;
+    e->p.dbg = getenv("SPA_DBG_REPEAT") ? 1 : 0;
     return SPA_OK;
 }
 
@@ -618,21 +631,30 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     p.q = query->data;
     p.scale_log2 = (float)scaleValue * kLog2e;
     p.items = p.B * p.Nkv;
-    if (p.items > 8192) return fail(SPA_ERR_UNSUPPORTED, "B*Nkv = %d > 8192 work items", p.items);
+    if (p.items > kMaxItems) return fail(SPA_ERR_UNSUPPORTED, "B*Nkv = %d > %d work items", p.items, kMaxItems);
 
     // ---- launch shape
     DevInfo d;
     if ((rc = dev_info(&d))) return rc;
     if (!d.coop) return fail(SPA_ERR_CUDA, "device lacks cooperative launch");
     e->nt_tiles = (p.g + 7) / 8;
+    // ---- scheduling of the page queue (spa_attn.cuh): static share + short claimed runs
+    p.static_pct = 50; p.dyn_runs = 3;                  // measured on c2 (B200): 0.1175 ms; 85/3: 0.1246, 0/6: 0.1200
+    if (const char *s = getenv("SPA_STATIC_PCT")) p.static_pct = std::min(100, std::max(0, atoi(s)));
+    if (const char *s = getenv("SPA_DYN_RUNS")) p.dyn_runs = std::max(1, atoi(s));
+    // Partials: one per (run, item) pair met by a CTA: <= 1 static + (dyn_runs + 1) claimed runs per CTA
+    // (+1: rounding of the run length), plus one per item boundary inside a run.
+    p.pool_cap = d.sms * (p.dyn_runs + 3) + p.items + 64;
+    p.list_cap = d.sms * (p.dyn_runs + 3) + 8;            // an item cannot have more partials than there are runs
+    if (p.num_blocks > kMaxBlocks) return fail(SPA_ERR_UNSUPPORTED, "more than %d KV blocks", kMaxBlocks);
     p.stage_bytes = e->kv_i8 ? 16384 : 32768;
-    const int budget = d.smem_optin - 1024;
+    const int budget = d.smem_optin - 1024 - 512;     // 1 KiB alignment slack + the kernels' static shared memory
     int nst = e->kv_i8 ? 12 : 6;
     for (; nst >= 2; --nst)
-        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.items).total <= budget) break;
+        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.list_cap).total <= budget) break;
     if (nst < 2) return fail(SPA_ERR_UNSUPPORTED, "attention working set exceeds shared memory");
     p.nstages = nst;
-    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.items).total;
+    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.list_cap).total;
     int sel_bytes = p.maxP * 4;
     if (p.mode == kModeFused) {
         if ((rc = plan_select_smem(&p, kSelScores | kSelSelect | kSelUnion, d.sms, budget - 1024, &sel_bytes))) return rc;
@@ -649,13 +671,16 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     // ---- workspace
     const int HP = e->nt_tiles * 8;
     uint64_t o = 0;
-    e->off_uphys = o; o = align_up(o + (uint64_t)p.items * p.maxP * 4, 256);
-    e->off_umeta = o; o = align_up(o + (uint64_t)p.items * p.maxP * 4, 256);
-    e->off_ulen = o;  o = align_up(o + (uint64_t)p.items * 4, 256);
-    e->off_tail = o;  o = align_up(o + (uint64_t)p.items * 4, 256);
-    const uint64_t slots = (uint64_t)p.items + e->grid;
-    e->off_po = o;    o = align_up(o + slots * HP * kD * 4, 256);
-    e->off_pml = o;   o = align_up(o + slots * HP * 2 * 4, 256);
+    // queue words that must be zero when a launch starts (the launch leaves them zero again)
+    const uint64_t qcap = (uint64_t)p.items * p.maxP * (p.mode == kModeAttnOnly ? 2 : 1);   // x2: split tail entries
+    if (qcap >= (uint64_t)kMaxQueue) return fail(SPA_ERR_UNSUPPORTED, "B*Nkv*maxBlocks = %llu exceeds the page queue", (unsigned long long)qcap);
+    e->off_ctrl = o;   o = align_up(o + (uint64_t)Ctrl::words(p.B, p.items) * 4, 256);
+    e->off_info = o;   o = align_up(o + (uint64_t)p.items * 8, 256);
+    e->off_flat = o;   o = align_up(o + qcap * 8, 256);
+    e->ctrl_bytes = o;
+    e->off_ippl = o;   o = align_up(o + (uint64_t)p.items * 4, 256);
+    e->off_po = o;     o = align_up(o + (uint64_t)p.pool_cap * HP * kD * 4, 256);
+    e->off_pml = o;    o = align_up(o + (uint64_t)p.pool_cap * HP * 2 * 4, 256);
     e->off_xs = o;
     if (p.mode == kModeFused) o = align_up(o + (uint64_t)e->grid * kConsumerWarps * std::max(p.C, 1) * 8, 256);
     e->ws_bytes = o;
@@ -671,15 +696,31 @@ static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaSt
     if (reinterpret_cast<uintptr_t>(workspace) & 255) return fail(SPA_ERR_WORKSPACE, "workspace must be 256-byte aligned");
     ChainParams p = e->p;
     char *w = (char *)workspace;
-    p.union_phys = (int *)(w + e->off_uphys); p.union_meta = (unsigned *)(w + e->off_umeta);
-    p.union_len = (int *)(w + e->off_ulen); p.tail_count = (int *)(w + e->off_tail);
+    p.ctrl = (int *)(w + e->off_ctrl); p.flat = (unsigned long long *)(w + e->off_flat);
+    p.item_info = (unsigned long long *)(w + e->off_info);
+    p.item_ppl = (int *)(w + e->off_ippl);
     p.part_o = (float *)(w + e->off_po); p.part_ml = (float *)(w + e->off_pml);
     p.exact_scratch = (double *)(w + e->off_xs);
     ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
-    void *args[] = {(void *)&p, (void *)&e->tmK, (void *)&e->tmV, (void *)&e->tmC};
-    CUDA_TRY(cudaLaunchCooperativeKernel((const void *)kern, dim3(e->grid), dim3(kThreads), args,
-                                         (size_t)p.smem_bytes, stream));
+    // queue words start at zero and the kernel leaves them at zero again, but the workspace is the
+    // caller's scratch: clear it unless the caller vouches for it (spaExecutorSetPersistentWorkspace)
+    if (!e->persistent_ws || e->clean_ws != workspace) {
+        CUDA_TRY(cudaMemsetAsync(p.ctrl, 0, e->ctrl_bytes, stream));
+        e->clean_ws = e->persistent_ws ? workspace : nullptr;
+    }
+    // One CTA per SM.  No grid-wide barrier: CTAs only wait for queue entries other CTAs publish after
+    // their selection, which never depends on the waiter, so an ordinary launch is enough (a CTA that is
+    // scheduled late only delays the others).  SPA_COOP=1 forces a cooperative launch.
+    static const bool coop = getenv("SPA_COOP") != nullptr;
+    if (coop) {
+        void *args[] = {(void *)&p, (void *)&e->tmK, (void *)&e->tmV, (void *)&e->tmC};
+        CUDA_TRY(cudaLaunchCooperativeKernel((const void *)kern, dim3(e->grid), dim3(kThreads), args,
+                                             (size_t)p.smem_bytes, stream));
+    } else {
+        kern<<<e->grid, kThreads, p.smem_bytes, stream>>>(p, e->tmK, e->tmV, e->tmC);
+        CUDA_TRY(cudaGetLastError());
+    }
     return SPA_OK;
 }
 

@@ -91,7 +91,7 @@ struct SelSmem {
         total = (o + 127) & ~127;
     }
 };
-// misc words: [0..7] per-warp max|cent|, [8] truncation flag, [9] union total
+// misc words: [0..7] per-warp max|cent|, [8] truncation flag, [9] union total, [10] queue base of the union
 
 __device__ __forceinline__ float key_float(uint32_t key) {      // inverse of float_key()
     return __uint_as_float((key & 0x80000000u) ? (key & 0x7fffffffu) : ~key);
@@ -124,16 +124,15 @@ __device__ __forceinline__ void issue_cent_tile(const CUtensorMap *tmC, const Ce
 // S^T[c][h] = cent[c][:] . q[h][:]  per 128-row tile: A = 16 clusters x 16 d via ldmatrix from the
 // swizzled tile, B = 16 d x 8 heads from registers.  Also gathers, per head, the key range of the
 // scores and ||q_h||_1, and max|cent| (for the error band).
+// Q fragments of the item's heads as mma B operands (b0 = Q[h][16ks+2t..], b1 = Q[h][16ks+2t+8..]) and
+// ||q_h||_1 -> hd[h].l1.  Issued first thing in an item so the global-load latency overlaps the set-up.
 template <typename QT>
-__device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorMap *tmC, int b, int n2, float *sc,
-                                           int scs, HeadRec *hd, float *misc, const CentRing &R, unsigned &tcount,
-                                           const Grp &G) {
+__device__ __forceinline__ void load_q_frags(const ChainParams &p, int b, int n2, HeadRec *hd, const Grp &G,
+                                             uint32_t (&qf)[2][8][2]) {
     const int lane = lane_id(), gid = lane >> 2, tig = lane & 3;
-    const int g = p.g, C = p.C;
-    const int ntl = (g + 7) >> 3;                      // head tiles (1 or 2)
+    const int g = p.g;
+    const int ntl = (g + 7) >> 3;
     const unsigned short *q = reinterpret_cast<const unsigned short *>(p.q);
-    uint32_t qf[2][8][2];
-    float l1[2] = {0.f, 0.f};
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
         const int h = nt * 8 + gid;
@@ -147,17 +146,42 @@ __device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorM
                 v1 = *reinterpret_cast<const uint32_t *>(qrow + ks * 16 + tig * 2 + 8);
             }
             qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
-            l1[nt] += fabsf(QTraits<QT>::to_float((unsigned short)(v0 & 0xffffu))) + fabsf(QTraits<QT>::to_float((unsigned short)(v0 >> 16))) +
-                      fabsf(QTraits<QT>::to_float((unsigned short)(v1 & 0xffffu))) + fabsf(QTraits<QT>::to_float((unsigned short)(v1 >> 16)));
         }
-        l1[nt] += __shfl_xor_sync(0xffffffffu, l1[nt], 1);
-        l1[nt] += __shfl_xor_sync(0xffffffffu, l1[nt], 2);
-        if (G.warp == 0 && tig == 0 && on) hd[h].l1 = l1[nt];
     }
+}
+template <typename QT>
+__device__ __forceinline__ void q_l1_norms(const ChainParams &p, HeadRec *hd, const Grp &G, const uint32_t (&qf)[2][8][2]) {
+    const int lane = lane_id(), gid = lane >> 2, tig = lane & 3;
+    const int ntl = (p.g + 7) >> 3;
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+        float l1 = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t v0 = qf[nt][ks][0], v1 = qf[nt][ks][1];
+            l1 += fabsf(QTraits<QT>::to_float((unsigned short)(v0 & 0xffffu))) + fabsf(QTraits<QT>::to_float((unsigned short)(v0 >> 16))) +
+                  fabsf(QTraits<QT>::to_float((unsigned short)(v1 & 0xffffu))) + fabsf(QTraits<QT>::to_float((unsigned short)(v1 >> 16)));
+        }
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+        const int h = nt * 8 + gid;
+        if (G.warp == 0 && tig == 0 && nt < ntl && h < p.g) hd[h].l1 = l1;
+    }
+}
+
+template <typename QT>
+__device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorMap *tmC, int b, int n2, float *sc,
+                                           int scs, HeadRec *hd, float *misc, const CentRing &R, unsigned &tcount,
+                                           const Grp &G, const uint32_t (&qf)[2][8][2]) {
+    const int lane = lane_id(), gid = lane >> 2, tig = lane & 3;
+    const int g = p.g, C = p.C;
+    const int ntl = (g + 7) >> 3;                      // head tiles (1 or 2)
+    q_l1_norms<QT>(p, hd, G, qf);
+    trace_clk(p, 20);
     const int ntiles = (C + kCentTileRows - 1) / kCentTileRows;
     const int sub = kConsumerWarps / G.gw;             // 16-row slabs per warp per tile
     unsigned kmn[2][2] = {{0xffffffffu, 0xffffffffu}, {0xffffffffu, 0xffffffffu}}, kmx[2][2] = {{0u, 0u}, {0u, 0u}};
-    uint32_t mx = 0u;
+    uint32_t mx4[4] = {0u, 0u, 0u, 0u};
     const uint32_t ring_u32 = smem_u32(R.base);
     const int a_chk = lane >> 4;
 #pragma unroll 1
@@ -166,23 +190,36 @@ __device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorM
         const int s = (int)(tc % (unsigned)R.ns);
         const unsigned par = (tc / (unsigned)R.ns) & 1u;
         mbar_wait(&R.full[s], par);
+        if (t == 0) trace_clk(p, 21);
 #pragma unroll 1
         for (int mi = 0; mi < sub; ++mi) {
             const int t0 = (G.warp + mi * G.gw) * 16;
             const int a_row = t0 + (lane & 15);
-            float acc[2][4];
+            float acc[2][4], acd[2][4];            // even / odd k-steps: two independent mma chains
 #pragma unroll
-            for (int nt = 0; nt < 2; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+            for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) { acc[nt][r] = 0.f; acd[nt][r] = 0.f; }
             const uint32_t rowaddr = ring_u32 + (uint32_t)s * kCentTileBytes + a_row * 128;
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks) {
                 const int chunk = (ks & 3) * 2 + a_chk;
                 uint32_t a0, a1, a2, a3;
                 ldmatrix_x4(a0, a1, a2, a3, rowaddr + (ks >> 2) * (kCentTileRows * 128) + ((chunk ^ (a_row & 7)) << 4));
-                mx = absmax2<QT>(absmax2<QT>(absmax2<QT>(absmax2<QT>(mx, a0), a1), a2), a3);
-                mma_16816<QT>(acc[0], a0, a1, a2, a3, qf[0][ks][0], qf[0][ks][1]);
-                if (ntl > 1) mma_16816<QT>(acc[1], a0, a1, a2, a3, qf[1][ks][0], qf[1][ks][1]);
+                mx4[0] = absmax2<QT>(mx4[0], a0); mx4[1] = absmax2<QT>(mx4[1], a1);
+                mx4[2] = absmax2<QT>(mx4[2], a2); mx4[3] = absmax2<QT>(mx4[3], a3);
+                if (ks & 1) {
+                    mma_16816<QT>(acd[0], a0, a1, a2, a3, qf[0][ks][0], qf[0][ks][1]);
+                    if (ntl > 1) mma_16816<QT>(acd[1], a0, a1, a2, a3, qf[1][ks][0], qf[1][ks][1]);
+                } else {
+                    mma_16816<QT>(acc[0], a0, a1, a2, a3, qf[0][ks][0], qf[0][ks][1]);
+                    if (ntl > 1) mma_16816<QT>(acc[1], a0, a1, a2, a3, qf[1][ks][0], qf[1][ks][1]);
+                }
             }
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) acc[nt][r] += acd[nt][r];
             const int r0 = t * kCentTileRows + t0 + gid, r1 = r0 + 8;
 #pragma unroll
             for (int nt = 0; nt < 2; ++nt) {
@@ -212,6 +249,7 @@ __device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorM
         }
     }
     tcount += (unsigned)ntiles;
+    trace_clk(p, 22);
     // key range per head: reduce over the 8 row-lanes, one shared atomic per (warp, head)
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt)
@@ -226,10 +264,12 @@ __device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorM
             const int h = nt * 8 + tig * 2 + e;
             if (gid == 0 && nt < ntl && h < g && lo <= hi) { atomicMin(&hd[h].kmin, lo); atomicMax(&hd[h].kmax, hi); }
         }
+    const uint32_t mx = absmax2<QT>(absmax2<QT>(mx4[0], mx4[1]), absmax2<QT>(mx4[2], mx4[3]));
     float m = fmaxf(QTraits<QT>::to_float((unsigned short)(mx & 0xffffu)), QTraits<QT>::to_float((unsigned short)(mx >> 16)));
 #pragma unroll
     for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     if (lane == 0) misc[G.warp] = m;
+    trace_clk(p, 23);
 }
 
 // exact partial dot of this lane's 4 head-dim elements (d = 4*lane .. 4*lane+3)
@@ -297,9 +337,10 @@ __device__ __forceinline__ void topk_bin(const ChainParams &p, const unsigned *h
     // level 1: lane covers bins [32 lane, 32 lane + 32); suffix sums from the top
     int s = 0;
     {
+        // rotated start: lanes of a quarter-warp hit 8 different 16-byte bank groups (stride is 128 B)
         const uint4 *hv = reinterpret_cast<const uint4 *>(hh + lane * 32);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { const uint4 v = hv[i]; s += v.x + v.y + v.z + v.w; }
+        for (int i = 0; i < 8; ++i) { const uint4 v = hv[(i + lane) & 7]; s += v.x + v.y + v.z + v.w; }
     }
     int suf = s;
 #pragma unroll
@@ -337,11 +378,22 @@ __device__ __forceinline__ void topk_classify(const ChainParams &p, const float 
     for (int h = 0; h < p.g; ++h) {
         const float lo_val = hd[h].lo_val, hi_val = hd[h].hi_val, band = hd[h].band;
         const float *row = sc + h * scs;
+        // a warp iteration covers one aligned 32-cluster chunk = one bitmap word: ballots, no per-lane atomics
+        const int lane = lane_id();
 #pragma unroll 2
-        for (int c = G.tid; c < p.C; c += G.gt) {
-            const float a = row[c];
-            if (a - band >= hi_val) atomicOr(&bitmap[h * bw + (c >> 5)], 1u << (c & 31));
-            else if (a + band >= lo_val) cand[(size_t)h * p.C + atomicAdd(&hd[h].ncand, 1)] = (unsigned short)c;
+        for (int c0 = G.warp * 32; c0 < p.C; c0 += G.gt) {
+            const int c = c0 + lane;
+            const float a = (c < p.C) ? row[c] : -INFINITY;
+            const bool in = (c < p.C) && (a - band >= hi_val);
+            const bool cd = (c < p.C) && !in && (a + band >= lo_val);
+            const unsigned bin = __ballot_sync(0xffffffffu, in), bcd = __ballot_sync(0xffffffffu, cd);
+            if (lane == 0) bitmap[h * bw + (c0 >> 5)] = bin;
+            if (bcd) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&hd[h].ncand, __popc(bcd));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (cd) cand[(size_t)h * p.C + base + __popc(bcd & ((1u << lane) - 1u))] = (unsigned short)c;
+            }
         }
     }
 }
@@ -461,26 +513,77 @@ __device__ __noinline__ int warp_compact_bit(unsigned *pm, int pl, int bit, int 
     return cnt;
 }
 
+// ---- publishing an item's union pages into the global page queue --------------------------------
+// Entries of one item are contiguous, [base, base + len).  Every entry and the item record are single
+// 64-bit stores that are non-zero once written, and a reader needs nothing else, so no ordering
+// between them is required: consumers poll the word they need (spa_attn.cuh, take_entry).
+__device__ __forceinline__ int queue_reserve(const ChainParams &p, int item, int len, int tail_cnt) {
+    if (len <= 0) return 0;
+    const int base = atomicAdd(p.ctrl + Ctrl::kTail, len);
+    st_relaxed_u64(p.item_info + item, item_record(base, len, tail_cnt));
+    return base;
+}
+// One thread, ordered after the item's reservation (same thread or a barrier): the item is complete.
+// "all items done" tells the consumers that the queue tail is final.
+__device__ __forceinline__ void queue_item_done(const ChainParams &p) {
+    __threadfence();
+    atomicAdd(p.ctrl + Ctrl::kItemsDone, 1);
+}
+// attention_out rows of an item without any page (seq 0 / nothing selected): zeros, as the combine of
+// an empty sum gives.  nthreads threads, tid in [0, nthreads).
+__device__ __forceinline__ void zero_item_output(const ChainParams &p, int b, int n2, int tid, int nthreads) {
+    for (int i = tid; i < p.g * (kD / 4); i += nthreads) {
+        const int h = i / (kD / 4), d4 = i % (kD / 4);
+        unsigned short *op = reinterpret_cast<unsigned short *>(p.out) + (size_t)b * p.out_sb +
+                             (size_t)(n2 * p.g + h) * p.out_sh + d4 * 4;
+        *reinterpret_cast<uint2 *>(op) = make_uint2(0u, 0u);
+    }
+}
+// max_page_position_length[b] once the last kv head of b has reported (one thread; cent_select.cpp:123-160)
+__device__ __forceinline__ void report_item_ppl(const ChainParams &p, int b, int item, int m, bool fenced = false) {
+    if (!fenced) { p.item_ppl[item] = m; __threadfence(); }
+    int *cnt = p.ctrl + Ctrl::b_done(b);
+    if (atomicAdd(cnt, 1) == p.Nkv - 1) {
+        __threadfence();
+        int mx = 0;
+        for (int n2 = 0; n2 < p.Nkv; ++n2) mx = max(mx, __ldcg(p.item_ppl + (size_t)b * p.Nkv + n2));
+        if (p.max_ppl)
+            for (int j = 0; j < kPad; ++j) p.max_ppl[(size_t)b * kPad + j] = (long long)mx * p.bs;
+        *cnt = 0;
+    }
+}
+
 // Union list of one item (one warp, serial over chunks).  pm[i] = head mask | tail mask << 16 for
-// logical page i; emits the ascending pages with a non-zero mask: physical block id + meta word.
-__device__ __noinline__ void warp_emit_union(const ChainParams &p, int item, const int *phys, const unsigned *pm, int pl) {
+// logical page i; queues the ascending pages with a non-zero mask.  A queue entry has ONE tail flag:
+// a page that is the tail page of some heads and a full page of others (possible only with per-head
+// block_position lists) is queued twice, once per head subset.  Returns the number of entries.
+__device__ __noinline__ int warp_emit_union(const ChainParams &p, int item, const int *phys, const unsigned *pm, int pl,
+                                            int tail_cnt) {
     const int lane = lane_id();
-    int *uphys = p.union_phys + (size_t)item * p.maxP;
-    unsigned *umeta = p.union_meta + (size_t)item * p.maxP;
+    const unsigned lt = (1u << lane) - 1u;
+    int len = 0;
+    for (int i0 = 0; i0 < pl; i0 += 32) {
+        const int i = i0 + lane;
+        const unsigned m = (i < pl) ? pm[i] : 0u;
+        const unsigned mt = (m >> 16) & m & 0xffffu, mf = m & 0xffffu & ~mt;
+        len += __popc(__ballot_sync(0xffffffffu, mf != 0u)) + __popc(__ballot_sync(0xffffffffu, mt != 0u));
+    }
+    int qbase = 0;
+    if (lane == 0) qbase = queue_reserve(p, item, len, tail_cnt);
+    qbase = __shfl_sync(0xffffffffu, qbase, 0);
     int base = 0;
     for (int i0 = 0; i0 < pl; i0 += 32) {
-        int i = i0 + lane;
-        unsigned m = (i < pl) ? pm[i] : 0u;
-        bool on = (m & 0xffffu) != 0u;
-        unsigned bal = __ballot_sync(0xffffffffu, on);
-        if (on) {
-            int pos = base + __popc(bal & ((1u << lane) - 1u));
-            uphys[pos] = phys[i];
-            umeta[pos] = m;
-        }
-        base += __popc(bal);
+        const int i = i0 + lane;
+        const unsigned m = (i < pl) ? pm[i] : 0u;
+        const unsigned mt = (m >> 16) & m & 0xffffu, mf = m & 0xffffu & ~mt;
+        const unsigned bf = __ballot_sync(0xffffffffu, mf != 0u), bt = __ballot_sync(0xffffffffu, mt != 0u);
+        if (mf) st_relaxed_u64(p.flat + (size_t)qbase + base + __popc(bf & lt), queue_entry(phys[i], mf, false, item, kBS));
+        if (mt) st_relaxed_u64(p.flat + (size_t)qbase + base + __popc(bf) + __popc(bt & lt), queue_entry(phys[i], mt, true, item, max(1, tail_cnt)));
+        base += __popc(bf) + __popc(bt);
     }
-    if (lane == 0) p.union_len[item] = base;
+    __syncwarp();
+    if (lane == 0) queue_item_done(p);
+    return len;
 }
 
 // ---- phase A for one item: fused op / cent_select / compute_cent / select_position ------------
@@ -509,17 +612,18 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     int *miscI = reinterpret_cast<int *>(smem + L.misc);
 
     // ---- S0: start everything asynchronous, initialise the per-item state
+    trace_clk(p, 16);
     int seq = 0, pl = 0, rem = 0;
     bool has_tail = false;
     const int *bid = nullptr;
+    uint32_t qf[2][8][2];
+    if (DS) load_q_frags<QT>(p, b, n2, hd, G, qf);                // in flight across the whole set-up
     if (DP) {
-        seq = p.seq_len[b];
-        pl = max(0, min((seq + p.bs - 1) / p.bs, p.maxP));
-        rem = (pl > 0) ? seq - (pl - 1) * p.bs : 0;               // tokens on the last page
-        has_tail = (pl > 0) && (rem < p.bs);
+        seq = p.seq_len[b];                                       // first used after the block_table wait
         const int *bt = p.block_table + (size_t)b * p.bt_stride;
         bid = p.block_ids + (size_t)n2 * p.bid_stride;
-        for (int i = G.tid; i < pl; i += G.gt) cp_async_4(&physS[i], bt + i);     // block_table row -> smem
+        // whole block_table row -> smem (not just the pages of seq: no dependent load in front of the copy)
+        for (int i = G.tid; i < p.maxP; i += G.gt) cp_async_4(&physS[i], bt + i);
     }
     if (DS) {
         if (G.tid == 0) {
@@ -532,7 +636,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
         for (int i = G.tid; i < g * (kSelBins / 4); i += G.gt) hz[i] = make_uint4(0u, 0u, 0u, 0u);
         for (int i = G.tid; i < g * L.bw; i += G.gt) bitmap[i] = 0u;
     }
-    if (G.tid == 0) { miscI[8] = 0; miscI[9] = 0; }
+    if (G.tid == 0) { miscI[8] = 0; miscI[9] = 0; miscI[10] = 0; }
     if (DP && p.page_position != nullptr) {
         // pad first: the real positions overwrite the head of each row later (ordered by the barriers)
         int *base = p.page_position + ((size_t)b * p.Nq + hq0) * p.MP;
@@ -544,18 +648,24 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             for (int i = G.tid; i < total; i += G.gt) base[i] = kSentinel;
         }
     }
+    trace_clk(p, 17);
     if (DP) cp_async_wait_all();
     grp_sync(G);
+    trace_clk(p, 18);
     if (DP) {
+        pl = max(0, min((seq + p.bs - 1) / p.bs, p.maxP));
+        rem = (pl > 0) ? seq - (pl - 1) * p.bs : 0;               // tokens on the last page
+        has_tail = (pl > 0) && (rem < p.bs);
         // c[i] = block_ids[n2, block_table[b, i]] (select_position.cpp:97-115), asynchronously into smem;
         // the table value is clamped as the golden does (tests/utils.py:62)
         for (int i = G.tid; i < pl; i += G.gt) cp_async_4(&cS[i], bid + max(0, min(physS[i], p.kvPageLen - 1)));
     }
+    trace_clk(p, 19);
     trace_mark(p, 8);
 
     const unsigned short *q = reinterpret_cast<const unsigned short *>(p.q);
     if (DS) {
-        score_item<QT>(p, tmC, b, n2, sc, L.scs, hd, misc, R, tcount, G);
+        score_item<QT>(p, tmC, b, n2, sc, L.scs, hd, misc, R, tcount, G, qf);
         grp_sync(G);
         trace_mark(p, 9);
         float maxabs = 0.f;
@@ -580,6 +690,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
                 emit_sorted<QT>(p, qrow, cent_rows, bitmap + h * L.bw, L.bw, selS + h * k, xs + h * kXCap, gscratch,
                                 p.indices_out + ((size_t)b * p.Nq + hq0 + h) * k);
         }
+        trace_clk(p, 24);
         trace_mark(p, 13);
     } else if (DP) {
         // indices are given (select_position op): arbitrary values, duplicates allowed
@@ -590,6 +701,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     if (!DP) { grp_sync(G); return; }
     cp_async_wait_all();
     grp_sync(G);
+    trace_clk(p, 25);
 
     // ---- membership mask per logical page (select_position.cpp:122-183; tests/utils.py:57-80)
 #pragma unroll 1
@@ -598,8 +710,10 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
         unsigned m = 0u;
         if (DS) {
             if (c >= 0 && c < C) {
-#pragma unroll 1
-                for (int h = 0; h < g; ++h) m |= ((bitmap[h * L.bw + (c >> 5)] >> (c & 31)) & 1u) << h;
+                const unsigned *bw = bitmap + (c >> 5);
+                const int sh = c & 31;
+#pragma unroll 4
+                for (int h = 0; h < g; ++h) m |= ((bw[h * L.bw] >> sh) & 1u) << h;
             }
         } else {
 #pragma unroll 1
@@ -617,6 +731,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     if (FLAGS & kSelGather)
         for (int i = pl + G.tid; i < p.maxP; i += G.gt)
             for (int h = 0; h < g; ++h) p.bt_gather[((size_t)b * p.Nq + hq0 + h) * p.maxP + i] = 0;
+    trace_clk(p, 26);
     grp_sync(G);
     trace_mark(p, 14);
 
@@ -624,6 +739,8 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     // pass 1: per 32-page chunk, the number of set bits of every head plane (and of the union)
     const int nch = (pl + 31) >> 5;
     const unsigned lt = (1u << lane) - 1u;
+    const bool may_trunc = pl > p.MP;
+    const int tail_cnt = has_tail ? rem : p.bs;
 #pragma unroll 1
     for (int ch = G.warp; ch < nch; ch += G.gw) {
         const int i = ch * 32 + lane;
@@ -637,11 +754,12 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
         }
         if (lane <= g) cnt[ch * KG1 + lane] = mine;
     }
+    trace_clk(p, 27);
     grp_sync(G);
     // exclusive prefix over chunks, one column (head / union) at a time; lanes = chunks
-    if (G.warp == 0) {
+    {
 #pragma unroll 1
-        for (int col = 0; col <= g; ++col) {
+        for (int col = G.warp; col <= g; col += G.gw) {
             int run = 0;
             for (int c0 = 0; c0 < nch; c0 += 32) {
                 const int ch = c0 + lane;
@@ -657,16 +775,26 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             }
             if (lane == 0) {
                 if (col < g) { hd[col].total = min(run, p.MP); if (run > p.MP) miscI[8] = 1; }
-                else miscI[9] = run;
+                else {
+                    miscI[9] = run;
+                    // no head can overflow max_page_num when the sequence has no more pages than that:
+                    // reserve the queue range now, under the other columns' scans
+                    if ((FLAGS & kSelUnion) && !may_trunc) miscI[10] = queue_reserve(p, item, run, tail_cnt);
+                }
             }
         }
     }
+    trace_clk(p, 28);
     grp_sync(G);
     int *pp0 = p.page_position ? p.page_position + ((size_t)b * p.Nq + hq0) * p.MP : nullptr;
     if (miscI[8] == 0) {
+        if ((FLAGS & kSelUnion) && may_trunc) {
+            if (G.tid == 0) miscI[10] = queue_reserve(p, item, miscI[9], tail_cnt);
+            grp_sync(G);
+        }
         // pass 2: scatter
-        int *uphys = p.union_phys + (size_t)item * p.maxP;
-        unsigned *umeta = p.union_meta + (size_t)item * p.maxP;
+        const int ulen = miscI[9];
+        unsigned long long *qent = p.flat + miscI[10];
 #pragma unroll 1
         for (int ch = G.warp; ch < nch; ch += G.gw) {
             const int i = ch * 32 + lane;
@@ -680,19 +808,23 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             if (FLAGS & kSelUnion) {
                 const bool on = (m & 0xffffu) != 0u;
                 const unsigned bal = __ballot_sync(0xffffffffu, on);
-                if (on) {
-                    const int pos = cnt[ch * KG1 + g] + __popc(bal & lt);
-                    uphys[pos] = physS[i];
-                    umeta[pos] = m;
-                }
+                if (on) st_relaxed_u64(qent + cnt[ch * KG1 + g] + __popc(bal & lt), queue_entry(physS[i], m, (m >> 16) != 0u, item, max(1, tail_cnt)));
             }
         }
+        trace_clk(p, 29);
         if (p.page_position_length)
             for (int i = G.tid; i < g * kPad; i += G.gt)
                 p.page_position_length[((size_t)b * p.Nq + hq0) * kPad + i] = hd[i / kPad].total;
-        if ((FLAGS & kSelUnion) && G.tid == 0) {
-            p.union_len[item] = miscI[9];
-            p.tail_count[item] = has_tail ? rem : p.bs;
+        if (FLAGS & kSelUnion) {
+            if (ulen == 0) zero_item_output(p, b, n2, G.tid, G.gt);
+            grp_sync(G);
+            if (G.tid == 0) {
+                int m = 0;
+                for (int h = 0; h < g; ++h) m = max(m, hd[h].total);
+                p.item_ppl[item] = m;
+                queue_item_done(p);                        // its fence also covers item_ppl
+                report_item_ppl(p, b, item, m, true);
+            }
         }
     } else {
         // a head selected more than max_page_num pages: serial path that truncates consistently
@@ -700,15 +832,22 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             const int c = warp_compact_bit(pm, pl, h, pp0 ? pp0 + (size_t)h * p.MP : nullptr, p.MP);
             if (p.page_position_length && lane < kPad)
                 p.page_position_length[((size_t)b * p.Nq + hq0 + h) * kPad + lane] = c;
+            if (lane == 0) hd[h].total = c;
         }
         if (FLAGS & kSelUnion) {
             grp_sync(G);
             if (G.warp == 0) {
-                warp_emit_union(p, item, physS, pm, pl);
-                if (lane == 0) p.tail_count[item] = has_tail ? rem : p.bs;
+                const int ulen = warp_emit_union(p, item, physS, pm, pl, tail_cnt);
+                if (ulen == 0) zero_item_output(p, b, n2, lane, 32);
+                if (lane == 0) {
+                    int m = 0;
+                    for (int h = 0; h < g; ++h) m = max(m, hd[h].total);
+                    report_item_ppl(p, b, item, m);
+                }
             }
         }
     }
+    trace_clk(p, 30);
     trace_mark(p, 15);
     grp_sync(G);
 }
@@ -750,8 +889,9 @@ __device__ inline void union_from_block_position(const ChainParams &p, int item,
     }
     __syncthreads();
     if (warp_id() == 0) {
-        warp_emit_union(p, item, p.block_table + (size_t)b * p.bt_stride, pm, p.maxP);
-        if (lane_id() == 0) p.tail_count[item] = (tail_slot >= 0) ? (int)(actual % p.bs) : p.bs;
+        const int ulen = warp_emit_union(p, item, p.block_table + (size_t)b * p.bt_stride, pm, p.maxP,
+                                         (tail_slot >= 0) ? (int)(actual % p.bs) : p.bs);
+        if (ulen == 0) zero_item_output(p, b, n2, lane_id(), 32);
     }
     __syncthreads();
 }

@@ -191,7 +191,7 @@ class FusedDecodePlan:
     def trace_phases(self) -> torch.Tensor:
         """Run one traced launch; returns int64 [grid, 16] of per-CTA %globaltimer ns at the phase
         boundaries (include/spa_b200.h: spaExecutorSetTrace)."""
-        buf = torch.zeros(self.grid_size, 16, dtype=torch.int64, device=self.attention_out.device)
+        buf = torch.zeros(self.grid_size, 32, dtype=torch.int64, device=self.attention_out.device)
         self._plan.set_trace(buf)
         try:
             custom_ops_lib.launch_fusion_plan(self._plan)

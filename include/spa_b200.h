@@ -69,12 +69,20 @@ SPA_API int spaGetCompiledArch(void);
 SPA_API int spaExecutorNumLaunches(const spaExecutor *executor);
 /* Profiling hook (the reference has device printf macros gated by V5_SPARSE_DEBUG_ENABLE,
  * sparse_paged_attention_split_Bbn2s2_Us2.h:28-36): when set, every CTA of the chain kernel stores
- * %globaltimer (ns) at its phase boundaries into deviceBuffer[grid][16] (uint64; 8..15 = stages of
- * the CTA's last selection item):
- * 0 start, 1 selection done, 2 past grid sync, 3 page stream done, 4 past grid sync, 5 combine done.
- * NULL switches it off (default).                                                              */
+ * %globaltimer (ns) at its phase boundaries into deviceBuffer[grid][32] (uint64):
+ * 0 start, 1 selection done, 3 page stream + combine done, 5 exit; 2 = last queue claim,
+ * 4 = pages streamed, 6 = runs, 7 = producer done; 8..15 = stages of the CTA's last selection item;
+ * 16..31 = SM clock probes inside the selection.  NULL switches it off (default).              */
 SPA_API int spaExecutorGridSize(const spaExecutor *executor);
 SPA_API int spaExecutorSetTrace(spaExecutor *executor, void *deviceBuffer);
+
+/* The chain kernels keep a page queue and counters in the first part of the workspace; they must be
+ * zero when a launch starts, and every launch leaves them zero again.  By default the library clears
+ * them before each launch (one cudaMemsetAsync on the stream), because an aclnn-style workspace is
+ * scratch the caller may reuse for anything between calls.  A caller that re-launches one executor on
+ * the SAME workspace and never lets anything else write to it (a decode loop, a captured CUDA graph)
+ * may set this flag: the workspace is then cleared once, on the first launch that sees it.       */
+SPA_API int spaExecutorSetPersistentWorkspace(spaExecutor *executor, int enable);
 
 /* ---- ComputeCent: replaces aclnnComputeCentGetWorkspaceSize / aclnnComputeCent
  *      (misc/aclnn_compute_cent.h; kernel compute_cent/compute_cent.cpp:345).

@@ -31,7 +31,7 @@ def main():
     for _ in range(3):
         plan.launch()
     torch.cuda.synchronize()
-    names = ["A select", "sync1", "B stream", "sync2", "C combine"]
+    spans = [("A select", 0, 1), ("B stream+combine", 1, 3), ("exit", 3, 5)]
     for rep in range(3):
         if not os.environ.get('NOFLUSH'):
             flush()
@@ -39,12 +39,25 @@ def main():
         t0 = t[:, 0].min()
         rel = (t - t0) / 1e3                                     # us
         print(f"[{name}] rep {rep}: kernel span {rel[:, 5].max():.1f} us; start skew {rel[:, 0].max():.1f} us")
-        for i, nm in enumerate(names):
-            d = rel[:, i + 1] - rel[:, i]
-            print(f"   {nm:10s} per-CTA min {d.min():7.1f}  mean {d.mean():7.1f}  max {d.max():7.1f} us | "
-                  f"phase ends at max {rel[:, i + 1].max():7.1f} us")
+        for nm, a, b in spans:
+            d = rel[:, b] - rel[:, a]
+            print(f"   {nm:18s} per-CTA min {d.min():7.1f}  mean {d.mean():7.1f}  max {d.max():7.1f} us | "
+                  f"ends at min {rel[:, b].min():7.1f} max {rel[:, b].max():7.1f} us")
+        order = torch.argsort(rel[:, 3], descending=True)[:6]
+        for c in order.tolist():
+            print(f"      late CTA {c:3d}: A end {rel[c, 1]:6.1f}  last claim {rel[c, 2]:6.1f}  producer exit {rel[c, 7]:6.1f}  "
+                  f"B end {rel[c, 3]:6.1f} us  pages {int(t[c, 4])}  runs {int(t[c, 6])}")
+            if os.environ.get("SPA_DBG_REPEAT"):
+                print(f"           sentinel seen {rel[c, 8]:6.1f}  last flush done {rel[c, 9]:6.1f}  combines(after sentinel) {int(t[c, 10])} "
+                      f"taking {t[c, 11] / 1e3:6.1f} us")
+        print(f"      pages per CTA min {int(t[:, 4].min())} mean {t[:, 4].mean():.1f} max {int(t[:, 4].max())}; "
+              f"runs per CTA mean {t[:, 6].mean():.1f} max {int(t[:, 6].max())}")
+        if rep == 2 and os.environ.get("SPA_SMID"):
+            smid = t[:, 12].long(); pages = t[:, 4].long()
+            idx = torch.argsort(smid)
+            print("      smid:pages " + " ".join(f"{int(smid[i])}:{int(pages[i])}" for i in idx.tolist()))
         if rep == 2:
-            sub = ["gathers issued", "scores(mma)", "grp sync", "topk", "grp sync", "page masks", "compaction", "union"]
+            sub = ["set-up", "scores(mma)", "hist", "bin", "classify", "resolve", "page masks", "compaction"]
             have = t[:, 15] > 0
             prev = t[have, 0]
             for i, nm in enumerate(sub):
@@ -52,7 +65,13 @@ def main():
                 d = (cur - prev) / 1e3
                 print(f"      A.{nm:15s} mean {d.mean():6.2f} max {d.max():6.2f} us (thread 0 of the CTA, last item)")
                 prev = cur
-
+            ck = t[have][:, 16:31]
+            names2 = ["S0 issue+init", "wait bt+sync", "issue bid gather", "q frags+l1", "wait tile0", "tile loop",
+                      "score reductions", "sync..resolve (hist,bin,classify,resolve)", "wait gather+sync", "masks",
+                      "sync+pass1", "sync+prefix", "sync+pass2", "lengths"]
+            for i, nm in enumerate(names2):
+                d = ck[:, i + 1] - ck[:, i]
+                print(f"      clk {nm:45s} mean {d.mean():8.0f} max {d.max():8.0f} cycles")
 
 if __name__ == "__main__":
     main()

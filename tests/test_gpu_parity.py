@@ -414,7 +414,10 @@ def test_torch_ops_namespace_and_plan(ops):
     for _ in range(3):
         plan.launch()
     torch.cuda.synchronize()
-    assert torch.equal(bp2, bp) and torch.equal(mppl2, mppl) and torch.equal(out2, out)
+    # selection is bit-exact; attention_out may differ in the last bits between launches because the
+    # page queue splits the items across CTAs dynamically (different summation order)
+    assert torch.equal(bp2, bp) and torch.equal(mppl2, mppl)
+    torch.testing.assert_close(out2.float(), out.float(), rtol=1e-3, atol=1e-3)
     # CUDA-graph capture of the fused launch
     gr = torch.cuda.CUDAGraph()
     s = torch.cuda.Stream()
@@ -427,4 +430,4 @@ def test_torch_ops_namespace_and_plan(ops):
     out2.zero_()
     gr.replay()
     torch.cuda.synchronize()
-    assert torch.equal(out2, out)
+    torch.testing.assert_close(out2.float(), out.float(), rtol=1e-3, atol=1e-3)
