@@ -68,7 +68,7 @@ struct ChainParams {
     int smem_bytes;
     int mode;                                            // see Mode
     int static_pct;                                      // share of the page queue cut statically, percent
-    int dyn_runs;                                        // the rest is claimed in about this many runs per CTA
+    int dyn_runs, dyn_min;                               // the rest is claimed in ~dyn_runs runs per CTA of >= dyn_min pages
     int list_cap;                                        // partial slots the post warp can list for one item
     // ---- optional phase trace: [gridDim.x, kTraceSlots] globaltimer ns (null = off)
     unsigned long long *trace;

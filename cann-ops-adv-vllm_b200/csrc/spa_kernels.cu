@@ -25,9 +25,11 @@ using namespace spa;
 // =============================================================================================
 // kernels
 // =============================================================================================
+// 1 KiB-aligned start of the dynamic shared memory (TMA 128B-swizzled tiles).  Plain pointer + offset:
+// going through an integer would hide the address space from the compiler, and every access below
+// would become a generic LD/ST/ATOM instead of LDS/STS/ATOMS.
 __device__ __forceinline__ unsigned char *aligned_smem(unsigned char *raw) {
-    uintptr_t a = reinterpret_cast<uintptr_t>(raw);
-    return reinterpret_cast<unsigned char *>((a + 1023) & ~static_cast<uintptr_t>(1023));
+    return raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u);
 }
 
 // The whole chain in one persistent launch (SparsePagedFusionAttention,
@@ -639,13 +641,17 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     if (!d.coop) return fail(SPA_ERR_CUDA, "device lacks cooperative launch");
     e->nt_tiles = (p.g + 7) / 8;
     // ---- scheduling of the page queue (spa_attn.cuh): static share + short claimed runs
-    p.static_pct = 50; p.dyn_runs = 3;                  // measured on c2 (B200): 0.1175 ms; 85/3: 0.1246, 0/6: 0.1200
+    p.static_pct = 50; p.dyn_runs = 3; p.dyn_min = 2;     // measured on c2 (B200): 50/3 0.1175 ms, 85/3 0.1246, 0/6 0.1200
     if (const char *s = getenv("SPA_STATIC_PCT")) p.static_pct = std::min(100, std::max(0, atoi(s)));
     if (const char *s = getenv("SPA_DYN_RUNS")) p.dyn_runs = std::max(1, atoi(s));
-    // Partials: one per (run, item) pair met by a CTA: <= 1 static + (dyn_runs + 1) claimed runs per CTA
-    // (+1: rounding of the run length), plus one per item boundary inside a run.
-    p.pool_cap = d.sms * (p.dyn_runs + 3) + p.items + 64;
-    p.list_cap = d.sms * (p.dyn_runs + 3) + 8;            // an item cannot have more partials than there are runs
+    if (const char *s = getenv("SPA_DYN_MIN")) p.dyn_min = std::max(1, atoi(s));
+    // Partials: one per (run, item) pair met by a CTA: <= 3 static runs per CTA, (dyn_runs + 2) * grid
+    // claimed runs (rounding of the run length; one overshooting claim per CTA), plus one per item
+    // boundary inside a run.
+    const double qmax = (double)p.items * p.maxP * (p.mode == kModeAttnOnly ? 2 : 1);
+    p.pool_cap = (int)std::min<double>((double)d.sms * (p.dyn_runs + 5) + p.items + 64, qmax + d.sms);
+    // partials of ONE item: every run that touches it
+    p.list_cap = std::min(p.pool_cap, d.sms * (p.dyn_runs + 5) + 8);
     if (p.num_blocks > kMaxBlocks) return fail(SPA_ERR_UNSUPPORTED, "more than %d KV blocks", kMaxBlocks);
     p.stage_bytes = e->kv_i8 ? 16384 : 32768;
     const int budget = d.smem_optin - 1024 - 512;     // 1 KiB alignment slack + the kernels' static shared memory

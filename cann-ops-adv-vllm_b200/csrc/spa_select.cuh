@@ -177,7 +177,7 @@ __device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorM
     const int g = p.g, C = p.C;
     const int ntl = (g + 7) >> 3;                      // head tiles (1 or 2)
     q_l1_norms<QT>(p, hd, G, qf);
-    trace_clk(p, 20);
+    trace_clk(p, 18);
     const int ntiles = (C + kCentTileRows - 1) / kCentTileRows;
     const int sub = kConsumerWarps / G.gw;             // 16-row slabs per warp per tile
     unsigned kmn[2][2] = {{0xffffffffu, 0xffffffffu}, {0xffffffffu, 0xffffffffu}}, kmx[2][2] = {{0u, 0u}, {0u, 0u}};
@@ -190,7 +190,6 @@ __device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorM
         const int s = (int)(tc % (unsigned)R.ns);
         const unsigned par = (tc / (unsigned)R.ns) & 1u;
         mbar_wait(&R.full[s], par);
-        if (t == 0) trace_clk(p, 21);
 #pragma unroll 1
         for (int mi = 0; mi < sub; ++mi) {
             const int t0 = (G.warp + mi * G.gw) * 16;
@@ -249,7 +248,7 @@ __device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorM
         }
     }
     tcount += (unsigned)ntiles;
-    trace_clk(p, 22);
+    trace_clk(p, 19);
     // key range per head: reduce over the 8 row-lanes, one shared atomic per (warp, head)
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt)
@@ -269,8 +268,24 @@ __device__ __forceinline__ void score_item(const ChainParams &p, const CUtensorM
 #pragma unroll
     for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     if (lane == 0) misc[G.warp] = m;
-    trace_clk(p, 23);
 }
+
+// Centroid rows for the exact refinement: the shared-memory tiles when the whole table of the kv head
+// is still resident in the group's TMA ring (C <= ns * 128 rows), else global memory (L2).
+struct CentSrc {
+    const uint2 *g;                      // [C][kD/4] rows of this kv head
+    const unsigned char *ring;           // null: not resident
+    int stage0, ns;                      // tile t of the item sits in stage (stage0 + t) % ns
+    // this lane's 4 head-dim elements (d = 4*lane .. 4*lane+3) of row c
+    __device__ __forceinline__ uint2 load(int c, int lane) const {
+        if (ring == nullptr) return __ldg(g + (size_t)c * (kD / 4) + lane);
+        const int t = c / kCentTileRows, r = c % kCentTileRows;
+        const int byte = (lane & 15) * 8;                        // within the 128-byte half row (128B swizzle)
+        const unsigned char *a = ring + (size_t)((stage0 + t) % ns) * kCentTileBytes + (lane >> 4) * (kCentTileBytes / 2) +
+                                 r * 128 + ((((byte >> 4) ^ (r & 7)) << 4) | (byte & 15));
+        return *reinterpret_cast<const uint2 *>(a);
+    }
+};
 
 // exact partial dot of this lane's 4 head-dim elements (d = 4*lane .. 4*lane+3)
 template <typename QT>
@@ -284,7 +299,7 @@ __device__ __forceinline__ double exact_partial(uint2 v, const double (&qd)[4]) 
 
 // exact scores of list[0..n) -> xs[0..n)   (one warp; rows come from L2, 4 in flight)
 template <typename QT>
-__device__ __noinline__ void exact_scores(const uint2 *cent_rows, const unsigned short *qrow, const int *list32,
+__device__ __noinline__ void exact_scores(const CentSrc cent_rows, const unsigned short *qrow, const int *list32,
                                           const unsigned short *list16, int n, double *xs) {
     const int lane = lane_id();
     double qd[4];
@@ -300,7 +315,7 @@ __device__ __noinline__ void exact_scores(const uint2 *cent_rows, const unsigned
         for (int u = 0; u < 4; ++u) {
             const int i = min(i0 + u, n - 1);
             const int c = list32 ? list32[i] : (int)list16[i];
-            v[u] = __ldg(cent_rows + (size_t)c * (kD / 4) + lane);
+            v[u] = cent_rows.load(c, lane);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -320,14 +335,27 @@ __device__ __forceinline__ int key_shift(unsigned kmin, unsigned kmax) {
 }
 __device__ __forceinline__ void topk_hist(const ChainParams &p, const float *sc, int scs, unsigned *hist,
                                           const HeadRec *hd, const Grp &G) {
+    // four heads per pass: four independent load -> key -> atomic chains per thread
 #pragma unroll 1
-    for (int h = 0; h < p.g; ++h) {
-        const unsigned lo = hd[h].kmin;
-        const int shift = key_shift(lo, hd[h].kmax);
-        const float *row = sc + h * scs;
-        unsigned *hh = hist + h * kSelBins;
+    for (int h0 = 0; h0 < p.g; h0 += 4) {
+        unsigned lo[4];
+        int shift[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int h = min(h0 + u, p.g - 1);
+            lo[u] = hd[h].kmin;
+            shift[u] = key_shift(lo[u], hd[h].kmax);
+        }
+        const int nh = min(4, p.g - h0);
 #pragma unroll 2
-        for (int c = G.tid; c < p.C; c += G.gt) atomicAdd(&hh[(float_key(row[c]) - lo) >> shift], 1u);
+        for (int c = G.tid; c < p.C; c += G.gt) {
+            float a[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) a[u] = sc[min(h0 + u, p.g - 1) * scs + c];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (u < nh) atomicAdd(&hist[(h0 + u) * kSelBins + ((float_key(a[u]) - lo[u]) >> shift[u])], 1u);
+        }
     }
 }
 
@@ -374,25 +402,43 @@ __device__ __forceinline__ void topk_bin(const ChainParams &p, const unsigned *h
 // ---- TopK, step 3 (group): certainly selected -> bitmap, near the cut -> candidate list ----------
 __device__ __forceinline__ void topk_classify(const ChainParams &p, const float *sc, int scs, HeadRec *hd,
                                               unsigned *bitmap, int bw, unsigned short *cand, const Grp &G) {
+    const int lane = lane_id();
+    const unsigned lt = (1u << lane) - 1u;
+    // four heads per pass (independent chains).  A warp iteration covers one aligned 32-cluster chunk =
+    // one bitmap word per head: ballots, no per-lane atomics.
 #pragma unroll 1
-    for (int h = 0; h < p.g; ++h) {
-        const float lo_val = hd[h].lo_val, hi_val = hd[h].hi_val, band = hd[h].band;
-        const float *row = sc + h * scs;
-        // a warp iteration covers one aligned 32-cluster chunk = one bitmap word: ballots, no per-lane atomics
-        const int lane = lane_id();
-#pragma unroll 2
+    for (int h0 = 0; h0 < p.g; h0 += 4) {
+        float lo_val[4], hi_val[4], band[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int h = min(h0 + u, p.g - 1);
+            lo_val[u] = hd[h].lo_val; hi_val[u] = hd[h].hi_val; band[u] = hd[h].band;
+        }
+        const int nh = min(4, p.g - h0);
+#pragma unroll 1
         for (int c0 = G.warp * 32; c0 < p.C; c0 += G.gt) {
             const int c = c0 + lane;
-            const float a = (c < p.C) ? row[c] : -INFINITY;
-            const bool in = (c < p.C) && (a - band >= hi_val);
-            const bool cd = (c < p.C) && !in && (a + band >= lo_val);
-            const unsigned bin = __ballot_sync(0xffffffffu, in), bcd = __ballot_sync(0xffffffffu, cd);
-            if (lane == 0) bitmap[h * bw + (c0 >> 5)] = bin;
-            if (bcd) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&hd[h].ncand, __popc(bcd));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (cd) cand[(size_t)h * p.C + base + __popc(bcd & ((1u << lane) - 1u))] = (unsigned short)c;
+            unsigned bin[4], bcd[4];
+            bool cd[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float a = (c < p.C) ? sc[min(h0 + u, p.g - 1) * scs + c] : -INFINITY;
+                const bool in = (c < p.C) && (a - band[u] >= hi_val[u]);
+                cd[u] = (c < p.C) && !in && (a + band[u] >= lo_val[u]);
+                bin[u] = __ballot_sync(0xffffffffu, in);
+                bcd[u] = __ballot_sync(0xffffffffu, cd[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (u >= nh) break;
+                const int h = h0 + u;
+                if (lane == 0) bitmap[h * bw + (c0 >> 5)] = bin[u];
+                if (bcd[u]) {
+                    int base = 0;
+                    if (lane == 0) base = atomicAdd(&hd[h].ncand, __popc(bcd[u]));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (cd[u]) cand[(size_t)h * p.C + base + __popc(bcd[u] & lt)] = (unsigned short)c;
+                }
             }
         }
     }
@@ -400,7 +446,7 @@ __device__ __forceinline__ void topk_classify(const ChainParams &p, const float 
 
 // ---- TopK, step 4 (one warp per head): settle the candidates ------------------------------------
 template <typename QT>
-__device__ __forceinline__ void topk_resolve(const ChainParams &p, const unsigned short *qrow, const uint2 *cent_rows,
+__device__ __forceinline__ void topk_resolve(const ChainParams &p, const unsigned short *qrow, const CentSrc cent_rows,
                                              const float *row, const HeadRec *r, unsigned short *cand,
                                              unsigned *bitmap_h, int bw, double *xs_smem, double *gscratch) {
     const int lane = lane_id();
@@ -455,7 +501,7 @@ __device__ __forceinline__ void topk_resolve(const ChainParams &p, const unsigne
 
 // compute_cent op output: the k selected clusters in (exact score desc, index asc) order  (one warp)
 template <typename QT>
-__device__ __forceinline__ void emit_sorted(const ChainParams &p, const unsigned short *qrow, const uint2 *cent_rows,
+__device__ __forceinline__ void emit_sorted(const ChainParams &p, const unsigned short *qrow, const CentSrc cent_rows,
                                             const unsigned *bitmap_h, int bw, int *sel, double *xs_smem,
                                             double *gscratch, int *out) {
     const int lane = lane_id(), k = p.k;
@@ -648,10 +694,9 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             for (int i = G.tid; i < total; i += G.gt) base[i] = kSentinel;
         }
     }
-    trace_clk(p, 17);
     if (DP) cp_async_wait_all();
     grp_sync(G);
-    trace_clk(p, 18);
+    trace_clk(p, 17);
     if (DP) {
         pl = max(0, min((seq + p.bs - 1) / p.bs, p.maxP));
         rem = (pl > 0) ? seq - (pl - 1) * p.bs : 0;               // tokens on the last page
@@ -660,26 +705,38 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
         // the table value is clamped as the golden does (tests/utils.py:62)
         for (int i = G.tid; i < pl; i += G.gt) cp_async_4(&cS[i], bid + max(0, min(physS[i], p.kvPageLen - 1)));
     }
-    trace_clk(p, 19);
     trace_mark(p, 8);
 
     const unsigned short *q = reinterpret_cast<const unsigned short *>(p.q);
     if (DS) {
         score_item<QT>(p, tmC, b, n2, sc, L.scs, hd, misc, R, tcount, G, qf);
+        trace_clk(p, 20);
         grp_sync(G);
+        trace_clk(p, 21);
         trace_mark(p, 9);
         float maxabs = 0.f;
         for (int w = 0; w < G.gw; ++w) maxabs = fmaxf(maxabs, misc[w]);
         topk_hist(p, sc, L.scs, hist, hd, G);
+        trace_clk(p, 22);
         grp_sync(G);
+        trace_clk(p, 23);
         trace_mark(p, 10);
         for (int h = G.warp; h < g; h += G.gw) topk_bin(p, hist + h * kSelBins, &hd[h], maxabs);
+        trace_clk(p, 24);
         grp_sync(G);
+        trace_clk(p, 25);
         trace_mark(p, 11);
         topk_classify(p, sc, L.scs, hd, bitmap, L.bw, cand, G);
+        trace_clk(p, 26);
         grp_sync(G);
+        trace_clk(p, 27);
         trace_mark(p, 12);
-        const uint2 *cent_rows = reinterpret_cast<const uint2 *>(p.cent) + (size_t)n2 * C * (kD / 4);
+        CentSrc cent_rows;
+        cent_rows.g = reinterpret_cast<const uint2 *>(p.cent) + (size_t)n2 * C * (kD / 4);
+        const int ntl_item = (C + kCentTileRows - 1) / kCentTileRows;
+        cent_rows.ring = (ntl_item <= R.ns) ? R.base : nullptr;
+        cent_rows.ns = R.ns;
+        cent_rows.stage0 = (int)((tcount - (unsigned)ntl_item) % (unsigned)R.ns);   // score_item advanced tcount past this item
         double *gscratch = p.exact_scratch + ((size_t)blockIdx.x * kConsumerWarps + warp_id()) * C;
 #pragma unroll 1
         for (int h = G.warp; h < g; h += G.gw) {
@@ -690,7 +747,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
                 emit_sorted<QT>(p, qrow, cent_rows, bitmap + h * L.bw, L.bw, selS + h * k, xs + h * kXCap, gscratch,
                                 p.indices_out + ((size_t)b * p.Nq + hq0 + h) * k);
         }
-        trace_clk(p, 24);
+        trace_clk(p, 28);
         trace_mark(p, 13);
     } else if (DP) {
         // indices are given (select_position op): arbitrary values, duplicates allowed
@@ -701,7 +758,6 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     if (!DP) { grp_sync(G); return; }
     cp_async_wait_all();
     grp_sync(G);
-    trace_clk(p, 25);
 
     // ---- membership mask per logical page (select_position.cpp:122-183; tests/utils.py:57-80)
 #pragma unroll 1
@@ -731,8 +787,8 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     if (FLAGS & kSelGather)
         for (int i = pl + G.tid; i < p.maxP; i += G.gt)
             for (int h = 0; h < g; ++h) p.bt_gather[((size_t)b * p.Nq + hq0 + h) * p.maxP + i] = 0;
-    trace_clk(p, 26);
     grp_sync(G);
+    trace_clk(p, 29);
     trace_mark(p, 14);
 
     // ---- compaction: per-head ascending page lists + the group's union list, all warps in parallel.
@@ -754,7 +810,6 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
         }
         if (lane <= g) cnt[ch * KG1 + lane] = mine;
     }
-    trace_clk(p, 27);
     grp_sync(G);
     // exclusive prefix over chunks, one column (head / union) at a time; lanes = chunks
     {
@@ -784,7 +839,6 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             }
         }
     }
-    trace_clk(p, 28);
     grp_sync(G);
     int *pp0 = p.page_position ? p.page_position + ((size_t)b * p.Nq + hq0) * p.MP : nullptr;
     if (miscI[8] == 0) {
@@ -811,10 +865,10 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
                 if (on) st_relaxed_u64(qent + cnt[ch * KG1 + g] + __popc(bal & lt), queue_entry(physS[i], m, (m >> 16) != 0u, item, max(1, tail_cnt)));
             }
         }
-        trace_clk(p, 29);
         if (p.page_position_length)
             for (int i = G.tid; i < g * kPad; i += G.gt)
                 p.page_position_length[((size_t)b * p.Nq + hq0) * kPad + i] = hd[i / kPad].total;
+        trace_clk(p, 30);
         if (FLAGS & kSelUnion) {
             if (ulen == 0) zero_item_output(p, b, n2, G.tid, G.gt);
             grp_sync(G);
@@ -847,7 +901,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             }
         }
     }
-    trace_clk(p, 30);
+    trace_clk(p, 31);
     trace_mark(p, 15);
     grp_sync(G);
 }

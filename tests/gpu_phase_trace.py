@@ -65,10 +65,10 @@ def main():
                 d = (cur - prev) / 1e3
                 print(f"      A.{nm:15s} mean {d.mean():6.2f} max {d.max():6.2f} us (thread 0 of the CTA, last item)")
                 prev = cur
-            ck = t[have][:, 16:31]
-            names2 = ["S0 issue+init", "wait bt+sync", "issue bid gather", "q frags+l1", "wait tile0", "tile loop",
-                      "score reductions", "sync..resolve (hist,bin,classify,resolve)", "wait gather+sync", "masks",
-                      "sync+pass1", "sync+prefix", "sync+pass2", "lengths"]
+            ck = t[have][:, 16:32]
+            names2 = ["S0: issue copies, init, wait block_table", "issue block_ids gather, q l1 norms", "centroid tiles (mma)",
+                      "score reductions", "sync", "hist", "sync", "bin", "sync", "classify", "sync", "resolve",
+                      "wait gather, masks, sync", "compaction (pass1, prefix, pass2, lengths)", "publish"]
             for i, nm in enumerate(names2):
                 d = ck[:, i + 1] - ck[:, i]
                 print(f"      clk {nm:45s} mean {d.mean():8.0f} max {d.max():8.0f} cycles")
