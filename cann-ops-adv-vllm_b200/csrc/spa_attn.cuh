@@ -369,8 +369,12 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         // is handed out in short runs, one claim always in flight, which evens out the SMs' speeds.
         int T = 0;
         if (lane == 0) {
-            while (ld_acquire(p.ctrl + Ctrl::kItemsDone) != p.items) __nanosleep(64);
-            T = ld_relaxed(p.ctrl + Ctrl::kTail);
+            for (;;) {
+                unsigned long long w;
+                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p.ctrl + Ctrl::kTail) : "memory");
+                if ((int)(w >> 32) == p.items) { T = (int)(unsigned)w; break; }
+                __nanosleep(40);
+            }
         }
         T = __shfl_sync(0xffffffffu, T, 0);
         const int G = gridDim.x;

@@ -84,7 +84,9 @@ enum Mode : int {
 // Queue control block (ints).  Every word is zero when a launch starts and is returned to zero by
 // the launch itself (per-item words by the item's combiner, the globals by the last CTA to leave).
 struct Ctrl {
-    enum { kHead = 0, kTail = 1, kItemsDone = 3, kPool = 4, kFinished = 5, kError = 6, kGlobals = 16 };
+    // kTail (low) and kItemsDone (high) form one aligned 64-bit word: a single load tells a consumer
+    // whether every item has reported and, if so, the final queue length
+    enum { kHead = 0, kTail = 2, kItemsDone = 3, kPool = 4, kFinished = 5, kError = 6, kGlobals = 16 };
     __host__ __device__ static inline int b_done(int b) { return kGlobals + b; }
     __host__ __device__ static inline int pages_done(int B, int item) { return kGlobals + B + item; }
     __host__ __device__ static inline int words(int B, int items) { return kGlobals + B + items; }
