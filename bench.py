@@ -45,6 +45,9 @@ import torch  # noqa: E402
 
 BS = 128
 D = 128
+# DRAM bytes of one chain-kernel launch from the committed ncu capture (read 541,777,408 + write 6,479,872)
+NCU_TRAFFIC = {"c2": 548257280}
+
 WORKLOADS = {
     # BASELINE.json configs[0..3]
     "c1": dict(B=1, Nq=32, Nkv=8, S=4096, C=64, k=8, q="f16", kv="f16",
@@ -426,7 +429,9 @@ def main():
                        "launch": "cuda graph replay" if graph is not None else "FusedDecodePlan.launch()"},
             "achieved_hbm_gbs_selected_kv": agg[1].item() / (ms_per_step * 1e-3) / 1e9,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC.get(args.workload) if world == 1 else None,
+                         "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch (profiles/r01_ncu_full_c2_summary.txt)" if world == 1 and args.workload in NCU_TRAFFIC else None,
+                         "peak_source": peak_src,
                          "kernel": "spa_chain_kernel (fused: select + flash-decode + combine)",
                          "bytes_alg_per_launch": ab["bytes_alg"], "bytes_kv_union": ab["bytes_kv_union"],
                          "bytes_logical_per_q_head": ab["bytes_logical"], "bytes_dense": ab["bytes_dense"],
