@@ -71,7 +71,9 @@ def qdtype(w):
 # synthetic inputs: generated on the device, seeded; block_table is a per-sequence
 # permutation of distinct physical pages so aliasing does not inflate L2 hits
 # ------------------------------------------------------------------------------------------------
-def make_inputs(w, B, rank, world, device, seed=1234):
+def make_inputs(w, B, rank, world, device, seed=1234, kv_layout="bsnd"):
+    """kv_layout: "bsnd" = vLLM pool [blocks, bs, Nkv, D] (primary, tests/ifa_v5_case.py:608-610);
+    "bnsd" = [blocks, Nkv, bs, D] (the reference's BNSD-paged KAT layout, tests/ifa_v5_case.py:36)."""
     Nq, Nkv, S, C = w["Nq"], w["Nkv"], w["S"], w["C"]
     assert Nkv % world == 0, "KV heads must divide across ranks"
     nkv = Nkv // world
@@ -86,13 +88,14 @@ def make_inputs(w, B, rank, world, device, seed=1234):
     q = torch.rand(B, nq, D, generator=g_rank, device=device).to(qd)
     l1 = torch.rand(nkv, C, D, generator=g_rank, device=device).to(qd)
     block_ids = torch.randint(0, C, (nkv, pages), generator=g_rank, device=device, dtype=torch.int32)
+    pool_shape = (pages, BS, nkv, D) if kv_layout == "bsnd" else (pages, nkv, BS, D)
     if w["kv"] == "i8":
-        key = torch.empty(pages, BS, nkv, D, dtype=torch.int8, device=device)
+        key = torch.empty(pool_shape, dtype=torch.int8, device=device)
         value = torch.empty_like(key)
         aq_scale = (torch.rand(2, nkv, D, generator=g_rank, device=device) * 0.02 + 0.005).to(qd)
         aq_offset = torch.randn(2, nkv, D, generator=g_rank, device=device).to(qd)
     else:
-        key = torch.empty(pages, BS, nkv, D, dtype=qd, device=device)
+        key = torch.empty(pool_shape, dtype=qd, device=device)
         value = torch.empty_like(key)
         aq_scale = torch.empty(0, dtype=qd, device=device)
         aq_offset = torch.empty(0, dtype=qd, device=device)
@@ -101,13 +104,13 @@ def make_inputs(w, B, rank, world, device, seed=1234):
         for p0 in range(0, pages, chunk):
             n = min(chunk, pages - p0)
             if w["kv"] == "i8":
-                t[p0:p0 + n] = torch.randint(-128, 128, (n, BS, nkv, D), generator=g_rank, device=device,
+                t[p0:p0 + n] = torch.randint(-128, 128, (n,) + pool_shape[1:], generator=g_rank, device=device,
                                              dtype=torch.int8)
             else:
-                t[p0:p0 + n] = (torch.rand(n, BS, nkv, D, generator=g_rank, device=device) * (1 - 1e-3) + 1e-3).to(qd)
+                t[p0:p0 + n] = (torch.rand((n,) + pool_shape[1:], generator=g_rank, device=device) * (1 - 1e-3) + 1e-3).to(qd)
     return dict(q=q, l1=l1, block_ids=block_ids, block_table=block_table, seq=seq, key=key, value=value,
                 aq_scale=aq_scale, aq_offset=aq_offset, B=B, Nq=nq, Nkv=nkv, C=C, S=S, P=P, k=w["k"],
-                scale=1.0 / math.sqrt(D), MP=256, qd=qd)
+                scale=1.0 / math.sqrt(D), MP=256, qd=qd, kv_layout=kv_layout)
 
 
 def algorithmic_bytes(inp, page_position, page_position_length):
@@ -258,6 +261,8 @@ def main():
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--graph", action="store_true", help="replay the step from a CUDA graph")
+    ap.add_argument("--kv-layout", default="bsnd", choices=["bsnd", "bnsd"],
+                    help="paged KV pool layout: bsnd = [blocks,bs,Nkv,D] (vLLM, default), bnsd = [blocks,Nkv,bs,D]")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -287,7 +292,7 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     B = w["B"] * world if args.scaling == "weak" else w["B"]
-    inp = make_inputs(w, B, rank, world, dev)
+    inp = make_inputs(w, B, rank, world, dev, kv_layout=args.kv_layout)
     nq, nkv = inp["Nq"], inp["Nkv"]
     qd = inp["qd"]
 
@@ -423,6 +428,7 @@ def main():
             "config": {"workload": f"{args.workload}: {w['desc']}", "global_batch": B, "q_heads": w["Nq"],
                        "kv_heads": w["Nkv"], "head_dim": D, "seq_len": w["S"], "block_size": BS, "clusters": w["C"],
                        "top_k": w["k"], "kv_dtype": w["kv"], "q_dtype": w["q"],
+                       "kv_layout": "[blocks,bs,Nkv,D]" if args.kv_layout == "bsnd" else "[blocks,Nkv,bs,D]",
                        "parallelism": f"kv-head tp{world}" if world > 1 else "single gpu",
                        "l2": ("flushed before every timed step (256 MiB write + 256 MiB read of a second buffer, so L2 holds clean lines); " if flush is not None else "not flushed; ") +
                              f"per-step read set {ab['bytes_kv_union'] / 2**20:.0f} MiB > 126 MB L2",

@@ -497,9 +497,11 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     const int v_chk = (lane >> 3) & 1;
 
     // running state of the current segment: O^T[d][head] fragments, m (log2 domain), l (thread-partial)
+    using MT = typename MmaType<QT, KVI8>::type;     // element type of the tensor-core operands
     uint32_t qf[NT][8][2];
     float o[NT][8][4];
     float m_run[NT][2], l_run[NT][2];
+    float hsc[NT][2];                                // int8 KV: per-head logit scale (see the Q fragments)
     int cur = -1, cnt = 0, first_idx = 0, slot_t0 = 0;
     unsigned long long rec = 0ull;
     int mi = 0;
@@ -525,33 +527,68 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             for (int nt = 0; nt < NT; ++nt) {
                 const int h = nt * 8 + gid;
                 const unsigned short *qrow = qg + (size_t)b * p.q_sb + (size_t)(n2 * p.g + h) * p.q_sh;
+                if (!KVI8) {
 #pragma unroll
-                for (int ks = 0; ks < 8; ++ks) {
-                    // fp16/bf16 KV: k-slots of the mma map to d in natural order.  int8 KV: one
-                    // ldmatrix row-quad holds 4 consecutive d, so slot (2*tig+e) <-> d = 16ks+4tig+e and
-                    // slot (2*tig+8+e) <-> d = 16ks+4tig+2+e (same permutation on both operands).
-                    const int d0 = KVI8 ? ks * 16 + tig * 4 : ks * 16 + tig * 2;
-                    const int dstep = KVI8 ? 2 : 8;
-                    uint32_t v0 = 0, v1 = 0;
+                    for (int ks = 0; ks < 8; ++ks) {
+                        const int d0 = ks * 16 + tig * 2;
+                        uint32_t v0 = 0, v1 = 0;
+                        if (h < p.g) {
+                            v0 = *reinterpret_cast<const uint32_t *>(qrow + d0);
+                            v1 = *reinterpret_cast<const uint32_t *>(qrow + d0 + 8);
+                        }
+                        qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
+                    }
+                } else {
+                    // int8 KV.  One ldmatrix row-quad holds 4 consecutive d, so k-slot (2*tig+e) <-> d =
+                    // 16ks+4tig+e and slot (2*tig+8+e) <-> d = 16ks+4tig+2+e (same permutation on both
+                    // operands).  The per-channel K scale is folded into Q (…_Us2.h:2142); the K offset adds
+                    // a per-head constant to every logit and cancels in the softmax (:2146-2155).  The
+                    // matmuls run in fp16 whatever the query dtype (int8 -> fp16 is exact and costs one
+                    // prmt + one hsub2 per pair; -> bf16 costs 2.5x that): q*scale_k is brought to [1, 2)
+                    // per head by a power of two (exact), rounded to fp16 (11 bits, more than bf16's 8), and
+                    // the power of two is returned to the logits in fp32.
+                    const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) +
+                                               (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
+                    auto qs4 = [&](int ks, float (&f)[4]) {
+                        const int d0 = ks * 16 + tig * 4;
+                        const uint2 qv = *reinterpret_cast<const uint2 *>(qrow + d0);
+                        uint2 sv;
+                        if (p.aq_per_tensor) sv.x = sv.y = (uint32_t)sk[0] * 0x10001u;
+                        else sv = *reinterpret_cast<const uint2 *>(sk + d0);
+                        f[0] = QTraits<QT>::to_float(qv.x & 0xffff) * QTraits<QT>::to_float(sv.x & 0xffff);
+                        f[1] = QTraits<QT>::to_float(qv.x >> 16) * QTraits<QT>::to_float(sv.x >> 16);
+                        f[2] = QTraits<QT>::to_float(qv.y & 0xffff) * QTraits<QT>::to_float(sv.y & 0xffff);
+                        f[3] = QTraits<QT>::to_float(qv.y >> 16) * QTraits<QT>::to_float(sv.y >> 16);
+                    };
+                    float amax = 0.f;
                     if (h < p.g) {
-                        v0 = *reinterpret_cast<const uint32_t *>(qrow + d0);
-                        v1 = *reinterpret_cast<const uint32_t *>(qrow + d0 + dstep);
-                        if (KVI8) {
-                            // fold the per-channel K scale into Q (…_Us2.h:2142); the K offset adds a
-                            // per-head constant to every logit and cancels in the softmax (:2146-2155)
-                            const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) +
-                                                       (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
-                            float s0 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0]);
-                            float s1 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + 1]);
-                            float s8 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + dstep]);
-                            float s9 = QTraits<QT>::to_float(sk[p.aq_per_tensor ? 0 : d0 + dstep + 1]);
-                            v0 = QTraits<QT>::pack2(QTraits<QT>::to_float(v0 & 0xffff) * s0,
-                                                    QTraits<QT>::to_float(v0 >> 16) * s1);
-                            v1 = QTraits<QT>::pack2(QTraits<QT>::to_float(v1 & 0xffff) * s8,
-                                                    QTraits<QT>::to_float(v1 >> 16) * s9);
+#pragma unroll
+                        for (int ks = 0; ks < 8; ++ks) {
+                            float f[4];
+                            qs4(ks, f);
+                            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(f[0]), fabsf(f[1])), fmaxf(fabsf(f[2]), fabsf(f[3]))));
                         }
                     }
-                    qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
+                    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+                    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+                    const uint32_t ex = min(max((__float_as_uint(amax) >> 23) & 0xffu, 1u), 253u);
+                    const float up = __uint_as_float((254u - ex) << 23);          // 2^(127-ex): amax -> [1, 2)
+                    const float down = __uint_as_float(ex << 23);                 // its inverse
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks) {
+                        uint32_t v0 = 0, v1 = 0;
+                        if (h < p.g) {
+                            float f[4];
+                            qs4(ks, f);
+                            v0 = QTraits<MT>::pack2(f[0] * up, f[1] * up);
+                            v1 = QTraits<MT>::pack2(f[2] * up, f[3] * up);
+                        }
+                        qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
+                    }
+                    // the softmax holds head nt*8 + 2*tig + e: fetch that head's factor
+#pragma unroll
+                    for (int e = 0; e < 2; ++e)
+                        hsc[nt][e] = p.scale_log2 * __shfl_sync(0xffffffffu, down, (tig * 2 + e) * 4);
                 }
             }
             // ---- running state: O^T[d][head] fragments, m (log2 domain), l (thread-partial)
@@ -583,7 +620,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     ldmatrix_x4(a0, a1, a2, a3, addr);
 #pragma unroll
                     for (int nt = 0; nt < NT; ++nt)
-                        mma_16816<QT>(s[nt], a0, a1, a2, a3, qf[nt][ks][0], qf[nt][ks][1]);
+                        mma_16816<MT>(s[nt], a0, a1, a2, a3, qf[nt][ks][0], qf[nt][ks][1]);
                 }
             } else {
                 // int8 page: [128 tokens][128 B]; one ldmatrix.x4 covers 16 tokens x 32 d
@@ -595,11 +632,11 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     ldmatrix_x4(r0, r1, r2, r3, addr);
 #pragma unroll
                     for (int nt = 0; nt < NT; ++nt) {
-                        mma_16816<QT>(s[nt], I8Pair<QT, 0, 1>::cvt(r0), I8Pair<QT, 0, 1>::cvt(r1),
-                                      I8Pair<QT, 2, 3>::cvt(r0), I8Pair<QT, 2, 3>::cvt(r1),
+                        mma_16816<MT>(s[nt], I8Pair<MT, 0, 1>::cvt(r0), I8Pair<MT, 0, 1>::cvt(r1),
+                                      I8Pair<MT, 2, 3>::cvt(r0), I8Pair<MT, 2, 3>::cvt(r1),
                                       qf[nt][2 * j][0], qf[nt][2 * j][1]);
-                        mma_16816<QT>(s[nt], I8Pair<QT, 0, 1>::cvt(r2), I8Pair<QT, 0, 1>::cvt(r3),
-                                      I8Pair<QT, 2, 3>::cvt(r2), I8Pair<QT, 2, 3>::cvt(r3),
+                        mma_16816<MT>(s[nt], I8Pair<MT, 0, 1>::cvt(r2), I8Pair<MT, 0, 1>::cvt(r3),
+                                      I8Pair<MT, 2, 3>::cvt(r2), I8Pair<MT, 2, 3>::cvt(r3),
                                       qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
                     }
                 }
@@ -620,8 +657,9 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                 const int h = nt * 8 + tig * 2 + e;
                 const bool member = (meta >> h) & 1u;
                 const int ntok = member ? (tail_page ? tail_cnt : kBS) : 0;
-                float x0 = (t0 + gid < ntok) ? s[nt][e] * p.scale_log2 : -INFINITY;
-                float x1 = (t0 + gid + 8 < ntok) ? s[nt][2 + e] * p.scale_log2 : -INFINITY;
+                const float sc2 = KVI8 ? hsc[nt][e] : p.scale_log2;
+                float x0 = (t0 + gid < ntok) ? s[nt][e] * sc2 : -INFINITY;
+                float x1 = (t0 + gid + 8 < ntok) ? s[nt][2 + e] * sc2 : -INFINITY;
                 float mx = fmaxf(x0, x1);
                 mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
                 mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
@@ -642,8 +680,8 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             }
             // P rounded to the matmul dtype before PV (…_Us2.h:3062-3063); 8x8 transposes turn
             // the accumulator layout [tok][head] into the B-operand layout [k=tok][n=head]
-            pb[nt][0] = movmatrix_trans(QTraits<QT>::pack2(pr[0], pr[1]));
-            pb[nt][1] = movmatrix_trans(QTraits<QT>::pack2(pr[2], pr[3]));
+            pb[nt][0] = movmatrix_trans(QTraits<MT>::pack2(pr[0], pr[1]));
+            pb[nt][1] = movmatrix_trans(QTraits<MT>::pack2(pr[2], pr[3]));
         }
 
         // ------------------------------ V: O^T += V^T P^T ------------------------------
@@ -660,7 +698,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     ldmatrix_x4_trans(a0, a1, a2, a3, addr);
 #pragma unroll
                     for (int nt = 0; nt < NT; ++nt)
-                        mma_16816<QT>(o[nt][mt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
+                        mma_16816<MT>(o[nt][mt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
                 }
             } else {
                 // int8 page, transposed 8x8 b16 loads: a register holds V[tok 2tig][d,d+1] and
@@ -674,10 +712,10 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     ldmatrix_x4_trans(r0, r1, r2, r3, addr);
 #pragma unroll
                     for (int nt = 0; nt < NT; ++nt) {
-                        mma_16816<QT>(o[nt][2 * j], I8Pair<QT, 0, 2>::cvt(r0), I8Pair<QT, 1, 3>::cvt(r0),
-                                      I8Pair<QT, 0, 2>::cvt(r1), I8Pair<QT, 1, 3>::cvt(r1), pb[nt][0], pb[nt][1]);
-                        mma_16816<QT>(o[nt][2 * j + 1], I8Pair<QT, 0, 2>::cvt(r2), I8Pair<QT, 1, 3>::cvt(r2),
-                                      I8Pair<QT, 0, 2>::cvt(r3), I8Pair<QT, 1, 3>::cvt(r3), pb[nt][0], pb[nt][1]);
+                        mma_16816<MT>(o[nt][2 * j], I8Pair<MT, 0, 2>::cvt(r0), I8Pair<MT, 1, 3>::cvt(r0),
+                                      I8Pair<MT, 0, 2>::cvt(r1), I8Pair<MT, 1, 3>::cvt(r1), pb[nt][0], pb[nt][1]);
+                        mma_16816<MT>(o[nt][2 * j + 1], I8Pair<MT, 0, 2>::cvt(r2), I8Pair<MT, 1, 3>::cvt(r2),
+                                      I8Pair<MT, 0, 2>::cvt(r3), I8Pair<MT, 1, 3>::cvt(r3), pb[nt][0], pb[nt][1]);
                     }
                 }
             }

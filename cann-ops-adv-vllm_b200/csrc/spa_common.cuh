@@ -180,6 +180,11 @@ template <> struct QTraits<__nv_bfloat16> {
     }
 };
 
+// Element type of the attention matmuls: the query dtype, except that int8 KV always runs in fp16
+// (exact and cheap int8 -> fp16 conversion; see attention_phase).
+template <typename QT, bool KVI8> struct MmaType { typedef QT type; };
+template <typename QT> struct MmaType<QT, true> { typedef __half type; };
+
 // ---- mbarrier / TMA (PTX ISA 8.x, sm_90+/sm_100a) -----------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

@@ -302,9 +302,14 @@ static int make_kv_map(CUtensorMap *map, const spaTensor *t, const KvLayout &L, 
     CUtensorMapDataType dt = t->dtype == SPA_I8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
                              : t->dtype == SPA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                     : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    // L2 fetch granularity: a token row of one kv head is kD*esz contiguous bytes.  With int8 KV in the vLLM
+    // layout that is 128 B and the neighbouring 128 B belong to another head (another CTA, another time):
+    // 256 B promotion would pull them from DRAM for nothing (ncu, c3: 1.55 GB read for 1.07 GB needed).
+    const bool rows_contiguous = (L.s_row == kD);
+    const CUtensorMapL2promotion promo = ((long long)kD * esz >= 256 || rows_contiguous)
+                                             ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
     CUresult r = enc(map, dt, 4, t->data, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                     CU_TENSOR_MAP_SWIZZLE_128B, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(SPA_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%d)", name, (int)r);
     return SPA_OK;
 }
