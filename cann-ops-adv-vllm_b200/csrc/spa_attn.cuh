@@ -325,6 +325,178 @@ __device__ __forceinline__ unsigned long long take_entry(const ChainParams &p, i
     return v;
 }
 
+// ---- consumers: PP (1 or 2) pages of the current item ------------------------------------------------
+// Per page and warp: S^T = K Q^T for the warp's 16 tokens, online softmax in the log2 domain,
+// O^T += V^T P^T.  With PP = 2 the two pages' chains are interleaved instruction by instruction, the
+// running max is reduced once over both and O is rescaled once (and only when some max moved).
+// ks/vs: ring stages of the K and V tiles (K full barriers already passed), vph: parities of the V stages.
+template <typename QT, bool KVI8, int NT, int PP>
+__device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t stage_u32, const int (&ks)[PP],
+                                              const int (&vs)[PP], const uint32_t (&vph)[PP],
+                                              const unsigned (&metas)[PP], const int (&tails)[PP],
+                                              const uint32_t (&qf)[NT][8][2], float (&o)[NT][8][4],
+                                              float (&m_run)[NT][2], float (&l_run)[NT][2],
+                                              const float (&hsc)[NT][2], uint64_t *full, uint64_t *empty) {
+    using MT = typename MmaType<QT, KVI8>::type;
+    const int lane = lane_id(), warp = warp_id(), gid = lane >> 2, tig = lane & 3;
+    const int t0 = warp * 16;                       // this warp's 16 tokens of every page
+    // ldmatrix lane offsets (128B-swizzled tile: row r, 16B chunk c stored at chunk c ^ (r & 7))
+    const int a_row = t0 + (lane & 15);             // K tile as A operand (non-transposed)
+    const int a_chk = lane >> 4;
+    const int v_row = t0 + (lane & 7) + ((lane >> 4) & 1) * 8;   // V tile as A^T operand (.trans)
+    const int v_chk = (lane >> 3) & 1;
+
+    // ------------------------------ K: S^T = K Q^T ------------------------------
+    float s[PP][NT][4];
+#pragma unroll
+    for (int pp = 0; pp < PP; ++pp)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) s[pp][nt][0] = s[pp][nt][1] = s[pp][nt][2] = s[pp][nt][3] = 0.f;
+    if (!KVI8) {
+#pragma unroll
+        for (int k8 = 0; k8 < 8; ++k8) {
+            const int chunk = (k8 & 3) * 2 + a_chk;
+            const uint32_t off = (k8 >> 2) * (kBS * 128) + a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
+#pragma unroll
+            for (int pp = 0; pp < PP; ++pp) {
+                uint32_t a0, a1, a2, a3;
+                ldmatrix_x4(a0, a1, a2, a3, stage_u32 + (uint32_t)ks[pp] * p.stage_bytes + off);
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt)
+                    mma_16816<MT>(s[pp][nt], a0, a1, a2, a3, qf[nt][k8][0], qf[nt][k8][1]);
+            }
+        }
+    } else {
+        // int8 page: [128 tokens][128 B]; one ldmatrix.x4 covers 16 tokens x 32 d
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int chunk = j * 2 + a_chk;
+            const uint32_t off = a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
+#pragma unroll
+            for (int pp = 0; pp < PP; ++pp) {
+                uint32_t r0, r1, r2, r3;
+                ldmatrix_x4(r0, r1, r2, r3, stage_u32 + (uint32_t)ks[pp] * p.stage_bytes + off);
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    mma_16816<MT>(s[pp][nt], I8Pair<MT, 0, 1>::cvt(r0), I8Pair<MT, 0, 1>::cvt(r1),
+                                  I8Pair<MT, 2, 3>::cvt(r0), I8Pair<MT, 2, 3>::cvt(r1),
+                                  qf[nt][2 * j][0], qf[nt][2 * j][1]);
+                    mma_16816<MT>(s[pp][nt], I8Pair<MT, 0, 1>::cvt(r2), I8Pair<MT, 0, 1>::cvt(r3),
+                                  I8Pair<MT, 2, 3>::cvt(r2), I8Pair<MT, 2, 3>::cvt(r3),
+                                  qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
+                }
+            }
+        }
+    }
+    __syncwarp();
+    if (lane == 0) {
+#pragma unroll
+        for (int pp = 0; pp < PP; ++pp) mbar_arrive(&empty[ks[pp]]);
+    }
+
+    // ------------------------------ online softmax ------------------------------
+    uint32_t pb[PP][NT][2];                      // P^T as B fragments (after transpose)
+    float alpha[NT][2];
+    bool moved = false;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        float pr[PP][4];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int h = nt * 8 + tig * 2 + e;
+            const float sc2 = KVI8 ? hsc[nt][e] : p.scale_log2;
+            float x[PP][2];
+            float mx = -INFINITY;
+#pragma unroll
+            for (int pp = 0; pp < PP; ++pp) {
+                const int ntok = ((metas[pp] >> h) & 1u) ? tails[pp] : 0;
+                x[pp][0] = (t0 + gid < ntok) ? s[pp][nt][e] * sc2 : -INFINITY;
+                x[pp][1] = (t0 + gid + 8 < ntok) ? s[pp][nt][2 + e] * sc2 : -INFINITY;
+                mx = fmaxf(mx, fmaxf(x[pp][0], x[pp][1]));
+            }
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+            const float m_new = fmaxf(m_run[nt][e], mx);
+            const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+            alpha[nt][e] = fast_exp2(m_run[nt][e] - m_use);
+            moved |= (m_new != m_run[nt][e]);
+            float psum = 0.f;
+#pragma unroll
+            for (int pp = 0; pp < PP; ++pp) {
+                const float p0 = fast_exp2(x[pp][0] - m_use);
+                const float p1 = fast_exp2(x[pp][1] - m_use);
+                psum += p0 + p1;
+                pr[pp][e] = p0; pr[pp][2 + e] = p1;
+            }
+            l_run[nt][e] = l_run[nt][e] * alpha[nt][e] + psum;
+            m_run[nt][e] = m_new;
+        }
+        // P rounded to the matmul dtype before PV (…_Us2.h:3062-3063); 8x8 transposes turn
+        // the accumulator layout [tok][head] into the B-operand layout [k=tok][n=head]
+#pragma unroll
+        for (int pp = 0; pp < PP; ++pp) {
+            pb[pp][nt][0] = movmatrix_trans(QTraits<MT>::pack2(pr[pp][0], pr[pp][1]));
+            pb[pp][nt][1] = movmatrix_trans(QTraits<MT>::pack2(pr[pp][2], pr[pp][3]));
+        }
+    }
+    // rescale O only when some head's running max moved (it settles after the first pages of an item)
+    if (__any_sync(0xffffffffu, moved)) {
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int mt = 0; mt < 8; ++mt) {
+                o[nt][mt][0] *= alpha[nt][0]; o[nt][mt][1] *= alpha[nt][1];
+                o[nt][mt][2] *= alpha[nt][0]; o[nt][mt][3] *= alpha[nt][1];
+            }
+    }
+
+    // ------------------------------ V: O^T += V^T P^T ------------------------------
+#pragma unroll
+    for (int pp = 0; pp < PP; ++pp) mbar_wait(&full[vs[pp]], vph[pp]);
+    if (!KVI8) {
+#pragma unroll
+        for (int mt = 0; mt < 8; ++mt) {
+            const int chunk = (mt & 3) * 2 + v_chk;
+            const uint32_t off = (mt >> 2) * (kBS * 128) + v_row * 128 + ((chunk ^ (v_row & 7)) << 4);
+#pragma unroll
+            for (int pp = 0; pp < PP; ++pp) {
+                uint32_t a0, a1, a2, a3;
+                ldmatrix_x4_trans(a0, a1, a2, a3, stage_u32 + (uint32_t)vs[pp] * p.stage_bytes + off);
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt)
+                    mma_16816<MT>(o[nt][mt], a0, a1, a2, a3, pb[pp][nt][0], pb[pp][nt][1]);
+            }
+        }
+    } else {
+        // int8 page, transposed 8x8 b16 loads: a register holds V[tok 2tig][d,d+1] and
+        // V[tok 2tig+1][d,d+1] with d = 16*chunk + 2*gid; m-tile row gid <-> d, row
+        // gid+8 <-> d+1 (see o_dim()).
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int chunk = j * 2 + a_chk;
+            const uint32_t off = a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
+#pragma unroll
+            for (int pp = 0; pp < PP; ++pp) {
+                uint32_t r0, r1, r2, r3;
+                ldmatrix_x4_trans(r0, r1, r2, r3, stage_u32 + (uint32_t)vs[pp] * p.stage_bytes + off);
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    mma_16816<MT>(o[nt][2 * j], I8Pair<MT, 0, 2>::cvt(r0), I8Pair<MT, 1, 3>::cvt(r0),
+                                  I8Pair<MT, 0, 2>::cvt(r1), I8Pair<MT, 1, 3>::cvt(r1), pb[pp][nt][0], pb[pp][nt][1]);
+                    mma_16816<MT>(o[nt][2 * j + 1], I8Pair<MT, 0, 2>::cvt(r2), I8Pair<MT, 1, 3>::cvt(r2),
+                                  I8Pair<MT, 0, 2>::cvt(r3), I8Pair<MT, 1, 3>::cvt(r3), pb[pp][nt][0], pb[pp][nt][1]);
+                }
+            }
+        }
+    }
+    __syncwarp();
+    if (lane == 0) {
+#pragma unroll
+        for (int pp = 0; pp < PP; ++pp) mbar_arrive(&empty[vs[pp]]);
+    }
+}
+
 template <typename QT, bool KVI8, int NT>
 __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, const CUtensorMap *tmV,
                                 unsigned char *smem) {
@@ -443,15 +615,20 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             const unsigned long long ent2 = (ok2 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
             if (lane < cn) ent = take_entry(p, cf + lane, ent);
             t_pages += cn;
+            bool second = false;                                           // this entry closes a pair
             for (int j = 0; j < cn; ++j) {
                 const unsigned long long e = __shfl_sync(0xffffffffu, ent, j);
+                const unsigned long long en = __shfl_sync(0xffffffffu, ent, min(j + 1, cn - 1));
+                // two consecutive pages of one item (inside a chunk) are handed to the consumers as a pair
+                const bool first = p.pair_pages && !second && j + 1 < cn && (((e ^ en) >> 48) & (kMaxItems - 1)) == 0;
+                second = first;
                 if (lane == 0) {
                     const unsigned hi = (unsigned)(e >> 32), lo = (unsigned)e;
                     const int ph = (int)(lo & 0xffffffu), item = (int)((hi >> 16) & (kMaxItems - 1));
                     const int n2 = item % p.Nkv;
-                    // stage header: head mask | tail flag << 16, item, queue index, tokens on a tail page
-                    const int4 md = make_int4((int)(hi & 0xffffu) | (int)(((hi >> 30) & 1u) << 16), item, cf + j,
-                                              (int)((lo >> 24) & 0x7fu) + 1);
+                    // stage header: head mask | tail flag << 16 | pair flag << 17, item, queue index, tokens on a tail page
+                    const int4 md = make_int4((int)(hi & 0xffffu) | (int)(((hi >> 30) & 1u) << 16) | (first ? (1 << 17) : 0),
+                                              item, cf + j, (int)((lo >> 24) & 0x7fu) + 1);
                     int c[4];
                     c[1] = (p.ax_head == 1) ? n2 : (p.ax_blk == 1 ? ph : 0);
                     c[2] = (p.ax_head == 2) ? n2 : (p.ax_blk == 2 ? ph : 0);
@@ -603,126 +780,38 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             }
 
         }
-        ++cnt;
-        // ------------------------------ K: S^T = K Q^T ------------------------------
-        float s[NT][4];
+        // ---- one page, or two pages of the same item at once (independent chains for the scheduler,
+        // one max reduction and one rescale of O for both)
+        if ((md.x >> 17) & 1) {
+            int st[4]; uint32_t ph[4];
+            st[0] = stage; ph[0] = phase;
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-        {
-            const uint32_t kb = stage_u32 + (uint32_t)stage * p.stage_bytes;
-            if (!KVI8) {
-#pragma unroll
-                for (int ks = 0; ks < 8; ++ks) {
-                    const int chunk = (ks & 3) * 2 + a_chk;
-                    const uint32_t addr = kb + (ks >> 2) * (kBS * 128) + a_row * 128 +
-                                          ((chunk ^ (a_row & 7)) << 4);
-                    uint32_t a0, a1, a2, a3;
-                    ldmatrix_x4(a0, a1, a2, a3, addr);
-#pragma unroll
-                    for (int nt = 0; nt < NT; ++nt)
-                        mma_16816<MT>(s[nt], a0, a1, a2, a3, qf[nt][ks][0], qf[nt][ks][1]);
-                }
-            } else {
-                // int8 page: [128 tokens][128 B]; one ldmatrix.x4 covers 16 tokens x 32 d
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int chunk = j * 2 + a_chk;
-                    const uint32_t addr = kb + a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
-                    uint32_t r0, r1, r2, r3;
-                    ldmatrix_x4(r0, r1, r2, r3, addr);
-#pragma unroll
-                    for (int nt = 0; nt < NT; ++nt) {
-                        mma_16816<MT>(s[nt], I8Pair<MT, 0, 1>::cvt(r0), I8Pair<MT, 0, 1>::cvt(r1),
-                                      I8Pair<MT, 2, 3>::cvt(r0), I8Pair<MT, 2, 3>::cvt(r1),
-                                      qf[nt][2 * j][0], qf[nt][2 * j][1]);
-                        mma_16816<MT>(s[nt], I8Pair<MT, 0, 1>::cvt(r2), I8Pair<MT, 0, 1>::cvt(r3),
-                                      I8Pair<MT, 2, 3>::cvt(r2), I8Pair<MT, 2, 3>::cvt(r3),
-                                      qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
-                    }
-                }
+            for (int i = 1; i < 4; ++i) {
+                st[i] = st[i - 1] + 1; ph[i] = ph[i - 1];
+                if (st[i] == nstages) { st[i] = 0; ph[i] ^= 1u; }
             }
+            mbar_wait(&full[st[2]], ph[2]);
+            const int4 md1 = metaS[st[2]];
+            const unsigned metas[2] = {meta, (unsigned)md1.x & 0xffffu};
+            const int tails[2] = {tail_page ? tail_cnt : kBS, ((md1.x >> 16) & 1) ? md1.w : kBS};
+            const int ks[2] = {st[0], st[2]}, vs[2] = {st[1], st[3]};
+            const uint32_t vph[2] = {ph[1], ph[3]};
+            cnt += 2;
+            consume_pages<QT, KVI8, NT, 2>(p, stage_u32, ks, vs, vph, metas, tails, qf, o, m_run, l_run, hsc, full, empty);
+            stage = st[3] + 1; phase = ph[3];
+            if (stage == nstages) { stage = 0; phase ^= 1u; }
+        } else {
+            int st1 = stage + 1; uint32_t ph1 = phase;
+            if (st1 == nstages) { st1 = 0; ph1 ^= 1u; }
+            const unsigned metas[1] = {meta};
+            const int tails[1] = {tail_page ? tail_cnt : kBS};
+            const int ks[1] = {stage}, vs[1] = {st1};
+            const uint32_t vph[1] = {ph1};
+            cnt += 1;
+            consume_pages<QT, KVI8, NT, 1>(p, stage_u32, ks, vs, vph, metas, tails, qf, o, m_run, l_run, hsc, full, empty);
+            stage = st1 + 1; phase = ph1;
+            if (stage == nstages) { stage = 0; phase ^= 1u; }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[stage]);
-        if (++stage == nstages) { stage = 0; phase ^= 1u; }
-
-        // ------------------------------ online softmax ------------------------------
-        uint32_t pb[NT][2];                      // P^T as B fragments (after transpose)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-            float pr[4];
-            float alpha[2];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int h = nt * 8 + tig * 2 + e;
-                const bool member = (meta >> h) & 1u;
-                const int ntok = member ? (tail_page ? tail_cnt : kBS) : 0;
-                const float sc2 = KVI8 ? hsc[nt][e] : p.scale_log2;
-                float x0 = (t0 + gid < ntok) ? s[nt][e] * sc2 : -INFINITY;
-                float x1 = (t0 + gid + 8 < ntok) ? s[nt][2 + e] * sc2 : -INFINITY;
-                float mx = fmaxf(x0, x1);
-                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
-                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
-                const float m_new = fmaxf(m_run[nt][e], mx);
-                const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-                alpha[e] = fast_exp2(m_run[nt][e] - m_use);
-                const float p0 = fast_exp2(x0 - m_use);
-                const float p1 = fast_exp2(x1 - m_use);
-                l_run[nt][e] = l_run[nt][e] * alpha[e] + p0 + p1;
-                m_run[nt][e] = m_new;
-                pr[e] = p0; pr[2 + e] = p1;
-            }
-#pragma unroll
-            for (int mt = 0; mt < 8; ++mt) {
-                o[nt][mt][0] *= alpha[0]; o[nt][mt][1] *= alpha[1];
-                o[nt][mt][2] *= alpha[0]; o[nt][mt][3] *= alpha[1];
-            }
-            // P rounded to the matmul dtype before PV (…_Us2.h:3062-3063); 8x8 transposes turn
-            // the accumulator layout [tok][head] into the B-operand layout [k=tok][n=head]
-            pb[nt][0] = movmatrix_trans(QTraits<MT>::pack2(pr[0], pr[1]));
-            pb[nt][1] = movmatrix_trans(QTraits<MT>::pack2(pr[2], pr[3]));
-        }
-
-        // ------------------------------ V: O^T += V^T P^T ------------------------------
-        mbar_wait(&full[stage], phase);
-        {
-            const uint32_t vb = stage_u32 + (uint32_t)stage * p.stage_bytes;
-            if (!KVI8) {
-#pragma unroll
-                for (int mt = 0; mt < 8; ++mt) {
-                    const int chunk = (mt & 3) * 2 + v_chk;
-                    const uint32_t addr = vb + (mt >> 2) * (kBS * 128) + v_row * 128 +
-                                          ((chunk ^ (v_row & 7)) << 4);
-                    uint32_t a0, a1, a2, a3;
-                    ldmatrix_x4_trans(a0, a1, a2, a3, addr);
-#pragma unroll
-                    for (int nt = 0; nt < NT; ++nt)
-                        mma_16816<MT>(o[nt][mt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
-                }
-            } else {
-                // int8 page, transposed 8x8 b16 loads: a register holds V[tok 2tig][d,d+1] and
-                // V[tok 2tig+1][d,d+1] with d = 16*chunk + 2*gid; m-tile row gid <-> d, row
-                // gid+8 <-> d+1 (see o_dim()).
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int chunk = j * 2 + a_chk;
-                    const uint32_t addr = vb + a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
-                    uint32_t r0, r1, r2, r3;
-                    ldmatrix_x4_trans(r0, r1, r2, r3, addr);
-#pragma unroll
-                    for (int nt = 0; nt < NT; ++nt) {
-                        mma_16816<MT>(o[nt][2 * j], I8Pair<MT, 0, 2>::cvt(r0), I8Pair<MT, 1, 3>::cvt(r0),
-                                      I8Pair<MT, 0, 2>::cvt(r1), I8Pair<MT, 1, 3>::cvt(r1), pb[nt][0], pb[nt][1]);
-                        mma_16816<MT>(o[nt][2 * j + 1], I8Pair<MT, 0, 2>::cvt(r2), I8Pair<MT, 1, 3>::cvt(r2),
-                                      I8Pair<MT, 0, 2>::cvt(r3), I8Pair<MT, 1, 3>::cvt(r3), pb[nt][0], pb[nt][1]);
-                    }
-                }
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[stage]);
-        if (++stage == nstages) { stage = 0; phase ^= 1u; }
     }
     if (tid == 0)                                                    // post warps: done
         for (int w = 0; w < kPostWarps; ++w) post_message(mail, mfull, mempty, mi, mph, make_int4(-1, 0, 0, 0), make_int4(0, 0, 0, 0));

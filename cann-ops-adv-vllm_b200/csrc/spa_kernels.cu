@@ -665,6 +665,8 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
         if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.list_cap).total <= budget) break;
     if (nst < 2) return fail(SPA_ERR_UNSUPPORTED, "attention working set exceeds shared memory");
     p.nstages = nst;
+    p.pair_pages = nst >= 4;
+    if (const char *s = getenv("SPA_PAIR")) p.pair_pages = p.pair_pages && atoi(s) != 0;
     int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.list_cap).total;
     int sel_bytes = p.maxP * 4;
     if (p.mode == kModeFused) {
