@@ -311,6 +311,47 @@ at::Tensor incre_flash_attention_v4(
                        "use sparse_paged_attention with an identity block_position");
 }
 
+// ---- Meta (shape inference) impls: output shapes/dtypes of the CUDA impls above, no data.  Mirrors the
+// role of op_plugin/python/meta/_meta_registrations.py:38-93 (FakeTensor / torch.compile tracing).
+at::Tensor meta_attention(
+    const at::Tensor &query, const std::vector<at::Tensor> &, const std::vector<at::Tensor> &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, int64_t, double, std::string, int64_t, int64_t, int64_t) {
+    return at::empty(query.sizes(), query.options());
+}
+at::Tensor meta_compute_cent(const at::Tensor &query, const at::Tensor &) {
+    return at::empty({query.size(0), query.size(1), kDefaultK}, query.options().dtype(at::kInt));
+}
+std::tuple<at::Tensor, at::Tensor, at::Tensor> meta_select_position(const at::Tensor &block_ids,
+                                                                    const at::Tensor &block_table,
+                                                                    const at::Tensor &, const at::Tensor &indices) {
+    auto opt = block_ids.options().dtype(at::kInt);
+    const int64_t B = indices.size(0), Nq = indices.size(1);
+    return std::make_tuple(at::empty({B, Nq, kDefaultMaxPageNum}, opt), at::empty({B, Nq, kPad}, opt),
+                           at::empty({B, Nq, block_table.size(1)}, opt));
+}
+std::tuple<at::Tensor, at::Tensor, at::Tensor> meta_cent_select(const at::Tensor &query, const at::Tensor &,
+                                                                const at::Tensor &block_ids, const at::Tensor &,
+                                                                const at::Tensor &seq_len) {
+    auto opt = block_ids.options().dtype(at::kInt);
+    const int64_t B = seq_len.size(0), Nq = query.size(1);
+    return std::make_tuple(at::empty({B, Nq, kDefaultMaxPageNum}, opt), at::empty({B, Nq, kPad}, opt),
+                           at::empty({B, kPad}, opt.dtype(at::kLong)));
+}
+std::tuple<at::Tensor, at::Tensor, at::Tensor> meta_fusion(
+    const at::Tensor &query, const std::vector<at::Tensor> &, const std::vector<at::Tensor> &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &block_position,
+    const at::Tensor &, const at::Tensor &max_page_position_length, int64_t, double, std::string, int64_t, int64_t,
+    int64_t) {
+    // fresh tensors of the caller-allocated shapes (a functional schema must not return its inputs)
+    return std::make_tuple(at::empty(query.sizes(), query.options()),
+                           at::empty(block_position.sizes(), block_position.options()),
+                           at::empty(max_page_position_length.sizes(), max_page_position_length.options()));
+}
+
 }  // namespace
 
 // Schema strings identical to the reference's (extension/csrc/registration.cpp:43-57).
@@ -337,6 +378,14 @@ TORCH_LIBRARY_IMPL(myops, CUDA, m) {
     m.impl("select_position", &select_position);
     m.impl("cent_select", &cent_select);
     m.impl("sparse_paged_fusion_attention", &sparse_paged_fusion_attention);
+}
+
+TORCH_LIBRARY_IMPL(myops, Meta, m) {
+    m.impl("sparse_paged_attention", &meta_attention);
+    m.impl("compute_cent", &meta_compute_cent);
+    m.impl("select_position", &meta_select_position);
+    m.impl("cent_select", &meta_cent_select);
+    m.impl("sparse_paged_fusion_attention", &meta_fusion);
 }
 
 PYBIND11_MODULE(custom_ops_lib, m) {

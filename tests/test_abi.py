@@ -158,3 +158,35 @@ def test_attention_rejects_unsupported_ifa_features_without_gpu(lib):
 def test_destroy_null_executor_is_ok(lib):
     assert lib.spaDestroyExecutor(None) == SPA_OK
     assert lib.spaExecutorNumLaunches(None) == 0
+
+
+def test_meta_impls_infer_output_shapes_without_gpu(lib):
+    """`myops` Meta registrations (shape inference for FakeTensor / torch.compile tracing; the
+    reference's are op_plugin/python/meta/_meta_registrations.py:38-93)."""
+    import sys
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "cann-ops-adv-vllm_b200"))
+    pytest.importorskip("custom_ops_lib")
+
+    def m(*s, dt=torch.float16):
+        return torch.empty(*s, dtype=dt, device="meta")
+
+    B, Nq, Nkv, C, P = 4, 32, 8, 512, 256
+    i32 = torch.int32
+    idx = torch.ops.myops.compute_cent(m(B, Nq, 128), m(Nkv, C, 128))
+    assert idx.shape == (B, Nq, 64) and idx.dtype == i32
+    pp, ppl, ga = torch.ops.myops.select_position(m(Nkv, 1280, dt=i32), m(B, P, dt=i32), m(B, dt=i32), m(B, Nq, 64, dt=i32))
+    assert pp.shape == (B, Nq, 256) and ppl.shape == (B, Nq, 8) and ga.shape == (B, Nq, P)
+    pp, ppl, mx = torch.ops.myops.cent_select(m(B, Nq, 128), m(Nkv, C, 128), m(Nkv, 1280, dt=i32), m(B, P, dt=i32),
+                                              m(B - 2, dt=i32))
+    assert pp.shape == (B - 2, Nq, 256) and ppl.shape == (B - 2, Nq, 8) and mx.shape == (B - 2, 8) and mx.dtype == torch.int64
+    e = m(0)
+    kv = m(1280, 128, Nkv, 128)
+    out = torch.ops.myops.sparse_paged_attention(m(B, Nq, 128), [kv], [kv], e, e, m(B, dt=torch.int64), e, e, e, e, e, e, e,
+                                                 m(B, P, dt=i32), e, m(B, Nkv, 256, dt=i32), Nq, 1.0, "BNSD", Nkv, 128, 1)
+    assert out.shape == (B, Nq, 128) and out.dtype == torch.float16
+    out, bp, mx = torch.ops.myops.sparse_paged_fusion_attention(
+        m(B, Nq, 128, dt=torch.bfloat16), [kv], [kv], e, e, m(B, dt=torch.int64), e, e, e, e, e, e, e, m(B, P, dt=i32), e,
+        m(Nkv, C, 128), m(Nkv, 1280, dt=i32), m(B, dt=i32), m(B, Nq, 512, dt=i32), m(B, Nq, 8, dt=i32),
+        m(B, 8, dt=torch.int64), Nq, 1.0, "BNSD", Nkv, 128, 1)
+    assert out.shape == (B, Nq, 128) and out.dtype == torch.bfloat16 and bp.shape == (B, Nq, 512) and mx.shape == (B, 8)
