@@ -260,7 +260,10 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-align", action="store_true", help="N>1: no rank-aligning all-reduce before the timed steps")
     ap.add_argument("--graph", action="store_true", help="replay the step from a CUDA graph")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl", "none"],
+                    help="N>1: output all-gather fused into the launch (NVLink peer stores, default) or NCCL after it")
     ap.add_argument("--kv-layout", default="bsnd", choices=["bsnd", "bnsd"],
                     help="paged KV pool layout: bsnd = [blocks,bs,Nkv,D] (vLLM, default), bnsd = [blocks,Nkv,bs,D]")
     args = ap.parse_args()
@@ -301,24 +304,47 @@ def main():
     mppl = torch.empty(B, 8, dtype=torch.int64, device=dev)
     out = torch.empty(B, nq, D, dtype=qd, device=dev)
     gather = out_full = None
+    i8 = w["kv"] == "i8"
+    peer = world > 1 and args.gather == "peer"
     if world > 1:
-        from kvhead_tp import HeadGather
+        from kvhead_tp import HeadGather, head_shard
         gather = HeadGather(out.shape, qd, dev)                      # NCCL all-gather of the output shards
         out_full = torch.empty(B, nq * world, D, dtype=qd, device=dev)
-    i8 = w["kv"] == "i8"
-    plan = custom_ops.FusedDecodePlan(
-        inp["q"], inp["key"], inp["value"], inp["block_table"], inp["l1"], inp["block_ids"], inp["seq"],
-        bp, ppl, mppl, out, nq, inp["scale"], nkv, BS, k=inp["k"],
-        antiquant_scale=inp["aq_scale"] if i8 else None, antiquant_offset=inp["aq_offset"] if i8 else None)
+    if peer:
+        # the launch itself delivers every rank's rows to every rank (peer stores + flag exchange)
+        from peer_gather import TPFusedDecode
+        plan = TPFusedDecode(head_shard(rank, world, nq * world, nkv * world), nq * world, inp["q"], inp["key"],
+                             inp["value"], inp["block_table"], inp["l1"], inp["block_ids"], inp["seq"], bp, ppl, mppl,
+                             inp["scale"], BS, k=inp["k"], antiquant_scale=inp["aq_scale"] if i8 else None,
+                             antiquant_offset=inp["aq_offset"] if i8 else None)
+    else:
+        plan = custom_ops.FusedDecodePlan(
+            inp["q"], inp["key"], inp["value"], inp["block_table"], inp["l1"], inp["block_ids"], inp["seq"],
+            bp, ppl, mppl, out, nq, inp["scale"], nkv, BS, k=inp["k"],
+            antiquant_scale=inp["aq_scale"] if i8 else None, antiquant_offset=inp["aq_offset"] if i8 else None)
     launches_per_step = plan.num_launches
     flush = None if args.no_flush else L2Flush(dev)
 
     def step():
         plan.launch()
-        if world > 1:
+        if world > 1 and args.gather == "nccl":
             gather(out, out_full)
 
+    # N>1: the ranks are coupled by the output exchange at the end of every step, so a rank whose L2 flush
+    # ran a few microseconds longer makes all the others wait inside THEIR timed region.  A one-element
+    # all-reduce after the flush (outside the timed region) lines the ranks up again, as the collective in
+    # front of the attention does in a tensor-parallel decoder layer.
+    align_buf = torch.zeros(1, device=dev) if world > 1 else None
+
+    def pre_step():
+        if flush is not None:
+            flush()
+        if align_buf is not None and not args.no_align:
+            dist.all_reduce(align_buf)
+
     graph = None
+    if args.graph and peer:
+        raise SystemExit("--graph with --gather peer: capture both plans of TPFusedDecode yourself (alternating buffers); use --gather nccl here")
     if args.graph:
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
@@ -343,8 +369,7 @@ def main():
 
     # ---------------- device-resident timing ----------------
     for _ in range(args.warmup):
-        if flush is not None:
-            flush()
+        pre_step()
         run_step()
     barrier()
     ab = algorithmic_bytes(inp, bp, ppl)
@@ -353,13 +378,14 @@ def main():
         sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
+    xch0 = plan.out.exchange_ns() if peer else 0
     for s0, s1 in ev:
-        if flush is not None:
-            flush()
+        pre_step()
         s0.record()
         run_step()
         s1.record()
     barrier()
+    xch_us = (plan.out.exchange_ns() - xch0) / args.steps / 1e3 if peer else None
     times = [a.elapsed_time(b) for a, b in ev]                      # ms
     total_ms = torch.tensor([sum(times)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -377,7 +403,17 @@ def main():
     h2d = hq.numel() * hq.element_size() + hbt.numel() * 4 + hseq.numel() * 4
     d2h = hout.numel() * hout.element_size()
 
+    def e2e_step_peer():
+        # same public surface as the TP serving step: inputs land in the plan's bound tensors, the launch
+        # returns the gathered output of all ranks
+        inp["q"].copy_(hq, non_blocking=True)
+        inp["block_table"].copy_(hbt, non_blocking=True)
+        inp["seq"].copy_(hseq, non_blocking=True)
+        hout.copy_(plan.launch(), non_blocking=True)
+
     def e2e_step():
+        if peer:
+            return e2e_step_peer()
         dq = hq.to(dev, non_blocking=True)
         dbt = hbt.to(dev, non_blocking=True)
         dseq = hseq.to(dev, non_blocking=True)
@@ -394,8 +430,7 @@ def main():
     barrier()
     ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     for s0, s1 in ev2:
-        if flush is not None:
-            flush()
+        pre_step()
         s0.record()
         e2e_step()
         s1.record()
@@ -429,9 +464,10 @@ def main():
                        "kv_heads": w["Nkv"], "head_dim": D, "seq_len": w["S"], "block_size": BS, "clusters": w["C"],
                        "top_k": w["k"], "kv_dtype": w["kv"], "q_dtype": w["q"],
                        "kv_layout": "[blocks,bs,Nkv,D]" if args.kv_layout == "bsnd" else "[blocks,Nkv,bs,D]",
-                       "parallelism": f"kv-head tp{world}" if world > 1 else "single gpu",
+                       "parallelism": (f"kv-head tp{world}, output all-gather " + ("fused into the launch (NVLink peer stores)" if peer else "by NCCL")) if world > 1 else "single gpu",
                        "l2": ("flushed before every timed step (256 MiB write + 256 MiB read of a second buffer, so L2 holds clean lines); " if flush is not None else "not flushed; ") +
-                             f"per-step read set {ab['bytes_kv_union'] / 2**20:.0f} MiB > 126 MB L2",
+                             f"per-step read set {ab['bytes_kv_union'] / 2**20:.0f} MiB > 126 MB L2" +
+                             ("; ranks aligned by a 1-element all-reduce before each timed step (outside the timed region)" if world > 1 and not args.no_align else ""),
                        "launch": "cuda graph replay" if graph is not None else "FusedDecodePlan.launch()"},
             "achieved_hbm_gbs_selected_kv": agg[1].item() / (ms_per_step * 1e-3) / 1e9,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
@@ -446,8 +482,9 @@ def main():
                        "max_ms": st[-1]},
             "e2e": {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
-                    "api": "custom_ops.sparse_paged_fusion_attention"},
+                    "api": "peer_gather.TPFusedDecode.launch" if peer else "custom_ops.sparse_paged_fusion_attention"},
             "gpu_launches": launches_per_step * args.steps,
+            "tp_flag_exchange_us_per_step_rank0": xch_us,
             "clocks": clocks,
         }
         if cpu is not None:

@@ -129,7 +129,7 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> select_position(const at::Tensor 
 std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select_ex(
     const at::Tensor &query, const at::Tensor &l1_cent, const at::Tensor &block_ids,
     const at::Tensor &block_table, const at::Tensor &seq_len, int64_t k, int64_t max_page_num,
-    int64_t block_size) {
+    int64_t block_size, int64_t sink_pages, int64_t recent_pages, int64_t max_fraction_den) {
     TORCH_CHECK(query.is_cuda(), "cent_select: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(query.device());
     const int64_t B = seq_len.size(0), Nq = query.size(1);          // add_custom.cpp:988
@@ -144,6 +144,8 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select_ex(
     uint64_t ws = 0; ExecGuard g;
     check(spaCentSelectGetWorkspaceSize(q.ptr(), c.ptr(), a.ptr(), b.ptr(), s.ptr(), k, block_size, o1.ptr(),
                                         o2.ptr(), o3.ptr(), &ws, &g.e), "cent_select");
+    if (sink_pages | recent_pages | max_fraction_den)
+        check(spaExecutorSetSelectOptions(g.e, (int)sink_pages, (int)recent_pages, (int)max_fraction_den), "cent_select");
     at::Tensor wsp = alloc_ws(ws, query);
     check(spaCentSelect(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "cent_select");
     return std::make_tuple(pp, ppl, mppl);
@@ -153,7 +155,7 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select(const at::Tensor &que
                                                            const at::Tensor &block_table,
                                                            const at::Tensor &seq_len) {
     return cent_select_ex(query, l1_cent, block_ids, block_table, seq_len, kDefaultK, kDefaultMaxPageNum,
-                          kDefaultBlockSize);
+                          kDefaultBlockSize, 0, 0, 0);
 }
 
 const at::Tensor &single(const std::vector<at::Tensor> &l, const char *name) {
@@ -210,7 +212,8 @@ std::shared_ptr<FusionPlan> make_fusion_plan(
     const at::Tensor &block_ids, const at::Tensor &total_seq_len, const at::Tensor &block_position,
     const at::Tensor &page_position_length, const at::Tensor &max_page_position_length,
     const at::Tensor &attention_out, int64_t num_heads, double scale_value, const std::string &input_layout,
-    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k) {
+    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k, int64_t sink_pages,
+    int64_t recent_pages, int64_t max_fraction_den) {
     TORCH_CHECK(query.is_cuda(), "sparse_paged_fusion_attention: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(query.device());
     auto plan = std::make_shared<FusionPlan>();
@@ -227,6 +230,9 @@ std::shared_ptr<FusionPlan> make_fusion_plan(
               input_layout.c_str(), num_key_value_heads, block_size, inner_precise, k, bp.ptr(), pl.ptr(), mp.ptr(),
               o.ptr(), &plan->ws_bytes, &plan->exec),
           "sparse_paged_fusion_attention");
+    if (sink_pages | recent_pages | max_fraction_den)
+        check(spaExecutorSetSelectOptions(plan->exec, (int)sink_pages, (int)recent_pages, (int)max_fraction_den),
+              "sparse_paged_fusion_attention");
     plan->workspace = alloc_ws(plan->ws_bytes, query);
     // the plan owns its workspace and nothing else writes to it: the queue words need clearing only once
     check(spaExecutorSetPersistentWorkspace(plan->exec, 1), "spaExecutorSetPersistentWorkspace");
@@ -251,7 +257,8 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention_ex(
     const at::Tensor &l1_cent, const at::Tensor &block_ids, const at::Tensor &total_seq_len,
     const at::Tensor &block_position, const at::Tensor &page_position_length,
     const at::Tensor &max_page_position_length, int64_t num_heads, double scale_value, std::string input_layout,
-    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k) {
+    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k, int64_t sink_pages,
+    int64_t recent_pages, int64_t max_fraction_den) {
     TORCH_CHECK(query.is_cuda(), "sparse_paged_fusion_attention: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(query.device());
     const at::Tensor &key = single(key_list, "key_list"), &value = single(value_list, "value_list");
@@ -275,6 +282,9 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention_ex(
               input_layout.c_str(), num_key_value_heads, block_size, inner_precise, k, bp.ptr(), pl.ptr(), mp.ptr(),
               o.ptr(), &ws, &g.e),
           "sparse_paged_fusion_attention");
+    if (sink_pages | recent_pages | max_fraction_den)
+        check(spaExecutorSetSelectOptions(g.e, (int)sink_pages, (int)recent_pages, (int)max_fraction_den),
+              "sparse_paged_fusion_attention");
     at::Tensor wsp = alloc_ws(ws, query);
     check(spaSparsePagedFusionAttention(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()),
           "sparse_paged_fusion_attention");
@@ -296,7 +306,8 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention(
                                             quant_scale2, quant_offset2, antiquant_scale, antiquant_offset, blocktable,
                                             kv_padding_size, l1_cent, block_ids, total_seq_len, block_position,
                                             page_position_length, max_page_position_length, num_heads, scale_value,
-                                            input_layout, num_key_value_heads, block_size, inner_precise, kDefaultK);
+                                            input_layout, num_key_value_heads, block_size, inner_precise, kDefaultK,
+                                            0, 0, 0);
 }
 
 at::Tensor incre_flash_attention_v4(
@@ -405,6 +416,13 @@ PYBIND11_MODULE(custom_ops_lib, m) {
         .def_property_readonly("workspace_bytes", [](const FusionPlan &p) { return p.ws_bytes; })
         .def_property_readonly("num_launches", [](const FusionPlan &p) { return spaExecutorNumLaunches(p.exec); })
         .def_property_readonly("grid_size", [](const FusionPlan &p) { return spaExecutorGridSize(p.exec); })
+        .def("set_peer_output", [](FusionPlan &p, int64_t rank, int64_t world, const std::vector<int64_t> &gathered,
+                                   const std::vector<int64_t> &signals) {
+            TORCH_CHECK((int64_t)gathered.size() == world && (int64_t)signals.size() == world, "set_peer_output: need one pointer per rank");
+            std::vector<void *> g(world), s(world);
+            for (int64_t i = 0; i < world; ++i) { g[i] = (void *)(uintptr_t)gathered[i]; s[i] = (void *)(uintptr_t)signals[i]; }
+            check(spaExecutorSetPeerOutput(p.exec, (int)rank, (int)world, g.data(), s.data()), "spaExecutorSetPeerOutput");
+        })
         .def("set_trace", [](FusionPlan &p, const at::Tensor &buf) {
             if (!buf.defined() || buf.numel() == 0) { spaExecutorSetTrace(p.exec, nullptr); return; }
             TORCH_CHECK(buf.is_cuda() && buf.scalar_type() == at::kLong && buf.is_contiguous() &&
@@ -412,6 +430,25 @@ PYBIND11_MODULE(custom_ops_lib, m) {
             p.keep.push_back(buf);
             spaExecutorSetTrace(p.exec, buf.data_ptr());
         });
+    // ---- KV-head tensor parallelism: peer buffers for the fused output all-gather (include/spa_b200.h)
+    m.def("peer_buffer_create", [](int64_t bytes) {
+        void *ptr = nullptr;
+        unsigned char h[SPA_IPC_HANDLE_BYTES];
+        check(spaPeerBufferCreate((uint64_t)bytes, &ptr, h), "spaPeerBufferCreate");
+        return std::make_pair((int64_t)(uintptr_t)ptr, pybind11::bytes((const char *)h, SPA_IPC_HANDLE_BYTES));
+    });
+    m.def("peer_buffer_open", [](const std::string &handle) {
+        TORCH_CHECK(handle.size() == SPA_IPC_HANDLE_BYTES, "peer_buffer_open: need a 64-byte IPC handle");
+        void *ptr = nullptr;
+        check(spaPeerBufferOpen((const unsigned char *)handle.data(), &ptr), "spaPeerBufferOpen");
+        return (int64_t)(uintptr_t)ptr;
+    });
+    m.def("peer_buffer_close", [](int64_t ptr) { check(spaPeerBufferClose((void *)(uintptr_t)ptr), "spaPeerBufferClose"); });
+    m.def("peer_buffer_destroy", [](int64_t ptr) { check(spaPeerBufferDestroy((void *)(uintptr_t)ptr), "spaPeerBufferDestroy"); });
+    m.def("peer_buffer_tensor", [](int64_t ptr, int64_t bytes, int64_t device) {
+        // uint8 view of a peer buffer (local or mapped); the caller keeps the buffer alive
+        return at::from_blob((void *)(uintptr_t)ptr, {bytes}, at::TensorOptions().dtype(at::kByte).device(at::kCUDA, (c10::DeviceIndex)device));
+    });
     m.def("make_fusion_plan", &make_fusion_plan);
     m.def("launch_fusion_plan", &launch_fusion_plan);
     m.def("abi_version", []() { return spaGetVersion(); });

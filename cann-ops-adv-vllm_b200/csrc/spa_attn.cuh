@@ -69,10 +69,21 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
             r[e] = (r[e] + off) * QTraits<QT>::to_float(sv[d]);
         }
     }
-    unsigned short *op = reinterpret_cast<unsigned short *>(p.out) + (size_t)b * p.out_sb +
-                         (size_t)(n2 * p.g + h) * p.out_sh + d0;
+    const size_t off = (size_t)b * p.out_sb + (size_t)(n2 * p.g + h) * p.out_sh + d0;
+    unsigned short *op = reinterpret_cast<unsigned short *>(p.out) + off;
+    uint32_t pk[NV / 2];
 #pragma unroll
-    for (int e = 0; e < NV; e += 2) *reinterpret_cast<uint32_t *>(op + e) = QTraits<QT>::pack2(r[e], r[e + 1]);
+    for (int e = 0; e < NV; e += 2) {
+        pk[e / 2] = QTraits<QT>::pack2(r[e], r[e + 1]);
+        *reinterpret_cast<uint32_t *>(op + e) = pk[e / 2];
+    }
+    // output all-gather fused into the epilogue: the same row goes to every peer's gathered buffer
+#pragma unroll 1
+    for (int i = 0; i < p.n_peer; ++i) {
+        unsigned short *pp = reinterpret_cast<unsigned short *>(p.out_peer[i]) + off;
+#pragma unroll
+        for (int e = 0; e < NV; e += 2) *reinterpret_cast<uint32_t *>(pp + e) = pk[e / 2];
+    }
 }
 
 // ---- combine (post warp): the CTA whose partial completed the item's page count merges all partials ----

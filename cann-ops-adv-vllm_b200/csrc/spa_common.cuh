@@ -19,6 +19,11 @@ constexpr int kMaxGroup = 16;        // q heads per kv head handled by one CTA (
 constexpr float kLog2e = 1.4426950408889634f;
 
 // One launch description, shared by every kernel of the chain.  Filled by the host plan.
+constexpr int kMaxPeers = 8;      // peers of one NVSwitch domain a launch stores its output rows to
+constexpr int kSigEpoch = 8;      // signal word holding this rank's launch count
+constexpr int kSigError = 9;      // set when a flag exchange timed out
+constexpr int kSigWaitNs = 10;    // words 10-11: uint64 total ns spent in the flag exchange (statistics)
+
 struct ChainParams {
     // ---- problem dims
     int B, Nq, Nkv, g;               // g = Nq / Nkv
@@ -35,6 +40,9 @@ struct ChainParams {
     const int *block_table; long long bt_stride;
     const int *seq_len;                                  // [B] int32 (total context length)
     const int *indices_in; long long idx_sb, idx_sh;     // select_position: given indices [B,Nq,k]
+    // reference deployment options, off by default as in the golden (spaExecutorSetSelectOptions)
+    int sink_pages, recent_pages;                        // always-selected first / last pages
+    int cap_den;                                         // > 0: at most pl / cap_den pages per head
     // ---- selection outputs
     int *indices_out;                                    // [B,Nq,k] (compute_cent) or null
     int *page_position;                                  // [B,Nq,MP] or null
@@ -47,6 +55,14 @@ struct ChainParams {
     const void *aq_scale, *aq_offset;                    // int8 KV: [2, Nkv, D] in q dtype (or null)
     int aq_per_tensor;
     void *out; long long out_sb, out_sh;
+    // ---- KV-head tensor parallelism: every output row is also stored into the gathered-output buffers of
+    // the peer GPUs (NVLink peer stores), and the launch ends with a flag exchange -- see spaExecutorSetPeerOutput
+    void *out_peer[kMaxPeers];                            // the n_peer peers' images of `out` (same strides); n_peer = 0: off
+    unsigned *sig_peer[kMaxPeers];                        // the peers' signal blocks; this rank writes word [tp_rank] of each
+    int peer_rank[kMaxPeers];                             // rank of peer i = word of sig_local it writes
+    unsigned *sig_local;                                  // own signal block: [rank] = launch count flagged by that rank,
+                                                          // [kSigEpoch] = own launch count, [kSigError] = time-out marker
+    int n_peer, tp_rank;
     float scale_log2;                                    // scale_value * log2(e)
     int ax_row, ax_head, ax_blk;                         // TMA coordinate slots (1..3)
     int num_blocks;

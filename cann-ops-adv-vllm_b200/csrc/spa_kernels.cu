@@ -38,6 +38,32 @@ __device__ __forceinline__ unsigned char *aligned_smem(unsigned char *raw) {
 // SyncAll between selection and attention becomes a producer/consumer page queue: CTAs only wait
 // for entries that are not published yet, so the launch is cooperative (co-residency) but has no
 // grid-wide barrier.
+// End of a tensor-parallel launch (last CTA, one thread).  Every CTA fenced its peer stores at system scope
+// before it reported, so after one more fence the flag stores below order behind ALL output rows of this
+// rank.  Then wait until every peer has flagged the same launch count: from there on the local gathered
+// buffer is complete and the stream may go on to its consumer.  The count lives in the signal words, not
+// in the parameters, so a captured CUDA graph replays correctly.
+__device__ __noinline__ void peer_exchange_flags(const ChainParams &p) {
+    const unsigned long long t_in = globaltimer_ns();
+    const unsigned e = p.sig_local[kSigEpoch] + 1u;
+    p.sig_local[kSigEpoch] = e;
+    __threadfence_system();
+    for (int i = 0; i < p.n_peer; ++i)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.sig_peer[i] + p.tp_rank), "r"(e) : "memory");
+    const unsigned long long t0 = globaltimer_ns();
+    for (int i = 0; i < p.n_peer; ++i) {
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p.sig_local + p.peer_rank[i]) : "memory");
+            if ((int)(v - e) >= 0) break;
+            if (globaltimer_ns() - t0 > 2000000000ull) { p.sig_local[kSigError] = e; return; }   // a peer never launched
+            __nanosleep(64);
+        }
+    }
+    // statistics: total ns this rank spent in the exchange (fence + flag stores + waiting for the peers)
+    *reinterpret_cast<unsigned long long *>(p.sig_local + kSigWaitNs) += globaltimer_ns() - t_in;
+}
+
 template <typename QT, bool KVI8, int NT>
 __global__ void __launch_bounds__(kThreads, 1)
 spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ CUtensorMap tmK,
@@ -59,10 +85,11 @@ spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ 
     __syncthreads();
     if (threadIdx.x == 0) {
         // the last CTA to leave returns the queue counters to zero for the next launch
-        __threadfence();
+        if (p.n_peer) __threadfence_system(); else __threadfence();
         if (atomicAdd(p.ctrl + Ctrl::kFinished, 1) == (int)gridDim.x - 1) {
             p.ctrl[Ctrl::kHead] = 0; p.ctrl[Ctrl::kTail] = 0;
             p.ctrl[Ctrl::kItemsDone] = 0; p.ctrl[Ctrl::kPool] = 0; p.ctrl[Ctrl::kFinished] = 0;
+            if (p.n_peer) peer_exchange_flags(p);
         }
     }
     trace_mark(p, 5);
@@ -372,10 +399,75 @@ int spaExecutorSetPersistentWorkspace(spaExecutor *e, int enable) {
     e->clean_ws = nullptr;
     return SPA_OK;
 }
+int spaExecutorSetSelectOptions(spaExecutor *e, int sinkPages, int recentPages, int maxFractionDen) {
+    if (!e) return fail(SPA_ERR_ARG, "bad executor");
+    if (e->op != OP_CENT_SELECT && e->op != OP_FUSION)
+        return fail(SPA_ERR_UNSUPPORTED, "select options apply to CentSelect and SparsePagedFusionAttention");
+    if (sinkPages < 0 || recentPages < 0 || maxFractionDen < 0 || sinkPages > 16 || recentPages > 16)
+        return fail(SPA_ERR_ARG, "select options: sink %d recent %d (0..16), fraction 1/%d", sinkPages, recentPages, maxFractionDen);
+    e->p.sink_pages = sinkPages; e->p.recent_pages = recentPages; e->p.cap_den = maxFractionDen;
+    return SPA_OK;
+}
 int spaExecutorSetTrace(spaExecutor *e, void *deviceBuffer) {
     if (!e) return fail(SPA_ERR_ARG, "bad executor");
     e->p.trace = (unsigned long long *)deviceBuffer;
     e->p.dbg = getenv("SPA_DBG_REPEAT") ? 1 : 0;
+    return SPA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// KV-head tensor parallelism: peer buffers and the fused output all-gather
+// ---------------------------------------------------------------------------------------------
+int spaPeerBufferCreate(uint64_t bytes, void **devPtr, unsigned char *ipcHandle) {
+    if (!devPtr || !ipcHandle || bytes == 0) return fail(SPA_ERR_ARG, "spaPeerBufferCreate: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == SPA_IPC_HANDLE_BYTES, "IPC handle size");
+    void *ptr = nullptr;
+    CUDA_TRY(cudaMalloc(&ptr, bytes));
+    cudaError_t rc = cudaMemset(ptr, 0, bytes);
+    cudaIpcMemHandle_t h;
+    if (rc == cudaSuccess) rc = cudaIpcGetMemHandle(&h, ptr);
+    if (rc != cudaSuccess) { cudaFree(ptr); return fail(SPA_ERR_CUDA, "spaPeerBufferCreate: %s", cudaGetErrorString(rc)); }
+    memcpy(ipcHandle, &h, sizeof(h));
+    *devPtr = ptr;
+    return SPA_OK;
+}
+int spaPeerBufferOpen(const unsigned char *ipcHandle, void **devPtr) {
+    if (!devPtr || !ipcHandle) return fail(SPA_ERR_ARG, "spaPeerBufferOpen: bad argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipcHandle, sizeof(h));
+    CUDA_TRY(cudaIpcOpenMemHandle(devPtr, h, cudaIpcMemLazyEnablePeerAccess));
+    return SPA_OK;
+}
+int spaPeerBufferClose(void *devPtr) {
+    if (devPtr) CUDA_TRY(cudaIpcCloseMemHandle(devPtr));
+    return SPA_OK;
+}
+int spaPeerBufferDestroy(void *devPtr) {
+    if (devPtr) CUDA_TRY(cudaFree(devPtr));
+    return SPA_OK;
+}
+int spaExecutorSetPeerOutput(spaExecutor *e, int rank, int world, void *const *gatheredOut, void *const *signals) {
+    if (!e) return fail(SPA_ERR_ARG, "bad executor");
+    ChainParams &p = e->p;
+    p.n_peer = 0; p.tp_rank = 0; p.sig_local = nullptr;
+    for (int i = 0; i < kMaxPeers; ++i) { p.out_peer[i] = nullptr; p.sig_peer[i] = nullptr; p.peer_rank[i] = 0; }
+    if (world <= 1 || !gatheredOut) return SPA_OK;
+    if (e->op != OP_FUSION && e->op != OP_ATTENTION) return fail(SPA_ERR_UNSUPPORTED, "peer output: only the attention ops write attentionOut");
+    if (world > kMaxPeers || rank < 0 || rank >= world || !signals) return fail(SPA_ERR_ARG, "peer output: rank %d of world %d (max %d)", rank, world, kMaxPeers);
+    for (int r = 0; r < world; ++r)
+        if (!gatheredOut[r] || !signals[r]) return fail(SPA_ERR_ARG, "peer output: null buffer for rank %d", r);
+    const ptrdiff_t delta = (const char *)p.out - (const char *)gatheredOut[rank];
+    if (delta < 0) return fail(SPA_ERR_ARG, "peer output: attentionOut is not a view into the local gathered buffer");
+    int n = 0;
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) continue;
+        p.out_peer[n] = (char *)gatheredOut[r] + delta;
+        p.sig_peer[n] = (unsigned *)signals[r];
+        p.peer_rank[n] = r;
+        ++n;
+    }
+    p.sig_local = (unsigned *)signals[rank];
+    p.n_peer = n; p.tp_rank = rank;
     return SPA_OK;
 }
 

@@ -779,6 +779,15 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
                 m |= (hit ? 1u : 0u) << h;
             }
         }
+        if (p.sink_pages | p.recent_pages) {
+            // anchor pages of the reference kernels (cent_select.cpp:350-362, fused ..._Us2.h:1930-1940): every
+            // position whose block_table entry equals that of one of the first `sink` / last `recent` pages
+            const int v = physS[i];
+            bool forced = false;
+            for (int j = 0; j < min(p.sink_pages, pl); ++j) forced |= (v == physS[j]);
+            for (int j = max(pl - p.recent_pages, 0); j < pl; ++j) forced |= (v == physS[j]);
+            if (forced) m |= (1u << g) - 1u;
+        }
         if (has_tail && i == pl - 1) m |= m << 16;
         pm[i] = m;
         if (FLAGS & kSelGather)
@@ -795,7 +804,10 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     // pass 1: per 32-page chunk, the number of set bits of every head plane (and of the union)
     const int nch = (pl + 31) >> 5;
     const unsigned lt = (1u << lane) - 1u;
-    const bool may_trunc = pl > p.MP;
+    // page budget per head: max_page_num, and pl / cap_den when the reference's workload clamp is on
+    // (cent_select.cpp:218,410-414: the first pl/8 positions are kept)
+    const int cap = (p.cap_den > 0) ? min(p.MP, pl / p.cap_den) : p.MP;
+    const bool may_trunc = pl > cap;
     const int tail_cnt = has_tail ? rem : p.bs;
 #pragma unroll 1
     for (int ch = G.warp; ch < nch; ch += G.gw) {
@@ -829,7 +841,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
                 run += __shfl_sync(0xffffffffu, inc, 31);
             }
             if (lane == 0) {
-                if (col < g) { hd[col].total = min(run, p.MP); if (run > p.MP) miscI[8] = 1; }
+                if (col < g) { hd[col].total = min(run, cap); if (run > cap) miscI[8] = 1; }
                 else {
                     miscI[9] = run;
                     // no head can overflow max_page_num when the sequence has no more pages than that:
@@ -883,7 +895,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     } else {
         // a head selected more than max_page_num pages: serial path that truncates consistently
         for (int h = G.warp; h < g; h += G.gw) {
-            const int c = warp_compact_bit(pm, pl, h, pp0 ? pp0 + (size_t)h * p.MP : nullptr, p.MP);
+            const int c = warp_compact_bit(pm, pl, h, pp0 ? pp0 + (size_t)h * p.MP : nullptr, cap);
             if (p.page_position_length && lane < kPad)
                 p.page_position_length[((size_t)b * p.Nq + hq0 + h) * kPad + lane] = c;
             if (lane == 0) hd[h].total = c;

@@ -104,11 +104,16 @@ def select_position(block_ids: torch.Tensor, block_table: torch.Tensor, seq_len:
 
 def cent_select(query: torch.Tensor, l1_cent: torch.Tensor, block_ids: torch.Tensor,
                 block_table: torch.Tensor, seq_len: torch.Tensor, *, k: int = 64,
-                max_page_num: int = 256,
-                block_size: int = 128) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    """-> (page_position, page_position_length, max_page_position_length) (add_custom.py:89-93)."""
+                max_page_num: int = 256, block_size: int = 128, sink_pages: int = 0, recent_pages: int = 0,
+                max_fraction_den: int = 0) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """-> (page_position, page_position_length, max_page_position_length) (add_custom.py:89-93).
+
+    `sink_pages`, `recent_pages`, `max_fraction_den`: what the reference KERNEL hard-codes as 1, 2 and 8
+    (anchor pages always selected, at most P/8 pages per head; cent_select.cpp:218,350-362,410-414) but its
+    golden lacks; off by default (= the golden)."""
     return custom_ops_lib.cent_select_ex(query, l1_cent, block_ids, block_table, seq_len, int(k),
-                                         int(max_page_num), int(block_size))
+                                         int(max_page_num), int(block_size), int(sink_pages), int(recent_pages),
+                                         int(max_fraction_den))
 
 
 def sparse_paged_fusion_attention(query: torch.Tensor,
@@ -138,7 +143,8 @@ def sparse_paged_fusion_attention(query: torch.Tensor,
                                   num_key_value_heads: int,
                                   block_size: int,
                                   inner_precise: int,
-                                  *, k: int = 64) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+                                  *, k: int = 64, sink_pages: int = 0, recent_pages: int = 0,
+                                  max_fraction_den: int = 0) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     """CentSelect + sparse paged attention in ONE launch (add_custom.py:96-135).
 
     `block_position`, `page_position_length`, `max_page_position_length` are caller-allocated and
@@ -154,7 +160,7 @@ def sparse_paged_fusion_attention(query: torch.Tensor,
         l1_cent, block_ids, total_seq_len,
         block_position, page_position_length, max_page_position_length,
         int(num_heads), float(scale_value), input_layout, int(num_key_value_heads), int(block_size),
-        int(inner_precise), int(k))
+        int(inner_precise), int(k), int(sink_pages), int(recent_pages), int(max_fraction_den))
 
 
 class FusedDecodePlan:
@@ -166,7 +172,8 @@ class FusedDecodePlan:
     def __init__(self, query, key, value, blocktable, l1_cent, block_ids, total_seq_len,
                  block_position, page_position_length, max_page_position_length, attention_out,
                  num_heads, scale_value, num_key_value_heads, block_size=128, *, k=64,
-                 antiquant_scale=None, antiquant_offset=None, input_layout="BNSD", inner_precise=1):
+                 antiquant_scale=None, antiquant_offset=None, input_layout="BNSD", inner_precise=1,
+                 sink_pages=0, recent_pages=0, max_fraction_den=0):
         empty = torch.empty(0, dtype=query.dtype, device=query.device)
         self.attention_out = attention_out
         self._plan = custom_ops_lib.make_fusion_plan(
@@ -174,7 +181,8 @@ class FusedDecodePlan:
             empty if antiquant_offset is None else antiquant_offset, blocktable, l1_cent, block_ids,
             total_seq_len, block_position, page_position_length, max_page_position_length,
             attention_out, int(num_heads), float(scale_value), input_layout,
-            int(num_key_value_heads), int(block_size), int(inner_precise), int(k))
+            int(num_key_value_heads), int(block_size), int(inner_precise), int(k), int(sink_pages),
+            int(recent_pages), int(max_fraction_den))
 
     @property
     def workspace_bytes(self) -> int:

@@ -84,6 +84,16 @@ SPA_API int spaExecutorSetTrace(spaExecutor *executor, void *deviceBuffer);
  * may set this flag: the workspace is then cleared once, on the first launch that sees it.       */
 SPA_API int spaExecutorSetPersistentWorkspace(spaExecutor *executor, int enable);
 
+/* Selection options the reference KERNELS hard-code but its golden (tests/utils.py) lacks -- off by default,
+ * so the default behaviour is the golden's.  For CentSelect and SparsePagedFusionAttention.
+ *   sinkPages, recentPages: every logical page whose block_table entry equals that of one of the first
+ *       sinkPages / last recentPages pages of the sequence is selected for every head (reference: 1 and 2,
+ *       cent_select.cpp:350-362; fused kernel sparse_paged_fusion_attention_split_Bbn2s2_Us2.h:1930-1940).
+ *   maxFractionDen > 0: a head keeps at most ceil(seq/blockSize) / maxFractionDen pages, the lowest positions
+ *       first (reference: 8, cent_select.cpp:218,410-414).  Entries of pagePosition beyond the kept length are
+ *       padded with 0x7fffffff here (the reference leaves them; its consumers read only `length` entries). */
+SPA_API int spaExecutorSetSelectOptions(spaExecutor *executor, int sinkPages, int recentPages, int maxFractionDen);
+
 /* ---- ComputeCent: replaces aclnnComputeCentGetWorkspaceSize / aclnnComputeCent
  *      (misc/aclnn_compute_cent.h; kernel compute_cent/compute_cent.cpp:345).
  * query [B,Nq,D] (or [B,Nq,1,D]) f16/bf16, l1Cent [Nkv,C,D] same dtype,
@@ -172,6 +182,36 @@ SPA_API int spaSparsePagedFusionAttentionGetWorkspaceSize(
     const spaTensor *attentionOut, uint64_t *workspaceSize, spaExecutor **executor);
 SPA_API int spaSparsePagedFusionAttention(void *workspace, uint64_t workspaceSize,
                                           spaExecutor *executor, spaStream stream);
+
+/* ---- KV-head tensor parallelism: the output all-gather fused into the launch (the reference
+ *      has no distributed code on this path, so there is no interface to cite).  One process per GPU; rank r
+ *      owns a contiguous range of KV heads and computes attentionOut[:, its query heads, :].  With peer output
+ *      set, every output row is stored into the gathered buffer [B, Nq_total, D] of EVERY rank by NVLink peer
+ *      stores from the combine epilogue, and the launch ends with a flag exchange (release/acquire at system
+ *      scope): when the launch completes on a rank's stream, that rank's gathered buffer holds the rows of all
+ *      ranks.  No NCCL call, no extra launch.
+ *
+ * spaPeerBufferCreate   cudaMalloc + zero-fill + CUDA IPC handle (64 bytes) to send to the other processes.
+ * spaPeerBufferOpen     map a peer's buffer into this process (cudaIpcOpenMemHandle, peer access enabled).
+ * spaExecutorSetPeerOutput
+ *     gatheredOut[r], r in [0, world): rank r's image of the gathered buffer as mapped in THIS process
+ *     (gatheredOut[rank] is the local one).  The executor's attentionOut must be a view into the local
+ *     image; the same byte offset and strides are used in every peer image.
+ *     signals[r]: rank r's signal block (>= 64 bytes, zero when first used, never written by the caller);
+ *     word [i] = launches flagged by rank i, word [8] = own launch count, word [9] != 0: an exchange timed out
+ *     (a peer did not launch within 2 s), words [10..11] = uint64 total ns this rank spent in the exchanges.
+ *     Every rank must launch the same number of times.  A caller that re-launches before its PEERS have
+ *     consumed their gathered buffer must alternate between two buffers (two executors): a rank cannot
+ *     finish launch t before every peer has finished launch t, so buffer t%2 is never overwritten while a
+ *     peer still reads it.   world <= 1 or gatheredOut == NULL switches peer output off.                   */
+#define SPA_IPC_HANDLE_BYTES 64
+#define SPA_MAX_PEERS 8
+SPA_API int spaPeerBufferCreate(uint64_t bytes, void **devPtr, unsigned char *ipcHandle);
+SPA_API int spaPeerBufferOpen(const unsigned char *ipcHandle, void **devPtr);
+SPA_API int spaPeerBufferClose(void *devPtr);
+SPA_API int spaPeerBufferDestroy(void *devPtr);
+SPA_API int spaExecutorSetPeerOutput(spaExecutor *executor, int rank, int world,
+                                     void *const *gatheredOut, void *const *signals);
 
 #ifdef __cplusplus
 }

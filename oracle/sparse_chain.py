@@ -82,6 +82,9 @@ def select_position(
     indices: torch.Tensor,       # [B, Nq, k] int
     block_size: int = 128,
     max_page_num: int = 256,
+    sink_pages: int = 0,
+    recent_pages: int = 0,
+    max_fraction_den: int = 0,
 ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     """Follows tests/utils.py:4-84 (golden) with the op's output shapes (add_custom.cpp:955-977):
 
@@ -92,6 +95,10 @@ def select_position(
     The table value is clamped into [0, kvPageLen-1] for the block_ids lookup exactly as the golden
     does (utils.py:62).  Selections beyond max_page_num are dropped (the golden's width is
     max_b(pl); the op's is the fixed 256, add_custom.cpp:958).
+
+    sink_pages / recent_pages / max_fraction_den restate what the reference KERNEL adds to the golden
+    (cent_select.cpp:350-362: mask |= block_table == block_table[0], [pl-2], [pl-1], compared by VALUE;
+    :218,410-414: length = min(count, pl // 8), lowest positions first).  0 = off = the golden.
     """
     bid = block_ids.detach().cpu().numpy().astype(np.int64)
     bt = block_table.detach().cpu().numpy().astype(np.int64)
@@ -116,7 +123,11 @@ def select_position(
             c = bid[h // g, page_idx]                      # [pl]
             gather[b, h, :pl] = c
             mask = np.isin(c, idx[b, h])
-            p = np.nonzero(mask)[0][:max_page_num]
+            if sink_pages or recent_pages:
+                anchors = np.concatenate([bt[b, :min(sink_pages, pl)], bt[b, max(pl - recent_pages, 0):pl]])
+                mask |= np.isin(bt[b, :pl], anchors)
+            cap = min(max_page_num, pl // max_fraction_den) if max_fraction_den > 0 else max_page_num
+            p = np.nonzero(mask)[0][:cap]
             pos[b, h, : p.size] = p
             plen[b, h, :] = p.size
     return torch.from_numpy(pos), torch.from_numpy(plen), torch.from_numpy(gather)
@@ -130,12 +141,14 @@ def max_page_position_length(page_position_length: torch.Tensor, block_size: int
 
 
 def cent_select(query, l1_cent, block_ids, block_table, seq_len, k: int = 64,
-                block_size: int = 128, max_page_num: int = 256):
+                block_size: int = 128, max_page_num: int = 256, sink_pages: int = 0, recent_pages: int = 0,
+                max_fraction_den: int = 0):
     """custom_ops.cent_select (add_custom.py:89-93; add_custom.cpp:979-1008).  Batch is taken from
     seq_len (add_custom.cpp:988), so query may carry more rows than seq_len."""
     B = seq_len.shape[0]
     indices = compute_cent(query[:B], l1_cent, k)
-    pos, plen, _ = select_position(block_ids, block_table, seq_len, indices, block_size, max_page_num)
+    pos, plen, _ = select_position(block_ids, block_table, seq_len, indices, block_size, max_page_num,
+                                   sink_pages, recent_pages, max_fraction_den)
     return pos, plen, max_page_position_length(plen, block_size)
 
 
@@ -317,13 +330,14 @@ def sparse_paged_fusion_attention(query, key, value, block_table, l1_cent, block
                                   num_heads: int, scale_value: float, num_key_value_heads: int,
                                   block_size: int = 128, k: int = 64, max_page_num: int = 256,
                                   antiquant_scale=None, antiquant_offset=None,
-                                  round_p: bool = True, dtype64: bool = False):
+                                  round_p: bool = True, dtype64: bool = False, sink_pages: int = 0,
+                                  recent_pages: int = 0, max_fraction_den: int = 0):
     """custom_ops.sparse_paged_fusion_attention (add_custom.py:96-135): cent_select followed by the
     attention over the selected pages (sparse_paged_fusion_attention.cpp:56-76).  Returns
     (attention_out, block_position, page_position_length, max_page_position_length)."""
     B = total_seq_len.shape[0]
     pos, plen, mx = cent_select(query, l1_cent, block_ids, block_table, total_seq_len, k,
-                                block_size, max_page_num)
+                                block_size, max_page_num, sink_pages, recent_pages, max_fraction_den)
     lists = lists_from_selection(pos, plen, total_seq_len, block_size)
     out = attend_lists(query[:B], key, value, block_table, lists, num_key_value_heads, scale_value,
                        block_size, antiquant_scale, antiquant_offset, round_p, dtype64)

@@ -431,3 +431,56 @@ def test_torch_ops_namespace_and_plan(ops):
     gr.replay()
     torch.cuda.synchronize()
     torch.testing.assert_close(out2.float(), out.float(), rtol=1e-3, atol=1e-3)
+
+
+# ------------------------------------------------------------------------------------------
+# the vLLM-style caller (persistent buffers, per-batch-size executors, CUDA graphs)
+# ------------------------------------------------------------------------------------------
+def test_decode_backend_matches_oracle_across_batch_sizes_and_graph_replay(ops):
+    from decode_backend import SparseDecodeBackend
+    Nq, Nkv, C, S, k = 32, 8, 128, 8192, 16
+    P = S // 128
+    c = make_case(311, 4, Nq, Nkv, C, S, kv_pages=4 * P + 5, ragged=True, permute_table=True)
+    g = to_device(c, DEV)
+    be = SparseDecodeBackend(Nq, Nkv, 128, 128, k, max_batch=4, max_blocks_per_seq=P + 3, dtype=torch.float16,
+                             device=DEV, scale=c["scale"])
+    be.bind_cache(g["key"], g["value"], g["l1"], g["block_ids"])
+    for B, graph in [(4, False), (2, False), (3, True), (3, True), (4, True)]:
+        q = (torch.rand(B, Nq, 128, generator=torch.Generator().manual_seed(B * 7 + graph)) * 0.9).half()
+        want = oc.sparse_paged_fusion_attention(q, c["key"], c["value"], c["block_table"][:B], c["l1"], c["block_ids"],
+                                                c["seq"][:B], Nq, c["scale"], Nkv, 128, k, be.max_page_num)
+        out = be.forward_decode(q.to(DEV).unsqueeze(2), g["block_table"][:B], g["seq"][:B], use_graph=graph)
+        torch.cuda.synchronize()
+        assert out.shape == (B, Nq, 128)
+        assert_close(out, want[0], 1e-3, f"backend B={B} graph={graph}")
+        bp, ppl, mx = be.selection(B)
+        assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2]) and torch.equal(mx.cpu(), want[3])
+    with pytest.raises(ValueError):
+        be.forward_decode(torch.zeros(5, Nq, 128, dtype=torch.float16, device=DEV), g["block_table"][:4], g["seq"][:4])
+
+
+# ------------------------------------------------------------------------------------------
+# reference-kernel compatibility options (anchor pages, P/8 clamp)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("opts", [dict(sink_pages=1, recent_pages=2), dict(sink_pages=1, recent_pages=2, max_fraction_den=8),
+                                  dict(max_fraction_den=4), dict(sink_pages=3)])
+def test_anchor_pages_and_clamp_options(ops, opts):
+    B, Nq, Nkv, C, S, k = 3, 32, 8, 128, 8192, 8
+    c = make_case(401, B, Nq, Nkv, C, S, kv_pages=160, ragged=True)       # block_table with collisions
+    g = to_device(c, DEV)
+    wpos, wlen, wmx = oc.cent_select(c["q"], c["l1"], c["block_ids"], c["block_table"], c["seq"], k, 128, 256, **opts)
+    pos, ln, mx = ops.cent_select(g["q"], g["l1"], g["block_ids"], g["block_table"], g["seq"], k=k, **opts)
+    assert torch.equal(pos.cpu(), wpos) and torch.equal(ln.cpu(), wlen) and torch.equal(mx.cpu(), wmx)
+    want = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"],
+                                            c["seq"], Nq, c["scale"], Nkv, 128, k, 256, **opts)
+    dev = g["q"].device
+    bp = torch.full((B, Nq, 256), 7, dtype=torch.int32, device=dev)
+    ppl = torch.full((B, Nq, 8), 7, dtype=torch.int32, device=dev)
+    mppl = torch.full((B, 8), 7, dtype=torch.int64, device=dev)
+    e = torch.empty(0, dtype=torch.float16, device=dev)
+    e64 = torch.empty(0, dtype=torch.int64, device=dev)
+    out, _, _ = ops.sparse_paged_fusion_attention(
+        g["q"], g["key"], g["value"], e, e, e64, e, e, e, e, e, e, e, g["block_table"], e64, g["l1"], g["block_ids"],
+        g["seq"], bp, ppl, mppl, Nq, c["scale"], "BNSD", Nkv, 128, 1, k=k, **opts)
+    assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2]) and torch.equal(mppl.cpu(), want[3])
+    assert_close(out, want[0], 1e-3, f"fused with {opts}")

@@ -74,3 +74,32 @@ def test_topk_tie_break_lowest_index():
     s[0, 0, [3, 7, 9]] = 1.0
     got = oc.topk_indices(s, 6)
     assert got.tolist() == [[[3, 7, 9, 0, 1, 2]]]
+
+
+def test_reference_kernel_anchor_and_clamp_options():
+    """sink / recent anchor pages and the P/8 clamp of the reference kernels
+    (cent_select.cpp:218,350-362,410-414) as oracle options; off = the golden."""
+    import torch
+    from oracle import sparse_chain as oc
+    Nkv, Nq, C, P = 2, 4, 16, 40
+    g = torch.Generator().manual_seed(5)
+    block_ids = torch.randint(0, C, (Nkv, 64), generator=g, dtype=torch.int32)
+    block_table = torch.randperm(64, generator=g)[:P].view(1, P).to(torch.int32)
+    seq = torch.tensor([P * 128 - 5], dtype=torch.int32)
+    idx = torch.randint(0, C, (1, Nq, 2), generator=g, dtype=torch.int32)
+    p0, l0, _ = oc.select_position(block_ids, block_table, seq, idx)
+    p1, l1, _ = oc.select_position(block_ids, block_table, seq, idx, sink_pages=1, recent_pages=2)
+    for h in range(Nq):
+        a = set(p0[0, h, :l0[0, h, 0]].tolist())
+        b = p1[0, h, :l1[0, h, 0]].tolist()
+        assert b == sorted(a | {0, P - 2, P - 1})
+    p2, l2, _ = oc.select_position(block_ids, block_table, seq, idx, sink_pages=1, recent_pages=2, max_fraction_den=8)
+    for h in range(Nq):
+        n = min(int(l1[0, h, 0]), P // 8)
+        assert int(l2[0, h, 0]) == n and p2[0, h, :n].tolist() == p1[0, h, :n].tolist()
+        assert (p2[0, h, n:] == oc.INT32_MAX).all()
+    # value comparison: a colliding block_table entry drags its position in, as the kernel's CompareScalar does
+    bt2 = block_table.clone()
+    bt2[0, 7] = bt2[0, 0]
+    p3, l3, _ = oc.select_position(block_ids, bt2, seq, idx, sink_pages=1)
+    assert all(7 in p3[0, h, :l3[0, h, 0]].tolist() for h in range(Nq))
