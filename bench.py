@@ -378,14 +378,20 @@ def main():
         sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
-    xch0 = plan.out.exchange_ns() if peer else 0
+    xch0 = (plan.out.exchange_ns(), plan.out.exchange_send_ns()) if peer else (0, 0)
     for s0, s1 in ev:
         pre_step()
         s0.record()
         run_step()
         s1.record()
     barrier()
-    xch_us = (plan.out.exchange_ns() - xch0) / args.steps / 1e3 if peer else None
+    xch_us = None
+    if peer:
+        mine = torch.tensor([(plan.out.exchange_ns() - xch0[0]) / args.steps / 1e3,
+                             (plan.out.exchange_send_ns() - xch0[1]) / args.steps / 1e3], dtype=torch.float64, device=dev)
+        allx = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allx, mine)
+        xch_us = {"total_per_rank": [round(x[0].item(), 2) for x in allx], "fence_and_flags_per_rank": [round(x[1].item(), 2) for x in allx]}
     times = [a.elapsed_time(b) for a, b in ev]                      # ms
     total_ms = torch.tensor([sum(times)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -484,7 +490,7 @@ def main():
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
                     "api": "peer_gather.TPFusedDecode.launch" if peer else "custom_ops.sparse_paged_fusion_attention"},
             "gpu_launches": launches_per_step * args.steps,
-            "tp_flag_exchange_us_per_step_rank0": xch_us,
+            "tp_flag_exchange_us_per_step": xch_us,
             "clocks": clocks,
         }
         if cpu is not None:

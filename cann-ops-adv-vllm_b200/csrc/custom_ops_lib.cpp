@@ -67,6 +67,12 @@ struct ExecGuard {
     ~ExecGuard() { if (e) spaDestroyExecutor(e); }
 };
 
+void set_lse(spaExecutor *e, const c10::optional<at::Tensor> &lse, const char *what) {
+    if (!lse.has_value() || !lse->defined() || lse->numel() == 0) return;
+    Desc d = desc(*lse, "softmax_lse");
+    check(spaExecutorSetSoftmaxLse(e, d.ptr()), what);
+}
+
 at::Tensor alloc_ws(uint64_t bytes, const at::Tensor &like) {
     return at::empty({(int64_t)std::max<uint64_t>(bytes, 256)}, like.options().dtype(at::kByte));
 }
@@ -158,19 +164,38 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select(const at::Tensor &que
                           kDefaultBlockSize, 0, 0, 0);
 }
 
+// centroid maintenance (no reference counterpart): updates block_ids in place, optionally returns page means
+at::Tensor assign_page_clusters(const at::Tensor &key, const at::Tensor &l1_cent, const at::Tensor &page_ids,
+                                const c10::optional<at::Tensor> &page_tokens, at::Tensor block_ids, int64_t block_size,
+                                bool return_mean) {
+    TORCH_CHECK(key.is_cuda(), "assign_page_clusters: the CUDA extension only runs on CUDA tensors");
+    c10::cuda::CUDAGuard guard(key.device());
+    at::Tensor mean;
+    if (return_mean) mean = at::empty({page_ids.numel(), l1_cent.size(0), l1_cent.size(2)}, key.options().dtype(at::kFloat));
+    Desc k = desc(key, "key"), c = desc(l1_cent, "l1_cent"), pi = desc(page_ids, "page_ids"),
+         pt = desc(page_tokens.has_value() ? *page_tokens : at::Tensor(), "page_tokens"),
+         bi = desc(block_ids, "block_ids"), pm = desc(mean, "page_mean");
+    uint64_t ws = 0; ExecGuard g;
+    check(spaAssignPageClustersGetWorkspaceSize(k.ptr(), c.ptr(), pi.ptr(), pt.ptr(), block_size, bi.ptr(), pm.ptr(), &ws, &g.e),
+          "assign_page_clusters");
+    check(spaAssignPageClusters(nullptr, 0, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "assign_page_clusters");
+    return return_mean ? mean : block_ids;
+}
+
 const at::Tensor &single(const std::vector<at::Tensor> &l, const char *name) {
     TORCH_CHECK(l.size() == 1, name, ": expected a 1-element tensor list (add_custom.py:70-75)");
     return l[0];
 }
 
-at::Tensor sparse_paged_attention(
+at::Tensor sparse_paged_attention_ex(
     const at::Tensor &query, const std::vector<at::Tensor> &key_list, const std::vector<at::Tensor> &value_list,
     const at::Tensor &pse_shift, const at::Tensor &attention_mask, const at::Tensor &actual_seq_lengths,
     const at::Tensor &dequant_scale1, const at::Tensor &quant_scale1, const at::Tensor &dequant_scale2,
     const at::Tensor &quant_scale2, const at::Tensor &quant_offset2, const at::Tensor &antiquant_scale,
     const at::Tensor &antiquant_offset, const at::Tensor &blocktable, const at::Tensor &kv_padding_size,
     const at::Tensor &blockposition, int64_t num_heads, double scale_value, std::string input_layout,
-    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise) {
+    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise,
+    const c10::optional<at::Tensor> &softmax_lse) {
     TORCH_CHECK(query.is_cuda(), "sparse_paged_attention: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(query.device());
     const at::Tensor &key = single(key_list, "key_list"), &value = single(value_list, "value_list");
@@ -191,10 +216,25 @@ at::Tensor sparse_paged_attention(
                                                   kp.ptr(), bp.ptr(), num_heads, scale_value, input_layout.c_str(),
                                                   num_key_value_heads, block_size, inner_precise, o.ptr(), &ws, &g.e),
           "sparse_paged_attention");
+    set_lse(g.e, softmax_lse, "sparse_paged_attention");
     at::Tensor wsp = alloc_ws(ws, query);
     check(spaSparsePagedAttention(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()),
           "sparse_paged_attention");
     return out;
+}
+at::Tensor sparse_paged_attention(
+    const at::Tensor &query, const std::vector<at::Tensor> &key_list, const std::vector<at::Tensor> &value_list,
+    const at::Tensor &pse_shift, const at::Tensor &attention_mask, const at::Tensor &actual_seq_lengths,
+    const at::Tensor &dequant_scale1, const at::Tensor &quant_scale1, const at::Tensor &dequant_scale2,
+    const at::Tensor &quant_scale2, const at::Tensor &quant_offset2, const at::Tensor &antiquant_scale,
+    const at::Tensor &antiquant_offset, const at::Tensor &blocktable, const at::Tensor &kv_padding_size,
+    const at::Tensor &blockposition, int64_t num_heads, double scale_value, std::string input_layout,
+    int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise) {
+    return sparse_paged_attention_ex(query, key_list, value_list, pse_shift, attention_mask, actual_seq_lengths,
+                                     dequant_scale1, quant_scale1, dequant_scale2, quant_scale2, quant_offset2,
+                                     antiquant_scale, antiquant_offset, blocktable, kv_padding_size, blockposition,
+                                     num_heads, scale_value, input_layout, num_key_value_heads, block_size,
+                                     inner_precise, c10::nullopt);
 }
 
 // ---- fused op: plan object so callers can keep a launch-ready executor (CUDA graphs, serving) --
@@ -213,7 +253,7 @@ std::shared_ptr<FusionPlan> make_fusion_plan(
     const at::Tensor &page_position_length, const at::Tensor &max_page_position_length,
     const at::Tensor &attention_out, int64_t num_heads, double scale_value, const std::string &input_layout,
     int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k, int64_t sink_pages,
-    int64_t recent_pages, int64_t max_fraction_den) {
+    int64_t recent_pages, int64_t max_fraction_den, const c10::optional<at::Tensor> &softmax_lse) {
     TORCH_CHECK(query.is_cuda(), "sparse_paged_fusion_attention: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(query.device());
     auto plan = std::make_shared<FusionPlan>();
@@ -233,11 +273,14 @@ std::shared_ptr<FusionPlan> make_fusion_plan(
     if (sink_pages | recent_pages | max_fraction_den)
         check(spaExecutorSetSelectOptions(plan->exec, (int)sink_pages, (int)recent_pages, (int)max_fraction_den),
               "sparse_paged_fusion_attention");
+    set_lse(plan->exec, softmax_lse, "sparse_paged_fusion_attention");
+    if (softmax_lse.has_value() && softmax_lse->defined()) plan->keep.push_back(*softmax_lse);
     plan->workspace = alloc_ws(plan->ws_bytes, query);
     // the plan owns its workspace and nothing else writes to it: the queue words need clearing only once
     check(spaExecutorSetPersistentWorkspace(plan->exec, 1), "spaExecutorSetPersistentWorkspace");
-    plan->keep = {query, key, value, antiquant_scale, antiquant_offset, blocktable, l1_cent, block_ids,
-                  total_seq_len, block_position, page_position_length, max_page_position_length, attention_out};
+    for (const at::Tensor &t : std::vector<at::Tensor>{query, key, value, antiquant_scale, antiquant_offset, blocktable, l1_cent, block_ids,
+                  total_seq_len, block_position, page_position_length, max_page_position_length, attention_out})
+        plan->keep.push_back(t);
     return plan;
 }
 
@@ -258,7 +301,7 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention_ex(
     const at::Tensor &block_position, const at::Tensor &page_position_length,
     const at::Tensor &max_page_position_length, int64_t num_heads, double scale_value, std::string input_layout,
     int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k, int64_t sink_pages,
-    int64_t recent_pages, int64_t max_fraction_den) {
+    int64_t recent_pages, int64_t max_fraction_den, const c10::optional<at::Tensor> &softmax_lse) {
     TORCH_CHECK(query.is_cuda(), "sparse_paged_fusion_attention: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(query.device());
     const at::Tensor &key = single(key_list, "key_list"), &value = single(value_list, "value_list");
@@ -285,6 +328,7 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention_ex(
     if (sink_pages | recent_pages | max_fraction_den)
         check(spaExecutorSetSelectOptions(g.e, (int)sink_pages, (int)recent_pages, (int)max_fraction_den),
               "sparse_paged_fusion_attention");
+    set_lse(g.e, softmax_lse, "sparse_paged_fusion_attention");
     at::Tensor wsp = alloc_ws(ws, query);
     check(spaSparsePagedFusionAttention(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()),
           "sparse_paged_fusion_attention");
@@ -307,7 +351,7 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention(
                                             kv_padding_size, l1_cent, block_ids, total_seq_len, block_position,
                                             page_position_length, max_page_position_length, num_heads, scale_value,
                                             input_layout, num_key_value_heads, block_size, inner_precise, kDefaultK,
-                                            0, 0, 0);
+                                            0, 0, 0, c10::nullopt);
 }
 
 at::Tensor incre_flash_attention_v4(
@@ -412,6 +456,8 @@ PYBIND11_MODULE(custom_ops_lib, m) {
     m.def("select_position_ex", &select_position_ex);
     m.def("cent_select_ex", &cent_select_ex);
     m.def("sparse_paged_fusion_attention_ex", &sparse_paged_fusion_attention_ex);
+    m.def("sparse_paged_attention_ex", &sparse_paged_attention_ex);
+    m.def("assign_page_clusters", &assign_page_clusters);
     pybind11::class_<FusionPlan, std::shared_ptr<FusionPlan>>(m, "FusionPlan")
         .def_property_readonly("workspace_bytes", [](const FusionPlan &p) { return p.ws_bytes; })
         .def_property_readonly("num_launches", [](const FusionPlan &p) { return spaExecutorNumLaunches(p.exec); })

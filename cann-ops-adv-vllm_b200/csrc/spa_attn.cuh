@@ -86,6 +86,13 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
     }
 }
 
+// softmax log-sum-exp of one (b, head) row: ln(sum_i exp(s_i)) with s = scale * q.k, from the running max (log2
+// domain) and the sum of 2^(s2 - max) (the reference's optional softmaxLse output, ..._Us2.h:2601-2623)
+__device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, int h, float m2, float lsum) {
+    p.lse[(size_t)b * p.lse_sb + (size_t)(n2 * p.g + h) * p.lse_sh] =
+        (lsum > 0.f) ? (m2 + log2f(lsum)) * 0.6931471805599453f : -INFINITY;
+}
+
 // ---- combine (post warp): the CTA whose partial completed the item's page count merges all partials ----
 // A CTA that left a partial for a segment starting at queue index i wrote (slot + 1) into flat[i]
 // (the entry itself was consumed and zeroed before); the item's range is scanned for those marks.
@@ -175,6 +182,7 @@ __device__ void combine_item_warp(const ChainParams &p, int item, int base, int 
 #pragma unroll
             for (int o = 16; o; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
             if (e < nh) write_out_vals<QT, KVI8, 4>(p, b, n2, h0 + e, lane * 4, acc[e], L);
+            if (e < nh && p.lse != nullptr && lane == 0) write_lse(p, b, n2, h0 + e, M[e], L);
         }
     }
     if (lane == 0) { p.item_info[item] = 0ull; p.ctrl[Ctrl::pages_done(p.B, item)] = 0; }
@@ -311,6 +319,7 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
             const int d0 = half * kMergeHalf + lane * 2;
             if (whole) {
                 if (h < p.g) write_out_vals<QT, KVI8, 2>(p, b, n2, h, d0, acc, Ls);
+                if (h < p.g && half == 0 && lane == 0 && p.lse != nullptr) write_lse(p, b, n2, h, M, Ls);
             } else {
                 *reinterpret_cast<float2 *>(p.part_o + ((size_t)slot * HP + h) * kD + d0) = make_float2(acc[0], acc[1]);
             }

@@ -55,6 +55,7 @@ struct ChainParams {
     const void *aq_scale, *aq_offset;                    // int8 KV: [2, Nkv, D] in q dtype (or null)
     int aq_per_tensor;
     void *out; long long out_sb, out_sh;
+    float *lse; long long lse_sb, lse_sh;                // optional softmax log-sum-exp [B, Nq] (natural log), or null
     // ---- KV-head tensor parallelism: every output row is also stored into the gathered-output buffers of
     // the peer GPUs (NVLink peer stores), and the launch ends with a flag exchange -- see spaExecutorSetPeerOutput
     void *out_peer[kMaxPeers];                            // the n_peer peers' images of `out` (same strides); n_peer = 0: off

@@ -15,6 +15,7 @@
 #include <new>
 
 #include "../../include/spa_b200.h"
+#include "spa_assign.cuh"
 #include "spa_attn.cuh"
 #include "spa_common.cuh"
 #include "spa_select.cuh"
@@ -47,10 +48,11 @@ __device__ __noinline__ void peer_exchange_flags(const ChainParams &p) {
     const unsigned long long t_in = globaltimer_ns();
     const unsigned e = p.sig_local[kSigEpoch] + 1u;
     p.sig_local[kSigEpoch] = e;
-    __threadfence_system();
+    asm volatile("fence.acq_rel.sys;" ::: "memory");        // one release fence, then relaxed flag stores
     for (int i = 0; i < p.n_peer; ++i)
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.sig_peer[i] + p.tp_rank), "r"(e) : "memory");
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p.sig_peer[i] + p.tp_rank), "r"(e) : "memory");
     const unsigned long long t0 = globaltimer_ns();
+    *reinterpret_cast<unsigned long long *>(p.sig_local + kSigWaitNs + 2) += t0 - t_in;    // fence + flag stores alone
     for (int i = 0; i < p.n_peer; ++i) {
         for (;;) {
             unsigned v;
@@ -85,7 +87,7 @@ spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ 
     __syncthreads();
     if (threadIdx.x == 0) {
         // the last CTA to leave returns the queue counters to zero for the next launch
-        if (p.n_peer) __threadfence_system(); else __threadfence();
+        if (p.n_peer) asm volatile("fence.acq_rel.sys;" ::: "memory"); else __threadfence();
         if (atomicAdd(p.ctrl + Ctrl::kFinished, 1) == (int)gridDim.x - 1) {
             p.ctrl[Ctrl::kHead] = 0; p.ctrl[Ctrl::kTail] = 0;
             p.ctrl[Ctrl::kItemsDone] = 0; p.ctrl[Ctrl::kPool] = 0; p.ctrl[Ctrl::kFinished] = 0;
@@ -127,7 +129,7 @@ static int fail(int code, const char *fmt, ...) {
             return fail(SPA_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__));        \
     } while (0)
 
-enum OpKind { OP_COMPUTE_CENT = 1, OP_SELECT_POSITION, OP_CENT_SELECT, OP_ATTENTION, OP_FUSION };
+enum OpKind { OP_COMPUTE_CENT = 1, OP_SELECT_POSITION, OP_CENT_SELECT, OP_ATTENTION, OP_FUSION, OP_ASSIGN };
 
 struct spaExecutor {
     int op;
@@ -140,6 +142,7 @@ struct spaExecutor {
     // workspace offsets (bytes)
     uint64_t off_ctrl, off_flat, off_info, off_ippl, off_po, off_pml, off_xs;
     uint64_t ctrl_bytes;
+    AssignParams ap;       // OP_ASSIGN
     int persistent_ws;     // see spaExecutorSetPersistentWorkspace
     void *clean_ws;        // workspace whose queue words are known to be zero
     int launches;
@@ -408,6 +411,17 @@ int spaExecutorSetSelectOptions(spaExecutor *e, int sinkPages, int recentPages, 
     e->p.sink_pages = sinkPages; e->p.recent_pages = recentPages; e->p.cap_den = maxFractionDen;
     return SPA_OK;
 }
+int spaExecutorSetSoftmaxLse(spaExecutor *e, const spaTensor *lse) {
+    if (!e) return fail(SPA_ERR_ARG, "bad executor");
+    if (e->op != OP_ATTENTION && e->op != OP_FUSION) return fail(SPA_ERR_UNSUPPORTED, "softmax lse: only the attention ops");
+    if (absent(lse)) { e->p.lse = nullptr; return SPA_OK; }
+    if (e->kv_i8) return fail(SPA_ERR_UNSUPPORTED, "softmax lse output is not available with int8 KV");
+    if (lse->dtype != SPA_F32) return fail(SPA_ERR_DTYPE, "softmax lse must be float32, got %s", dtype_name(lse->dtype));
+    if (lse->ndim < 2 || lse->sizes[0] != e->p.B || lse->sizes[1] != e->p.Nq || numel(lse) != (int64_t)e->p.B * e->p.Nq)
+        return fail(SPA_ERR_SHAPE, "softmax lse must be [B=%d, Nq=%d(, 1)]", e->p.B, e->p.Nq);
+    e->p.lse = (float *)lse->data; e->p.lse_sb = lse->strides[0]; e->p.lse_sh = lse->strides[1];
+    return SPA_OK;
+}
 int spaExecutorSetTrace(spaExecutor *e, void *deviceBuffer) {
     if (!e) return fail(SPA_ERR_ARG, "bad executor");
     e->p.trace = (unsigned long long *)deviceBuffer;
@@ -468,6 +482,71 @@ int spaExecutorSetPeerOutput(spaExecutor *e, int rank, int world, void *const *g
     }
     p.sig_local = (unsigned *)signals[rank];
     p.n_peer = n; p.tp_rank = rank;
+    return SPA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// centroid maintenance: page -> cluster assignment
+// ---------------------------------------------------------------------------------------------
+int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor *l1Cent, const spaTensor *pageIds,
+                                          const spaTensor *pageTokens, int64_t blockSize, const spaTensor *blockIds,
+                                          const spaTensor *pageMeanOut, uint64_t *ws, spaExecutor **executor) {
+    if (!ws || !executor) return fail(SPA_ERR_ARG, "null output pointer");
+    *executor = nullptr; *ws = 0;
+    REQUIRE_PRESENT(l1Cent, "l1Cent"); REQUIRE_PRESENT(blockIds, "blockIds");
+    if (l1Cent->ndim != 3 || l1Cent->sizes[2] != kD) return fail(SPA_ERR_SHAPE, "l1Cent: expected [Nkv,C,%d]", kD);
+    REQUIRE_CONTIG(l1Cent, "l1Cent");
+    if (l1Cent->dtype != SPA_F16 && l1Cent->dtype != SPA_BF16) return fail(SPA_ERR_DTYPE, "l1Cent: expected float16/bfloat16");
+    const int Nkv = (int)l1Cent->sizes[0], C = (int)l1Cent->sizes[1];
+    if (C < 1 || C > 8192) return fail(SPA_ERR_UNSUPPORTED, "clusters %d outside 1..8192", C);
+    if (blockSize < 4 || blockSize > 1024 || (blockSize & 3)) return fail(SPA_ERR_UNSUPPORTED, "block size %lld", (long long)blockSize);
+    REQUIRE_PRESENT(key, "key");
+    if (key->dtype != l1Cent->dtype) return fail(SPA_ERR_DTYPE, "key must have the centroid dtype %s (int8 pools: unsupported), got %s",
+                                                 dtype_name(l1Cent->dtype), dtype_name(key->dtype));
+    KvLayout L;
+    int rc = parse_kv(key, "key", Nkv, (int)blockSize, &L);
+    if (rc) return rc;
+    REQUIRE_DTYPE(blockIds, SPA_I32, "blockIds");
+    if (blockIds->ndim != 2 || blockIds->sizes[0] != Nkv || blockIds->strides[1] != 1)
+        return fail(SPA_ERR_SHAPE, "blockIds: expected [Nkv=%d, kvPageLen]", Nkv);
+    spaExecutor *e = new (std::nothrow) spaExecutor();
+    if (!e) return fail(SPA_ERR_ARG, "out of memory");
+    e->op = OP_ASSIGN; e->launches = 1; e->q_bf16 = l1Cent->dtype == SPA_BF16;
+    AssignParams &a = e->ap;
+    a.n = absent(pageIds) ? 0 : (int)numel(pageIds);
+    if (a.n) {
+        if (pageIds->dtype != SPA_I32 || !contiguous(pageIds)) { delete e; return fail(SPA_ERR_DTYPE, "pageIds: expected contiguous int32"); }
+        if (!absent(pageTokens) && (pageTokens->dtype != SPA_I32 || !contiguous(pageTokens) || numel(pageTokens) != a.n)) {
+            delete e; return fail(SPA_ERR_SHAPE, "pageTokens: expected contiguous int32 [%d]", a.n);
+        }
+        if (!absent(pageMeanOut) && (pageMeanOut->dtype != SPA_F32 || !contiguous(pageMeanOut) ||
+                                     numel(pageMeanOut) != (int64_t)a.n * Nkv * kD)) {
+            delete e; return fail(SPA_ERR_SHAPE, "pageMeanOut: expected contiguous float32 [%d,%d,%d]", a.n, Nkv, kD);
+        }
+    }
+    a.key = key->data; a.s_blk = L.s_blk; a.s_row = L.s_row; a.s_head = L.s_head;
+    a.cent = l1Cent->data;
+    a.page_ids = a.n ? (const int *)pageIds->data : nullptr;
+    a.page_tokens = (a.n && !absent(pageTokens)) ? (const int *)pageTokens->data : nullptr;
+    a.block_ids = (int *)blockIds->data; a.bid_stride = blockIds->strides[0];
+    a.page_mean = (a.n && !absent(pageMeanOut)) ? (float *)pageMeanOut->data : nullptr;
+    a.Nkv = Nkv; a.C = C; a.bs = (int)blockSize; a.num_blocks = (int)L.nblocks; a.kvPageLen = (int)blockIds->sizes[1];
+    if (a.n) {
+        DevInfo d;
+        if ((rc = dev_info(&d))) { delete e; return rc; }
+        e->grid = (int)std::min<int64_t>((int64_t)a.n * Nkv, (int64_t)d.sms * 8);
+    }
+    *executor = e;
+    return SPA_OK;
+}
+int spaAssignPageClusters(void *, uint64_t, spaExecutor *e, spaStream stream_) {
+    if (!e || e->op != OP_ASSIGN) return fail(SPA_ERR_ARG, "bad executor");
+    if (e->ap.n == 0) return SPA_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const size_t smem = (size_t)e->ap.C * sizeof(float);
+    if (e->q_bf16) spa_assign_kernel<__nv_bfloat16><<<e->grid, kAssignThreads, smem, stream>>>(e->ap);
+    else spa_assign_kernel<__half><<<e->grid, kAssignThreads, smem, stream>>>(e->ap);
+    CUDA_TRY(cudaGetLastError());
     return SPA_OK;
 }
 

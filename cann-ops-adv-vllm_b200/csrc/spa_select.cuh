@@ -580,10 +580,13 @@ __device__ __forceinline__ void queue_item_done(const ChainParams &p) {
 __device__ __forceinline__ void zero_item_output(const ChainParams &p, int b, int n2, int tid, int nthreads) {
     for (int i = tid; i < p.g * (kD / 4); i += nthreads) {
         const int h = i / (kD / 4), d4 = i % (kD / 4);
-        unsigned short *op = reinterpret_cast<unsigned short *>(p.out) + (size_t)b * p.out_sb +
-                             (size_t)(n2 * p.g + h) * p.out_sh + d4 * 4;
-        *reinterpret_cast<uint2 *>(op) = make_uint2(0u, 0u);
+        const size_t off = (size_t)b * p.out_sb + (size_t)(n2 * p.g + h) * p.out_sh + d4 * 4;
+        *reinterpret_cast<uint2 *>(reinterpret_cast<unsigned short *>(p.out) + off) = make_uint2(0u, 0u);
+        for (int r = 0; r < p.n_peer; ++r)                 // tensor parallel: the peers' gathered buffers too
+            *reinterpret_cast<uint2 *>(reinterpret_cast<unsigned short *>(p.out_peer[r]) + off) = make_uint2(0u, 0u);
     }
+    if (p.lse != nullptr)                                  // log of an empty sum
+        for (int h = tid; h < p.g; h += nthreads) p.lse[(size_t)b * p.lse_sb + (size_t)(n2 * p.g + h) * p.lse_sh] = -INFINITY;
 }
 // max_page_position_length[b] once the last kv head of b has reported (one thread; cent_select.cpp:123-160)
 __device__ __forceinline__ void report_item_ppl(const ChainParams &p, int b, int item, int m, bool fenced = false) {

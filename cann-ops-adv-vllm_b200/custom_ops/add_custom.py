@@ -9,7 +9,7 @@ than 256 selected pages are reachable without changing any existing call site.
 All compute happens in `custom_ops_lib` (C++ binding -> C ABI -> CUDA kernels).  There is no CPU or
 eager fallback: importing this module without the built extension raises ImportError.
 """
-from typing import List, Tuple
+from typing import List, Optional, Tuple
 
 import torch
 
@@ -78,15 +78,19 @@ def sparse_paged_attention(query: torch.Tensor,
                            input_layout: str,
                            num_key_value_heads: int,
                            block_size: int,
-                           inner_precise: int) -> torch.Tensor:
-    """Paged flash-decode over the pages listed in `blockposition` (add_custom.py:41-75)."""
+                           inner_precise: int,
+                           *, softmax_lse: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Paged flash-decode over the pages listed in `blockposition` (add_custom.py:41-75).
+
+    `softmax_lse`: optional caller-allocated float32 [B, Nq], filled with ln(sum exp(scale * q.k)) per row
+    (the reference kernels' softmaxLse output); fp16/bf16 KV only."""
     actual_seq_lengths = _tensor(actual_seq_lengths, torch.int64, query.device)
-    return custom_ops_lib.sparse_paged_attention(
+    return custom_ops_lib.sparse_paged_attention_ex(
         query, [key], [value], pse_shift, attention_mask, actual_seq_lengths,
         dequant_scale1, quant_scale1, dequant_scale2, quant_scale2, quant_offset2,
         antiquant_scale, antiquant_offset, blocktable, kv_padding_size,
         blockposition, int(num_heads), float(scale_value), input_layout, int(num_key_value_heads),
-        int(block_size), int(inner_precise))
+        int(block_size), int(inner_precise), softmax_lse)
 
 
 def compute_cent(query: torch.Tensor, l1_cent: torch.Tensor, *, k: int = 64) -> torch.Tensor:
@@ -144,7 +148,8 @@ def sparse_paged_fusion_attention(query: torch.Tensor,
                                   block_size: int,
                                   inner_precise: int,
                                   *, k: int = 64, sink_pages: int = 0, recent_pages: int = 0,
-                                  max_fraction_den: int = 0) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+                                  max_fraction_den: int = 0,
+                                  softmax_lse: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     """CentSelect + sparse paged attention in ONE launch (add_custom.py:96-135).
 
     `block_position`, `page_position_length`, `max_page_position_length` are caller-allocated and
@@ -160,7 +165,19 @@ def sparse_paged_fusion_attention(query: torch.Tensor,
         l1_cent, block_ids, total_seq_len,
         block_position, page_position_length, max_page_position_length,
         int(num_heads), float(scale_value), input_layout, int(num_key_value_heads), int(block_size),
-        int(inner_precise), int(k), int(sink_pages), int(recent_pages), int(max_fraction_den))
+        int(inner_precise), int(k), int(sink_pages), int(recent_pages), int(max_fraction_den), softmax_lse)
+
+
+def assign_page_clusters(key: torch.Tensor, l1_cent: torch.Tensor, page_ids: torch.Tensor, block_ids: torch.Tensor,
+                         page_tokens: Optional[torch.Tensor] = None, *, block_size: int = 128,
+                         return_mean: bool = False) -> torch.Tensor:
+    """Centroid maintenance, the step before the chain (no reference counterpart: its tests draw block_ids at
+    random, tests/cent_select.py:49-50).  For every physical page in `page_ids` [n] int32 and every KV head,
+    pools the page's keys and writes the index of the centroid with the largest inner product into
+    block_ids[n2, page] (in place; ties -> lowest index).  Returns block_ids, or with `return_mean` the fp32
+    page means [n, Nkv, D] (input of a k-means centroid update)."""
+    return custom_ops_lib.assign_page_clusters(key, l1_cent, page_ids, page_tokens, block_ids, int(block_size),
+                                               bool(return_mean))
 
 
 class FusedDecodePlan:
@@ -173,7 +190,7 @@ class FusedDecodePlan:
                  block_position, page_position_length, max_page_position_length, attention_out,
                  num_heads, scale_value, num_key_value_heads, block_size=128, *, k=64,
                  antiquant_scale=None, antiquant_offset=None, input_layout="BNSD", inner_precise=1,
-                 sink_pages=0, recent_pages=0, max_fraction_den=0):
+                 sink_pages=0, recent_pages=0, max_fraction_den=0, softmax_lse=None):
         empty = torch.empty(0, dtype=query.dtype, device=query.device)
         self.attention_out = attention_out
         self._plan = custom_ops_lib.make_fusion_plan(
@@ -182,7 +199,7 @@ class FusedDecodePlan:
             total_seq_len, block_position, page_position_length, max_page_position_length,
             attention_out, int(num_heads), float(scale_value), input_layout,
             int(num_key_value_heads), int(block_size), int(inner_precise), int(k), int(sink_pages),
-            int(recent_pages), int(max_fraction_den))
+            int(recent_pages), int(max_fraction_den), softmax_lse)
 
     @property
     def workspace_bytes(self) -> int:

@@ -74,6 +74,10 @@ class PeerGatheredOutput:
         waiting for the slowest peer).  Synchronises."""
         return int(self.signals[10:12].view(torch.int64).item())
 
+    def exchange_send_ns(self) -> int:
+        """The part of exchange_ns() spent before the wait (system fence + flag stores)."""
+        return int(self.signals[12:14].view(torch.int64).item())
+
     def close(self) -> None:
         torch.cuda.synchronize(self.device)
         for r, p in enumerate(self._ptrs):

@@ -94,6 +94,13 @@ SPA_API int spaExecutorSetPersistentWorkspace(spaExecutor *executor, int enable)
  *       padded with 0x7fffffff here (the reference leaves them; its consumers read only `length` entries). */
 SPA_API int spaExecutorSetSelectOptions(spaExecutor *executor, int sinkPages, int recentPages, int maxFractionDen);
 
+/* Optional softmax log-sum-exp output of the attention ops (the reference kernels' softmaxLse,
+ * sparse_paged_attention_split_Bbn2s2_Us2.h:2601-2623): lse [B, Nq] (or [B, Nq, 1]) float32, caller-allocated,
+ * lse[b,h] = ln(sum_i exp(scale * q.k_i)) over the tokens the row attended to; -inf when it attended to none.
+ * Needed to merge this result with attention over other token ranges (chunked / prefix merging).
+ * fp16/bf16 KV only (SPA_ERR_UNSUPPORTED for int8 KV).  NULL switches it off.                              */
+SPA_API int spaExecutorSetSoftmaxLse(spaExecutor *executor, const spaTensor *lse);
+
 /* ---- ComputeCent: replaces aclnnComputeCentGetWorkspaceSize / aclnnComputeCent
  *      (misc/aclnn_compute_cent.h; kernel compute_cent/compute_cent.cpp:345).
  * query [B,Nq,D] (or [B,Nq,1,D]) f16/bf16, l1Cent [Nkv,C,D] same dtype,
@@ -182,6 +189,25 @@ SPA_API int spaSparsePagedFusionAttentionGetWorkspaceSize(
     const spaTensor *attentionOut, uint64_t *workspaceSize, spaExecutor **executor);
 SPA_API int spaSparsePagedFusionAttention(void *workspace, uint64_t workspaceSize,
                                           spaExecutor *executor, spaStream stream);
+
+/* ---- AssignPageClusters: centroid maintenance, the step BEFORE the chain.  The reference
+ *      consumes blockIds [Nkv, kvPageLen] but never produces them (tests/cent_select.py:49-50 draws them at
+ *      random), so there is no aclnn interface to cite; the two-phase shape is the same.
+ * For every listed physical page and every KV head: pool the page's keys (fp32 sum of the valid tokens) and
+ * store the index of the centroid with the largest inner product -- the metric ComputeCent ranks clusters by
+ * (compute_cent.cpp:277-343) -- into blockIds[n2, page]; ties -> lowest index.  Run it when a page fills up
+ * (or for every page after the centroids changed).
+ * key [blocks,bs,Nkv,D] / [blocks,bs,Nkv*D] / [blocks,Nkv,bs,D] f16/bf16 (the dtype of l1Cent; int8 pools:
+ * SPA_ERR_UNSUPPORTED), l1Cent [Nkv,C,D], pageIds [n] int32, pageTokens [n] int32 or absent (= blockSize),
+ * blockIds [Nkv,kvPageLen] int32 in/out, pageMeanOut optional [n,Nkv,D] float32 (mean key of each page, the
+ * input of a k-means centroid update).  Entries of pageIds outside the pool are skipped.                  */
+SPA_API int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor *l1Cent,
+                                                  const spaTensor *pageIds, const spaTensor *pageTokens,
+                                                  int64_t blockSize, const spaTensor *blockIds,
+                                                  const spaTensor *pageMeanOut,
+                                                  uint64_t *workspaceSize, spaExecutor **executor);
+SPA_API int spaAssignPageClusters(void *workspace, uint64_t workspaceSize, spaExecutor *executor,
+                                  spaStream stream);
 
 /* ---- KV-head tensor parallelism: the output all-gather fused into the launch (the reference
  *      has no distributed code on this path, so there is no interface to cite).  One process per GPU; rank r

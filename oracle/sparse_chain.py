@@ -185,9 +185,12 @@ def attend_lists(
     lists: Sequence[Sequence[Sequence[Tuple[int, int]]]],   # lists[b][hq] = [(logical_page, ntok), ...]
     num_key_value_heads: int, scale_value: float, block_size: int,
     antiquant_scale: Optional[torch.Tensor] = None, antiquant_offset: Optional[torch.Tensor] = None,
-    round_p: bool = True, dtype64: bool = False,
+    round_p: bool = True, dtype64: bool = False, lse_out: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
     """Attention over explicit per-(b, q-head) page lists.
+
+    lse_out: optional float32 [B, Nq], filled with the softmax log-sum-exp ln(sum_i exp(s_i)) = ln(l) + m
+      (the reference's softmaxLse output, ..._Us2.h:2601-2623); -inf for an empty list.
 
     Addressing: phys = block_table[b, logical]; row r of that block, KV head n2 = hq // g
       (sparse_paged_attention_allvec_new.h:1338-1391 K, :1489-1538 V;
@@ -213,6 +216,8 @@ def attend_lists(
     if is_i8:
         sc, of = _antiquant(antiquant_scale, antiquant_offset, Nkv, D)
     out = torch.zeros(B, Nq, D, dtype=ft)
+    if lse_out is not None:
+        lse_out.fill_(-float("inf"))
     nblk = K.shape[0]
     for b in range(len(lists)):
         for hq in range(Nq):
@@ -242,6 +247,8 @@ def attend_lists(
                 continue
             p = torch.exp(s - m)
             l = p.sum()
+            if lse_out is not None:
+                lse_out[b, hq] = float(torch.log(l) + m)
             if round_p and not dtype64:
                 p = p.to(qd if is_i8 else K.dtype).to(ft)
             o = (p @ Vf) / l
@@ -291,12 +298,12 @@ def lists_from_block_position(block_position: torch.Tensor, actual_seq_lengths, 
 def sparse_paged_attention(query, key, value, actual_seq_lengths, block_table, block_position,
                            num_heads: int, scale_value: float, num_key_value_heads: int,
                            block_size: int, antiquant_scale=None, antiquant_offset=None,
-                           round_p: bool = True, dtype64: bool = False) -> torch.Tensor:
+                           round_p: bool = True, dtype64: bool = False, lse_out=None) -> torch.Tensor:
     """custom_ops.sparse_paged_attention (add_custom.py:41-75)."""
     lists = lists_from_block_position(block_position, actual_seq_lengths, num_heads,
                                       num_key_value_heads, block_size, block_table.shape[1])
     return attend_lists(query, key, value, block_table, lists, num_key_value_heads, scale_value,
-                        block_size, antiquant_scale, antiquant_offset, round_p, dtype64)
+                        block_size, antiquant_scale, antiquant_offset, round_p, dtype64, lse_out)
 
 
 def lists_from_selection(page_position: torch.Tensor, page_position_length: torch.Tensor,
@@ -331,7 +338,7 @@ def sparse_paged_fusion_attention(query, key, value, block_table, l1_cent, block
                                   block_size: int = 128, k: int = 64, max_page_num: int = 256,
                                   antiquant_scale=None, antiquant_offset=None,
                                   round_p: bool = True, dtype64: bool = False, sink_pages: int = 0,
-                                  recent_pages: int = 0, max_fraction_den: int = 0):
+                                  recent_pages: int = 0, max_fraction_den: int = 0, lse_out=None):
     """custom_ops.sparse_paged_fusion_attention (add_custom.py:96-135): cent_select followed by the
     attention over the selected pages (sparse_paged_fusion_attention.cpp:56-76).  Returns
     (attention_out, block_position, page_position_length, max_page_position_length)."""
@@ -340,7 +347,7 @@ def sparse_paged_fusion_attention(query, key, value, block_table, l1_cent, block
                                 block_size, max_page_num, sink_pages, recent_pages, max_fraction_den)
     lists = lists_from_selection(pos, plen, total_seq_len, block_size)
     out = attend_lists(query[:B], key, value, block_table, lists, num_key_value_heads, scale_value,
-                       block_size, antiquant_scale, antiquant_offset, round_p, dtype64)
+                       block_size, antiquant_scale, antiquant_offset, round_p, dtype64, lse_out)
     return out, pos, plen, mx
 
 
@@ -369,3 +376,44 @@ def algorithmic_bytes(page_position: torch.Tensor, page_position_length: torch.T
     bytes_io = 2 * B * Nq * D * q_elem
     return {"bytes_alg": bytes_kv + bytes_sel + bytes_io, "bytes_kv_union": bytes_kv,
             "bytes_logical": bytes_logical, "union_pages": union, "selected_pages": int(ln.sum())}
+
+
+# --------------------------------------------------------------------------------------------
+# centroid maintenance (page -> cluster assignment).  No reference counterpart (its tests
+# draw block_ids at random, tests/cent_select.py:49-50); this restates the arithmetic the CUDA kernel
+# defines (csrc/spa_assign.cuh) with the metric of ComputeCent (compute_cent.cpp:277-343).
+# --------------------------------------------------------------------------------------------
+def assign_page_clusters(key: torch.Tensor, l1_cent: torch.Tensor, page_ids: torch.Tensor,
+                         block_ids: torch.Tensor, page_tokens: Optional[torch.Tensor] = None,
+                         block_size: int = 128) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Returns (block_ids updated copy, page_mean [n, Nkv, D] float32).
+
+    pooled[d] = (s0 + s1) + (s2 + s3), s_w = float32 sum in token order of the valid tokens of the w-th
+    quarter of the page; score[c] = float64 sum over d in order of pooled[d] * cent[c, d];
+    block_ids[n2, page] = argmax_c score[c], ties -> lowest c.  Pages outside the pool are skipped."""
+    Nkv, C, D = l1_cent.shape
+    K = _kv_view(key.detach().cpu(), Nkv, block_size, D)                      # [blocks, bs, Nkv, D]
+    cent = l1_cent.detach().cpu().to(torch.float64).numpy()
+    out = block_ids.detach().cpu().clone()
+    ids = page_ids.detach().cpu().numpy().astype(np.int64).reshape(-1)
+    toks = None if page_tokens is None else page_tokens.detach().cpu().numpy().astype(np.int64).reshape(-1)
+    mean = np.zeros((ids.size, Nkv, D), dtype=np.float32)
+    q4 = block_size // 4
+    for i, page in enumerate(ids):
+        if page < 0 or page >= K.shape[0] or page >= out.shape[1]:
+            continue
+        ntok = block_size if toks is None else int(min(max(toks[i], 0), block_size))
+        kp = K[page].to(torch.float32).numpy()                                # [bs, Nkv, D]
+        part = np.zeros((4, Nkv, D), dtype=np.float32)
+        for w in range(4):
+            for t in range(w * q4, min((w + 1) * q4, ntok)):
+                part[w] = part[w] + kp[t]                                     # float32, token order
+        pooled = (part[0] + part[1]) + (part[2] + part[3])                    # float32
+        mean[i] = pooled / np.float32(ntok) if ntok > 0 else 0.0
+        p64 = pooled.astype(np.float64)
+        for n2 in range(Nkv):
+            acc = np.zeros(C, dtype=np.float64)
+            for d in range(D):
+                acc = acc + p64[n2, d] * cent[n2, :, d]                       # sequential in d; products exact
+            out[n2, page] = int(np.argmax(acc))                               # first maximum = lowest index
+    return out, torch.from_numpy(mean)

@@ -33,6 +33,7 @@ def main():
     for (B, Nq, Nkv, C, S, k, kv) in [(3, 32, 8, 128, 8192, 16, "f16"), (2, 64, 8, 256, 4096, 32, "i8")]:
         c = make_case(4242, B, Nq, Nkv, C, S, kv_pages=B * (S // 128) + 7, ragged=True, kv_int8=(kv == "i8"),
                       permute_table=True)
+        c["seq"][B - 1] = 0                     # a sequence that attends to nothing: its zero rows must reach the peers too
         sh = tp.head_shard(rank, world, Nq, Nkv)
         loc = tp.shard_inputs(sh, c["q"], c["l1"], c["block_ids"], c["key"], c["value"], Nkv, 128)
         aqs = aqo = None

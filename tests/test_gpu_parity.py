@@ -484,3 +484,87 @@ def test_anchor_pages_and_clamp_options(ops, opts):
         g["seq"], bp, ppl, mppl, Nq, c["scale"], "BNSD", Nkv, 128, 1, k=k, **opts)
     assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2]) and torch.equal(mppl.cpu(), want[3])
     assert_close(out, want[0], 1e-3, f"fused with {opts}")
+
+
+# ------------------------------------------------------------------------------------------
+# softmax log-sum-exp output
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("qdtype,tol", [(torch.float16, 1e-3), (torch.bfloat16, 2e-2)])
+def test_softmax_lse_output_fused_and_separate(ops, qdtype, tol):
+    B, Nq, Nkv, C, S, k = 3, 32, 8, 128, 8192, 16
+    c = make_case(501, B, Nq, Nkv, C, S, kv_pages=B * 64 + 3, ragged=True, permute_table=True, qdtype=qdtype)
+    c["seq"][1] = 0                                          # a row that attends to nothing: lse = -inf, out = 0
+    g = to_device(c, DEV)
+    want_lse = torch.empty(B, Nq, dtype=torch.float32)
+    want = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"],
+                                            c["seq"], Nq, c["scale"], Nkv, 128, k, 256, lse_out=want_lse)
+    dev = g["q"].device
+    bp = torch.empty(B, Nq, 256, dtype=torch.int32, device=dev)
+    ppl = torch.empty(B, Nq, 8, dtype=torch.int32, device=dev)
+    mppl = torch.empty(B, 8, dtype=torch.int64, device=dev)
+    lse = torch.full((B, Nq), 123.0, dtype=torch.float32, device=dev)
+    e = torch.empty(0, dtype=qdtype, device=dev)
+    e64 = torch.empty(0, dtype=torch.int64, device=dev)
+    out, _, _ = ops.sparse_paged_fusion_attention(
+        g["q"], g["key"], g["value"], e, e, e64, e, e, e, e, e, e, e, g["block_table"], e64, g["l1"], g["block_ids"],
+        g["seq"], bp, ppl, mppl, Nq, c["scale"], "BNSD", Nkv, 128, 1, k=k, softmax_lse=lse)
+    assert_close(out, want[0], tol, "fused out with lse")
+    got = lse.cpu()
+    assert bool((got[1] == -float("inf")).all()) and bool((want_lse[1] == -float("inf")).all())
+    fin = torch.isfinite(want_lse)
+    assert bool(torch.isfinite(got)[fin].all())
+    assert float((got[fin] - want_lse[fin]).abs().max()) < 2e-3
+    # separate op on the selection the fused op produced: same lse
+    lse2 = torch.zeros(B, Nq, 1, dtype=torch.float32, device=dev)
+    asl = (ppl[:, :, 0].max(dim=1)[0].long() * 128)
+    out2 = ops.sparse_paged_attention(g["q"], g["key"], g["value"], e, e, asl, e, e, e, e, e, e, e, g["block_table"], e64, bp,
+                                      Nq, c["scale"], "BNSD", Nkv, 128, 1, softmax_lse=lse2)
+    want_lse2 = torch.empty(B, Nq, dtype=torch.float32)
+    want2 = oc.sparse_paged_attention(c["q"], c["key"], c["value"], asl.cpu(), c["block_table"], bp.cpu(), Nq, c["scale"],
+                                      Nkv, 128, lse_out=want_lse2)
+    assert_close(out2, want2, tol, "separate out with lse")
+    got2 = lse2.cpu().view(B, Nq)
+    fin2 = torch.isfinite(want_lse2)
+    assert bool((got2[~fin2] == -float("inf")).all())
+    assert float((got2[fin2] - want_lse2[fin2]).abs().max()) < 2e-3
+    # int8 KV: refused
+    ci = to_device(make_case(502, 1, 8, 2, 64, 1024, kv_pages=16, kv_int8=True), DEV)
+    with pytest.raises(RuntimeError):
+        ops.sparse_paged_fusion_attention(
+            ci["q"], ci["key"], ci["value"], e, e, e64, e, e, e, e, e, ci["aq_scale"], ci["aq_offset"], ci["block_table"], e64,
+            ci["l1"], ci["block_ids"], ci["seq"], torch.empty(1, 8, 256, dtype=torch.int32, device=dev),
+            torch.empty(1, 8, 8, dtype=torch.int32, device=dev), torch.empty(1, 8, dtype=torch.int64, device=dev),
+            8, 1.0, "BNSD", 2, 128, 1, k=8, softmax_lse=torch.empty(1, 8, dtype=torch.float32, device=dev))
+
+
+# ------------------------------------------------------------------------------------------
+# centroid maintenance (page -> cluster assignment)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("qdtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["bsnd", "bnsd"])
+def test_assign_page_clusters_bit_exact(ops, qdtype, layout):
+    Nkv, C, blocks = 4, 200, 24
+    g = torch.Generator().manual_seed(77)
+    key = (torch.randn(blocks, 128, Nkv, 128, generator=g) * 0.5).to(qdtype)
+    l1 = torch.randn(Nkv, C, 128, generator=g).to(qdtype)
+    l1[:, 17] = l1[:, 5]                                       # exact ties -> lowest index
+    l1[1, 150] = (l1[1, 150].float() * (1 + 2 ** -7)).to(qdtype)
+    page_ids = torch.tensor([3, 0, 23, 7, 7, 11, 99, -1, 5], dtype=torch.int32)      # repeats and out-of-pool entries
+    toks = torch.tensor([128, 1, 37, 128, 128, 0, 128, 128, 64], dtype=torch.int32)
+    bid0 = torch.randint(0, C, (Nkv, blocks), generator=g, dtype=torch.int32)
+    want, wmean = oc.assign_page_clusters(key, l1, page_ids, bid0, toks)
+    kd = key.to(DEV) if layout == "bsnd" else key.permute(0, 2, 1, 3).contiguous().to(DEV)
+    bid = bid0.clone().to(DEV)
+    mean = ops.assign_page_clusters(kd, l1.to(DEV), page_ids.to(DEV), bid, toks.to(DEV), return_mean=True)
+    assert torch.equal(bid.cpu(), want)
+    live = torch.tensor([0 <= p < blocks for p in page_ids.tolist()])
+    assert torch.equal(mean.cpu()[live], wmean[live])
+    # full pages, no token list: every page of the pool
+    allp = torch.arange(blocks, dtype=torch.int32)
+    want2, _ = oc.assign_page_clusters(key, l1, allp, bid0)
+    bid2 = bid0.clone().to(DEV)
+    r = ops.assign_page_clusters(kd, l1.to(DEV), allp.to(DEV), bid2)
+    assert r.data_ptr() == bid2.data_ptr() and torch.equal(bid2.cpu(), want2)
+    # the assignment is what the chain then selects by: a query equal to a page's pooled key ranks that page's cluster first
+    with pytest.raises(RuntimeError):
+        ops.assign_page_clusters(kd.to(torch.int8), l1.to(DEV), allp.to(DEV), bid2)

@@ -103,3 +103,27 @@ def test_reference_kernel_anchor_and_clamp_options():
     bt2[0, 7] = bt2[0, 0]
     p3, l3, _ = oc.select_position(block_ids, bt2, seq, idx, sink_pages=1)
     assert all(7 in p3[0, h, :l3[0, h, 0]].tolist() for h in range(Nq))
+
+
+def test_assign_page_clusters_oracle_agrees_with_plain_float64():
+    """the page -> cluster assignment picks the centroid with the largest inner product with
+    the page's pooled key (metric of ComputeCent); partial pages pool only their valid tokens."""
+    import torch
+    from oracle import sparse_chain as oc
+    g = torch.Generator().manual_seed(9)
+    Nkv, C, blocks = 2, 12, 6
+    key = torch.randn(blocks, 128, Nkv, 128, generator=g).half()
+    l1 = torch.randn(Nkv, C, 128, generator=g).half()
+    ids = torch.tensor([4, 1, 5, 9], dtype=torch.int32)
+    toks = torch.tensor([128, 50, 1, 128], dtype=torch.int32)
+    bid0 = torch.full((Nkv, blocks), -7, dtype=torch.int32)
+    out, mean = oc.assign_page_clusters(key, l1, ids, bid0, toks)
+    for i, (pg, nt) in enumerate(zip(ids.tolist(), toks.tolist())):
+        if pg >= blocks:
+            continue
+        pooled = key[pg, :nt].double().sum(0)                      # [Nkv, D]
+        want = torch.einsum("nd,ncd->nc", pooled, l1.double()).argmax(dim=1)
+        assert out[:, pg].tolist() == want.tolist()
+        assert torch.allclose(mean[i].double(), pooled / nt, rtol=1e-5, atol=1e-6)
+    untouched = [p for p in range(blocks) if p not in ids.tolist()]
+    assert bool((out[:, untouched] == -7).all())
