@@ -534,7 +534,11 @@ int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor 
     if (a.n) {
         DevInfo d;
         if ((rc = dev_info(&d))) { delete e; return rc; }
-        e->grid = (int)std::min<int64_t>((int64_t)a.n * Nkv, (int64_t)d.sms * 8);
+        const int64_t units = (int64_t)((a.n + kAssignPages - 1) / kAssignPages) * Nkv;
+        const AssignSmem S(C, e->q_bf16 ? 3 : 2);
+        if (S.total > d.smem_optin) { delete e; return fail(SPA_ERR_UNSUPPORTED, "clusters %d need %d bytes of shared memory", C, S.total); }
+        const int per_sm = std::max(1, std::min(4, (d.smem_optin - 1024) / (S.total + 1024)));
+        e->grid = (int)std::min<int64_t>(units, (int64_t)d.sms * per_sm);
     }
     *executor = e;
     return SPA_OK;
@@ -543,9 +547,14 @@ int spaAssignPageClusters(void *, uint64_t, spaExecutor *e, spaStream stream_) {
     if (!e || e->op != OP_ASSIGN) return fail(SPA_ERR_ARG, "bad executor");
     if (e->ap.n == 0) return SPA_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
-    const size_t smem = (size_t)e->ap.C * sizeof(float);
-    if (e->q_bf16) spa_assign_kernel<__nv_bfloat16><<<e->grid, kAssignThreads, smem, stream>>>(e->ap);
-    else spa_assign_kernel<__half><<<e->grid, kAssignThreads, smem, stream>>>(e->ap);
+    const AssignSmem S(e->ap.C, e->q_bf16 ? 3 : 2);
+    if (e->q_bf16) {
+        CUDA_TRY(cudaFuncSetAttribute(spa_assign_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total));
+        spa_assign_kernel<__nv_bfloat16><<<e->grid, kAssignThreads, S.total, stream>>>(e->ap);
+    } else {
+        CUDA_TRY(cudaFuncSetAttribute(spa_assign_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total));
+        spa_assign_kernel<__half><<<e->grid, kAssignThreads, S.total, stream>>>(e->ap);
+    }
     CUDA_TRY(cudaGetLastError());
     return SPA_OK;
 }
