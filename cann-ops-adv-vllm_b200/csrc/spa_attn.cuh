@@ -66,7 +66,7 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
         for (int e = 0; e < NV; ++e) {
             const int d = p.aq_per_tensor ? 0 : d0 + e;
             const float off = ov ? QTraits<QT>::to_float(ov[d]) : 0.f;
-            r[e] = (r[e] + off) * QTraits<QT>::to_float(sv[d]);
+            r[e] = ((r[e] - kI8Bias) + off) * QTraits<QT>::to_float(sv[d]);      // O'/l - 1152 = O/l, see consume_pages
         }
     }
     const size_t off = (size_t)b * p.out_sb + (size_t)(n2 * p.g + h) * p.out_sh + d0;
@@ -396,14 +396,16 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
             for (int pp = 0; pp < PP; ++pp) {
                 uint32_t r0, r1, r2, r3;
                 ldmatrix_x4(r0, r1, r2, r3, stage_u32 + (uint32_t)ks[pp] * p.stage_bytes + off);
+                // biased int8 -> fp16 (1152 + k, one PRMT per pair): the softmax cancels the per-head constant
+                r0 ^= 0x80808080u; r1 ^= 0x80808080u; r2 ^= 0x80808080u; r3 ^= 0x80808080u;
+                const uint32_t k00 = I8PairBiased<0, 1>::cvt(r0), k01 = I8PairBiased<0, 1>::cvt(r1),
+                               k02 = I8PairBiased<2, 3>::cvt(r0), k03 = I8PairBiased<2, 3>::cvt(r1),
+                               k10 = I8PairBiased<0, 1>::cvt(r2), k11 = I8PairBiased<0, 1>::cvt(r3),
+                               k12 = I8PairBiased<2, 3>::cvt(r2), k13 = I8PairBiased<2, 3>::cvt(r3);
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) {
-                    mma_16816<MT>(s[pp][nt], I8Pair<MT, 0, 1>::cvt(r0), I8Pair<MT, 0, 1>::cvt(r1),
-                                  I8Pair<MT, 2, 3>::cvt(r0), I8Pair<MT, 2, 3>::cvt(r1),
-                                  qf[nt][2 * j][0], qf[nt][2 * j][1]);
-                    mma_16816<MT>(s[pp][nt], I8Pair<MT, 0, 1>::cvt(r2), I8Pair<MT, 0, 1>::cvt(r3),
-                                  I8Pair<MT, 2, 3>::cvt(r2), I8Pair<MT, 2, 3>::cvt(r3),
-                                  qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
+                    mma_16816<MT>(s[pp][nt], k00, k01, k02, k03, qf[nt][2 * j][0], qf[nt][2 * j][1]);
+                    mma_16816<MT>(s[pp][nt], k10, k11, k12, k13, qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
                 }
             }
         }
@@ -446,7 +448,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
             for (int pp = 0; pp < PP; ++pp) {
                 const float p0 = fast_exp2(x[pp][0] - m_use);
                 const float p1 = fast_exp2(x[pp][1] - m_use);
-                psum += p0 + p1;
+                if (!KVI8) psum += p0 + p1;              // int8 KV: l is summed from the ROUNDED P below
                 pr[pp][e] = p0; pr[pp][2 + e] = p1;
             }
             l_run[nt][e] = l_run[nt][e] * alpha[nt][e] + psum;
@@ -456,8 +458,19 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
         // the accumulator layout [tok][head] into the B-operand layout [k=tok][n=head]
 #pragma unroll
         for (int pp = 0; pp < PP; ++pp) {
-            pb[pp][nt][0] = movmatrix_trans(QTraits<MT>::pack2(pr[pp][0], pr[pp][1]));
-            pb[pp][nt][1] = movmatrix_trans(QTraits<MT>::pack2(pr[pp][2], pr[pp][3]));
+            const uint32_t pk0 = QTraits<MT>::pack2(pr[pp][0], pr[pp][1]);
+            const uint32_t pk1 = QTraits<MT>::pack2(pr[pp][2], pr[pp][3]);
+            if (KVI8) {
+                // V enters the matmul as 1152 + v: O' = O + 1152 * sum(P16).  With l = sum(P16) -- the very
+                // values the tensor cores multiply by -- the constant leaves as O'/l - 1152 in write_out_vals.
+                // (l differs from the fp32 sum of the unrounded p by < 2^-12 relative.)
+                const float2 f0 = __half22float2(*reinterpret_cast<const __half2 *>(&pk0));
+                const float2 f1 = __half22float2(*reinterpret_cast<const __half2 *>(&pk1));
+                l_run[nt][0] += f0.x + f1.x;
+                l_run[nt][1] += f0.y + f1.y;
+            }
+            pb[pp][nt][0] = movmatrix_trans(pk0);
+            pb[pp][nt][1] = movmatrix_trans(pk1);
         }
     }
     // rescale O only when some head's running max moved (it settles after the first pages of an item)
@@ -500,12 +513,15 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
             for (int pp = 0; pp < PP; ++pp) {
                 uint32_t r0, r1, r2, r3;
                 ldmatrix_x4_trans(r0, r1, r2, r3, stage_u32 + (uint32_t)vs[pp] * p.stage_bytes + off);
+                r0 ^= 0x80808080u; r1 ^= 0x80808080u; r2 ^= 0x80808080u; r3 ^= 0x80808080u;
+                const uint32_t v00 = I8PairBiased<0, 2>::cvt(r0), v01 = I8PairBiased<1, 3>::cvt(r0),
+                               v02 = I8PairBiased<0, 2>::cvt(r1), v03 = I8PairBiased<1, 3>::cvt(r1),
+                               v10 = I8PairBiased<0, 2>::cvt(r2), v11 = I8PairBiased<1, 3>::cvt(r2),
+                               v12 = I8PairBiased<0, 2>::cvt(r3), v13 = I8PairBiased<1, 3>::cvt(r3);
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) {
-                    mma_16816<MT>(o[nt][2 * j], I8Pair<MT, 0, 2>::cvt(r0), I8Pair<MT, 1, 3>::cvt(r0),
-                                  I8Pair<MT, 0, 2>::cvt(r1), I8Pair<MT, 1, 3>::cvt(r1), pb[pp][nt][0], pb[pp][nt][1]);
-                    mma_16816<MT>(o[nt][2 * j + 1], I8Pair<MT, 0, 2>::cvt(r2), I8Pair<MT, 1, 3>::cvt(r2),
-                                  I8Pair<MT, 0, 2>::cvt(r3), I8Pair<MT, 1, 3>::cvt(r3), pb[pp][nt][0], pb[pp][nt][1]);
+                    mma_16816<MT>(o[nt][2 * j], v00, v01, v02, v03, pb[pp][nt][0], pb[pp][nt][1]);
+                    mma_16816<MT>(o[nt][2 * j + 1], v10, v11, v12, v13, pb[pp][nt][0], pb[pp][nt][1]);
                 }
             }
         }

@@ -321,6 +321,16 @@ template <int I, int J> struct I8Pair<__half, I, J> {
         return *reinterpret_cast<uint32_t *>(&v);
     }
 };
+// Biased variant for the attention matmuls (fp16 only): 1152 + b, i.e. the same PRMT without the subtraction.
+// The constant never has to be taken out element by element: in Q.K^T it adds 1152 * sum_d q_d to every
+// logit of a head, which the softmax cancels; in P.V it adds 1152 * sum_t P_t, removed once per output
+// row as O/l - 1152 because l is accumulated from the same rounded P (see consume_pages / write_out_vals).
+constexpr float kI8Bias = 1152.f;
+template <int I, int J> struct I8PairBiased {
+    static __device__ __forceinline__ uint32_t cvt(uint32_t x /* bytes already xor 0x80 */) {
+        return prmt(x, 0x64646464u, 0x4040u | I | (J << 8));
+    }
+};
 template <int I, int J> struct I8Pair<__nv_bfloat16, I, J> {
     // 0x4B000000 | (b + 128) is the float 2^23 + (b + 128); |b| <= 128 is exact in bf16
     static __device__ __forceinline__ uint32_t cvt(uint32_t r) {
