@@ -355,15 +355,29 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention(
 }
 
 at::Tensor incre_flash_attention_v4(
-    const at::Tensor &, const std::vector<at::Tensor> &, const std::vector<at::Tensor> &, const at::Tensor &,
-    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
-    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
-    const at::Tensor &, int64_t, double, std::string, int64_t, int64_t, int64_t) {
-    // The reference routes this entry to the STOCK CANN IncreFlashAttention op (dense baseline, out
-    // of scope: SURVEY 2.2).  The dense comparison is obtained from sparse_paged_attention with an
-    // identity block_position.
-    TORCH_CHECK(false, "incre_flash_attention_v4 (stock dense IFA) is outside the sparse hot path; "
-                       "use sparse_paged_attention with an identity block_position");
+    const at::Tensor &query, const std::vector<at::Tensor> &key_list, const std::vector<at::Tensor> &value_list,
+    const at::Tensor &pse_shift, const at::Tensor &attention_mask, const at::Tensor &actual_seq_lengths,
+    const at::Tensor &dequant_scale1, const at::Tensor &quant_scale1, const at::Tensor &dequant_scale2,
+    const at::Tensor &quant_scale2, const at::Tensor &quant_offset2, const at::Tensor &antiquant_scale,
+    const at::Tensor &antiquant_offset, const at::Tensor &blocktable, const at::Tensor &kv_padding_size,
+    int64_t num_heads, double scale_value, std::string input_layout, int64_t num_key_value_heads, int64_t block_size,
+    int64_t inner_precise) {
+    // The reference routes this entry to the STOCK CANN IncreFlashAttention op (its dense baseline,
+    // add_custom.cpp:120-318).  Here the dense paged decode is the sparse kernel over EVERY page: an identity
+    // block_position per KV head, clipped by actual_seq_lengths.  Only the paged layout with a block table
+    // is served (what the sparse tests compare against); the stock op's other options are refused by the
+    // attention op's validation.
+    TORCH_CHECK(query.is_cuda(), "incre_flash_attention_v4: the CUDA extension only runs on CUDA tensors");
+    TORCH_CHECK(blocktable.defined() && blocktable.dim() == 2 && blocktable.numel() > 0,
+                "incre_flash_attention_v4: only the paged KV layout (blocktable [B, maxBlocks]) is supported");
+    c10::cuda::CUDAGuard guard(query.device());
+    const int64_t B = query.size(0), maxP = blocktable.size(1);
+    at::Tensor ident = at::arange(maxP, blocktable.options().dtype(at::kInt))
+                           .view({1, 1, maxP}).expand({B, num_key_value_heads, maxP}).contiguous();
+    return sparse_paged_attention(query, key_list, value_list, pse_shift, attention_mask, actual_seq_lengths,
+                                  dequant_scale1, quant_scale1, dequant_scale2, quant_scale2, quant_offset2,
+                                  antiquant_scale, antiquant_offset, blocktable, kv_padding_size, ident, num_heads,
+                                  scale_value, input_layout, num_key_value_heads, block_size, inner_precise);
 }
 
 // ---- Meta (shape inference) impls: output shapes/dtypes of the CUDA impls above, no data.  Mirrors the
@@ -373,6 +387,13 @@ at::Tensor meta_attention(
     const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
     const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
     const at::Tensor &, const at::Tensor &, int64_t, double, std::string, int64_t, int64_t, int64_t) {
+    return at::empty(query.sizes(), query.options());
+}
+at::Tensor meta_attention_v4(
+    const at::Tensor &query, const std::vector<at::Tensor> &, const std::vector<at::Tensor> &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &, int64_t, double, std::string, int64_t, int64_t, int64_t) {
     return at::empty(query.sizes(), query.options());
 }
 at::Tensor meta_compute_cent(const at::Tensor &query, const at::Tensor &) {
@@ -436,6 +457,7 @@ TORCH_LIBRARY_IMPL(myops, CUDA, m) {
 }
 
 TORCH_LIBRARY_IMPL(myops, Meta, m) {
+    m.impl("incre_flash_attention_v4", &meta_attention_v4);
     m.impl("sparse_paged_attention", &meta_attention);
     m.impl("compute_cent", &meta_compute_cent);
     m.impl("select_position", &meta_select_position);
@@ -445,7 +467,7 @@ TORCH_LIBRARY_IMPL(myops, Meta, m) {
 
 PYBIND11_MODULE(custom_ops_lib, m) {
     // the six reference entry points (registration.cpp:71-79)
-    m.def("incre_flash_attention_v4", &incre_flash_attention_v4, "FlashAttention V4 (out of scope: raises)");
+    m.def("incre_flash_attention_v4", &incre_flash_attention_v4, "FlashAttention V4 (dense paged decode on the sparse kernel)");
     m.def("sparse_paged_attention", &sparse_paged_attention, "Sparse Paged Attention");
     m.def("compute_cent", &compute_cent, "Compute Cent");
     m.def("select_position", &select_position, "Select Position");

@@ -49,7 +49,10 @@ def incre_flash_attention_v4(query: torch.Tensor,
                              num_key_value_heads: int,
                              block_size: int,
                              inner_precise: int) -> torch.Tensor:
-    """Stock dense IFA entry (add_custom.py:10-40): outside the sparse hot path, raises."""
+    """Dense paged decode attention (add_custom.py:10-40; the reference routes it to the stock CANN
+    IncreFlashAttention).  Served by the sparse kernel over every page of the block table (identity
+    block_position), clipped by actual_seq_lengths; paged layout only, the stock op's other options are refused."""
+    actual_seq_lengths = _tensor(actual_seq_lengths, torch.int64, query.device)
     return custom_ops_lib.incre_flash_attention_v4(
         query, key_list, value_list, pse_shift, attention_mask, actual_seq_lengths,
         dequant_scale1, quant_scale1, dequant_scale2, quant_scale2, quant_offset2,

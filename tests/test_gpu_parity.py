@@ -393,9 +393,31 @@ def test_unsupported_arguments_raise(ops):
         ops.compute_cent(c["q"], c["l1"])
     with pytest.raises(RuntimeError, match="exceeds cluster count"):
         ops.compute_cent(g["q"], g["l1"], k=65)
-    with pytest.raises(RuntimeError):
-        ops.incre_flash_attention_v4(g["q"], [g["key"]], [g["value"]], e, e, asl, e, e, e, e, e, e, e,
+    with pytest.raises(RuntimeError, match="pse_shift"):          # the stock IFA's other options stay refused
+        ops.incre_flash_attention_v4(g["q"], [g["key"]], [g["value"]], torch.zeros(1, device=DEV), e, asl, e, e, e, e, e, e, e,
                                      g["block_table"], e, 8, 1.0, "BNSD", 2, 128, 1)
+
+
+def test_incre_flash_attention_v4_is_dense_paged_decode(ops):
+    """The sixth reference entry (add_custom.py:10-40, stock dense IFA) served by the same kernel over every
+    page: must equal torch SDPA on the gathered KV, ragged lengths included."""
+    B, Nq, Nkv, S = 3, 32, 8, 4096
+    P = S // 128
+    c = make_case(611, B, Nq, Nkv, 64, S, kv_pages=B * P + 9, permute_table=True)
+    g = to_device(c, DEV)
+    lens = torch.tensor([S, S - 300, 129], dtype=torch.int64)
+    e = torch.empty(0, dtype=torch.float16, device=DEV)
+    e64 = torch.empty(0, dtype=torch.int64, device=DEV)
+    got = ops.incre_flash_attention_v4(g["q"], [g["key"]], [g["value"]], e, e, lens.to(DEV), e, e, e, e, e, e, e,
+                                       g["block_table"], e64, Nq, c["scale"], "BNSD", Nkv, 128, 1)
+    bt = c["block_table"].long()
+    for b in range(B):
+        n = int(lens[b])
+        K = c["key"][bt[b]].reshape(P * 128, Nkv, 128)[:n].permute(1, 0, 2).float()
+        V = c["value"][bt[b]].reshape(P * 128, Nkv, 128)[:n].permute(1, 0, 2).float()
+        qf = c["q"][b].float().view(Nkv, Nq // Nkv, 128)
+        ref = torch.nn.functional.scaled_dot_product_attention(qf, K, V, scale=c["scale"]).reshape(Nq, 128)
+        assert_close(got[b], ref, 2e-3, f"dense IFA b={b}")
 
 
 def test_torch_ops_namespace_and_plan(ops):
