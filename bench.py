@@ -45,8 +45,8 @@ import torch  # noqa: E402
 
 BS = 128
 D = 128
-# DRAM bytes of one chain-kernel launch from the committed ncu capture (read 541,777,408 + write 6,479,872)
-NCU_TRAFFIC = {"c2": 548257280}
+# DRAM bytes of one chain-kernel launch from the committed ncu capture (read 541,532,672 + write 6,386,432)
+NCU_TRAFFIC = {"c2": 547919104}
 
 WORKLOADS = {
     # BASELINE.json configs[0..3]
@@ -58,6 +58,11 @@ WORKLOADS = {
                desc="Llama-3-8B decode, int8 KV (antiquant), bf16 query: B=64 seq 32k C=512 top-k=64, fused"),
     "c4": dict(B=32, Nq=64, Nkv=8, S=131072, C=2048, k=128, q="f16", kv="f16",
                desc="Llama-3-70B decode: B=32 64Q/8KV D=128 seq 128k C=2048 top-k=128 fp16 KV, fused"),
+    # corners of the configs[4] sweep (tools/sweep.py), for traces
+    "c5_8k_64": dict(B=16, Nq=32, Nkv=8, S=8192, C=512, k=8, q="f16", kv="f16",
+                     desc="sweep corner: B=16 32Q/8KV seq 8k C=512 top-k=8 (k/C = 1/64) fp16"),
+    "c5_128k_64": dict(B=16, Nq=32, Nkv=8, S=131072, C=512, k=8, q="f16", kv="f16",
+                       desc="sweep corner: B=16 32Q/8KV seq 128k C=512 top-k=8 (k/C = 1/64) fp16"),
 }
 METRIC = "decode_attn_tokens_per_s"
 UNIT = "tokens/s"

@@ -586,8 +586,13 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         }
         T = __shfl_sync(0xffffffffu, T, 0);
         const int G = gridDim.x;
-        const int S = (int)((long long)T * p.static_pct / 100 / G);        // static pages per CTA
-        const int dyn0 = G * S;
+        // Little work (a few pages per CTA): cutting items between CTAs buys no balance worth having, but
+        // every cut item pays the partial -> publish -> combine chain (five dependent L2 round trips,
+        // ~10 us) after its last page.  Then every CTA streams WHOLE items -- items blockIdx.x, + G, + 2G --
+        // and writes their output straight from the consumers' merge (no partial, no combine, no claims).
+        const bool whole_items = p.small_pages > 0 && T <= G * p.small_pages && p.items <= 3 * G;
+        const int S = whole_items ? 0 : (int)((long long)T * p.static_pct / 100 / G);   // static pages per CTA
+        const int dyn0 = whole_items ? T : G * S;
         // claimed runs: equal length, about dyn_runs per CTA.  (Run lengths that shrink with the work left
         // were measured too, guided by the counter or by the CTA's own progress: every extra run costs
         // more in flushes and claim latency than the finer balance returns; c2 0.1175 ms vs 0.120-0.122.)
@@ -621,6 +626,23 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                 srun[1][0] = bb; srun[1][1] = e0 - bb;
                 srun[2][0] = b1; srun[2][1] = bb - b1;
                 nsr = 3;
+            }
+        }
+        if (whole_items) {
+            unsigned long long pr = 0ull;
+            const int it = (int)blockIdx.x + lane * G;
+            if (lane < 3 && it < p.items) {
+                // every item has reported (its record precedes its report): after this lane's own acquire of
+                // the report count a record that is still zero means an item without pages
+                unsigned long long w;
+                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p.ctrl + Ctrl::kTail) : "memory");
+                pr = ld_relaxed_u64(p.item_info + it);
+            }
+            nsr = 0;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const unsigned long long r = __shfl_sync(0xffffffffu, pr, j);
+                if ((r >> 63) && record_len(r) > 0) { srun[nsr][0] = record_base(r); srun[nsr][1] = record_len(r); ++nsr; }
             }
         }
         int sri = 0;                                                       // next static run

@@ -87,6 +87,7 @@ struct ChainParams {
     int static_pct;                                      // share of the page queue cut statically, percent
     int dyn_runs, dyn_min;                               // the rest is claimed in ~dyn_runs runs per CTA of >= dyn_min pages
     int list_cap;                                        // partial slots the post warp can list for one item
+    int small_pages;                                     // <= this many queue pages per CTA: every CTA streams whole items (0 = off)
     int pair_pages;                                      // consumers take two pages of an item per step (needs >= 4 stages)
     // ---- optional phase trace: [gridDim.x, kTraceSlots] globaltimer ns (null = off)
     unsigned long long *trace;

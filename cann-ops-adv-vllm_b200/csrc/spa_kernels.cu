@@ -247,6 +247,7 @@ static int plan_select_smem(ChainParams *p, int flags, int grid, int budget, int
     const int ntiles = (Ceff + kCentTileRows - 1) / kCentTileRows;
     SelSmem L(p->g, Ceff, keff, p->maxP, flags);
     int gw = (p->g > 4 || p->items <= grid) ? 8 : 4;
+    if (const char *s = getenv("SPA_SEL_GW")) { const int v = atoi(s); if (v == 2 || v == 4 || v == 8) gw = v; }
     for (; gw <= 8; gw *= 2) {
         const int ngroups = kConsumerWarps / gw;
         const long long state = (long long)L.total * ngroups;
@@ -827,6 +828,8 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     e->nt_tiles = (p.g + 7) / 8;
     // ---- scheduling of the page queue (spa_attn.cuh): static share + short claimed runs
     p.static_pct = 50; p.dyn_runs = 3; p.dyn_min = 2;     // measured on c2 (B200): 50/3 0.1175 ms, 85/3 0.1246, 0/6 0.1200
+    p.small_pages = 16;    // measured crossover on the configs[4] sweep: ~16.5 queue pages per CTA
+    if (const char *s = getenv("SPA_SMALL_PAGES")) p.small_pages = std::max(0, atoi(s));
     if (const char *s = getenv("SPA_STATIC_PCT")) p.static_pct = std::min(100, std::max(0, atoi(s)));
     if (const char *s = getenv("SPA_DYN_RUNS")) p.dyn_runs = std::max(1, atoi(s));
     if (const char *s = getenv("SPA_DYN_MIN")) p.dyn_min = std::max(1, atoi(s));

@@ -969,7 +969,7 @@ __device__ inline void union_from_block_position(const ChainParams &p, int item,
 // smem: [ngroups x sel_ns centroid-tile stages][ngroups x group state]
 template <typename QT, int FLAGS>
 __device__ __forceinline__ void select_phase(const ChainParams &p, const CUtensorMap *tmC, unsigned char *smem) {
-    __shared__ uint64_t sel_bars[2][16];               // per group: full[0..8), empty[8..16)
+    __shared__ uint64_t sel_bars[4][16];               // per group: full[0..8), empty[8..16)
     const int ngroups = kConsumerWarps / p.sel_gw;
     if ((FLAGS & kSelScores) && threadIdx.x == 0) {
         for (int gi = 0; gi < ngroups; ++gi)

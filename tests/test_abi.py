@@ -190,3 +190,38 @@ def test_meta_impls_infer_output_shapes_without_gpu(lib):
         m(Nkv, C, 128), m(Nkv, 1280, dt=i32), m(B, dt=i32), m(B, Nq, 512, dt=i32), m(B, Nq, 8, dt=i32),
         m(B, 8, dt=torch.int64), Nq, 1.0, "BNSD", Nkv, 128, 1)
     assert out.shape == (B, Nq, 128) and out.dtype == torch.bfloat16 and bp.shape == (B, Nq, 512) and mx.shape == (B, 8)
+
+
+def test_extension_entry_points_validate_without_gpu(lib):
+    """The entry points added beyond the five aclnn pairs (centroid maintenance, executor options, peer
+    output) reject malformed arguments with the documented codes before touching CUDA."""
+    ws = ctypes.c_uint64(0)
+    ex = ctypes.c_void_p()
+    Nkv, C, blocks = 4, 64, 16
+    key = tensor([blocks, 128, Nkv, 128], SPA_F16)
+    cent = tensor([Nkv, C, 128], SPA_F16)
+    ids = tensor([5], SPA_I32)
+    bid = tensor([Nkv, blocks], SPA_I32)
+    f = lib.spaAssignPageClustersGetWorkspaceSize
+    args = lambda k=key, c=cent, i=ids, b=bid, bs=128: (ctypes.byref(k), ctypes.byref(c), ctypes.byref(i), None,
+                                                        ctypes.c_int64(bs), ctypes.byref(b), None, ctypes.byref(ws),
+                                                        ctypes.byref(ex))
+    assert f(*args(k=tensor([blocks, 128, Nkv, 128], SPA_I8))) == SPA_ERR_DTYPE        # int8 pools: unsupported
+    assert b"centroid dtype" in lib.spaGetLastError()
+    assert f(*args(b=tensor([Nkv + 1, blocks], SPA_I32))) == SPA_ERR_SHAPE
+    assert f(*args(c=tensor([Nkv, 9000, 128], SPA_F16))) == SPA_ERR_UNSUPPORTED
+    assert f(*args(k=tensor([blocks, 64, Nkv, 128], SPA_F16))) == SPA_ERR_SHAPE        # pool does not match blockSize
+    assert f(*args(i=tensor([5], SPA_I64))) == SPA_ERR_DTYPE
+    # an empty page list plans (and launches) nothing and needs no device
+    empty = tensor([0], SPA_I32)
+    assert f(*args(i=empty)) == SPA_OK and ex.value
+    assert lib.spaAssignPageClusters(None, ctypes.c_uint64(0), ex, None) == SPA_OK
+    # executor setters: type-checked against the op the executor was planned for
+    assert lib.spaExecutorSetSelectOptions(ex, 1, 2, 8) == SPA_ERR_UNSUPPORTED
+    assert lib.spaExecutorSetSoftmaxLse(ex, None) == SPA_ERR_UNSUPPORTED
+    assert lib.spaExecutorSetPeerOutput(ex, 0, 1, None, None) == SPA_OK                 # world 1: off
+    assert lib.spaDestroyExecutor(ex) == SPA_OK
+    assert lib.spaExecutorSetSelectOptions(None, 0, 0, 0) == SPA_ERR_ARG
+    assert lib.spaExecutorSetPeerOutput(None, 0, 2, None, None) == SPA_ERR_ARG
+    assert lib.spaPeerBufferOpen(None, None) == SPA_ERR_ARG
+    assert lib.spaPeerBufferCreate(ctypes.c_uint64(0), None, None) == SPA_ERR_ARG

@@ -590,3 +590,32 @@ def test_assign_page_clusters_bit_exact(ops, qdtype, layout):
     # the assignment is what the chain then selects by: a query equal to a page's pooled key ranks that page's cluster first
     with pytest.raises(RuntimeError):
         ops.assign_page_clusters(kd.to(torch.int8), l1.to(DEV), allp.to(DEV), bid2)
+
+
+# ------------------------------------------------------------------------------------------
+# The page stream has two schedules: little work -> every CTA streams whole items (no partials, no combine);
+# otherwise the queue is cut into static shares + claimed runs with partials and last-arriver combines.
+# Small test shapes would only ever see the first, so the main cases run under both (SPA_SMALL_PAGES=0
+# switches the whole-item schedule off; the variable is read when an executor is planned).
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("small_pages", ["0", "64"])
+@pytest.mark.parametrize("kind", ["f16", "bf16", "i8", "g16"])
+def test_fused_chain_under_both_stream_schedules(ops, monkeypatch, small_pages, kind):
+    monkeypatch.setenv("SPA_SMALL_PAGES", small_pages)
+    if kind == "g16":
+        B, Nq, Nkv, C, S, k = 3, 32, 2, 128, 8192, 16
+    else:
+        B, Nq, Nkv, C, S, k = 5, 32, 8, 128, 8192, 16
+    qd = torch.bfloat16 if kind in ("bf16", "i8") else torch.float16
+    c = make_case(701, B, Nq, Nkv, C, S, kv_pages=B * 64 + 11, ragged=True, permute_table=True, qdtype=qd,
+                  kv_int8=(kind == "i8"))
+    c["seq"][B - 1] = 0
+    g = to_device(c, DEV)
+    i8 = kind == "i8"
+    want = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"],
+                                            c["seq"], Nq, c["scale"], Nkv, 128, k, 256,
+                                            c["aq_scale"] if i8 else None, c["aq_offset"] if i8 else None)
+    for rep in range(2):                                      # twice: the workspace must be left clean
+        out, bp, ppl, mppl, _ = fused_call(ops, g, k)
+        assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2]) and torch.equal(mppl.cpu(), want[3])
+        assert_close(out, want[0], 1e-3 if kind in ("f16", "g16") else 2e-2, f"{kind} small_pages={small_pages} rep {rep}")
