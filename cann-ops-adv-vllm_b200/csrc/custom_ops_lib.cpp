@@ -9,6 +9,9 @@
 #include <torch/extension.h>
 #include <torch/library.h>
 
+#include <cstdlib>
+#include <cstring>
+#include <list>
 #include <string>
 #include <tuple>
 #include <vector>
@@ -66,6 +69,36 @@ struct ExecGuard {
     spaExecutor *e = nullptr;
     ~ExecGuard() { if (e) spaDestroyExecutor(e); }
 };
+
+// ---- executor cache of the fused op (per thread; entries own an executor and its private workspace) ----
+struct CachedExec { std::vector<int64_t> key; spaExecutor *exec; uint64_t ws; at::Tensor workspace; };
+std::list<CachedExec> &plan_cache() {
+    static thread_local std::list<CachedExec> *c = new std::list<CachedExec>();   // never destroyed: no CUDA calls at exit
+    return *c;
+}
+bool plan_cache_enabled() {
+    // off while any scheduling knob is set from the environment (they are read when an executor is planned)
+    for (const char *v : {"SPA_SMALL_PAGES", "SPA_STATIC_PCT", "SPA_DYN_RUNS", "SPA_DYN_MIN", "SPA_SEL_GW", "SPA_PAIR", "SPA_COOP"})
+        if (getenv(v)) return false;
+    const char *s = getenv("SPA_PLAN_CACHE");
+    return !(s && s[0] == '0');
+}
+void key_add(std::vector<int64_t> &k, const Desc &d) {
+    if (!d.present) { k.push_back(-1); return; }
+    k.push_back((int64_t)(uintptr_t)d.t.data); k.push_back(d.t.dtype); k.push_back(d.t.ndim);
+    for (int i = 0; i < d.t.ndim; ++i) { k.push_back(d.t.sizes[i]); k.push_back(d.t.strides[i]); }
+}
+CachedExec *plan_cache_find(const std::vector<int64_t> &key) {
+    auto &c = plan_cache();
+    for (auto it = c.begin(); it != c.end(); ++it)
+        if (it->key == key) { c.splice(c.begin(), c, it); return &c.front(); }
+    return nullptr;
+}
+void plan_cache_insert(std::vector<int64_t> &&key, spaExecutor *e, uint64_t ws, const at::Tensor &workspace) {
+    auto &c = plan_cache();
+    c.push_front(CachedExec{std::move(key), e, ws, workspace});
+    while (c.size() > 16) { spaDestroyExecutor(c.back().exec); c.pop_back(); }
+}
 
 void set_lse(spaExecutor *e, const c10::optional<at::Tensor> &lse, const char *what) {
     if (!lse.has_value() || !lse->defined() || lse->numel() == 0) return;
@@ -317,6 +350,30 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention_ex(
          bp = desc(block_position, "block_position", true), pl = desc(page_position_length, "page_position_length", true),
          mp = desc(max_page_position_length, "max_page_position_length", true), o = desc(out, "attention_out", true);
     if (total_seq_len.numel() == 0) return std::make_tuple(out, block_position, max_page_position_length);
+    spaStream stream = (spaStream)at::cuda::getCurrentCUDAStream().stream();
+    // Executor cache (aclnn keeps repeatable executors the same way, add_custom.cpp:847): a decode loop calls
+    // this op with the same tensors' addresses and shapes step after step; the planned executor and its
+    // private, already-clean workspace are then reused -- no validation, descriptor encoding, allocation or
+    // workspace clear on the step's critical path.
+    std::vector<int64_t> ckey;
+    const bool use_cache = plan_cache_enabled();
+    if (use_cache) {
+        ckey.reserve(256);
+        for (const Desc *d : {&q, &kk, &v, &pse, &am, &d1, &q1, &d2, &q2, &qo2, &as, &ao, &bt, &kp, &lc, &bi, &ts, &bp, &pl, &mp, &o})
+            key_add(ckey, *d);
+        Desc ls = desc(softmax_lse.has_value() ? *softmax_lse : at::Tensor(), "softmax_lse");
+        key_add(ckey, ls);
+        int64_t sbits; std::memcpy(&sbits, &scale_value, sizeof(sbits));
+        for (int64_t a : {num_heads, sbits, num_key_value_heads, block_size, inner_precise, k, sink_pages, recent_pages,
+                          max_fraction_den, (int64_t)(uintptr_t)stream, (int64_t)query.get_device()})
+            ckey.push_back(a);
+        for (char ch : input_layout) ckey.push_back(ch);
+        if (CachedExec *hit = plan_cache_find(ckey)) {
+            check(spaSparsePagedFusionAttention(hit->workspace.data_ptr(), hit->ws, hit->exec, stream),
+                  "sparse_paged_fusion_attention");
+            return std::make_tuple(out, block_position, max_page_position_length);
+        }
+    }
     uint64_t ws = 0; ExecGuard g;
     // C-level order: inputs, attrs, the three aux outputs, attention_out (add_custom.cpp:836-844)
     check(spaSparsePagedFusionAttentionGetWorkspaceSize(
@@ -330,8 +387,9 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention_ex(
               "sparse_paged_fusion_attention");
     set_lse(g.e, softmax_lse, "sparse_paged_fusion_attention");
     at::Tensor wsp = alloc_ws(ws, query);
-    check(spaSparsePagedFusionAttention(wsp.data_ptr(), ws, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()),
-          "sparse_paged_fusion_attention");
+    if (use_cache) check(spaExecutorSetPersistentWorkspace(g.e, 1), "sparse_paged_fusion_attention");
+    check(spaSparsePagedFusionAttention(wsp.data_ptr(), ws, g.e, stream), "sparse_paged_fusion_attention");
+    if (use_cache) { plan_cache_insert(std::move(ckey), g.e, ws, wsp); g.e = nullptr; }
     return std::make_tuple(out, block_position, max_page_position_length);       // add_custom.cpp:931
 }
 
