@@ -619,3 +619,95 @@ def test_fused_chain_under_both_stream_schedules(ops, monkeypatch, small_pages, 
         out, bp, ppl, mppl, _ = fused_call(ops, g, k)
         assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2]) and torch.equal(mppl.cpu(), want[3])
         assert_close(out, want[0], 1e-3 if kind in ("f16", "g16") else 2e-2, f"{kind} small_pages={small_pages} rep {rep}")
+
+
+# ------------------------------------------------------------------------------------------
+# BASELINE.json's FULL sizes, through size-independent properties (the CPU oracle takes minutes there):
+# exact top-k property in float64, structural invariants of the selection outputs, fused == separate chain,
+# attention against a plain torch fp32 reference over the selected pages, invariance under a relabelling
+# of the physical pages.
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("workload", ["c2", "c3"])
+def test_full_size_properties(ops, workload):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    w = bench.WORKLOADS[workload]
+    dev = torch.device(DEV, 0)
+    inp = bench.make_inputs(w, w["B"], 0, 1, dev)
+    B, Nq, Nkv, C, k, P, MP = inp["B"], inp["Nq"], inp["Nkv"], inp["C"], inp["k"], inp["P"], 256
+    g = Nq // Nkv
+    i8 = w["kv"] == "i8"
+    tol = 2e-2 if (i8 or w["q"] == "bf16") else 1e-3
+    e = torch.empty(0, dtype=inp["qd"], device=dev)
+    e64 = torch.empty(0, dtype=torch.int64, device=dev)
+
+    def fused(bt, bid, key, value):
+        bp = torch.full((B, Nq, MP), 5, dtype=torch.int32, device=dev)
+        ppl = torch.full((B, Nq, 8), 5, dtype=torch.int32, device=dev)
+        mppl = torch.full((B, 8), 5, dtype=torch.int64, device=dev)
+        out, _, _ = ops.sparse_paged_fusion_attention(
+            inp["q"], key, value, e, e, e64, e, e, e, e, e, inp["aq_scale"], inp["aq_offset"], bt, e64, inp["l1"], bid,
+            inp["seq"], bp, ppl, mppl, Nq, inp["scale"], "BNSD", Nkv, 128, 1, k=k)
+        return out, bp, ppl, mppl
+
+    out, bp, ppl, mppl = fused(inp["block_table"], inp["block_ids"], inp["key"], inp["value"])
+    # (1) exact top-k property: float64 scores of fp16/bf16 operands are exact
+    idx = ops.compute_cent(inp["q"], inp["l1"], k=k).long()                          # [B, Nq, k]
+    sc = torch.einsum("bngd,ncd->bngc", inp["q"].double().view(B, Nkv, g, 128), inp["l1"].double()).reshape(B, Nq, C)
+    assert bool((idx.sort(dim=-1)[0].diff(dim=-1) > 0).all()), "duplicate cluster in a top-k row"
+    sel = torch.zeros(B, Nq, C, dtype=torch.bool, device=dev).scatter_(2, idx, True)
+    lo_sel = torch.where(sel, sc, torch.full_like(sc, float("inf"))).amin(dim=-1)
+    hi_rest = torch.where(sel, torch.full_like(sc, -float("inf")), sc).amax(dim=-1)
+    assert bool((lo_sel >= hi_rest).all()), "a selected cluster scores below an unselected one"
+    got_sc = sc.gather(2, idx)
+    assert bool((got_sc.diff(dim=-1) <= 0).all()), "indices are not sorted by descending score"
+    # (2) structure of the selection outputs + membership: page i selected <=> its cluster is in the top-k set
+    ln = ppl[:, :, 0].long()
+    assert bool((ppl == ppl[:, :, :1]).all()) and bool((mppl == (ln.amax(dim=1) * 128).view(B, 1)).all())
+    ar = torch.arange(MP, device=dev).view(1, 1, MP)
+    assert bool((bp[ar.expand(B, Nq, MP) >= ln.unsqueeze(-1)] == oc.INT32_MAX).all())
+    cl = inp["block_ids"].long()[:, inp["block_table"].long()]                       # [Nkv, B, P] cluster of every logical page
+    cl = cl.permute(1, 0, 2).repeat_interleave(g, dim=1)                             # [B, Nq, P]
+    member = sel.gather(2, cl)                                                       # [B, Nq, P]
+    want_len = member.sum(dim=-1).clamp(max=MP)
+    assert torch.equal(ln, want_len)
+    onehot = torch.zeros(B, Nq, P + 1, dtype=torch.bool, device=dev)
+    onehot.scatter_(2, bp.long().clamp(max=P), torch.ones_like(bp, dtype=torch.bool))
+    full = want_len == member.sum(dim=-1)                                            # rows not truncated at max_page_num
+    assert torch.equal(onehot[:, :, :P][full], member[full])
+    valid = ar < ln.unsqueeze(-1)
+    assert bool(((bp[:, :, 1:] > bp[:, :, :-1]) | ~valid[:, :, 1:]).all()), "page_position not ascending"
+    # (3) fused == separate chain
+    pos2, len2, mx2 = ops.cent_select(inp["q"], inp["l1"], inp["block_ids"], inp["block_table"], inp["seq"], k=k)
+    assert torch.equal(pos2, bp) and torch.equal(len2, ppl) and torch.equal(mx2, mppl)
+    out2 = ops.sparse_paged_attention(inp["q"], inp["key"], inp["value"], e, e, mppl[:, 0].contiguous(), e, e, e, e, e,
+                                      inp["aq_scale"], inp["aq_offset"], inp["block_table"], e64, bp, Nq, inp["scale"],
+                                      "BNSD", Nkv, 128, 1)
+    assert_close(out2, out, tol, "separate vs fused")
+    # (4) plain torch fp32 reference over the selected pages, every (b, head) row
+    ref = torch.zeros(B, Nq, 128, dtype=torch.float32, device=dev)
+    for b in range(B):
+        for n2 in range(Nkv):
+            for hh in range(g):
+                h = n2 * g + hh
+                pages = bp[b, h, :ln[b, h]].long()
+                phys = inp["block_table"][b].long()[pages]
+                K = inp["key"][phys, :, n2, :].reshape(-1, 128).float()
+                V = inp["value"][phys, :, n2, :].reshape(-1, 128).float()
+                if i8:
+                    K = (K + inp["aq_offset"][0, n2].float()) * inp["aq_scale"][0, n2].float()
+                    V = (V + inp["aq_offset"][1, n2].float()) * inp["aq_scale"][1, n2].float()
+                pr = torch.softmax((K @ inp["q"][b, h].float()) * inp["scale"], dim=0)
+                ref[b, h] = pr @ V
+    assert_close(out, ref, tol, "fused vs torch fp32 over the selected pages")
+    # (5) relabelling the physical pages changes nothing: selection bit-identical, output within tolerance
+    perm = torch.randperm(inp["key"].shape[0], device=dev, generator=torch.Generator(device=dev).manual_seed(3))
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(perm.numel(), device=dev)
+    key_p, val_p = inp["key"][perm], inp["value"][perm]                              # new page j holds old page perm[j]
+    bt_p = inv[inp["block_table"].long()].to(torch.int32)
+    bid_p = inp["block_ids"][:, perm].contiguous()
+    out_p, bp_p, ppl_p, mppl_p = fused(bt_p, bid_p, key_p, val_p)
+    assert torch.equal(bp_p, bp) and torch.equal(ppl_p, ppl) and torch.equal(mppl_p, mppl)
+    assert_close(out_p, out, tol, "relabelled pages")
