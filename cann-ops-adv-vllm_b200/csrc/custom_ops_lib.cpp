@@ -200,16 +200,20 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> cent_select(const at::Tensor &que
 // centroid maintenance (no reference counterpart): updates block_ids in place, optionally returns page means
 at::Tensor assign_page_clusters(const at::Tensor &key, const at::Tensor &l1_cent, const at::Tensor &page_ids,
                                 const c10::optional<at::Tensor> &page_tokens, at::Tensor block_ids, int64_t block_size,
-                                bool return_mean) {
+                                bool return_mean, const c10::optional<at::Tensor> &antiquant_scale,
+                                const c10::optional<at::Tensor> &antiquant_offset) {
     TORCH_CHECK(key.is_cuda(), "assign_page_clusters: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(key.device());
     at::Tensor mean;
     if (return_mean) mean = at::empty({page_ids.numel(), l1_cent.size(0), l1_cent.size(2)}, key.options().dtype(at::kFloat));
     Desc k = desc(key, "key"), c = desc(l1_cent, "l1_cent"), pi = desc(page_ids, "page_ids"),
          pt = desc(page_tokens.has_value() ? *page_tokens : at::Tensor(), "page_tokens"),
-         bi = desc(block_ids, "block_ids"), pm = desc(mean, "page_mean");
+         bi = desc(block_ids, "block_ids"), pm = desc(mean, "page_mean"),
+         as = desc(antiquant_scale.has_value() ? *antiquant_scale : at::Tensor(), "antiquant_scale"),
+         ao = desc(antiquant_offset.has_value() ? *antiquant_offset : at::Tensor(), "antiquant_offset");
     uint64_t ws = 0; ExecGuard g;
-    check(spaAssignPageClustersGetWorkspaceSize(k.ptr(), c.ptr(), pi.ptr(), pt.ptr(), block_size, bi.ptr(), pm.ptr(), &ws, &g.e),
+    check(spaAssignPageClustersGetWorkspaceSize(k.ptr(), c.ptr(), pi.ptr(), pt.ptr(), as.ptr(), ao.ptr(), block_size, bi.ptr(),
+                                                pm.ptr(), &ws, &g.e),
           "assign_page_clusters");
     check(spaAssignPageClusters(nullptr, 0, g.e, (spaStream)at::cuda::getCurrentCUDAStream().stream()), "assign_page_clusters");
     return return_mean ? mean : block_ids;

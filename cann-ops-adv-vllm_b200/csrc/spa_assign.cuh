@@ -25,6 +25,8 @@ struct AssignParams {
     const int *page_tokens;                               // [n] valid tokens per page, or null (= bs)
     int *block_ids; long long bid_stride;                 // [Nkv, kvPageLen] in/out
     float *page_mean;                                     // optional [n, Nkv, D] fp32 mean key of the page
+    const void *aq_scale, *aq_offset;                     // int8 pool: K antiquant [Nkv, D] (or one value) in the centroid dtype
+    int aq_per_tensor;
     int n, Nkv, C, bs, num_blocks, kvPageLen;
 };
 
@@ -74,7 +76,7 @@ struct AssignSmem {
 // flight per lane); (2) all warps: scores[cluster][page] = cent . pooled on the tensor cores (M = 16 clusters
 // per tile, N = 8 pages, K = D), centroid fragments straight from L2 -- the table is read once per 8 pages;
 // (3) warp w settles page w: maximum, clusters within the rounding band, exact fp64 scores, argmax.
-template <typename QT>
+template <typename QT, bool KVI8>
 __global__ void __launch_bounds__(kAssignThreads, 4) spa_assign_kernel(const __grid_constant__ AssignParams p) {
     using SP = AssignSplit<QT>;
     constexpr int NS = SP::NS;
@@ -98,6 +100,37 @@ __global__ void __launch_bounds__(kAssignThreads, 4) spa_assign_kernel(const __g
         if (page >= p.num_blocks || page >= p.kvPageLen) page = -1;
         const int ntok = (page < 0) ? 0 : (p.page_tokens ? max(0, min(p.page_tokens[i], p.bs)) : p.bs);
         float quarter[4][4];
+        if (KVI8) {
+            // int8 pool: the integer sum of the page is exact (no order to define); antiquant once per channel:
+            // pooled = (sum + ntok * offset) * scale in fp32 (x = (x_i8 + offset) * scale, ..._Us2.h:2142)
+            const signed char *kp = reinterpret_cast<const signed char *>(p.key) + (size_t)max(page, 0) * p.s_blk +
+                                    (size_t)n2 * p.s_head + lane * 4;
+            int a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            for (int t = 0; t < ntok; t += 16) {
+                int v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    v[j] = __ldcs(reinterpret_cast<const int *>(kp + (size_t)min(t + j, ntok - 1) * p.s_row));
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    if (t + j < ntok) {
+                        a0 = __dp4a(v[j], 0x00000001, a0); a1 = __dp4a(v[j], 0x00000100, a1);
+                        a2 = __dp4a(v[j], 0x00010000, a2); a3 = __dp4a(v[j], 0x01000000, a3);
+                    }
+                }
+            }
+            const int acc[4] = {a0, a1, a2, a3};
+            const unsigned short *sv = reinterpret_cast<const unsigned short *>(p.aq_scale);
+            const unsigned short *ov = reinterpret_cast<const unsigned short *>(p.aq_offset);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int d = p.aq_per_tensor ? 0 : n2 * kD + lane * 4 + e;
+                const float off = ov ? QTraits<QT>::to_float(ov[d]) : 0.f;
+                const float sc = QTraits<QT>::to_float(sv[d]);
+                quarter[0][e] = __fmul_rn(__fadd_rn((float)acc[e], __fmul_rn((float)ntok, off)), sc);
+                quarter[1][e] = quarter[2][e] = quarter[3][e] = 0.f;          // (x + 0) + (0 + 0) = x exactly
+            }
+        } else {
         {
             const unsigned short *kp = kbase + (size_t)max(page, 0) * p.s_blk + (size_t)n2 * p.s_head + lane * 4;
 #pragma unroll
@@ -121,6 +154,7 @@ __global__ void __launch_bounds__(kAssignThreads, 4) spa_assign_kernel(const __g
                 }
                 quarter[w][0] = s0; quarter[w][1] = s1; quarter[w][2] = s2; quarter[w][3] = s3;
             }
+        }
         }
         __syncthreads();                                      // the previous unit is done with the shared buffers
         {

@@ -490,7 +490,8 @@ int spaExecutorSetPeerOutput(spaExecutor *e, int rank, int world, void *const *g
 // centroid maintenance: page -> cluster assignment
 // ---------------------------------------------------------------------------------------------
 int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor *l1Cent, const spaTensor *pageIds,
-                                          const spaTensor *pageTokens, int64_t blockSize, const spaTensor *blockIds,
+                                          const spaTensor *pageTokens, const spaTensor *antiquantScale,
+                                          const spaTensor *antiquantOffset, int64_t blockSize, const spaTensor *blockIds,
                                           const spaTensor *pageMeanOut, uint64_t *ws, spaExecutor **executor) {
     if (!ws || !executor) return fail(SPA_ERR_ARG, "null output pointer");
     *executor = nullptr; *ws = 0;
@@ -502,8 +503,25 @@ int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor 
     if (C < 1 || C > 8192) return fail(SPA_ERR_UNSUPPORTED, "clusters %d outside 1..8192", C);
     if (blockSize < 4 || blockSize > 1024 || (blockSize & 3)) return fail(SPA_ERR_UNSUPPORTED, "block size %lld", (long long)blockSize);
     REQUIRE_PRESENT(key, "key");
-    if (key->dtype != l1Cent->dtype) return fail(SPA_ERR_DTYPE, "key must have the centroid dtype %s (int8 pools: unsupported), got %s",
-                                                 dtype_name(l1Cent->dtype), dtype_name(key->dtype));
+    const bool i8 = key->dtype == SPA_I8;
+    if (!i8 && key->dtype != l1Cent->dtype) return fail(SPA_ERR_DTYPE, "key must be int8 or have the centroid dtype %s, got %s",
+                                                        dtype_name(l1Cent->dtype), dtype_name(key->dtype));
+    int aq_per_tensor = 0;
+    if (i8) {
+        // K antiquant: x = (x_i8 + offset) * scale per channel (antiquant tensors [2, Nkv, D]: row 0 = K), or one value
+        if (absent(antiquantScale)) return fail(SPA_ERR_ARG, "int8 key pool needs antiquantScale");
+        for (const spaTensor *t : {antiquantScale, antiquantOffset}) {
+            if (absent(t)) continue;
+            if (t->dtype != l1Cent->dtype) return fail(SPA_ERR_DTYPE, "antiquant tensors must have the centroid dtype");
+            if (!contiguous(t)) return fail(SPA_ERR_SHAPE, "antiquant tensors must be contiguous");
+            const int64_t n = numel(t);
+            if (n != 2 && n != 2ll * Nkv * kD) return fail(SPA_ERR_SHAPE, "antiquant tensors: expected [2,%d,%d] or [2]", Nkv, kD);
+            if (t == antiquantScale) aq_per_tensor = n == 2;
+            else if ((n == 2) != (aq_per_tensor != 0)) return fail(SPA_ERR_SHAPE, "antiquant scale and offset must have the same shape");
+        }
+    } else if (!absent(antiquantScale) || !absent(antiquantOffset)) {
+        return fail(SPA_ERR_ARG, "antiquant tensors given for a non-int8 key pool");
+    }
     KvLayout L;
     int rc = parse_kv(key, "key", Nkv, (int)blockSize, &L);
     if (rc) return rc;
@@ -512,7 +530,7 @@ int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor 
         return fail(SPA_ERR_SHAPE, "blockIds: expected [Nkv=%d, kvPageLen]", Nkv);
     spaExecutor *e = new (std::nothrow) spaExecutor();
     if (!e) return fail(SPA_ERR_ARG, "out of memory");
-    e->op = OP_ASSIGN; e->launches = 1; e->q_bf16 = l1Cent->dtype == SPA_BF16;
+    e->op = OP_ASSIGN; e->launches = 1; e->q_bf16 = l1Cent->dtype == SPA_BF16; e->kv_i8 = i8;
     AssignParams &a = e->ap;
     a.n = absent(pageIds) ? 0 : (int)numel(pageIds);
     if (a.n) {
@@ -531,6 +549,9 @@ int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor 
     a.page_tokens = (a.n && !absent(pageTokens)) ? (const int *)pageTokens->data : nullptr;
     a.block_ids = (int *)blockIds->data; a.bid_stride = blockIds->strides[0];
     a.page_mean = (a.n && !absent(pageMeanOut)) ? (float *)pageMeanOut->data : nullptr;
+    a.aq_scale = i8 ? antiquantScale->data : nullptr;
+    a.aq_offset = (i8 && !absent(antiquantOffset)) ? antiquantOffset->data : nullptr;
+    a.aq_per_tensor = aq_per_tensor;
     a.Nkv = Nkv; a.C = C; a.bs = (int)blockSize; a.num_blocks = (int)L.nblocks; a.kvPageLen = (int)blockIds->sizes[1];
     if (a.n) {
         DevInfo d;
@@ -549,13 +570,10 @@ int spaAssignPageClusters(void *, uint64_t, spaExecutor *e, spaStream stream_) {
     if (e->ap.n == 0) return SPA_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
     const AssignSmem S(e->ap.C, e->q_bf16 ? 3 : 2);
-    if (e->q_bf16) {
-        CUDA_TRY(cudaFuncSetAttribute(spa_assign_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total));
-        spa_assign_kernel<__nv_bfloat16><<<e->grid, kAssignThreads, S.total, stream>>>(e->ap);
-    } else {
-        CUDA_TRY(cudaFuncSetAttribute(spa_assign_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total));
-        spa_assign_kernel<__half><<<e->grid, kAssignThreads, S.total, stream>>>(e->ap);
-    }
+    void (*kern)(AssignParams) = e->q_bf16 ? (e->kv_i8 ? spa_assign_kernel<__nv_bfloat16, true> : spa_assign_kernel<__nv_bfloat16, false>)
+                                           : (e->kv_i8 ? spa_assign_kernel<__half, true> : spa_assign_kernel<__half, false>);
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total));
+    kern<<<e->grid, kAssignThreads, S.total, stream>>>(e->ap);
     CUDA_TRY(cudaGetLastError());
     return SPA_OK;
 }

@@ -173,14 +173,16 @@ def sparse_paged_fusion_attention(query: torch.Tensor,
 
 def assign_page_clusters(key: torch.Tensor, l1_cent: torch.Tensor, page_ids: torch.Tensor, block_ids: torch.Tensor,
                          page_tokens: Optional[torch.Tensor] = None, *, block_size: int = 128,
-                         return_mean: bool = False) -> torch.Tensor:
+                         return_mean: bool = False, antiquant_scale: Optional[torch.Tensor] = None,
+                         antiquant_offset: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Centroid maintenance, the step before the chain (no reference counterpart: its tests draw block_ids at
     random, tests/cent_select.py:49-50).  For every physical page in `page_ids` [n] int32 and every KV head,
     pools the page's keys and writes the index of the centroid with the largest inner product into
     block_ids[n2, page] (in place; ties -> lowest index).  Returns block_ids, or with `return_mean` the fp32
-    page means [n, Nkv, D] (input of a k-means centroid update)."""
+    page means [n, Nkv, D] (input of a k-means centroid update).  An int8 pool takes the attention ops'
+    `antiquant_scale` / `antiquant_offset` ([2, Nkv, D] or [2]; the K row is used)."""
     return custom_ops_lib.assign_page_clusters(key, l1_cent, page_ids, page_tokens, block_ids, int(block_size),
-                                               bool(return_mean))
+                                               bool(return_mean), antiquant_scale, antiquant_offset)
 
 
 class FusedDecodePlan:

@@ -197,12 +197,15 @@ SPA_API int spaSparsePagedFusionAttention(void *workspace, uint64_t workspaceSiz
  * store the index of the centroid with the largest inner product -- the metric ComputeCent ranks clusters by
  * (compute_cent.cpp:277-343) -- into blockIds[n2, page]; ties -> lowest index.  Run it when a page fills up
  * (or for every page after the centroids changed).
- * key [blocks,bs,Nkv,D] / [blocks,bs,Nkv*D] / [blocks,Nkv,bs,D] f16/bf16 (the dtype of l1Cent; int8 pools:
- * SPA_ERR_UNSUPPORTED), l1Cent [Nkv,C,D], pageIds [n] int32, pageTokens [n] int32 or absent (= blockSize),
+ * key [blocks,bs,Nkv,D] / [blocks,bs,Nkv*D] / [blocks,Nkv,bs,D] in the dtype of l1Cent (f16/bf16), or int8 with
+ * the attention ops' antiquantScale / antiquantOffset ([2,Nkv,D] or [2] in the l1Cent dtype; the K row is used:
+ * pooled = (integer sum + tokens * offset) * scale), l1Cent [Nkv,C,D], pageIds [n] int32, pageTokens [n] int32
+ * or absent (= blockSize),
  * blockIds [Nkv,kvPageLen] int32 in/out, pageMeanOut optional [n,Nkv,D] float32 (mean key of each page, the
  * input of a k-means centroid update).  Entries of pageIds outside the pool are skipped.                  */
 SPA_API int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor *l1Cent,
                                                   const spaTensor *pageIds, const spaTensor *pageTokens,
+                                                  const spaTensor *antiquantScale, const spaTensor *antiquantOffset,
                                                   int64_t blockSize, const spaTensor *blockIds,
                                                   const spaTensor *pageMeanOut,
                                                   uint64_t *workspaceSize, spaExecutor **executor);

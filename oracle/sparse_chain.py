@@ -385,12 +385,15 @@ def algorithmic_bytes(page_position: torch.Tensor, page_position_length: torch.T
 # --------------------------------------------------------------------------------------------
 def assign_page_clusters(key: torch.Tensor, l1_cent: torch.Tensor, page_ids: torch.Tensor,
                          block_ids: torch.Tensor, page_tokens: Optional[torch.Tensor] = None,
-                         block_size: int = 128) -> Tuple[torch.Tensor, torch.Tensor]:
+                         block_size: int = 128, antiquant_scale: Optional[torch.Tensor] = None,
+                         antiquant_offset: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """Returns (block_ids updated copy, page_mean [n, Nkv, D] float32).
 
     pooled[d] = (s0 + s1) + (s2 + s3), s_w = float32 sum in token order of the valid tokens of the w-th
     quarter of the page; score[c] = float64 sum over d in order of pooled[d] * cent[c, d];
-    block_ids[n2, page] = argmax_c score[c], ties -> lowest c.  Pages outside the pool are skipped."""
+    block_ids[n2, page] = argmax_c score[c], ties -> lowest c.  Pages outside the pool are skipped.
+    int8 pool: pooled = (integer sum + float32(ntok) * offset_k) * scale_k in float32 (x = (x_i8 + offset) * scale,
+    ..._Us2.h:2142), antiquant tensors [2, Nkv, D] or [2] as the attention ops take them (row 0 = K)."""
     Nkv, C, D = l1_cent.shape
     K = _kv_view(key.detach().cpu(), Nkv, block_size, D)                      # [blocks, bs, Nkv, D]
     cent = l1_cent.detach().cpu().to(torch.float64).numpy()
@@ -403,12 +406,18 @@ def assign_page_clusters(key: torch.Tensor, l1_cent: torch.Tensor, page_ids: tor
         if page < 0 or page >= K.shape[0] or page >= out.shape[1]:
             continue
         ntok = block_size if toks is None else int(min(max(toks[i], 0), block_size))
-        kp = K[page].to(torch.float32).numpy()                                # [bs, Nkv, D]
-        part = np.zeros((4, Nkv, D), dtype=np.float32)
-        for w in range(4):
-            for t in range(w * q4, min((w + 1) * q4, ntok)):
-                part[w] = part[w] + kp[t]                                     # float32, token order
-        pooled = (part[0] + part[1]) + (part[2] + part[3])                    # float32
+        if K.dtype == torch.int8:
+            sc, of = _antiquant(antiquant_scale, antiquant_offset, Nkv, D)
+            isum = K[page, :ntok].to(torch.int64).sum(dim=0).numpy().astype(np.float32)       # exact
+            pooled = (isum + np.float32(ntok) * of[0].numpy().astype(np.float32)) * sc[0].numpy().astype(np.float32)
+            pooled = pooled.astype(np.float32)
+        else:
+            kp = K[page].to(torch.float32).numpy()                            # [bs, Nkv, D]
+            part = np.zeros((4, Nkv, D), dtype=np.float32)
+            for w in range(4):
+                for t in range(w * q4, min((w + 1) * q4, ntok)):
+                    part[w] = part[w] + kp[t]                                 # float32, token order
+            pooled = (part[0] + part[1]) + (part[2] + part[3])                # float32
         mean[i] = pooled / np.float32(ntok) if ntok > 0 else 0.0
         p64 = pooled.astype(np.float64)
         for n2 in range(Nkv):

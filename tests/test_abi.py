@@ -203,11 +203,14 @@ def test_extension_entry_points_validate_without_gpu(lib):
     ids = tensor([5], SPA_I32)
     bid = tensor([Nkv, blocks], SPA_I32)
     f = lib.spaAssignPageClustersGetWorkspaceSize
-    args = lambda k=key, c=cent, i=ids, b=bid, bs=128: (ctypes.byref(k), ctypes.byref(c), ctypes.byref(i), None,
-                                                        ctypes.c_int64(bs), ctypes.byref(b), None, ctypes.byref(ws),
-                                                        ctypes.byref(ex))
-    assert f(*args(k=tensor([blocks, 128, Nkv, 128], SPA_I8))) == SPA_ERR_DTYPE        # int8 pools: unsupported
-    assert b"centroid dtype" in lib.spaGetLastError()
+    args = lambda k=key, c=cent, i=ids, b=bid, bs=128, aq=None: (ctypes.byref(k), ctypes.byref(c), ctypes.byref(i), None,
+                                                                 aq, None, ctypes.c_int64(bs), ctypes.byref(b), None,
+                                                                 ctypes.byref(ws), ctypes.byref(ex))
+    assert f(*args(k=tensor([blocks, 128, Nkv, 128], SPA_I8))) == SPA_ERR_ARG          # int8 pool without antiquant scale
+    assert b"antiquantScale" in lib.spaGetLastError()
+    assert f(*args(k=tensor([blocks, 128, Nkv, 128], SPA_BF16))) == SPA_ERR_DTYPE       # neither int8 nor the centroid dtype
+    assert f(*args(aq=ctypes.byref(tensor([2, Nkv, 128], SPA_F16)))) == SPA_ERR_ARG     # antiquant for a non-int8 pool
+    assert f(*args(k=tensor([blocks, 128, Nkv, 128], SPA_I8), aq=ctypes.byref(tensor([2, Nkv, 64], SPA_F16)))) == SPA_ERR_SHAPE
     assert f(*args(b=tensor([Nkv + 1, blocks], SPA_I32))) == SPA_ERR_SHAPE
     assert f(*args(c=tensor([Nkv, 9000, 128], SPA_F16))) == SPA_ERR_UNSUPPORTED
     assert f(*args(k=tensor([blocks, 64, Nkv, 128], SPA_F16))) == SPA_ERR_SHAPE        # pool does not match blockSize

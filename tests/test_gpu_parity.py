@@ -589,7 +589,19 @@ def test_assign_page_clusters_bit_exact(ops, qdtype, layout):
     assert r.data_ptr() == bid2.data_ptr() and torch.equal(bid2.cpu(), want2)
     # the assignment is what the chain then selects by: a query equal to a page's pooled key ranks that page's cluster first
     with pytest.raises(RuntimeError):
-        ops.assign_page_clusters(kd.to(torch.int8), l1.to(DEV), allp.to(DEV), bid2)
+        ops.assign_page_clusters(kd.to(torch.int8), l1.to(DEV), allp.to(DEV), bid2)        # int8 pool without antiquant
+    # int8 pool with the attention ops' antiquant tensors ([2, Nkv, D]: the K row is used) and per-tensor ([2])
+    k8 = torch.randint(-128, 128, (blocks, 128, Nkv, 128), generator=g, dtype=torch.int8)
+    k8d = k8.to(DEV) if layout == "bsnd" else k8.permute(0, 2, 1, 3).contiguous().to(DEV)
+    for shape in [(2, Nkv, 128), (2,)]:
+        aqs = (torch.rand(*shape, generator=g) * 0.02 + 0.005).to(qdtype)
+        aqo = torch.randn(*shape, generator=g).to(qdtype)
+        want8, wmean8 = oc.assign_page_clusters(k8, l1, page_ids, bid0, toks, antiquant_scale=aqs, antiquant_offset=aqo)
+        bid8 = bid0.clone().to(DEV)
+        mean8 = ops.assign_page_clusters(k8d, l1.to(DEV), page_ids.to(DEV), bid8, toks.to(DEV), return_mean=True,
+                                         antiquant_scale=aqs.to(DEV), antiquant_offset=aqo.to(DEV))
+        assert torch.equal(bid8.cpu(), want8), f"int8 pool, antiquant {shape}"
+        assert torch.equal(mean8.cpu()[live], wmean8[live])
 
 
 # ------------------------------------------------------------------------------------------
@@ -711,3 +723,30 @@ def test_full_size_properties(ops, workload):
     out_p, bp_p, ppl_p, mppl_p = fused(bt_p, bid_p, key_p, val_p)
     assert torch.equal(bp_p, bp) and torch.equal(ppl_p, ppl) and torch.equal(mppl_p, mppl)
     assert_close(out_p, out, tol, "relabelled pages")
+
+
+def test_kmeans_step_m_step_and_consistency(ops):
+    """centroids.kmeans_step: E-step by the CUDA kernel (bit-exact vs the oracle), M-step = token-weighted mean
+    of the member pages' keys, empty clusters keep their centroid."""
+    import centroids
+    Nkv, C, blocks = 2, 16, 40
+    g = torch.Generator().manual_seed(21)
+    key = torch.randn(blocks, 128, Nkv, 128, generator=g).half()
+    l1 = torch.randn(Nkv, C, 128, generator=g).half()
+    ids = torch.randperm(blocks, generator=g)[:30].to(torch.int32)
+    toks = torch.randint(1, 129, (30,), generator=g, dtype=torch.int32)
+    bid0 = torch.zeros(Nkv, blocks, dtype=torch.int32)
+    want_bid, want_mean = oc.assign_page_clusters(key, l1, ids, bid0, toks)
+    bid = bid0.clone().to(DEV)
+    new, cnt = centroids.kmeans_step(key.to(DEV), l1.to(DEV), bid, ids.to(DEV), toks.to(DEV))
+    assert torch.equal(bid.cpu(), want_bid)
+    assert int(cnt.sum()) == 30 * Nkv
+    ref = l1.float().clone()
+    for n2 in range(Nkv):
+        for c in range(C):
+            m = [i for i in range(30) if int(want_bid[n2, ids[i]]) == c]
+            assert int(cnt[n2, c]) == len(m)
+            if m:
+                w = toks[m].float()
+                ref[n2, c] = (want_mean[m, n2] * w.view(-1, 1)).sum(0) / w.sum()
+    assert torch.allclose(new.float().cpu(), ref.half().float(), rtol=2e-3, atol=2e-3)
