@@ -74,6 +74,28 @@ def main():
             print(f"rank {rank}: flag exchange timed out", flush=True)
         dist.barrier()
         step.close()
+    # ---- the caller-side backend under tensor parallelism (decode_backend.SparseDecodeBackend)
+    from decode_backend import SparseDecodeBackend
+    B, Nq, Nkv, C, S, k = 3, 32, 8, 128, 4096, 16
+    c = make_case(777, B, Nq, Nkv, C, S, kv_pages=B * 32 + 5, ragged=True, permute_table=True)
+    sh = tp.head_shard(rank, world, Nq, Nkv)
+    loc = tp.shard_inputs(sh, c["q"], c["l1"], c["block_ids"], c["key"], c["value"], Nkv, 128)
+    be = SparseDecodeBackend(Nq, Nkv, 128, 128, k, max_batch=4, max_blocks_per_seq=S // 128, dtype=torch.float16,
+                             device=dev, scale=c["scale"], tensor_parallel=True)
+    be.bind_cache(loc["key"].to(dev), loc["value"].to(dev), loc["l1_cent"].to(dev), loc["block_ids"].to(dev))
+    for it, Bs in enumerate([3, 2, 3, 3]):
+        q_full = torch.rand(Bs, Nq, 128, generator=torch.Generator().manual_seed(500 + it)).half()
+        got = be.forward_decode(q_full[:, sh.q_lo:sh.q_hi].to(dev), c["block_table"][:Bs].to(dev), c["seq"][:Bs].to(dev))
+        torch.cuda.synchronize()
+        if rank == 0:
+            want = oc.sparse_paged_fusion_attention(q_full, c["key"], c["value"], c["block_table"][:Bs], c["l1"],
+                                                    c["block_ids"], c["seq"][:Bs], Nq, c["scale"], Nkv, 128, k, be.max_page_num)[0]
+            err = (got.float().cpu() - want.float()).abs()
+            if got.shape != want.shape or not bool((err <= 1e-3 + 1e-3 * want.float().abs()).all()):
+                ok = False
+                print(f"backend TP step {it} B={Bs}: max err {err.max().item():.3e}", flush=True)
+        dist.barrier()
+    be.close()
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
     if rank == 0:
