@@ -453,6 +453,8 @@ def main():
         dist.all_reduce(tot2, op=dist.ReduceOp.MAX)
     e2e_ms = tot2.item() / args.steps
     clocks = sampler.stop() if rank == 0 else None
+    if peer and plan.out.timed_out():
+        raise SystemExit(f"rank {rank}: a flag exchange of the fused output gather timed out (a peer did not launch)")
 
     # sum the per-rank algorithmic bytes (whole job)
     agg = torch.tensor([ab["bytes_alg"], ab["bytes_kv_union"], ab["bytes_logical"], ab["bytes_dense"]],
