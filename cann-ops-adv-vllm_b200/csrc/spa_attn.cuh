@@ -87,10 +87,43 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
 }
 
 // softmax log-sum-exp of one (b, head) row: ln(sum_i exp(s_i)) with s = scale * q.k, from the running max (log2
-// domain) and the sum of 2^(s2 - max) (the reference's optional softmaxLse output, ..._Us2.h:2601-2623)
+// domain) and the sum of 2^(s2 - max) (the reference's optional softmaxLse output, ..._Us2.h:2601-2623).
+// Whole warp.  int8 KV: the kernel's logits are short of the true ones by a per-head constant -- K enters the
+// matmul as 1152 + k instead of k + offset_k, with q*scale_k rounded to fp16 after a power-of-two
+// normalisation (see the Q fragments in attention_phase) -- which the softmax never sees but its log-sum
+// does: it is rebuilt here from the same rounded operands, 4 head dims per lane.
+template <typename QT, bool KVI8>
 __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, int h, float m2, float lsum) {
-    p.lse[(size_t)b * p.lse_sb + (size_t)(n2 * p.g + h) * p.lse_sh] =
-        (lsum > 0.f) ? (m2 + log2f(lsum)) * 0.6931471805599453f : -INFINITY;
+    const int lane = lane_id();
+    float shift = 0.f;
+    if (KVI8) {
+        const unsigned short *qrow = reinterpret_cast<const unsigned short *>(p.q) + (size_t)b * p.q_sb +
+                                     (size_t)(n2 * p.g + h) * p.q_sh + lane * 4;
+        const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) + (p.aq_per_tensor ? 0 : (size_t)n2 * kD + lane * 4);
+        const unsigned short *ok = p.aq_offset ? reinterpret_cast<const unsigned short *>(p.aq_offset) +
+                                   (p.aq_per_tensor ? 0 : (size_t)n2 * kD + lane * 4) : nullptr;
+        float f[4], off[4], amax = 0.f;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int j = p.aq_per_tensor ? 0 : e;
+            f[e] = QTraits<QT>::to_float(qrow[e]) * QTraits<QT>::to_float(sk[j]);
+            off[e] = ok ? QTraits<QT>::to_float(ok[j]) : 0.f;
+            amax = fmaxf(amax, fabsf(f[e]));
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const uint32_t ex = min(max((__float_as_uint(amax) >> 23) & 0xffu, 1u), 253u);
+        const float up = __uint_as_float((254u - ex) << 23), down = __uint_as_float(ex << 23);
+        float sum = 0.f;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) sum += __half2float(__float2half_rn(f[e] * up)) * (off[e] - kI8Bias);
+#pragma unroll
+        for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        shift = p.scale_log2 * down * sum;
+    }
+    if (lane == 0)
+        p.lse[(size_t)b * p.lse_sb + (size_t)(n2 * p.g + h) * p.lse_sh] =
+            (lsum > 0.f) ? (m2 + log2f(lsum) + shift) * 0.6931471805599453f : -INFINITY;
 }
 
 // ---- combine (post warp): the CTA whose partial completed the item's page count merges all partials ----
@@ -182,7 +215,7 @@ __device__ void combine_item_warp(const ChainParams &p, int item, int base, int 
 #pragma unroll
             for (int o = 16; o; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
             if (e < nh) write_out_vals<QT, KVI8, 4>(p, b, n2, h0 + e, lane * 4, acc[e], L);
-            if (e < nh && p.lse != nullptr && lane == 0) write_lse(p, b, n2, h0 + e, M[e], L);
+            if (e < nh && p.lse != nullptr) write_lse<QT, KVI8>(p, b, n2, h0 + e, M[e], L);
         }
     }
     if (lane == 0) { p.item_info[item] = 0ull; p.ctrl[Ctrl::pages_done(p.B, item)] = 0; }
@@ -319,7 +352,7 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
             const int d0 = half * kMergeHalf + lane * 2;
             if (whole) {
                 if (h < p.g) write_out_vals<QT, KVI8, 2>(p, b, n2, h, d0, acc, Ls);
-                if (h < p.g && half == 0 && lane == 0 && p.lse != nullptr) write_lse(p, b, n2, h, M, Ls);
+                if (h < p.g && half == 0 && p.lse != nullptr) write_lse<QT, KVI8>(p, b, n2, h, M, Ls);
             } else {
                 *reinterpret_cast<float2 *>(p.part_o + ((size_t)slot * HP + h) * kD + d0) = make_float2(acc[0], acc[1]);
             }
@@ -778,8 +811,8 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     // 16ks+4tig+e and slot (2*tig+8+e) <-> d = 16ks+4tig+2+e (same permutation on both
                     // operands).  The per-channel K scale is folded into Q (…_Us2.h:2142); the K offset adds
                     // a per-head constant to every logit and cancels in the softmax (:2146-2155).  The
-                    // matmuls run in fp16 whatever the query dtype (int8 -> fp16 is exact and costs one
-                    // prmt + one hsub2 per pair; -> bf16 costs 2.5x that): q*scale_k is brought to [1, 2)
+                    // matmuls run in fp16 whatever the query dtype (int8 -> biased fp16 is exact and costs one
+                    // prmt per pair, see I8PairBiased; -> bf16 costs 5x that): q*scale_k is brought to [1, 2)
                     // per head by a power of two (exact), rounded to fp16 (11 bits, more than bf16's 8), and
                     // the power of two is returned to the logits in fp32.
                     const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) +

@@ -416,7 +416,6 @@ int spaExecutorSetSoftmaxLse(spaExecutor *e, const spaTensor *lse) {
     if (!e) return fail(SPA_ERR_ARG, "bad executor");
     if (e->op != OP_ATTENTION && e->op != OP_FUSION) return fail(SPA_ERR_UNSUPPORTED, "softmax lse: only the attention ops");
     if (absent(lse)) { e->p.lse = nullptr; return SPA_OK; }
-    if (e->kv_i8) return fail(SPA_ERR_UNSUPPORTED, "softmax lse output is not available with int8 KV");
     if (lse->dtype != SPA_F32) return fail(SPA_ERR_DTYPE, "softmax lse must be float32, got %s", dtype_name(lse->dtype));
     if (lse->ndim < 2 || lse->sizes[0] != e->p.B || lse->sizes[1] != e->p.Nq || numel(lse) != (int64_t)e->p.B * e->p.Nq)
         return fail(SPA_ERR_SHAPE, "softmax lse must be [B=%d, Nq=%d(, 1)]", e->p.B, e->p.Nq);

@@ -98,7 +98,8 @@ SPA_API int spaExecutorSetSelectOptions(spaExecutor *executor, int sinkPages, in
  * sparse_paged_attention_split_Bbn2s2_Us2.h:2601-2623): lse [B, Nq] (or [B, Nq, 1]) float32, caller-allocated,
  * lse[b,h] = ln(sum_i exp(scale * q.k_i)) over the tokens the row attended to; -inf when it attended to none.
  * Needed to merge this result with attention over other token ranges (chunked / prefix merging).
- * fp16/bf16 KV only (SPA_ERR_UNSUPPORTED for int8 KV).  NULL switches it off.                              */
+ * With int8 KV the kernel's logits differ from the true ones by a per-head constant the softmax cancels (K
+ * offset, conversion bias); the log-sum-exp puts it back.  NULL switches it off.                           */
 SPA_API int spaExecutorSetSoftmaxLse(spaExecutor *executor, const spaTensor *lse);
 
 /* ---- ComputeCent: replaces aclnnComputeCentGetWorkspaceSize / aclnnComputeCent

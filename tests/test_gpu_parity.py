@@ -549,14 +549,22 @@ def test_softmax_lse_output_fused_and_separate(ops, qdtype, tol):
     fin2 = torch.isfinite(want_lse2)
     assert bool((got2[~fin2] == -float("inf")).all())
     assert float((got2[fin2] - want_lse2[fin2]).abs().max()) < 2e-3
-    # int8 KV: refused
-    ci = to_device(make_case(502, 1, 8, 2, 64, 1024, kv_pages=16, kv_int8=True), DEV)
-    with pytest.raises(RuntimeError):
-        ops.sparse_paged_fusion_attention(
-            ci["q"], ci["key"], ci["value"], e, e, e64, e, e, e, e, e, ci["aq_scale"], ci["aq_offset"], ci["block_table"], e64,
-            ci["l1"], ci["block_ids"], ci["seq"], torch.empty(1, 8, 256, dtype=torch.int32, device=dev),
-            torch.empty(1, 8, 8, dtype=torch.int32, device=dev), torch.empty(1, 8, dtype=torch.int64, device=dev),
-            8, 1.0, "BNSD", 2, 128, 1, k=8, softmax_lse=torch.empty(1, 8, dtype=torch.float32, device=dev))
+    # int8 KV: the per-head constant the softmax cancels (K offset, conversion bias) is put back into the lse
+    Bi, Nqi, Nkvi = 2, 16, 4
+    ci = make_case(502, Bi, Nqi, Nkvi, 64, 4096, kv_pages=80, kv_int8=True, qdtype=qdtype, ragged=True, permute_table=True)
+    gi = to_device(ci, DEV)
+    want_lse_i = torch.empty(Bi, Nqi, dtype=torch.float32)
+    want_i = oc.sparse_paged_fusion_attention(ci["q"], ci["key"], ci["value"], ci["block_table"], ci["l1"], ci["block_ids"],
+                                              ci["seq"], Nqi, ci["scale"], Nkvi, 128, 8, 256, ci["aq_scale"], ci["aq_offset"],
+                                              lse_out=want_lse_i)
+    lse_i = torch.zeros(Bi, Nqi, dtype=torch.float32, device=dev)
+    out_i, _, _ = ops.sparse_paged_fusion_attention(
+        gi["q"], gi["key"], gi["value"], e, e, e64, e, e, e, e, e, gi["aq_scale"], gi["aq_offset"], gi["block_table"], e64,
+        gi["l1"], gi["block_ids"], gi["seq"], torch.empty(Bi, Nqi, 256, dtype=torch.int32, device=dev),
+        torch.empty(Bi, Nqi, 8, dtype=torch.int32, device=dev), torch.empty(Bi, 8, dtype=torch.int64, device=dev),
+        Nqi, ci["scale"], "BNSD", Nkvi, 128, 1, k=8, softmax_lse=lse_i)
+    assert_close(out_i, want_i[0], 2e-2, "int8 fused out with lse")
+    assert float((lse_i.cpu() - want_lse_i).abs().max()) < 5e-3
 
 
 # ------------------------------------------------------------------------------------------
