@@ -308,6 +308,22 @@ def main():
     ppl = torch.empty(B, nq, 8, dtype=torch.int32, device=dev)
     mppl = torch.empty(B, 8, dtype=torch.int64, device=dev)
     out = torch.empty(B, nq, D, dtype=qd, device=dev)
+    # The step's inputs are staged the way a serving engine stages them: ONE pinned host blob (query | block_table |
+    # seq_len, 256-byte aligned sections) -> one H2D copy per step into a device blob the op's tensors are views of.
+    def _sec(n):
+        return (n + 255) // 256 * 256
+    nb_q, nb_bt, nb_seq = inp["q"].numel() * inp["q"].element_size(), inp["block_table"].numel() * 4, inp["seq"].numel() * 4
+    o_bt, o_seq, nb_all = _sec(nb_q), _sec(nb_q) + _sec(nb_bt), _sec(nb_q) + _sec(nb_bt) + _sec(nb_seq)
+    hblob = torch.zeros(nb_all, dtype=torch.uint8).pin_memory()
+    dblob = torch.zeros(nb_all, dtype=torch.uint8, device=dev)
+    hq = hblob[:nb_q].view(qd).view(inp["q"].shape)
+    hbt = hblob[o_bt:o_bt + nb_bt].view(torch.int32).view(inp["block_table"].shape)
+    hseq = hblob[o_seq:o_seq + nb_seq].view(torch.int32).view(inp["seq"].shape)
+    hq.copy_(inp["q"]); hbt.copy_(inp["block_table"]); hseq.copy_(inp["seq"])
+    sq = dblob[:nb_q].view(qd).view(inp["q"].shape)
+    sbt = dblob[o_bt:o_bt + nb_bt].view(torch.int32).view(inp["block_table"].shape)
+    sseq = dblob[o_seq:o_seq + nb_seq].view(torch.int32).view(inp["seq"].shape)
+    dblob.copy_(hblob)
     gather = out_full = None
     i8 = w["kv"] == "i8"
     peer = world > 1 and args.gather == "peer"
@@ -318,8 +334,8 @@ def main():
     if peer:
         # the launch itself delivers every rank's rows to every rank (peer stores + flag exchange)
         from peer_gather import TPFusedDecode
-        plan = TPFusedDecode(head_shard(rank, world, nq * world, nkv * world), nq * world, inp["q"], inp["key"],
-                             inp["value"], inp["block_table"], inp["l1"], inp["block_ids"], inp["seq"], bp, ppl, mppl,
+        plan = TPFusedDecode(head_shard(rank, world, nq * world, nkv * world), nq * world, sq, inp["key"],
+                             inp["value"], sbt, inp["l1"], inp["block_ids"], sseq, bp, ppl, mppl,
                              inp["scale"], BS, k=inp["k"], antiquant_scale=inp["aq_scale"] if i8 else None,
                              antiquant_offset=inp["aq_offset"] if i8 else None)
     else:
@@ -405,29 +421,23 @@ def main():
     st = sorted(times)
 
     # ---------------- end-to-end through the reference-facing call ----------------
-    hq = inp["q"].cpu().pin_memory()
-    hbt = inp["block_table"].cpu().pin_memory()
-    hseq = inp["seq"].cpu().pin_memory()
     hout = torch.empty(B, nq * world, D, dtype=qd).pin_memory() if world > 1 else torch.empty(B, nq, D, dtype=qd).pin_memory()
     e = torch.empty(0, dtype=qd, device=dev)
     e64 = torch.empty(0, dtype=torch.int64, device=dev)
-    h2d = hq.numel() * hq.element_size() + hbt.numel() * 4 + hseq.numel() * 4
+    h2d = nb_all
     d2h = hout.numel() * hout.element_size()
 
     def e2e_step_peer():
         # same public surface as the TP serving step: inputs land in the plan's bound tensors, the launch
         # returns the gathered output of all ranks
-        inp["q"].copy_(hq, non_blocking=True)
-        inp["block_table"].copy_(hbt, non_blocking=True)
-        inp["seq"].copy_(hseq, non_blocking=True)
+        dblob.copy_(hblob, non_blocking=True)                       # the plan is bound to views of dblob
         hout.copy_(plan.launch(), non_blocking=True)
 
     def e2e_step():
         if peer:
             return e2e_step_peer()
-        dq = hq.to(dev, non_blocking=True)
-        dbt = hbt.to(dev, non_blocking=True)
-        dseq = hseq.to(dev, non_blocking=True)
+        dblob.copy_(hblob, non_blocking=True)
+        dq, dbt, dseq = sq, sbt, sseq
         o, _, _ = custom_ops.sparse_paged_fusion_attention(
             dq, inp["key"], inp["value"], e, e, e64, e, e, e, e, e, inp["aq_scale"], inp["aq_offset"], dbt, e64,
             inp["l1"], inp["block_ids"], dseq, bp, ppl, mppl, nq, inp["scale"], "BNSD", nkv, BS, 1, k=inp["k"])
