@@ -758,3 +758,69 @@ def test_kmeans_step_m_step_and_consistency(ops):
                 w = toks[m].float()
                 ref[n2, c] = (want_mean[m, n2] * w.view(-1, 1)).sum(0) / w.sum()
     assert torch.allclose(new.float().cpu(), ref.half().float(), rtol=2e-3, atol=2e-3)
+
+
+# ------------------------------------------------------------------------------------------
+# The pieces together: a short decode loop of one layer -- append a token's K/V to the paged cache, keep
+# block_ids current with assign_page_clusters (F1), decode through SparseDecodeBackend (F3) -- against the
+# same loop on the CPU oracle.
+# ------------------------------------------------------------------------------------------
+def test_decode_loop_with_cache_append_and_page_assignment(ops):
+    from decode_backend import SparseDecodeBackend
+    Nq, Nkv, C, k, blocks, maxP = 16, 4, 32, 4, 40, 8
+    gen = torch.Generator().manual_seed(909)
+    key = torch.zeros(blocks, 128, Nkv, 128, dtype=torch.float16)
+    value = torch.zeros_like(key)
+    l1 = torch.randn(Nkv, C, 128, generator=gen).half()
+    lens = [3 * 128 + 126, 2 * 128 + 5]                               # sequence 0 is about to fill its 4th page
+    free = list(range(blocks - 1, -1, -1))
+    table = torch.zeros(2, maxP, dtype=torch.int32)
+    for b, n in enumerate(lens):
+        for j in range((n + 127) // 128):
+            pg = free.pop()
+            table[b, j] = pg
+            cnt = min(128, n - j * 128)
+            key[pg, :cnt] = (torch.randn(cnt, Nkv, 128, generator=gen) * 0.5).half()
+            value[pg, :cnt] = torch.rand(cnt, Nkv, 128, generator=gen).half()
+    bid = torch.zeros(Nkv, blocks, dtype=torch.int32)
+    dkey, dvalue, dl1, dbid = key.to(DEV), value.to(DEV), l1.to(DEV), bid.clone().to(DEV)
+
+    def assign(pages, toks):
+        nonlocal bid
+        ids = torch.tensor(pages, dtype=torch.int32)
+        tk = torch.tensor(toks, dtype=torch.int32)
+        bid, _ = oc.assign_page_clusters(key, l1, ids, bid, tk)
+        ops.assign_page_clusters(dkey, dl1, ids.to(DEV), dbid, tk.to(DEV))
+
+    pages, toks = [], []
+    for b, n in enumerate(lens):
+        for j in range((n + 127) // 128):
+            pages.append(int(table[b, j])); toks.append(min(128, n - j * 128))
+    assign(pages, toks)
+    assert torch.equal(dbid.cpu(), bid)
+    be = SparseDecodeBackend(Nq, Nkv, 128, 128, k, max_batch=2, max_blocks_per_seq=maxP, dtype=torch.float16, device=DEV)
+    be.bind_cache(dkey, dvalue, dl1, dbid)
+    for step in range(4):
+        touched, tcount = [], []
+        for b in range(2):                                            # append this step's token to the cache
+            pos = lens[b]
+            if pos % 128 == 0:
+                table[b, pos // 128] = free.pop()
+            pg = int(table[b, pos // 128])
+            kv_k = (torch.randn(Nkv, 128, generator=gen) * 0.5).half()
+            kv_v = torch.rand(Nkv, 128, generator=gen).half()
+            key[pg, pos % 128], value[pg, pos % 128] = kv_k, kv_v
+            dkey[pg, pos % 128], dvalue[pg, pos % 128] = kv_k.to(DEV), kv_v.to(DEV)
+            lens[b] = pos + 1
+            touched.append(pg); tcount.append(pos % 128 + 1)
+        assign(touched, tcount)                                       # the page's cluster follows its pooled key
+        assert torch.equal(dbid.cpu(), bid), f"block_ids differ at step {step}"
+        q = torch.rand(2, Nq, 128, generator=gen).half()
+        seq = torch.tensor(lens, dtype=torch.int32)
+        want = oc.sparse_paged_fusion_attention(q, key, value, table, l1, bid, seq, Nq, 128 ** -0.5, Nkv, 128, k, be.max_page_num)
+        out = be.forward_decode(q.to(DEV), table.to(DEV), seq.to(DEV), use_graph=(step >= 2))
+        torch.cuda.synchronize()
+        bp, ppl, mx = be.selection(2)
+        assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2]), f"selection differs at step {step}"
+        assert_close(out, want[0], 1e-3, f"decode loop step {step}")
+    assert lens[0] == 3 * 128 + 130                                   # sequence 0 crossed into a fifth page
