@@ -301,7 +301,9 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
         }
     while (!(rec >> 63)) rec = ld_relaxed_u64(p.item_info + item);     // published before the entries; normally valid at once
     const int len = record_len(rec);
-    const bool whole = (cnt == len);                                    // uniform over the CTA
+    // uniform over the CTA.  With the optional LSE output every segment takes the partial -> combine route (the
+    // combiner writes the LSE): the consumers' path carries no code for it
+    const bool whole = (cnt == len) && p.lse == nullptr;
     int slot = __shfl_sync(0xffffffffu, slot_t0, 0);                    // thread 0's reservation ...
     if (lane == 0 && warp == 0) reinterpret_cast<int *>(wml)[kConsumerWarps * HP * 2] = slot;
     named_bar_sync(1, kAll);
@@ -352,7 +354,6 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
             const int d0 = half * kMergeHalf + lane * 2;
             if (whole) {
                 if (h < p.g) write_out_vals<QT, KVI8, 2>(p, b, n2, h, d0, acc, Ls);
-                if (h < p.g && half == 0 && p.lse != nullptr) write_lse<QT, KVI8>(p, b, n2, h, M, Ls);
             } else {
                 *reinterpret_cast<float2 *>(p.part_o + ((size_t)slot * HP + h) * kD + d0) = make_float2(acc[0], acc[1]);
             }

@@ -577,7 +577,7 @@ __device__ __forceinline__ void queue_item_done(const ChainParams &p) {
 }
 // attention_out rows of an item without any page (seq 0 / nothing selected): zeros, as the combine of
 // an empty sum gives.  nthreads threads, tid in [0, nthreads).
-__device__ __forceinline__ void zero_item_output(const ChainParams &p, int b, int n2, int tid, int nthreads) {
+__device__ __noinline__ void zero_item_output(const ChainParams &p, int b, int n2, int tid, int nthreads) {
     for (int i = tid; i < p.g * (kD / 4); i += nthreads) {
         const int h = i / (kD / 4), d4 = i % (kD / 4);
         const size_t off = (size_t)b * p.out_sb + (size_t)(n2 * p.g + h) * p.out_sh + d4 * 4;
