@@ -4,15 +4,16 @@
 // selected K/V page slice is fetched from HBM once per group (the compulsory traffic)
 // even though each query head has its own page set: per-page head masks switch heads off.
 //
-// Scheduling: phase A publishes each item's union pages into one global page queue (spa_select.cuh,
-// queue_commit).  A CTA claims runs of consecutive queue entries with one atomicAdd; run lengths
-// shrink with the remaining work (guided self-scheduling), so all SMs drain HBM until the very end
-// and no grid-wide barrier separates selection, streaming and combine.  (The reference authors
-// prototyped equal static ranges in tests/test_block_lookup.py:22-48; the dynamic queue also
-// absorbs the spread of phase A and of the HBM channels.)  A run is streamed through a
-// TMA -> shared-memory ring; whenever the item changes the CTA leaves one partial (O, m, l), and
-// the CTA that completes an item's page count merges that item's partials (flash-decode combine,
-// sparse_paged_attention_split_Bbn2s2_Us2.h:2392-2495) and writes attention_out.
+// Scheduling: phase A leaves each item's union pages at a fixed place of the page array and publishes them
+// (spa_select.cuh, publish_item): a private prefix that the selecting CTA streams itself, first thing after its
+// own selection -- while other CTAs may still be selecting -- and chunks of the rest in one global chunk queue
+// that every CTA claims from, one atomicAdd per chunk with the next claim and the next descriptor always in
+// flight.  So all SMs drain HBM until the very end and no grid-wide barrier separates selection, streaming and
+// combine.  (The reference separates them with SyncAll and prototyped equal static ranges in
+// tests/test_block_lookup.py:22-48.)  Pages are streamed through a TMA -> shared-memory ring; whenever the item
+// changes the CTA leaves one partial (O, m, l), and the CTA that completes an item's page count merges that
+// item's partials (flash-decode combine, sparse_paged_attention_split_Bbn2s2_Us2.h:2392-2495) and writes
+// attention_out.
 #pragma once
 #include "spa_common.cuh"
 
@@ -218,12 +219,36 @@ __device__ void combine_item_warp(const ChainParams &p, int item, int base, int 
             if (e < nh && p.lse != nullptr) write_lse<QT, KVI8>(p, b, n2, h0 + e, M[e], L);
         }
     }
-    if (lane == 0) { p.item_info[item] = 0ull; p.ctrl[Ctrl::pages_done(p.B, item)] = 0; }
+    if (lane == 0) { p.item_info[item] = 0ull; p.ctrl[Ctrl::pages_done(item)] = 0; }
 }
 
 // ---- post warp: takes the flush messages of this CTA's consumers; publishes each partial (mark in the
 // queue, fence, page count) and combines the items this CTA completed.  Keeps every global round trip
 // of the bookkeeping off the consumers' path: under a saturated HBM each one costs microseconds.
+// max_page_position_length[b, 0..7] = bs * (longest per-head page list of b) (cent_select.cpp:123-160), fused op:
+// the items' publishers leave 1 + their maximum in item_ppl (non-zero once written); post warp 0 of CTA
+// (b mod grid) waits for the Nkv words of b, reduces, writes, and returns the words to zero.  Nothing else in the
+// launch waits for this, and the waiting warp has nothing to do until its CTA's first partial.
+__device__ __noinline__ void max_ppl_poll(const ChainParams &p) {
+    const int lane = lane_id();
+    for (int b = blockIdx.x; b < p.B; b += gridDim.x) {
+        int m = 0;
+        for (int n0 = 0; n0 < p.Nkv; n0 += 32) {
+            const int n2 = n0 + lane;
+            if (n2 < p.Nkv) {
+                int *w = p.item_ppl + (size_t)b * p.Nkv + n2;
+                int v;
+                while ((v = ld_relaxed(w)) == 0) __nanosleep(100);
+                *w = 0;
+                m = max(m, v - 1);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane < kPad) p.max_ppl[(size_t)b * kPad + lane] = (long long)m * p.bs;
+    }
+}
+
 template <typename QT, bool KVI8, int NT>
 __device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t *mfull, uint64_t *mempty, int *list,
                                int list_cap) {
@@ -243,7 +268,7 @@ __device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t 
         if (lane == 0) {
             st_relaxed_u64(p.flat + first_idx, (unsigned long long)slot + 1ull);
             __threadfence();
-            old = atomicAdd(p.ctrl + Ctrl::pages_done(p.B, item), cnt);
+            old = atomicAdd(p.ctrl + Ctrl::pages_done(item), cnt);
         }
         old = __shfl_sync(0xffffffffu, old, 0);
         if (old == len - cnt) {
@@ -364,14 +389,13 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
     if (threadIdx.x == 0) {
         if (whole) p.item_info[item] = 0ull;                          // consumed: nobody else holds pages of it
         else post_message(mail, mfull, mempty, mi, mph, make_int4(item, first_idx, cnt, slot),
-                          make_int4(record_base(rec), len, 0, 0));
+                          make_int4(item * p.qstride, len, 0, 0));
     }
 }
 
 // ---- producer side ------------------------------------------------------------------------------------
-// One queue entry (any lane).  The producer only reads entries after it has seen "all items done"
-// (acquire), so the first read normally succeeds; the loop covers the memory model.
-// A consumed entry is returned to zero, so the queue is clean for the next launch.
+// One page entry (any lane).  An item is on offer as soon as its page count is known, possibly before its
+// entries are written: poll.  A consumed entry is returned to zero, so the array is clean for the next launch.
 __device__ __forceinline__ unsigned long long take_entry(const ChainParams &p, int idx, unsigned long long v) {
     unsigned long long *e = p.flat + idx;
     while (!(v >> 63)) { __nanosleep(32); v = ld_relaxed_u64(e); }
@@ -569,7 +593,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
 
 template <typename QT, bool KVI8, int NT>
 __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, const CUtensorMap *tmV,
-                                unsigned char *smem) {
+                                unsigned char *smem, PubState *pub) {
     AttnSmem L(p.nstages, p.stage_bytes, NT, p.list_cap);
     unsigned char *stage_base = smem + L.stages;
     float *mbuf = reinterpret_cast<float *>(smem + L.mbuf);
@@ -599,6 +623,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
 
     if (warp >= kPostWarp) {
         const int pw = warp - kPostWarp;
+        if (pw == 0 && p.mode == kModeFused && p.max_ppl != nullptr) max_ppl_poll(p);
         post_warp_loop<QT, KVI8, NT>(p, mail + pw * kMailSlots * 2, mfull + pw * kMailSlots, mempty + pw * kMailSlots,
                                      list + pw * L.list_cap, L.list_cap);
         return;
@@ -606,109 +631,92 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     if (warp == kConsumerWarps) {
         // =============================== TMA producer ===============================
         if (lane == 0) { tma_prefetch_desc(tmK); tma_prefetch_desc(tmV); }
-        // The queue is final once every item has reported.  Most of it is cut statically (no traffic on
-        // the critical path: every control access costs microseconds while HBM is saturated); the rest
-        // is handed out in short runs, one claim always in flight, which evens out the SMs' speeds.
-        int T = 0;
-        if (lane == 0) {
-            for (;;) {
-                unsigned long long w;
-                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p.ctrl + Ctrl::kTail) : "memory");
-                if ((int)(w >> 32) == p.items) { T = (int)(unsigned)w; break; }
-                __nanosleep(40);
-            }
-        }
-        T = __shfl_sync(0xffffffffu, T, 0);
-        const int G = gridDim.x;
-        // Little work (a few pages per CTA): cutting items between CTAs buys no balance worth having, but
-        // every cut item pays the partial -> publish -> combine chain (five dependent L2 round trips,
-        // ~10 us) after its last page.  Then every CTA streams WHOLE items -- items blockIdx.x, + G, + 2G --
-        // and writes their output straight from the consumers' merge (no partial, no combine, no claims).
-        const bool whole_items = p.small_pages > 0 && T <= G * p.small_pages && p.items <= 3 * G;
-        const int S = whole_items ? 0 : (int)((long long)T * p.static_pct / 100 / G);   // static pages per CTA
-        const int dyn0 = whole_items ? T : G * S;
-        // claimed runs: equal length, about dyn_runs per CTA.  (Run lengths that shrink with the work left
-        // were measured too, guided by the counter or by the CTA's own progress: every extra run costs
-        // more in flushes and claim latency than the finer balance returns; c2 0.1175 ms vs 0.120-0.122.)
-        const int Rd = max(p.dyn_min, (T - dyn0 + p.dyn_runs * G - 1) / (p.dyn_runs * G));
-        int nf = 0;                                                        // next claim, in flight (lane 0)
-        if (lane == 0) nf = atomicAdd(p.ctrl + Ctrl::kHead, Rd);
-        unsigned long long t_runs = 1, t_pages = 0;
+        // Runs of page entries, in this order: the private prefixes of this CTA's own items (known since its own
+        // selection: streaming starts while other CTAs may still be selecting), then chunks claimed from the
+        // global chunk queue.  A chunk is claimed LATE -- when the current run has claim_lead pages left to
+        // issue -- so that at the end of the launch no CTA sits on a chunk it has not started while others are
+        // idle; the claim (atomic) and the descriptor load are issued at different page counts, so neither
+        // round trip (microseconds while HBM is saturated) is waited for.
+        const int nown = pub->n_own;
+        int oi = 0;
+        int rf = 0, rn = 0;                                                // current run: flat[rf, rf + rn)
+        int nf = 0, claim_idx = 0;                                         // claim in flight (lane 0) / claimed index
+        unsigned long long dv = 0ull;                                      // descriptor word of claim_idx as last loaded (lane 0)
+        int cst = 0;                                                       // claim state: 0 none, 1 atomic in flight, 2 descriptor loading
         bool more = true;
-        // Static share [s0, e0).  An item cut by a range boundary is finished by two CTAs; if each CTA
-        // walked its range front to back, every such item would complete at the very end (this CTA's last
-        // pages, the neighbour's first) and all combines would pile up after the stream.  So the part of
-        // the last item is streamed right after the first item: cut items complete early, their combine
-        // hides under the stream, and the range ends with whole items (no partial, no combine).
-        const int s0 = blockIdx.x * S, e0 = s0 + S;
-        int srun[3][2] = {{s0, S}, {0, 0}, {0, 0}};
-        int nsr = (S > 0) ? 1 : 0;
-        if (S > 0) {
-            unsigned long long pr = 0ull;
-            if (lane < 2) {
-                const unsigned long long *pe = p.flat + (lane == 0 ? s0 : e0 - 1);
-                unsigned long long ev;
-                do { ev = ld_relaxed_u64(pe); } while (!(ev >> 63));
-                const unsigned long long *pi = p.item_info + (int)((ev >> 48) & (kMaxItems - 1));
-                do { pr = ld_relaxed_u64(pi); } while (!(pr >> 63));
+        unsigned long long t_runs = 0, t_pages = 0;
+        const int lead = p.claim_lead;
+        // called per issued page with the pages the current run still has to issue
+        auto advance_claim = [&](int remaining) {
+            if (!more || oi < nown) return;
+            if (cst == 0 && remaining <= lead) {
+                if (lane == 0) nf = atomicAdd(p.ctrl + Ctrl::kHead, 1);
+                cst = 1;
+            } else if (cst == 1 && remaining <= (lead >> 1)) {
+                claim_idx = __shfl_sync(0xffffffffu, nf, 0);
+                if (lane == 0) dv = ld_relaxed_u64(p.desc + claim_idx);
+                cst = 2;
             }
-            const unsigned long long ra = __shfl_sync(0xffffffffu, pr, 0), rb = __shfl_sync(0xffffffffu, pr, 1);
-            const int b1 = min(e0, record_base(ra) + record_len(ra));       // end of the first item
-            const int bb = max(s0, record_base(rb));                        // start of the last item
-            if (bb > b1 && record_base(rb) + record_len(rb) > e0) {
-                srun[0][1] = b1 - s0;
-                srun[1][0] = bb; srun[1][1] = e0 - bb;
-                srun[2][0] = b1; srun[2][1] = bb - b1;
-                nsr = 3;
-            }
-        }
-        if (whole_items) {
-            unsigned long long pr = 0ull;
-            const int it = (int)blockIdx.x + lane * G;
-            if (lane < 3 && it < p.items) {
-                // every item has reported (its record precedes its report): after this lane's own acquire of
-                // the report count a record that is still zero means an item without pages
-                unsigned long long w;
-                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p.ctrl + Ctrl::kTail) : "memory");
-                pr = ld_relaxed_u64(p.item_info + it);
-            }
-            nsr = 0;
-#pragma unroll
-            for (int j = 0; j < 3; ++j) {
-                const unsigned long long r = __shfl_sync(0xffffffffu, pr, j);
-                if ((r >> 63) && record_len(r) > 0) { srun[nsr][0] = record_base(r); srun[nsr][1] = record_len(r); ++nsr; }
-            }
-        }
-        int sri = 0;                                                       // next static run
-        int rf = 0, rn = 0;                                                // current run: [rf, rf + rn)
-        // next chunk (<= 32 entries of one run) -> cf, cn; false when the queue is exhausted
-        auto next_chunk = [&](int &cf, int &cn) -> bool {
-            while (rn == 0 && sri < nsr) { rf = srun[sri][0]; rn = srun[sri][1]; ++sri; }
-            if (rn == 0) {
-                if (!more) return false;
-                const int got = __shfl_sync(0xffffffffu, nf, 0);
-                const int f = dyn0 + got;
-                const int n = min(Rd, T - f);
-                if (n <= 0) { more = false; return false; }
-                rf = f; rn = n; ++t_runs;
-                if (lane == 0) { nf = atomicAdd(p.ctrl + Ctrl::kHead, Rd); trace_put(p, 2, globaltimer_ns()); }
+        };
+        // next chunk (<= 32 entries of one run) -> cf, cn, last (it ends its run).  Returns 1: got one, 0: the queue
+        // is exhausted, -1 (only with block == false): the next run is not known yet -- issue what you have first
+        auto next_chunk = [&](int &cf, int &cn, bool &last, bool block) -> int {
+            while (rn == 0) {
+                if (oi < nown) { rf = pub->own_item[oi] * p.qstride; rn = pub->own_len[oi]; ++oi; ++t_runs; continue; }
+                if (!more) return 0;
+                if (!block) return -1;
+                if (cst == 0) { if (lane == 0) nf = atomicAdd(p.ctrl + Ctrl::kHead, 1); cst = 1; }
+                if (cst == 1) {
+                    claim_idx = __shfl_sync(0xffffffffu, nf, 0);
+                    if (lane == 0) dv = ld_relaxed_u64(p.desc + claim_idx);
+                    cst = 2;
+                }
+                unsigned long long d = 0ull;
+                int verdict = 1;                                           // 1 chunk, 0 empty slot (claim again), -1 end of the queue
+                if (lane == 0) {
+                    d = dv;
+                    while (!(d >> 63)) {
+                        // not published yet -- or never: once every item has reported, a zero descriptor is an
+                        // empty slot (its item has fewer chunks) and kTail * items is the end of the queue
+                        const unsigned long long w = ld_acquire_u64(reinterpret_cast<const unsigned long long *>(p.ctrl + Ctrl::kTail));
+                        d = ld_relaxed_u64(p.desc + claim_idx);
+                        if (d >> 63) break;
+                        if ((int)(w >> 32) == p.items) { verdict = (claim_idx >= (int)(unsigned)w * p.items) ? -1 : 0; break; }
+                        __nanosleep(64);
+                    }
+                    if (d >> 63) { st_relaxed_u64(p.desc + claim_idx, 0ull); trace_put(p, 2, globaltimer_ns()); }
+                }
+                d = __shfl_sync(0xffffffffu, d, 0);
+                verdict = __shfl_sync(0xffffffffu, verdict, 0);
+                cst = 0;
+                if (!(d >> 63)) {
+                    if (verdict < 0) { more = false; return 0; }
+                    continue;                                              // empty slot
+                }
+                rf = (int)((d >> 48) & (kMaxItems - 1)) * p.qstride + (int)(unsigned)d;
+                rn = (int)((d >> 32) & 0xffffu);
+                ++t_runs;
             }
             cf = rf; cn = min(32, rn);
             rf += cn; rn -= cn;
-            return true;
+            last = rn == 0;
+            return 1;
         };
         int cf = 0, cn = 0;
-        bool ok = next_chunk(cf, cn);
-        unsigned long long ent = (ok && lane < cn) ? ld_relaxed_u64(p.flat + cf + lane) : 0ull;
-        while (ok) {
+        bool last = false;
+        int ok = next_chunk(cf, cn, last, true);
+        unsigned long long ent = (ok == 1 && lane < cn) ? ld_relaxed_u64(p.flat + cf + lane) : 0ull;
+        while (ok == 1) {
             // entries of the following chunk travel while this chunk is issued
             int cf2 = 0, cn2 = 0;
-            const bool ok2 = next_chunk(cf2, cn2);
-            const unsigned long long ent2 = (ok2 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
+            bool last2 = false;
+            int ok2 = next_chunk(cf2, cn2, last2, false);
+            unsigned long long ent2 = (ok2 == 1 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
             if (lane < cn) ent = take_entry(p, cf + lane, ent);
             t_pages += cn;
             bool second = false;                                           // this entry closes a pair
             for (int j = 0; j < cn; ++j) {
+                if (last) advance_claim(cn - j);
                 const unsigned long long e = __shfl_sync(0xffffffffu, ent, j);
                 const unsigned long long en = __shfl_sync(0xffffffffu, ent, min(j + 1, cn - 1));
                 // two consecutive pages of one item (inside a chunk) are handed to the consumers as a pair
@@ -743,8 +751,13 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                 }
             }
             __syncwarp();
-            ok = ok2; cf = cf2; cn = cn2; ent = ent2;
+            if (ok2 < 0) {
+                ok2 = next_chunk(cf2, cn2, last2, true);
+                ent2 = (ok2 == 1 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
+            }
+            ok = ok2; cf = cf2; cn = cn2; last = last2; ent = ent2;
         }
+        if (lane == 0 && cst == 1) pub->priv_used = nf;  // a claim in flight has landed before this CTA reports "finished"
         if (lane == 0) { unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid)); trace_put(p, 12, smid); }
         if (lane == 0) { trace_put(p, 4, t_pages); trace_put(p, 6, t_runs); trace_put(p, 7, globaltimer_ns()); }
         if (lane == 0) {                                  // end marker: a stage without data

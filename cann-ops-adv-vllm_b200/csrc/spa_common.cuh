@@ -68,9 +68,11 @@ struct ChainParams {
     int ax_row, ax_head, ax_blk;                         // TMA coordinate slots (1..3)
     int num_blocks;
     // ---- workspace
-    unsigned long long *flat;                            // page queue, see queue_entry(); zero = not published
+    unsigned long long *flat;                            // [items, qstride] union pages of every item, see queue_entry(); zero = not published
+    unsigned long long *desc;                            // chunk queue, see chunk_desc(); zero = not published
     unsigned long long *item_info;                       // [items] see item_record(); zero = not published
-    int *item_ppl;                                       // [items] max selected pages over the item's heads
+    int *item_ppl;                                       // [items] 1 + max selected pages over the item's heads; zero = not published
+    int qstride;                                         // entries reserved per item in `flat`
     int *ctrl;                                           // queue counters, see Ctrl (all zero between launches)
     int pool_cap;                                        // partial slots available
     float *part_o;                                       // [pool_cap, HP, D]
@@ -84,10 +86,12 @@ struct ChainParams {
     int stage_bytes;
     int smem_bytes;
     int mode;                                            // see Mode
-    int static_pct;                                      // share of the page queue cut statically, percent
-    int dyn_runs, dyn_min;                               // the rest is claimed in ~dyn_runs runs per CTA of >= dyn_min pages
+    int static_pct;                                      // share of a CTA's fair share it keeps of its OWN items (streamed first), percent
+    int dyn_runs, dyn_min;                               // (dyn_runs unused) chunks of the rest are >= dyn_min pages
+    int chunk_num, chunk_den;                            // each chunk takes chunk_num / chunk_den of what is left of the item
+    int claim_lead;                                      // a chunk is claimed when the current run has this many pages left to issue
     int list_cap;                                        // partial slots the post warp can list for one item
-    int small_pages;                                     // <= this many queue pages per CTA: every CTA streams whole items (0 = off)
+    int small_pages;                                     // a CTA keeps its own items whole while they add up to <= this many pages (0 = off)
     int pair_pages;                                      // consumers take two pages of an item per step (needs >= 4 stages)
     // ---- optional phase trace: [gridDim.x, kTraceSlots] globaltimer ns (null = off)
     unsigned long long *trace;
@@ -103,12 +107,12 @@ enum Mode : int {
 // Queue control block (ints).  Every word is zero when a launch starts and is returned to zero by
 // the launch itself (per-item words by the item's combiner, the globals by the last CTA to leave).
 struct Ctrl {
-    // kTail (low) and kItemsDone (high) form one aligned 64-bit word: a single load tells a consumer
-    // whether every item has reported and, if so, the final queue length
+    // kTail (low: the largest number of chunks any item was cut into) and kItemsDone (high: items reported) form
+    // one aligned 64-bit word: a single load tells a consumer whether every item has reported and, if so, where
+    // the chunk queue ends (kTail * items)
     enum { kHead = 0, kTail = 2, kItemsDone = 3, kPool = 4, kFinished = 5, kError = 6, kGlobals = 16 };
-    __host__ __device__ static inline int b_done(int b) { return kGlobals + b; }
-    __host__ __device__ static inline int pages_done(int B, int item) { return kGlobals + B + item; }
-    __host__ __device__ static inline int words(int B, int items) { return kGlobals + B + items; }
+    __host__ __device__ static inline int pages_done(int item) { return kGlobals + item; }
+    __host__ __device__ static inline int words(int items) { return kGlobals + items; }
 };
 
 // ------------------------------------------------------------------------------------------
@@ -131,15 +135,29 @@ __host__ __device__ __forceinline__ unsigned long long queue_entry(int phys, uns
     return ((unsigned long long)hi << 32) | lo;
 }
 constexpr int kMaxItems = 1 << 14;
-// Per-item record: valid | tail tokens (8 bits, 1..128) | union pages (24 bits) | queue base (28 bits)
+// Per-item record: valid | tail tokens (8 bits, 1..128) | union pages (24 bits).  The item's entries sit at the
+// fixed place flat[item * qstride ...), so publishing needs no reservation.
 constexpr int kMaxQueue = 1 << 28;
-__host__ __device__ __forceinline__ unsigned long long item_record(int base, int len, int tail_cnt) {
-    return (1ull << 63) | ((unsigned long long)(tail_cnt & 0xff) << 52) | ((unsigned long long)(len & 0xffffff) << 28) |
-           (unsigned long long)(base & (kMaxQueue - 1));
+__host__ __device__ __forceinline__ unsigned long long item_record(int len, int tail_cnt) {
+    return (1ull << 63) | ((unsigned long long)(tail_cnt & 0xff) << 52) | ((unsigned long long)(len & 0xffffff) << 28);
 }
-__host__ __device__ __forceinline__ int record_base(unsigned long long r) { return (int)(r & (kMaxQueue - 1)); }
 __host__ __device__ __forceinline__ int record_len(unsigned long long r) { return (int)((r >> 28) & 0xffffff); }
 __host__ __device__ __forceinline__ int record_tail(unsigned long long r) { return (int)((r >> 52) & 0xff); }
+// Chunk of an item's pages offered to every CTA: valid | item (14 bits) | pages (16 bits) | first entry (32 bits)
+constexpr int kMaxChunks = 8;         // chunks one item is cut into at most
+constexpr int kMaxOwn = 8;            // own items a CTA keeps a private prefix of
+__host__ __device__ __forceinline__ unsigned long long chunk_desc(int item, int start, int n) {
+    return (1ull << 63) | ((unsigned long long)(item & (kMaxItems - 1)) << 48) | ((unsigned long long)(n & 0xffff) << 32) |
+           (unsigned long long)(unsigned)start;
+}
+// Per-CTA publisher state (shared memory): what this CTA keeps of its own items
+struct PubState {
+    int n_own, priv_used;
+    int own_item[kMaxOwn], own_len[kMaxOwn];
+    // selection group -> publisher (TMA producer warp) mailbox: {item, union pages, tail tokens, max pages per head}
+    volatile int req[2][4];
+    volatile unsigned req_seq[2], ack_seq[2];
+};
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p) {
     unsigned long long v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");

@@ -72,17 +72,22 @@ spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ 
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmC) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = aligned_smem(smem_raw);
+    __shared__ PubState pub;
 
     trace_mark(p, 0);
+    if (threadIdx.x == 0) {
+        pub.n_own = 0; pub.priv_used = 0;
+        pub.req_seq[0] = pub.req_seq[1] = 0u; pub.ack_seq[0] = pub.ack_seq[1] = 0u;
+    }
     // ---- phase A: selection (or union building) per (b, kv head); every item ends by publishing its
-    // pages into the queue
+    // pages (both branches start with a __syncthreads: the publisher state above is visible)
     if (p.mode == kModeFused)
-        select_phase<QT, kSelScores | kSelSelect | kSelUnion>(p, &tmC, smem);
+        select_phase<QT, kSelScores | kSelSelect | kSelUnion>(p, &tmC, smem, &pub);
     else
-        for (int item = blockIdx.x; item < p.items; item += gridDim.x) union_from_block_position(p, item, smem);
+        for (int item = blockIdx.x; item < p.items; item += gridDim.x) union_from_block_position(p, item, smem, &pub);
     trace_mark(p, 1);
-    // ---- phase B + C: stream queue runs; the CTA completing an item combines it
-    attention_phase<QT, KVI8, NT>(p, &tmK, &tmV, smem);
+    // ---- phase B + C: stream own prefixes and claimed chunks; the CTA completing an item combines it
+    attention_phase<QT, KVI8, NT>(p, &tmK, &tmV, smem, &pub);
     trace_mark(p, 3);
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -103,7 +108,7 @@ __global__ void __launch_bounds__(kThreads, 1) spa_select_kernel(const __grid_co
                                                                  const __grid_constant__ CUtensorMap tmC) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = aligned_smem(smem_raw);
-    select_phase<QT, FLAGS>(p, &tmC, smem);
+    select_phase<QT, FLAGS>(p, &tmC, smem, nullptr);
 }
 
 __global__ void spa_max_ppl_kernel(const __grid_constant__ ChainParams p) {
@@ -140,7 +145,7 @@ struct spaExecutor {
     int q_bf16, kv_i8, nt_tiles;
     uint64_t ws_bytes;
     // workspace offsets (bytes)
-    uint64_t off_ctrl, off_flat, off_info, off_ippl, off_po, off_pml, off_xs;
+    uint64_t off_ctrl, off_flat, off_desc, off_info, off_ippl, off_po, off_pml, off_xs;
     uint64_t ctrl_bytes;
     AssignParams ap;       // OP_ASSIGN
     int persistent_ws;     // see spaExecutorSetPersistentWorkspace
@@ -247,7 +252,7 @@ static int plan_select_smem(ChainParams *p, int flags, int grid, int budget, int
     const int ntiles = (Ceff + kCentTileRows - 1) / kCentTileRows;
     SelSmem L(p->g, Ceff, keff, p->maxP, flags);
     int gw = (p->g > 4 || p->items <= grid) ? 8 : 4;
-    if (const char *s = getenv("SPA_SEL_GW")) { const int v = atoi(s); if (v == 2 || v == 4 || v == 8) gw = v; }
+    if (const char *s = getenv("SPA_SEL_GW")) { const int v = atoi(s); if (v == 4 || v == 8) gw = v; }
     for (; gw <= 8; gw *= 2) {
         const int ngroups = kConsumerWarps / gw;
         const long long state = (long long)L.total * ngroups;
@@ -843,20 +848,26 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     if ((rc = dev_info(&d))) return rc;
     if (!d.coop) return fail(SPA_ERR_CUDA, "device lacks cooperative launch");
     e->nt_tiles = (p.g + 7) / 8;
-    // ---- scheduling of the page queue (spa_attn.cuh): static share + short claimed runs
-    p.static_pct = 50; p.dyn_runs = 3; p.dyn_min = 2;     // measured on c2 (B200): 50/3 0.1175 ms, 85/3 0.1246, 0/6 0.1200
-    p.small_pages = 16;    // measured crossover on the configs[4] sweep: ~16.5 queue pages per CTA
+    // ---- scheduling (spa_select.cuh publish_item, spa_attn.cuh producer): a CTA keeps static_pct % of its fair
+    // share as a private prefix of its own items; the rest is offered in chunks, about dyn_runs per CTA
+    p.static_pct = 50; p.dyn_runs = 3; p.dyn_min = 2;
+    p.small_pages = 16;    // measured crossover on the configs[4] sweep: ~16.5 pages per CTA
     if (const char *s = getenv("SPA_SMALL_PAGES")) p.small_pages = std::max(0, atoi(s));
     if (const char *s = getenv("SPA_STATIC_PCT")) p.static_pct = std::min(100, std::max(0, atoi(s)));
     if (const char *s = getenv("SPA_DYN_RUNS")) p.dyn_runs = std::max(1, atoi(s));
     if (const char *s = getenv("SPA_DYN_MIN")) p.dyn_min = std::max(1, atoi(s));
-    // Partials: one per (run, item) pair met by a CTA: <= 3 static runs per CTA, (dyn_runs + 2) * grid
-    // claimed runs (rounding of the run length; one overshooting claim per CTA), plus one per item
-    // boundary inside a run.
-    const double qmax = (double)p.items * p.maxP * (p.mode == kModeAttnOnly ? 2 : 1);
-    p.pool_cap = (int)std::min<double>((double)d.sms * (p.dyn_runs + 5) + p.items + 64, qmax + d.sms);
-    // partials of ONE item: every run that touches it
-    p.list_cap = std::min(p.pool_cap, d.sms * (p.dyn_runs + 5) + 8);
+    p.chunk_num = 1; p.chunk_den = 2; p.claim_lead = 4;
+    if (const char *s = getenv("SPA_CHUNK_FRAC")) { int a = 0, b = 0; if (sscanf(s, "%d/%d", &a, &b) == 2 && a > 0 && b >= a) { p.chunk_num = a; p.chunk_den = b; } }
+    if (const char *s = getenv("SPA_CLAIM_LEAD")) p.claim_lead = std::max(0, atoi(s));
+    p.qstride = p.maxP * (p.mode == kModeAttnOnly ? 2 : 1);     // x2: a page may be listed twice (split tail entries)
+    // Partials: one per (run, item) pair met by a CTA -- a run (own prefix or chunk) lies inside one item
+    const double qmax = (double)p.items * p.qstride;
+    // (a prefix and <= kMaxChunks chunks per item; chunks are not smaller than 1/32 of a CTA's fair share)
+    int cmax = kMaxChunks;
+    if ((long long)p.items >= 32ll * d.sms) cmax = 1;
+    p.pool_cap = (int)std::min<double>((double)p.items * (cmax + 1), qmax) + 1;
+    // partials of ONE item: its private prefix and its chunks
+    p.list_cap = kMaxChunks + 2;
     if (p.num_blocks > kMaxBlocks) return fail(SPA_ERR_UNSUPPORTED, "more than %d KV blocks", kMaxBlocks);
     p.stage_bytes = e->kv_i8 ? 16384 : 32768;
     const int budget = d.smem_optin - 1024 - 512;     // 1 KiB alignment slack + the kernels' static shared memory
@@ -884,14 +895,16 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     // ---- workspace
     const int HP = e->nt_tiles * 8;
     uint64_t o = 0;
-    // queue words that must be zero when a launch starts (the launch leaves them zero again)
-    const uint64_t qcap = (uint64_t)p.items * p.maxP * (p.mode == kModeAttnOnly ? 2 : 1);   // x2: split tail entries
-    if (qcap >= (uint64_t)kMaxQueue) return fail(SPA_ERR_UNSUPPORTED, "B*Nkv*maxBlocks = %llu exceeds the page queue", (unsigned long long)qcap);
-    e->off_ctrl = o;   o = align_up(o + (uint64_t)Ctrl::words(p.B, p.items) * 4, 256);
+    // words that must be zero when a launch starts (the launch leaves them zero again)
+    const uint64_t qcap = (uint64_t)p.items * p.qstride;
+    if (qcap >= (uint64_t)kMaxQueue) return fail(SPA_ERR_UNSUPPORTED, "B*Nkv*maxBlocks = %llu exceeds the page array", (unsigned long long)qcap);
+    e->off_ctrl = o;   o = align_up(o + (uint64_t)Ctrl::words(p.items) * 4, 256);
     e->off_info = o;   o = align_up(o + (uint64_t)p.items * 8, 256);
+    e->off_ippl = o;   o = align_up(o + (uint64_t)p.items * 4, 256);
+    // chunk queue: every CTA claims up to two indices past the end
+    e->off_desc = o;   o = align_up(o + ((uint64_t)p.items * kMaxChunks + 2ull * d.sms + 64) * 8, 256);
     e->off_flat = o;   o = align_up(o + qcap * 8, 256);
     e->ctrl_bytes = o;
-    e->off_ippl = o;   o = align_up(o + (uint64_t)p.items * 4, 256);
     e->off_po = o;     o = align_up(o + (uint64_t)p.pool_cap * HP * kD * 4, 256);
     e->off_pml = o;    o = align_up(o + (uint64_t)p.pool_cap * HP * 2 * 4, 256);
     e->off_xs = o;
@@ -910,6 +923,7 @@ static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaSt
     ChainParams p = e->p;
     char *w = (char *)workspace;
     p.ctrl = (int *)(w + e->off_ctrl); p.flat = (unsigned long long *)(w + e->off_flat);
+    p.desc = (unsigned long long *)(w + e->off_desc);
     p.item_info = (unsigned long long *)(w + e->off_info);
     p.item_ppl = (int *)(w + e->off_ippl);
     p.part_o = (float *)(w + e->off_po); p.part_ml = (float *)(w + e->off_pml);
@@ -922,10 +936,11 @@ static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaSt
         CUDA_TRY(cudaMemsetAsync(p.ctrl, 0, e->ctrl_bytes, stream));
         e->clean_ws = e->persistent_ws ? workspace : nullptr;
     }
-    // One CTA per SM.  No grid-wide barrier: CTAs only wait for queue entries other CTAs publish after
-    // their selection, which never depends on the waiter, so an ordinary launch is enough (a CTA that is
-    // scheduled late only delays the others).  SPA_COOP=1 forces a cooperative launch.
-    static const bool coop = getenv("SPA_COOP") != nullptr;
+    // One CTA per SM, launched cooperatively: there is no grid-wide barrier, but CTAs wait for words that other
+    // CTAs publish after their own selection, so all of them must be co-resident.  The cooperative launch makes
+    // the runtime guarantee that -- or refuse the launch with an error (SM partitioning, MPS limits) instead of
+    // leaving resident CTAs spinning for one that can never be scheduled.  SPA_COOP=0: ordinary launch.
+    static const bool coop = !(getenv("SPA_COOP") && atoi(getenv("SPA_COOP")) == 0);
     if (coop) {
         void *args[] = {(void *)&p, (void *)&e->tmK, (void *)&e->tmV, (void *)&e->tmC};
         CUDA_TRY(cudaLaunchCooperativeKernel((const void *)kern, dim3(e->grid), dim3(kThreads), args,

@@ -559,21 +559,86 @@ __device__ __noinline__ int warp_compact_bit(unsigned *pm, int pl, int bit, int 
     return cnt;
 }
 
-// ---- publishing an item's union pages into the global page queue --------------------------------
-// Entries of one item are contiguous, [base, base + len).  Every entry and the item record are single
-// 64-bit stores that are non-zero once written, and a reader needs nothing else, so no ordering
-// between them is required: consumers poll the word they need (spa_attn.cuh, take_entry).
-__device__ __forceinline__ int queue_reserve(const ChainParams &p, int item, int len, int tail_cnt) {
-    if (len <= 0) return 0;
-    const int base = atomicAdd(p.ctrl + Ctrl::kTail, len);
-    st_relaxed_u64(p.item_info + item, item_record(base, len, tail_cnt));
-    return base;
+// ---- publishing an item's union pages ------------------------------------------------------------
+// The entries of an item sit at the fixed place flat[item * qstride + u), u < ulen, in ascending page order:
+// writing them needs no reservation.  Every entry, record and chunk descriptor is a single 64-bit store that is
+// non-zero once written, and a reader needs nothing else, so no ordering (fence) is required anywhere on this
+// path: readers poll the word they need (spa_attn.cuh, take_entry / the producer's chunk loop).
+//
+// Who streams what is decided here, per item, by the publishing CTA alone (nothing global is known yet):
+//   * the CTA keeps a PRIVATE PREFIX [0, S) of each of its own items -- together about static_pct % of a CTA's
+//     fair share of the launch, estimated from this item -- and starts streaming it as soon as its own selection
+//     is over, while other CTAs are still selecting (the reference separates the phases with SyncAll,
+//     sparse_paged_fusion_attention.cpp:56-76);
+//   * the rest [S, ulen) is cut into chunks of HALVING size (down to 1/32 of a CTA's fair share, at most
+//     kMaxChunks): chunk j of item i is descriptor desc[j * items + i], and CTAs claim descriptors in index
+//     order, so all the large chunks go first and the launch ends on the small ones (guided self-scheduling
+//     without knowing the total).  No reservation: the slot is fixed;
+//   * one release-add reports the item (high half of the kTail word) after an atomicMax of its chunk count
+//     (low half): once every item has reported, a descriptor that is still zero is an empty slot and
+//     rounds * items is the end of the queue;
+//   * little work (own items adding up to <= small_pages pages): the item stays whole and private -- no
+//     partial, no combine (five dependent L2 round trips after the item's last page).
+// One thread.  m >= 0: also report the item's longest per-head page list (max_page_position_length).
+__device__ __noinline__ void publish_item(const ChainParams &p, PubState *pub, int item, int ulen, int tail_cnt, int m) {
+    if (m >= 0) p.item_ppl[item] = m + 1;                             // picked up by a post warp (max_ppl_poll)
+    int nch = 0;
+    if (ulen > 0) {
+        st_relaxed_u64(p.item_info + item, item_record(ulen, tail_cnt));
+        const int G = (int)gridDim.x;
+        const float fair = (float)p.items * (float)ulen / (float)G;    // a CTA's share, if every item were like this one
+        const int n_mine = ((int)blockIdx.x < p.items) ? (p.items - 1 - (int)blockIdx.x) / G + 1 : 1;   // items this CTA selects
+        const int used = pub->priv_used;
+        int S = min(ulen, (int)(fair * (float)p.static_pct / (100.f * (float)n_mine) + 0.5f));
+        if (used + ulen <= p.small_pages) S = ulen;
+        if (pub->n_own >= kMaxOwn) S = 0;
+        const int min_chunk = max(p.dyn_min, (int)(fair * (1.f / 32.f)));
+        if (S > 0 && ulen - S < min_chunk) S = ulen;                   // no crumbs on either side
+        if (S < p.dyn_min && S < ulen) S = 0;
+        if (S > 0) {
+            const int o = pub->n_own;
+            pub->own_item[o] = item; pub->own_len[o] = S;
+            pub->n_own = o + 1; pub->priv_used = used + S;
+        }
+        int at = S, left = ulen - S;
+        while (left > 0) {
+            int c = max(min_chunk, (left * p.chunk_num) / p.chunk_den);
+            if (nch == kMaxChunks - 1 || left - c < min_chunk) c = left;
+            st_relaxed_u64(p.desc + (size_t)nch * p.items + item, chunk_desc(item, at, c));
+            at += c; left -= c; ++nch;
+        }
+    }
+    if (nch > 0) atomicMax(p.ctrl + Ctrl::kTail, nch);
+    asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.ctrl + Ctrl::kItemsDone) : "memory");
 }
-// One thread, ordered after the item's reservation (same thread or a barrier): the item is complete.
-// "all items done" tells the consumers that the queue tail is final.
-__device__ __forceinline__ void queue_item_done(const ChainParams &p) {
-    __threadfence();
-    atomicAdd(p.ctrl + Ctrl::kItemsDone, 1);
+// A selection group hands its finished item (or, item < 0, "this group is done") to the publisher -- the TMA
+// producer warp, idle during phase A -- so that the atomic's round trip stays off the selection's path.  One thread.
+__device__ __forceinline__ void post_publish_request(PubState *pub, int gi, unsigned &seq, int item, int ulen, int tail_cnt, int m) {
+    while (pub->ack_seq[gi] != seq) __nanosleep(20);                   // previous request taken (an item ago: never waits)
+    pub->req[gi][0] = item; pub->req[gi][1] = ulen; pub->req[gi][2] = tail_cnt; pub->req[gi][3] = m;
+    __threadfence_block();
+    pub->req_seq[gi] = ++seq;
+}
+// Publisher loop of the TMA producer warp during phase A (lane 0).
+__device__ __forceinline__ void publisher_loop(const ChainParams &p, PubState *pub, int ngroups) {
+    unsigned seen[2] = {0u, 0u};
+    int finished = 0;
+    while (finished < ngroups) {
+        bool any = false;
+#pragma unroll
+        for (int gi = 0; gi < 2; ++gi) {
+            if (gi >= ngroups) break;
+            const unsigned s = pub->req_seq[gi];
+            if (s == seen[gi]) continue;
+            __threadfence_block();
+            const int item = pub->req[gi][0], ulen = pub->req[gi][1], tail = pub->req[gi][2], m = pub->req[gi][3];
+            seen[gi] = s;
+            pub->ack_seq[gi] = s;
+            any = true;
+            if (item < 0) ++finished; else publish_item(p, pub, item, ulen, tail, m);
+        }
+        if (!any) __nanosleep(64);
+    }
 }
 // attention_out rows of an item without any page (seq 0 / nothing selected): zeros, as the combine of
 // an empty sum gives.  nthreads threads, tid in [0, nthreads).
@@ -588,57 +653,33 @@ __device__ __noinline__ void zero_item_output(const ChainParams &p, int b, int n
     if (p.lse != nullptr)                                  // log of an empty sum
         for (int h = tid; h < p.g; h += nthreads) p.lse[(size_t)b * p.lse_sb + (size_t)(n2 * p.g + h) * p.lse_sh] = -INFINITY;
 }
-// max_page_position_length[b] once the last kv head of b has reported (one thread; cent_select.cpp:123-160)
-__device__ __forceinline__ void report_item_ppl(const ChainParams &p, int b, int item, int m, bool fenced = false) {
-    if (!fenced) { p.item_ppl[item] = m; __threadfence(); }
-    int *cnt = p.ctrl + Ctrl::b_done(b);
-    if (atomicAdd(cnt, 1) == p.Nkv - 1) {
-        __threadfence();
-        int mx = 0;
-        for (int n2 = 0; n2 < p.Nkv; ++n2) mx = max(mx, __ldcg(p.item_ppl + (size_t)b * p.Nkv + n2));
-        if (p.max_ppl)
-            for (int j = 0; j < kPad; ++j) p.max_ppl[(size_t)b * kPad + j] = (long long)mx * p.bs;
-        *cnt = 0;
-    }
-}
-
 // Union list of one item (one warp, serial over chunks).  pm[i] = head mask | tail mask << 16 for
-// logical page i; queues the ascending pages with a non-zero mask.  A queue entry has ONE tail flag:
-// a page that is the tail page of some heads and a full page of others (possible only with per-head
-// block_position lists) is queued twice, once per head subset.  Returns the number of entries.
+// logical page i; writes the ascending pages with a non-zero mask to the item's place in `flat`.  An entry has
+// ONE tail flag: a page that is the tail page of some heads and a full page of others (possible only with
+// per-head block_position lists) is listed twice, once per head subset.  Returns the number of entries.
 __device__ __noinline__ int warp_emit_union(const ChainParams &p, int item, const int *phys, const unsigned *pm, int pl,
                                             int tail_cnt) {
     const int lane = lane_id();
     const unsigned lt = (1u << lane) - 1u;
-    int len = 0;
-    for (int i0 = 0; i0 < pl; i0 += 32) {
-        const int i = i0 + lane;
-        const unsigned m = (i < pl) ? pm[i] : 0u;
-        const unsigned mt = (m >> 16) & m & 0xffffu, mf = m & 0xffffu & ~mt;
-        len += __popc(__ballot_sync(0xffffffffu, mf != 0u)) + __popc(__ballot_sync(0xffffffffu, mt != 0u));
-    }
-    int qbase = 0;
-    if (lane == 0) qbase = queue_reserve(p, item, len, tail_cnt);
-    qbase = __shfl_sync(0xffffffffu, qbase, 0);
+    unsigned long long *q = p.flat + (size_t)item * p.qstride;
     int base = 0;
     for (int i0 = 0; i0 < pl; i0 += 32) {
         const int i = i0 + lane;
         const unsigned m = (i < pl) ? pm[i] : 0u;
         const unsigned mt = (m >> 16) & m & 0xffffu, mf = m & 0xffffu & ~mt;
         const unsigned bf = __ballot_sync(0xffffffffu, mf != 0u), bt = __ballot_sync(0xffffffffu, mt != 0u);
-        if (mf) st_relaxed_u64(p.flat + (size_t)qbase + base + __popc(bf & lt), queue_entry(phys[i], mf, false, item, kBS));
-        if (mt) st_relaxed_u64(p.flat + (size_t)qbase + base + __popc(bf) + __popc(bt & lt), queue_entry(phys[i], mt, true, item, max(1, tail_cnt)));
+        if (mf) st_relaxed_u64(q + base + __popc(bf & lt), queue_entry(phys[i], mf, false, item, kBS));
+        if (mt) st_relaxed_u64(q + base + __popc(bf) + __popc(bt & lt), queue_entry(phys[i], mt, true, item, max(1, tail_cnt)));
         base += __popc(bf) + __popc(bt);
     }
     __syncwarp();
-    if (lane == 0) queue_item_done(p);
-    return len;
+    return base;
 }
 
 // ---- phase A for one item: fused op / cent_select / compute_cent / select_position ------------
 template <typename QT, int FLAGS>
 __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int item, unsigned char *smem,
-                            const CentRing &R, unsigned &tcount, const Grp &G) {
+                            const CentRing &R, unsigned &tcount, const Grp &G, PubState *pub, unsigned &pub_seq) {
     constexpr bool DS = (FLAGS & kSelScores) != 0, DP = (FLAGS & kSelSelect) != 0;
     constexpr int KG1 = kMaxGroup + 1;
     const int b = item / p.Nkv, n2 = item % p.Nkv;
@@ -810,7 +851,6 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     // page budget per head: max_page_num, and pl / cap_den when the reference's workload clamp is on
     // (cent_select.cpp:218,410-414: the first pl/8 positions are kept)
     const int cap = (p.cap_den > 0) ? min(p.MP, pl / p.cap_den) : p.MP;
-    const bool may_trunc = pl > cap;
     const int tail_cnt = has_tail ? rem : p.bs;
 #pragma unroll 1
     for (int ch = G.warp; ch < nch; ch += G.gw) {
@@ -845,25 +885,22 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             }
             if (lane == 0) {
                 if (col < g) { hd[col].total = min(run, cap); if (run > cap) miscI[8] = 1; }
-                else {
-                    miscI[9] = run;
-                    // no head can overflow max_page_num when the sequence has no more pages than that:
-                    // reserve the queue range now, under the other columns' scans
-                    if ((FLAGS & kSelUnion) && !may_trunc) miscI[10] = queue_reserve(p, item, run, tail_cnt);
-                }
+                else miscI[9] = run;
             }
         }
     }
     grp_sync(G);
     int *pp0 = p.page_position ? p.page_position + ((size_t)b * p.Nq + hq0) * p.MP : nullptr;
     if (miscI[8] == 0) {
-        if ((FLAGS & kSelUnion) && may_trunc) {
-            if (G.tid == 0) miscI[10] = queue_reserve(p, item, miscI[9], tail_cnt);
-            grp_sync(G);
+        const int ulen = miscI[9];
+        if ((FLAGS & kSelUnion) && G.tid == 0) {
+            // the item goes to the publisher now: its chunks are on offer while pass 2 still writes the entries
+            int m = 0;
+            for (int h = 0; h < g; ++h) m = max(m, hd[h].total);
+            post_publish_request(pub, G.id, pub_seq, item, ulen, tail_cnt, m);
         }
         // pass 2: scatter
-        const int ulen = miscI[9];
-        unsigned long long *qent = p.flat + miscI[10];
+        unsigned long long *qent = p.flat + (size_t)item * p.qstride;
 #pragma unroll 1
         for (int ch = G.warp; ch < nch; ch += G.gw) {
             const int i = ch * 32 + lane;
@@ -884,17 +921,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             for (int i = G.tid; i < g * kPad; i += G.gt)
                 p.page_position_length[((size_t)b * p.Nq + hq0) * kPad + i] = hd[i / kPad].total;
         trace_clk(p, 30);
-        if (FLAGS & kSelUnion) {
-            if (ulen == 0) zero_item_output(p, b, n2, G.tid, G.gt);
-            grp_sync(G);
-            if (G.tid == 0) {
-                int m = 0;
-                for (int h = 0; h < g; ++h) m = max(m, hd[h].total);
-                p.item_ppl[item] = m;
-                queue_item_done(p);                        // its fence also covers item_ppl
-                report_item_ppl(p, b, item, m, true);
-            }
-        }
+        if ((FLAGS & kSelUnion) && ulen == 0) zero_item_output(p, b, n2, G.tid, G.gt);
     } else {
         // a head selected more than max_page_num pages: serial path that truncates consistently
         for (int h = G.warp; h < g; h += G.gw) {
@@ -911,7 +938,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
                 if (lane == 0) {
                     int m = 0;
                     for (int h = 0; h < g; ++h) m = max(m, hd[h].total);
-                    report_item_ppl(p, b, item, m);
+                    post_publish_request(pub, G.id, pub_seq, item, ulen, tail_cnt, m);
                 }
             }
         }
@@ -925,7 +952,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
 // block_position[b, n2 or hq, j]: logical page of sparse-sequence slot j, 0x7fffffff-terminated
 // (sparse_paged_attention_split_Bbn2s2_Us2.h:258,277-279,293).  Slot j covers sparse tokens
 // [j*bs, (j+1)*bs) clipped to actual_seq_lengths[b].  Whole CTA.
-__device__ inline void union_from_block_position(const ChainParams &p, int item, unsigned char *smem) {
+__device__ inline void union_from_block_position(const ChainParams &p, int item, unsigned char *smem, PubState *pub) {
     const int b = item / p.Nkv, n2 = item % p.Nkv;
     const int g = p.g;
     const int tid = threadIdx.x, nt = blockDim.x;
@@ -958,9 +985,10 @@ __device__ inline void union_from_block_position(const ChainParams &p, int item,
     }
     __syncthreads();
     if (warp_id() == 0) {
-        const int ulen = warp_emit_union(p, item, p.block_table + (size_t)b * p.bt_stride, pm, p.maxP,
-                                         (tail_slot >= 0) ? (int)(actual % p.bs) : p.bs);
+        const int tail_cnt = (tail_slot >= 0) ? (int)(actual % p.bs) : p.bs;
+        const int ulen = warp_emit_union(p, item, p.block_table + (size_t)b * p.bt_stride, pm, p.maxP, tail_cnt);
         if (ulen == 0) zero_item_output(p, b, n2, lane_id(), 32);
+        if (lane_id() == 0) publish_item(p, pub, item, ulen, tail_cnt, -1);
     }
     __syncthreads();
 }
@@ -968,7 +996,7 @@ __device__ inline void union_from_block_position(const ChainParams &p, int item,
 // ---- all items of phase A handled by this CTA's worker groups (warps 0..kConsumerWarps-1) --------
 // smem: [ngroups x sel_ns centroid-tile stages][ngroups x group state]
 template <typename QT, int FLAGS>
-__device__ __forceinline__ void select_phase(const ChainParams &p, const CUtensorMap *tmC, unsigned char *smem) {
+__device__ __forceinline__ void select_phase(const ChainParams &p, const CUtensorMap *tmC, unsigned char *smem, PubState *pub) {
     __shared__ uint64_t sel_bars[4][16];               // per group: full[0..8), empty[8..16)
     const int ngroups = kConsumerWarps / p.sel_gw;
     if ((FLAGS & kSelScores) && threadIdx.x == 0) {
@@ -979,15 +1007,23 @@ __device__ __forceinline__ void select_phase(const ChainParams &p, const CUtenso
         tma_prefetch_desc(tmC);
     }
     __syncthreads();
-    if (warp_id() >= kConsumerWarps) return;
+    if (warp_id() >= kConsumerWarps) {
+        // fused chain: the TMA producer warp publishes the groups' items while they select (publish_item)
+        if ((FLAGS & kSelUnion) && warp_id() == kConsumerWarps) {
+            if (lane_id() == 0) publisher_loop(p, pub, ngroups);
+            __syncwarp();
+        }
+        return;
+    }
     const Grp G = make_group(p.sel_gw);
     CentRing R;
     R.base = smem + (size_t)G.id * p.sel_ns * kCentTileBytes;
     R.full = &sel_bars[G.id][0]; R.empty = &sel_bars[G.id][8]; R.ns = p.sel_ns;
     unsigned char *gs = smem + (size_t)ngroups * p.sel_ns * kCentTileBytes + (size_t)G.id * p.sel_group_bytes;
-    unsigned tcount = 0;
+    unsigned tcount = 0, pub_seq = 0;
     for (int item = blockIdx.x + G.id * gridDim.x; item < p.items; item += gridDim.x * ngroups)
-        select_item<QT, FLAGS>(p, tmC, item, gs, R, tcount, G);
+        select_item<QT, FLAGS>(p, tmC, item, gs, R, tcount, G, pub, pub_seq);
+    if ((FLAGS & kSelUnion) && G.tid == 0) post_publish_request(pub, G.id, pub_seq, -1, 0, 0, 0);
 }
 
 // max_page_position_length[b, 0..7] = bs * max_h count   (cent_select.cpp:123-160)
