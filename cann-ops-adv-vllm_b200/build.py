@@ -31,7 +31,9 @@ def _run(cmd):
 
 
 def build_kernels(force=False, verbose=False):
-    srcs = [os.path.join(CSRC, f) for f in ("spa_kernels.cu", "spa_common.cuh", "spa_select.cuh", "spa_attn.cuh")]
+    import glob
+    main = os.path.join(CSRC, "spa_kernels.cu")
+    srcs = [main] + sorted(f for f in glob.glob(os.path.join(CSRC, "*.cu*")) if f != main)   # every header it includes
     srcs.append(os.path.join(HERE, "..", "include", "spa_b200.h"))
     if not force and not _newer(LIB, srcs):
         return LIB

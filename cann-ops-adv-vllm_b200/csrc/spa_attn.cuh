@@ -26,10 +26,9 @@ constexpr int kMailSlots = 4;                           // flush -> post-warp me
 constexpr int kPostWarp = kConsumerWarps + 1;           // warp 8: TMA producer, warps 9..11: partial bookkeeping + combine
 
 struct AttnSmem {
-    int stages, mbuf, wml, meta, bars, mail, list, total;
-    int list_cap;
+    int stages, mbuf, wml, meta, bars, mail, total;
     __host__ __device__ static inline int align(int x, int a) { return (x + a - 1) / a * a; }
-    __host__ __device__ AttnSmem(int nstages, int stage_bytes, int nt_tiles, int max_partials) {
+    __host__ __device__ AttnSmem(int nstages, int stage_bytes, int nt_tiles) {
         int o = 0;
         stages = o;   o = align(o + nstages * stage_bytes, 1024);
         mbuf = o;     o = align(o + kConsumerWarps * kMergeWarpFloats * 4, 16);   // 8 heads x 64 dims per warp
@@ -37,8 +36,6 @@ struct AttnSmem {
         meta = o;     o = align(o + nstages * 16, 16);
         bars = o;     o = align(o + (nstages * 2 + kPostWarps * kMailSlots * 2) * 8, 16);
         mail = o;     o = align(o + kPostWarps * kMailSlots * 32, 16);
-        list_cap = max_partials;
-        list = o;     o = align(o + kPostWarps * max_partials * 4, 16);
         total = o;
     }
 };
@@ -90,9 +87,9 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
 // softmax log-sum-exp of one (b, head) row: ln(sum_i exp(s_i)) with s = scale * q.k, from the running max (log2
 // domain) and the sum of 2^(s2 - max) (the reference's optional softmaxLse output, ..._Us2.h:2601-2623).
 // Whole warp.  int8 KV: the kernel's logits are short of the true ones by a per-head constant -- K enters the
-// matmul as 1152 + k instead of k + offset_k, with q*scale_k rounded to fp16 after a power-of-two
+// matmul as k instead of k + offset_k, with q*scale_k split into two int8 digits after a power-of-two
 // normalisation (see the Q fragments in attention_phase) -- which the softmax never sees but its log-sum
-// does: it is rebuilt here from the same rounded operands, 4 head dims per lane.
+// does: it is rebuilt here from the same quantised operands, 4 head dims per lane.
 template <typename QT, bool KVI8>
 __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, int h, float m2, float lsum) {
     const int lane = lane_id();
@@ -114,13 +111,17 @@ __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, i
 #pragma unroll
         for (int o = 16; o; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
         const uint32_t ex = min(max((__float_as_uint(amax) >> 23) & 0xffu, 1u), 253u);
-        const float up = __uint_as_float((254u - ex) << 23), down = __uint_as_float(ex << 23);
+        const float up = __uint_as_float((254u - ex) << 23) * kQDigitRange, down = __uint_as_float(ex << 23);
         float sum = 0.f;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) sum += __half2float(__float2half_rn(f[e] * up)) * (off[e] - kI8Bias);
+        for (int e = 0; e < 4; ++e) {
+            int d1, d2;
+            split_digits(f[e] * up, d1, d2);
+            sum += ((float)d1 + (float)d2 * (1.f / kQDigit2)) * off[e];
+        }
 #pragma unroll
         for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        shift = p.scale_log2 * down * sum;
+        shift = p.scale_log2 * down * (1.f / kQDigitRange) * sum;
     }
     if (lane == 0)
         p.lse[(size_t)b * p.lse_sb + (size_t)(n2 * p.g + h) * p.lse_sh] =
@@ -128,102 +129,82 @@ __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, i
 }
 
 // ---- combine (post warp): the CTA whose partial completed the item's page count merges all partials ----
-// A CTA that left a partial for a segment starting at queue index i wrote (slot + 1) into flat[i]
-// (the entry itself was consumed and zeroed before); the item's range is scanned for those marks.
-// Latency-bound (everything sits in L2): marks, then (m, l) of every partial and head, then the O rows
-// of two heads x eight partials per round trip.
+// Partial slots are fixed: slot = item * pslots + pid, pid = 0 for the owner's prefix, 1 + j for chunk j.  The
+// word that counts the item's finished pages also collects one bit per partial (see post_warp_loop), so the
+// last arriver knows the slots without searching.  Latency-bound (everything sits in L2): (m, l) of every
+// partial and head in one round of loads, then the O rows of two heads x all partials per round trip.
 template <typename QT, bool KVI8, int NT>
-__device__ void combine_item_warp(const ChainParams &p, int item, int base, int len, int *list, int list_cap) {
+__device__ void combine_item_warp(const ChainParams &p, int item, unsigned bits) {
     constexpr int HP = NT * 8;
+    constexpr int NP = kMaxChunks + 1;
     const int lane = lane_id();
-    const unsigned lt = (1u << lane) - 1u;
     const int b = item / p.Nkv, n2 = item % p.Nkv, g = p.g;
-    unsigned long long *marks = p.flat + base;
-    int n = 0;
-    for (int j0 = 0; j0 < len; j0 += 128) {
-        unsigned long long mk[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int j = j0 + u * 32 + lane;
-            mk[u] = (j < len) ? ld_relaxed_u64(marks + j) : 0ull;
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const bool ok = mk[u] != 0ull && !(mk[u] >> 63);
-            const unsigned bal = __ballot_sync(0xffffffffu, ok);
-            if (ok) {
-                const int at = n + __popc(bal & lt);
-                if (at < list_cap) list[at] = (int)(mk[u] - 1);
-                st_relaxed_u64(marks + j0 + u * 32 + lane, 0ull);       // leave the queue words as found
-            }
-            n += __popc(bal);
+    const int n = __popc(bits);
+    // lane j < n holds the j-th partial: its slot and, head by head, its (m, l)
+    int slot = -1;
+    {
+        unsigned rest = bits;
+        for (int j = 0; j < n; ++j) {
+            const int pid = __ffs(rest) - 1;
+            rest &= rest - 1;
+            if (lane == j) slot = item * p.pslots + pid;
         }
     }
-    if (n > list_cap) __trap();                                          // more partials than runs exist: unreachable
-    __syncwarp();
+    float2 ml[HP];
+#pragma unroll
+    for (int h = 0; h < HP; ++h)
+        ml[h] = (slot >= 0 && h < g) ? __ldcg(reinterpret_cast<const float2 *>(p.part_ml + ((size_t)slot * HP + h) * 2))
+                                     : make_float2(-INFINITY, 0.f);
+    int sj[NP];
+#pragma unroll
+    for (int u = 0; u < NP; ++u) sj[u] = __shfl_sync(0xffffffffu, slot, min(u, n - 1));
 #pragma unroll 1
     for (int h0 = 0; h0 < g; h0 += 2) {
         const int nh = min(2, g - h0);
-        float M[2] = {-INFINITY, -INFINITY}, Ls[2] = {0.f, 0.f};
-        float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
-#pragma unroll 1
-        for (int c0 = 0; c0 < n; c0 += 32) {
-            const int slot = (c0 + lane < n) ? list[c0 + lane] : -1;
-            float w[2];
+        float4 v[2][NP];
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                float2 ml = make_float2(-INFINITY, 0.f);
-                if (slot >= 0 && e < nh) ml = __ldcg(reinterpret_cast<const float2 *>(p.part_ml + ((size_t)slot * HP + h0 + e) * 2));
-                float cm = ml.x;
+        for (int u = 0; u < NP; ++u)
 #pragma unroll
-                for (int o = 16; o; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
-                const float newM = fmaxf(M[e], cm);
-                const float r = (M[e] == -INFINITY) ? 0.f : fast_exp2(M[e] - newM);
-                acc[e][0] *= r; acc[e][1] *= r; acc[e][2] *= r; acc[e][3] *= r;
-                Ls[e] *= r;
-                M[e] = newM;
-                w[e] = (ml.x == -INFINITY) ? 0.f : fast_exp2(ml.x - newM);
-                Ls[e] += ml.y * w[e];
-            }
-            const int nn = min(32, n - c0);
-#pragma unroll 1
-            for (int j0 = 0; j0 < nn; j0 += 8) {
-                float4 v[2][8];
-                float wj[2][8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int jj = min(j0 + u, nn - 1);
-                    const int sj = __shfl_sync(0xffffffffu, slot, jj);
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const float we = __shfl_sync(0xffffffffu, w[e], jj);
-                        wj[e][u] = (j0 + u < nn && e < nh) ? we : 0.f;
-                        v[e][u] = __ldcg(reinterpret_cast<const float4 *>(p.part_o + ((size_t)sj * HP + h0 + min(e, nh - 1)) * kD) + lane);
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < 8; ++u)
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        acc[e][0] += v[e][u].x * wj[e][u]; acc[e][1] += v[e][u].y * wj[e][u];
-                        acc[e][2] += v[e][u].z * wj[e][u]; acc[e][3] += v[e][u].w * wj[e][u];
-                    }
-            }
-        }
+            for (int e = 0; e < 2; ++e)
+                if (u < n) v[e][u] = __ldcg(reinterpret_cast<const float4 *>(p.part_o + ((size_t)sj[u] * HP + h0 + min(e, nh - 1)) * kD) + lane);
+        float M[2], Ls[2], w[2];
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-            float L = Ls[e];
+            float2 me = make_float2(-INFINITY, 0.f);
+#pragma unroll
+            for (int h = 0; h < HP; ++h) if (h == h0 + e) me = ml[h];
+            float cm = me.x;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+            M[e] = cm;
+            w[e] = (me.x == -INFINITY) ? 0.f : fast_exp2(me.x - cm);
+            float L = me.y * w[e];
 #pragma unroll
             for (int o = 16; o; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
-            if (e < nh) write_out_vals<QT, KVI8, 4>(p, b, n2, h0 + e, lane * 4, acc[e], L);
-            if (e < nh && p.lse != nullptr) write_lse<QT, KVI8>(p, b, n2, h0 + e, M[e], L);
+            Ls[e] = L;
+        }
+        float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+        for (int u = 0; u < NP; ++u)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const float we = __shfl_sync(0xffffffffu, w[e], min(u, n - 1));
+                if (u < n) {
+                    acc[e][0] += v[e][u].x * we; acc[e][1] += v[e][u].y * we;
+                    acc[e][2] += v[e][u].z * we; acc[e][3] += v[e][u].w * we;
+                }
+            }
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            if (e < nh) write_out_vals<QT, KVI8, 4>(p, b, n2, h0 + e, lane * 4, acc[e], Ls[e]);
+            if (e < nh && p.lse != nullptr) write_lse<QT, KVI8>(p, b, n2, h0 + e, M[e], Ls[e]);
         }
     }
     if (lane == 0) { p.item_info[item] = 0ull; p.ctrl[Ctrl::pages_done(item)] = 0; }
 }
 
-// ---- post warp: takes the flush messages of this CTA's consumers; publishes each partial (mark in the
-// queue, fence, page count) and combines the items this CTA completed.  Keeps every global round trip
+// ---- post warp: takes the flush messages of this CTA's consumers; publishes each partial (fence, page count +
+// partial bit) and combines the items this CTA completed.  Keeps every global round trip
 // of the bookkeeping off the consumers' path: under a saturated HBM each one costs microseconds.
 // max_page_position_length[b, 0..7] = bs * (longest per-head page list of b) (cent_select.cpp:123-160), fused op:
 // the items' publishers leave 1 + their maximum in item_ppl (non-zero once written); post warp 0 of CTA
@@ -250,31 +231,29 @@ __device__ __noinline__ void max_ppl_poll(const ChainParams &p) {
 }
 
 template <typename QT, bool KVI8, int NT>
-__device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t *mfull, uint64_t *mempty, int *list,
-                               int list_cap) {
+__device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t *mfull, uint64_t *mempty) {
     const int lane = lane_id();
     int mi = 0;
     uint32_t mph = 0;
     for (;;) {
         mbar_wait(&mfull[mi], mph);
-        const int4 m0 = mail[mi * 2], m1 = mail[mi * 2 + 1];
+        const int4 m0 = mail[mi * 2];
         __syncwarp();
         if (lane == 0) mbar_arrive(&mempty[mi]);
         if (++mi == kMailSlots) { mi = 0; mph ^= 1u; }
-        const int item = m0.x, first_idx = m0.y, cnt = m0.z, slot = m0.w;
+        const int item = m0.x, pid = m0.y, cnt = m0.z, len = m0.w;
         if (item < 0) break;
-        const int base = m1.x, len = m1.y;
+        // one word per item: finished pages in the low half, one bit per partial in the high half
         int old = 0;
         if (lane == 0) {
-            st_relaxed_u64(p.flat + first_idx, (unsigned long long)slot + 1ull);
             __threadfence();
-            old = atomicAdd(p.ctrl + Ctrl::pages_done(item), cnt);
+            old = atomicAdd(p.ctrl + Ctrl::pages_done(item), cnt | (1 << (16 + pid)));
         }
         old = __shfl_sync(0xffffffffu, old, 0);
-        if (old == len - cnt) {
+        if ((old & 0xffff) + cnt == len) {
             __threadfence();
             const unsigned long long tc0 = (p.dbg && lane == 0) ? globaltimer_ns() : 0ull;
-            combine_item_warp<QT, KVI8, NT>(p, item, base, len, list, list_cap);
+            combine_item_warp<QT, KVI8, NT>(p, item, ((unsigned)old >> 16) | (1u << pid));
             if (p.dbg && lane == 0 && p.trace) {
                 p.trace[(size_t)blockIdx.x * kTraceSlots + 10] += 1;
                 p.trace[(size_t)blockIdx.x * kTraceSlots + 11] += globaltimer_ns() - tc0;
@@ -300,8 +279,8 @@ __device__ __forceinline__ void post_message(int4 *mail, uint64_t *mfull, uint64
 // ---- segment flush: merge the 8 warps' running states of `item`; either finish the item (all of its
 // pages were in this segment) or leave a partial and tell the post warp.  All consumers.
 template <typename QT, bool KVI8, int NT>
-__device__ __forceinline__ void flush_segment(const ChainParams &p, int item, int first_idx, int cnt,
-                                              unsigned long long rec, int slot_t0, float (&o)[NT][8][4],
+__device__ __forceinline__ void flush_segment(const ChainParams &p, int item, int pid, int cnt,
+                                              unsigned long long rec, float (&o)[NT][8][4],
                                               float (&m_run)[NT][2], float (&l_run)[NT][2], float *mbuf,
                                               float *wml, int4 *mail, uint64_t *mfull, uint64_t *mempty, int &mi,
                                               uint32_t &mph) {
@@ -329,11 +308,8 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
     // uniform over the CTA.  With the optional LSE output every segment takes the partial -> combine route (the
     // combiner writes the LSE): the consumers' path carries no code for it
     const bool whole = (cnt == len) && p.lse == nullptr;
-    int slot = __shfl_sync(0xffffffffu, slot_t0, 0);                    // thread 0's reservation ...
-    if (lane == 0 && warp == 0) reinterpret_cast<int *>(wml)[kConsumerWarps * HP * 2] = slot;
+    const int slot = item * p.pslots + pid;                              // the segment's fixed partial slot
     named_bar_sync(1, kAll);
-    slot = reinterpret_cast<const int *>(wml)[kConsumerWarps * HP * 2];  // ... for everyone
-    if (!whole && slot >= p.pool_cap) __trap();                          // cannot happen: see plan_attention
     // bring every warp's accumulators to the common max of the head
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
@@ -388,8 +364,7 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
     named_bar_sync(1, kAll);      // every thread's partial stores precede the message; smem free for the next flush
     if (threadIdx.x == 0) {
         if (whole) p.item_info[item] = 0ull;                          // consumed: nobody else holds pages of it
-        else post_message(mail, mfull, mempty, mi, mph, make_int4(item, first_idx, cnt, slot),
-                          make_int4(item * p.qstride, len, 0, 0));
+        else post_message(mail, mfull, mempty, mi, mph, make_int4(item, pid, cnt, len), make_int4(0, 0, 0, 0));
     }
 }
 
@@ -445,7 +420,17 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
             }
         }
     } else {
-        // int8 page: [128 tokens][128 B]; one ldmatrix.x4 covers 16 tokens x 32 d
+        // int8 page: [128 tokens][128 B]; one ldmatrix.x4 covers 16 tokens x 32 d = the A fragment of an
+        // int8 mma (m16n8k32) as it lies in memory: no conversion.  Q enters as two int8 digits per element
+        // (see the Q fragments), the products accumulate exactly in int32, and the digits are joined once
+        // per logit: 254 * S1 + S2 (|S1| < 2^21, so the sum fits).
+        int s1[PP][NT][4], s2[PP][NT][4];
+#pragma unroll
+        for (int pp = 0; pp < PP; ++pp)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { s1[pp][nt][i] = 0; s2[pp][nt][i] = 0; }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int chunk = j * 2 + a_chk;
@@ -454,19 +439,19 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
             for (int pp = 0; pp < PP; ++pp) {
                 uint32_t r0, r1, r2, r3;
                 ldmatrix_x4(r0, r1, r2, r3, stage_u32 + (uint32_t)ks[pp] * p.stage_bytes + off);
-                // biased int8 -> fp16 (1152 + k, one PRMT per pair): the softmax cancels the per-head constant
-                r0 ^= 0x80808080u; r1 ^= 0x80808080u; r2 ^= 0x80808080u; r3 ^= 0x80808080u;
-                const uint32_t k00 = I8PairBiased<0, 1>::cvt(r0), k01 = I8PairBiased<0, 1>::cvt(r1),
-                               k02 = I8PairBiased<2, 3>::cvt(r0), k03 = I8PairBiased<2, 3>::cvt(r1),
-                               k10 = I8PairBiased<0, 1>::cvt(r2), k11 = I8PairBiased<0, 1>::cvt(r3),
-                               k12 = I8PairBiased<2, 3>::cvt(r2), k13 = I8PairBiased<2, 3>::cvt(r3);
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) {
-                    mma_16816<MT>(s[pp][nt], k00, k01, k02, k03, qf[nt][2 * j][0], qf[nt][2 * j][1]);
-                    mma_16816<MT>(s[pp][nt], k10, k11, k12, k13, qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
+                    mma_16832_s8(s1[pp][nt], r0, r1, r2, r3, qf[nt][2 * j][0], qf[nt][2 * j][1]);
+                    mma_16832_s8(s2[pp][nt], r0, r1, r2, r3, qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
                 }
             }
         }
+#pragma unroll
+        for (int pp = 0; pp < PP; ++pp)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) s[pp][nt][i] = (float)(s1[pp][nt][i] * 254 + s2[pp][nt][i]);
     }
     __syncwarp();
     if (lane == 0) {
@@ -594,7 +579,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
 template <typename QT, bool KVI8, int NT>
 __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, const CUtensorMap *tmV,
                                 unsigned char *smem, PubState *pub) {
-    AttnSmem L(p.nstages, p.stage_bytes, NT, p.list_cap);
+    AttnSmem L(p.nstages, p.stage_bytes, NT);
     unsigned char *stage_base = smem + L.stages;
     float *mbuf = reinterpret_cast<float *>(smem + L.mbuf);
     float *wml = reinterpret_cast<float *>(smem + L.wml);
@@ -604,7 +589,6 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     uint64_t *mfull = empty + p.nstages;
     uint64_t *mempty = mfull + kPostWarps * kMailSlots;
     int4 *mail = reinterpret_cast<int4 *>(smem + L.mail);
-    int *list = reinterpret_cast<int *>(smem + L.list);
 
     const int tid = threadIdx.x, lane = lane_id(), warp = warp_id();
     const int nstages = p.nstages;
@@ -624,8 +608,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     if (warp >= kPostWarp) {
         const int pw = warp - kPostWarp;
         if (pw == 0 && p.mode == kModeFused && p.max_ppl != nullptr) max_ppl_poll(p);
-        post_warp_loop<QT, KVI8, NT>(p, mail + pw * kMailSlots * 2, mfull + pw * kMailSlots, mempty + pw * kMailSlots,
-                                     list + pw * L.list_cap, L.list_cap);
+        post_warp_loop<QT, KVI8, NT>(p, mail + pw * kMailSlots * 2, mfull + pw * kMailSlots, mempty + pw * kMailSlots);
         return;
     }
     if (warp == kConsumerWarps) {
@@ -639,7 +622,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         // round trip (microseconds while HBM is saturated) is waited for.
         const int nown = pub->n_own;
         int oi = 0;
-        int rf = 0, rn = 0;                                                // current run: flat[rf, rf + rn)
+        int rf = 0, rn = 0, rpid = 0;                                      // current run: flat[rf, rf + rn), its partial id
         int nf = 0, claim_idx = 0;                                         // claim in flight (lane 0) / claimed index
         unsigned long long dv = 0ull;                                      // descriptor word of claim_idx as last loaded (lane 0)
         int cst = 0;                                                       // claim state: 0 none, 1 atomic in flight, 2 descriptor loading
@@ -660,9 +643,9 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         };
         // next chunk (<= 32 entries of one run) -> cf, cn, last (it ends its run).  Returns 1: got one, 0: the queue
         // is exhausted, -1 (only with block == false): the next run is not known yet -- issue what you have first
-        auto next_chunk = [&](int &cf, int &cn, bool &last, bool block) -> int {
+        auto next_chunk = [&](int &cf, int &cn, int &cpid, bool &last, bool block) -> int {
             while (rn == 0) {
-                if (oi < nown) { rf = pub->own_item[oi] * p.qstride; rn = pub->own_len[oi]; ++oi; ++t_runs; continue; }
+                if (oi < nown) { rf = pub->own_item[oi] * p.qstride; rn = pub->own_len[oi]; rpid = 0; ++oi; ++t_runs; continue; }
                 if (!more) return 0;
                 if (!block) return -1;
                 if (cst == 0) { if (lane == 0) nf = atomicAdd(p.ctrl + Ctrl::kHead, 1); cst = 1; }
@@ -695,22 +678,23 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                 }
                 rf = (int)((d >> 48) & (kMaxItems - 1)) * p.qstride + (int)(unsigned)d;
                 rn = (int)((d >> 32) & 0xffffu);
+                rpid = 1 + claim_idx / p.items;
                 ++t_runs;
             }
-            cf = rf; cn = min(32, rn);
+            cf = rf; cn = min(32, rn); cpid = rpid;
             rf += cn; rn -= cn;
             last = rn == 0;
             return 1;
         };
-        int cf = 0, cn = 0;
+        int cf = 0, cn = 0, cpid = 0;
         bool last = false;
-        int ok = next_chunk(cf, cn, last, true);
+        int ok = next_chunk(cf, cn, cpid, last, true);
         unsigned long long ent = (ok == 1 && lane < cn) ? ld_relaxed_u64(p.flat + cf + lane) : 0ull;
         while (ok == 1) {
             // entries of the following chunk travel while this chunk is issued
-            int cf2 = 0, cn2 = 0;
+            int cf2 = 0, cn2 = 0, cpid2 = 0;
             bool last2 = false;
-            int ok2 = next_chunk(cf2, cn2, last2, false);
+            int ok2 = next_chunk(cf2, cn2, cpid2, last2, false);
             unsigned long long ent2 = (ok2 == 1 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
             if (lane < cn) ent = take_entry(p, cf + lane, ent);
             t_pages += cn;
@@ -726,9 +710,9 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     const unsigned hi = (unsigned)(e >> 32), lo = (unsigned)e;
                     const int ph = (int)(lo & 0xffffffu), item = (int)((hi >> 16) & (kMaxItems - 1));
                     const int n2 = item % p.Nkv;
-                    // stage header: head mask | tail flag << 16 | pair flag << 17, item, queue index, tokens on a tail page
+                    // stage header: head mask | tail flag << 16 | pair flag << 17, item, partial id of the run, tokens on a tail page
                     const int4 md = make_int4((int)(hi & 0xffffu) | (int)(((hi >> 30) & 1u) << 16) | (first ? (1 << 17) : 0),
-                                              item, cf + j, (int)((lo >> 24) & 0x7fu) + 1);
+                                              item, cpid, (int)((lo >> 24) & 0x7fu) + 1);
                     int c[4];
                     c[1] = (p.ax_head == 1) ? n2 : (p.ax_blk == 1 ? ph : 0);
                     c[2] = (p.ax_head == 2) ? n2 : (p.ax_blk == 2 ? ph : 0);
@@ -752,10 +736,10 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             }
             __syncwarp();
             if (ok2 < 0) {
-                ok2 = next_chunk(cf2, cn2, last2, true);
+                ok2 = next_chunk(cf2, cn2, cpid2, last2, true);
                 ent2 = (ok2 == 1 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
             }
-            ok = ok2; cf = cf2; cn = cn2; last = last2; ent = ent2;
+            ok = ok2; cf = cf2; cn = cn2; cpid = cpid2; last = last2; ent = ent2;
         }
         if (lane == 0 && cst == 1) pub->priv_used = nf;  // a claim in flight has landed before this CTA reports "finished"
         if (lane == 0) { unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid)); trace_put(p, 12, smid); }
@@ -784,7 +768,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     float o[NT][8][4];
     float m_run[NT][2], l_run[NT][2];
     float hsc[NT][2];                                // int8 KV: per-head logit scale (see the Q fragments)
-    int cur = -1, cnt = 0, first_idx = 0, slot_t0 = 0;
+    int cur = -1, cnt = 0, pid = 0;
     unsigned long long rec = 0ull;
     int mi = 0;
     uint32_t mph = 0;
@@ -796,13 +780,11 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         const int tail_cnt = md.w;
         if (md.y != cur) {
             if (p.dbg && tid == 0 && md.y < 0) { trace_put(p, 10, 0); trace_put(p, 11, 0); trace_put(p, 8, globaltimer_ns()); }
-            if (cur >= 0) flush_segment<QT, KVI8, NT>(p, cur, first_idx, cnt, rec, slot_t0, o, m_run, l_run, mbuf, wml, mail, mfull, mempty, mi, mph);
+            if (cur >= 0) flush_segment<QT, KVI8, NT>(p, cur, pid, cnt, rec, o, m_run, l_run, mbuf, wml, mail, mfull, mempty, mi, mph);
             if (p.dbg && tid == 0 && md.y < 0) trace_put(p, 9, globaltimer_ns());
             if (md.y < 0) break;
-            cur = md.y; cnt = 0; first_idx = md.z;
+            cur = md.y; cnt = 0; pid = md.z;
             rec = ld_relaxed_u64(p.item_info + cur);             // first used at the flush
-            // partial slot for this segment: the atomic's result is first used at the flush
-            if (tid == 0) slot_t0 = atomicAdd(p.ctrl + Ctrl::kPool, 1);
             const int b = cur / p.Nkv, n2 = cur % p.Nkv;
             // ---- Q fragments (B operand of S^T = K Q^T): b0 = Q[head][d0,d0+1], b1 = Q[head][d0+8,+9]
 #pragma unroll
@@ -821,14 +803,13 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                         qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
                     }
                 } else {
-                    // int8 KV.  One ldmatrix row-quad holds 4 consecutive d, so k-slot (2*tig+e) <-> d =
-                    // 16ks+4tig+e and slot (2*tig+8+e) <-> d = 16ks+4tig+2+e (same permutation on both
-                    // operands).  The per-channel K scale is folded into Q (…_Us2.h:2142); the K offset adds
-                    // a per-head constant to every logit and cancels in the softmax (:2146-2155).  The
-                    // matmuls run in fp16 whatever the query dtype (int8 -> biased fp16 is exact and costs one
-                    // prmt per pair, see I8PairBiased; -> bf16 costs 5x that): q*scale_k is brought to [1, 2)
-                    // per head by a power of two (exact), rounded to fp16 (11 bits, more than bf16's 8), and
-                    // the power of two is returned to the logits in fp32.
+                    // int8 KV: S^T = K Q^T runs on the int8 tensor-core path with K as it lies in the page.  An
+                    // mma k-slot quad (4*tig .. 4*tig+3) is 4 consecutive d, so b0 = Q[h][32j + 4tig ..+3] and
+                    // b1 = Q[h][32j + 16 + 4tig ..+3].  The per-channel K scale is folded into Q (..._Us2.h:2142);
+                    // the K offset adds a per-head constant to every logit and cancels in the softmax
+                    // (:2146-2155).  q*scale_k is brought to [1, 2) per head by a power of two (exact), then split
+                    // into two int8 digits (split_digits: 2^-16 of the head's range, finer than the fp16 rounding
+                    // of the non-quantised path); the factor returns to the logits in fp32 (hsc).
                     const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) +
                                                (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
                     auto qs4 = [&](int ks, float (&f)[4]) {
@@ -854,23 +835,29 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
                     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
                     const uint32_t ex = min(max((__float_as_uint(amax) >> 23) & 0xffu, 1u), 253u);
-                    const float up = __uint_as_float((254u - ex) << 23);          // 2^(127-ex): amax -> [1, 2)
-                    const float down = __uint_as_float(ex << 23);                 // its inverse
+                    const float up = __uint_as_float((254u - ex) << 23) * kQDigitRange;     // amax -> [63.5, 127)
+                    const float down = __uint_as_float(ex << 23);                          // inverse of the power of two
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks) {
-                        uint32_t v0 = 0, v1 = 0;
+                        // ks = 2j: the b0 quad of k-step j, ks = 2j + 1: its b1 quad; digit 1 -> qf[2j], digit 2 -> qf[2j+1]
+                        uint32_t v1 = 0, v2 = 0;
                         if (h < p.g) {
                             float f[4];
                             qs4(ks, f);
-                            v0 = QTraits<MT>::pack2(f[0] * up, f[1] * up);
-                            v1 = QTraits<MT>::pack2(f[2] * up, f[3] * up);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                int d1, d2;
+                                split_digits(f[e] * up, d1, d2);
+                                v1 |= ((uint32_t)d1 & 0xffu) << (8 * e);
+                                v2 |= ((uint32_t)d2 & 0xffu) << (8 * e);
+                            }
                         }
-                        qf[nt][ks][0] = v0; qf[nt][ks][1] = v1;
+                        qf[nt][(ks & ~1)][ks & 1] = v1; qf[nt][(ks & ~1) + 1][ks & 1] = v2;
                     }
                     // the softmax holds head nt*8 + 2*tig + e: fetch that head's factor
 #pragma unroll
                     for (int e = 0; e < 2; ++e)
-                        hsc[nt][e] = p.scale_log2 * __shfl_sync(0xffffffffu, down, (tig * 2 + e) * 4);
+                        hsc[nt][e] = p.scale_log2 * (1.f / (kQDigitRange * kQDigit2)) * __shfl_sync(0xffffffffu, down, (tig * 2 + e) * 4);
                 }
             }
             // ---- running state: O^T[d][head] fragments, m (log2 domain), l (thread-partial)

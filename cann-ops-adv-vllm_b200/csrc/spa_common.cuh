@@ -74,9 +74,9 @@ struct ChainParams {
     int *item_ppl;                                       // [items] 1 + max selected pages over the item's heads; zero = not published
     int qstride;                                         // entries reserved per item in `flat`
     int *ctrl;                                           // queue counters, see Ctrl (all zero between launches)
-    int pool_cap;                                        // partial slots available
-    float *part_o;                                       // [pool_cap, HP, D]
-    float *part_ml;                                      // [pool_cap, HP, 2]
+    int pslots;                                          // partial slots per item: the owner's prefix + its chunks
+    float *part_o;                                       // [items * pslots, HP, D]
+    float *part_ml;                                      // [items * pslots, HP, 2]
     double *exact_scratch;                               // [grid, kConsumerWarps, C] (rare: > 512 near-ties)
     // ---- launch shape
     int sel_gw;                                          // warps per selection group (4 or 8)
@@ -90,7 +90,6 @@ struct ChainParams {
     int dyn_runs, dyn_min;                               // (dyn_runs unused) chunks of the rest are >= dyn_min pages
     int chunk_num, chunk_den;                            // each chunk takes chunk_num / chunk_den of what is left of the item
     int claim_lead;                                      // a chunk is claimed when the current run has this many pages left to issue
-    int list_cap;                                        // partial slots the post warp can list for one item
     int small_pages;                                     // a CTA keeps its own items whole while they add up to <= this many pages (0 = off)
     int pair_pages;                                      // consumers take two pages of an item per step (needs >= 4 stages)
     // ---- optional phase trace: [gridDim.x, kTraceSlots] globaltimer ns (null = off)
@@ -320,6 +319,24 @@ __device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&c)[4], uint32_t
         "{%0,%1,%2,%3};"
         : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// int8 x int8 -> int32 (IMMA): A = 16 rows x 32 k (row-major bytes), B = 32 k x 8 columns
+__device__ __forceinline__ void mma_16832_s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                             uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// Two-digit int8 split of a value u with |u| <= 127: u ~ d1 + d2 / 254, d1 = rint(u), d2 = rint((u - d1) * 254);
+// |u - (d1 + d2/254)| <= 1/508, i.e. 2^-16 of the range (the reference's MSD scheme for int8 KV,
+// sparse_paged_attention_split_Bbn2s2_Us2.h:2051-2110, restated for two digits)
+constexpr float kQDigitRange = 63.5f;     // q * scale_k is brought to [1, 2) per head, then to (-127, 127)
+constexpr float kQDigit2 = 254.f;
+__device__ __forceinline__ void split_digits(float u, int &d1, int &d2) {
+    d1 = __float2int_rn(u);
+    d2 = __float2int_rn((u - (float)d1) * kQDigit2);
 }
 
 // ---- int8 -> fp16/bf16 pairs (exact), for the fused KV antiquant ------------------------------

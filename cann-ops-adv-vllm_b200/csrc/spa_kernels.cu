@@ -850,35 +850,31 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     e->nt_tiles = (p.g + 7) / 8;
     // ---- scheduling (spa_select.cuh publish_item, spa_attn.cuh producer): a CTA keeps static_pct % of its fair
     // share as a private prefix of its own items; the rest is offered in chunks, about dyn_runs per CTA
-    p.static_pct = 50; p.dyn_runs = 3; p.dyn_min = 2;
+    p.static_pct = 80; p.dyn_runs = 3; p.dyn_min = 2;
     p.small_pages = 16;    // measured crossover on the configs[4] sweep: ~16.5 pages per CTA
     if (const char *s = getenv("SPA_SMALL_PAGES")) p.small_pages = std::max(0, atoi(s));
     if (const char *s = getenv("SPA_STATIC_PCT")) p.static_pct = std::min(100, std::max(0, atoi(s)));
     if (const char *s = getenv("SPA_DYN_RUNS")) p.dyn_runs = std::max(1, atoi(s));
     if (const char *s = getenv("SPA_DYN_MIN")) p.dyn_min = std::max(1, atoi(s));
-    p.chunk_num = 1; p.chunk_den = 2; p.claim_lead = 4;
+    p.chunk_num = 1; p.chunk_den = 2; p.claim_lead = 3;
     if (const char *s = getenv("SPA_CHUNK_FRAC")) { int a = 0, b = 0; if (sscanf(s, "%d/%d", &a, &b) == 2 && a > 0 && b >= a) { p.chunk_num = a; p.chunk_den = b; } }
     if (const char *s = getenv("SPA_CLAIM_LEAD")) p.claim_lead = std::max(0, atoi(s));
     p.qstride = p.maxP * (p.mode == kModeAttnOnly ? 2 : 1);     // x2: a page may be listed twice (split tail entries)
-    // Partials: one per (run, item) pair met by a CTA -- a run (own prefix or chunk) lies inside one item
-    const double qmax = (double)p.items * p.qstride;
-    // (a prefix and <= kMaxChunks chunks per item; chunks are not smaller than 1/32 of a CTA's fair share)
-    int cmax = kMaxChunks;
-    if ((long long)p.items >= 32ll * d.sms) cmax = 1;
-    p.pool_cap = (int)std::min<double>((double)p.items * (cmax + 1), qmax) + 1;
-    // partials of ONE item: its private prefix and its chunks
-    p.list_cap = kMaxChunks + 2;
+    // Partials: fixed slots, one for the owner's prefix and one per chunk of every item; chunks are not smaller
+    // than 1/32 of a CTA's fair share (publish_item), so with very many items an item is never cut more than once
+    p.pslots = ((long long)p.items >= 32ll * d.sms) ? 2 : kMaxChunks + 1;
+    if (p.qstride >= 65536) return fail(SPA_ERR_UNSUPPORTED, "more than 65535 page entries per work item");
     if (p.num_blocks > kMaxBlocks) return fail(SPA_ERR_UNSUPPORTED, "more than %d KV blocks", kMaxBlocks);
     p.stage_bytes = e->kv_i8 ? 16384 : 32768;
     const int budget = d.smem_optin - 1024 - 512;     // 1 KiB alignment slack + the kernels' static shared memory
     int nst = e->kv_i8 ? 12 : 6;
     for (; nst >= 2; --nst)
-        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.list_cap).total <= budget) break;
+        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles).total <= budget) break;
     if (nst < 2) return fail(SPA_ERR_UNSUPPORTED, "attention working set exceeds shared memory");
     p.nstages = nst;
     p.pair_pages = nst >= 4;
     if (const char *s = getenv("SPA_PAIR")) p.pair_pages = p.pair_pages && atoi(s) != 0;
-    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.list_cap).total;
+    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles).total;
     int sel_bytes = p.maxP * 4;
     if (p.mode == kModeFused) {
         if ((rc = plan_select_smem(&p, kSelScores | kSelSelect | kSelUnion, d.sms, budget - 1024, &sel_bytes))) return rc;
@@ -905,8 +901,8 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     e->off_desc = o;   o = align_up(o + ((uint64_t)p.items * kMaxChunks + 2ull * d.sms + 64) * 8, 256);
     e->off_flat = o;   o = align_up(o + qcap * 8, 256);
     e->ctrl_bytes = o;
-    e->off_po = o;     o = align_up(o + (uint64_t)p.pool_cap * HP * kD * 4, 256);
-    e->off_pml = o;    o = align_up(o + (uint64_t)p.pool_cap * HP * 2 * 4, 256);
+    e->off_po = o;     o = align_up(o + (uint64_t)p.items * p.pslots * HP * kD * 4, 256);
+    e->off_pml = o;    o = align_up(o + (uint64_t)p.items * p.pslots * HP * 2 * 4, 256);
     e->off_xs = o;
     if (p.mode == kModeFused) o = align_up(o + (uint64_t)e->grid * kConsumerWarps * std::max(p.C, 1) * 8, 256);
     e->ws_bytes = o;

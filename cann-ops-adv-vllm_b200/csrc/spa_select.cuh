@@ -570,7 +570,7 @@ __device__ __noinline__ int warp_compact_bit(unsigned *pm, int pl, int bit, int 
 //     fair share of the launch, estimated from this item -- and starts streaming it as soon as its own selection
 //     is over, while other CTAs are still selecting (the reference separates the phases with SyncAll,
 //     sparse_paged_fusion_attention.cpp:56-76);
-//   * the rest [S, ulen) is cut into chunks of HALVING size (down to 1/32 of a CTA's fair share, at most
+//   * the rest [S, ulen) is cut into chunks of HALVING size (between 1/8 and 1/32 of a CTA's fair share, at most
 //     kMaxChunks): chunk j of item i is descriptor desc[j * items + i], and CTAs claim descriptors in index
 //     order, so all the large chunks go first and the launch ends on the small ones (guided self-scheduling
 //     without knowing the total).  No reservation: the slot is fixed;
@@ -592,7 +592,7 @@ __device__ __noinline__ void publish_item(const ChainParams &p, PubState *pub, i
         int S = min(ulen, (int)(fair * (float)p.static_pct / (100.f * (float)n_mine) + 0.5f));
         if (used + ulen <= p.small_pages) S = ulen;
         if (pub->n_own >= kMaxOwn) S = 0;
-        const int min_chunk = max(p.dyn_min, (int)(fair * (1.f / 32.f)));
+        const int min_chunk = max(p.dyn_min, (int)(fair * (1.f / 32.f))), max_chunk = max(min_chunk, (int)(fair * (1.f / 8.f)));
         if (S > 0 && ulen - S < min_chunk) S = ulen;                   // no crumbs on either side
         if (S < p.dyn_min && S < ulen) S = 0;
         if (S > 0) {
@@ -602,8 +602,8 @@ __device__ __noinline__ void publish_item(const ChainParams &p, PubState *pub, i
         }
         int at = S, left = ulen - S;
         while (left > 0) {
-            int c = max(min_chunk, (left * p.chunk_num) / p.chunk_den);
-            if (nch == kMaxChunks - 1 || left - c < min_chunk) c = left;
+            int c = max(min_chunk, min((left * p.chunk_num) / p.chunk_den, max_chunk));
+            if (nch == p.pslots - 2 || left - c < min_chunk) c = left;
             st_relaxed_u64(p.desc + (size_t)nch * p.items + item, chunk_desc(item, at, c));
             at += c; left -= c; ++nch;
         }
