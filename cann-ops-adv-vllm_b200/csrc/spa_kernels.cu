@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <new>
 
 #include "../../include/spa_b200.h"
@@ -1025,6 +1026,72 @@ int spaSparsePagedFusionAttentionGetWorkspaceSize(
 int spaSparsePagedFusionAttention(void *workspace, uint64_t wsSize, spaExecutor *e, spaStream stream) {
     if (!e || e->op != OP_FUSION) return fail(SPA_ERR_ARG, "bad executor");
     return launch_chain(workspace, wsSize, e, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of the fused op (no counterpart in the reference):
+// the workspace is a file-scope device array instead of caller memory, the plan lives on
+// the stack, and nothing on this path calls cudaMalloc / cudaFree or any allocating routine.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[SPA_STATIC_SCRATCH_BYTES];
+constexpr int kMaxDevices = 64;
+static void *g_static_scratch_ptr[kMaxDevices];       // device address of g_static_scratch on device i (0 = not asked yet)
+static std::mutex g_static_scratch_mu;
+
+// In host code `g_static_scratch` is only the symbol's host-side stand-in: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int static_scratch_address(void **ptr) {
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(SPA_ERR_CUDA, "device ordinal %d outside 0..%d", dev, kMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+    if (!g_static_scratch_ptr[dev]) {
+        void *addr = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&addr, g_static_scratch));
+        if (!addr) return fail(SPA_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_static_scratch_ptr[dev] = addr;
+    }
+    *ptr = g_static_scratch_ptr[dev];
+    return SPA_OK;
+}
+
+uint64_t spaStaticScratchBytes(void) { return SPA_STATIC_SCRATCH_BYTES; }
+
+int spaSparsePagedFusionAttentionStatic(
+    const spaTensor *query, const spaTensor *key, const spaTensor *value, const spaTensor *pseShift,
+    const spaTensor *attenMask, const spaTensor *actualSeqLengths, const spaTensor *dequantScale1,
+    const spaTensor *quantScale1, const spaTensor *dequantScale2, const spaTensor *quantScale2,
+    const spaTensor *quantOffset2, const spaTensor *antiquantScale, const spaTensor *antiquantOffset,
+    const spaTensor *blocktable, const spaTensor *kvPaddingSize, const spaTensor *l1Cent,
+    const spaTensor *blockIds, const spaTensor *totalSeqLen, int64_t numHeads, double scaleValue,
+    const char *inputLayout, int64_t numKeyValueHeads, int64_t blockSize, int64_t innerPrecise,
+    int64_t topK, const spaTensor *blockPosition, const spaTensor *pagePositionLength,
+    const spaTensor *maxPagePositionLength, const spaTensor *attentionOut, spaStream stream) {
+    (void)innerPrecise; (void)actualSeqLengths;
+    spaExecutor plan;                                   // on the stack: no host allocation either
+    memset(&plan, 0, sizeof(plan));
+    spaExecutor *e = &plan;
+    ChainParams &p = e->p;
+    int rc;
+    if ((rc = reject_unsupported(pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize))) return rc;
+    p.mode = kModeFused;
+    if ((rc = parse_cent_select_common(e, query, l1Cent, blockIds, blocktable, totalSeqLen, topK, blockSize,
+                                       blockPosition, pagePositionLength, maxPagePositionLength))) return rc;
+    if (numKeyValueHeads > 0 && numKeyValueHeads != p.Nkv)
+        return fail(SPA_ERR_SHAPE, "num_key_value_heads=%lld disagrees with l1_cent heads %d", (long long)numKeyValueHeads, p.Nkv);
+    uint64_t need = 0;
+    if ((rc = plan_attention(e, query, key, value, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
+                             inputLayout, p.Nkv, blockSize, attentionOut, &need))) return rc;
+    e->op = OP_FUSION;
+    if (need > SPA_STATIC_SCRATCH_BYTES)
+        return fail(SPA_ERR_WORKSPACE, "this problem needs %llu bytes of scratch; the static scratch of "
+                    "spaSparsePagedFusionAttentionStatic holds %llu (use the two-phase entry points with a caller workspace)",
+                    (unsigned long long)need, (unsigned long long)SPA_STATIC_SCRATCH_BYTES);
+    void *scratch = nullptr;
+    if ((rc = static_scratch_address(&scratch))) return rc;
+    // The array keeps the previous call's contents: launch_chain clears the words that must start at zero
+    // (cudaMemsetAsync on the stream, persistent_ws == 0) in front of every launch; the rest is written before read.
+    return launch_chain(scratch, SPA_STATIC_SCRATCH_BYTES, e, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -191,6 +191,37 @@ SPA_API int spaSparsePagedFusionAttentionGetWorkspaceSize(
 SPA_API int spaSparsePagedFusionAttention(void *workspace, uint64_t workspaceSize,
                                           spaExecutor *executor, spaStream stream);
 
+/* ---- SparsePagedFusionAttentionStatic: allocation-free, single-call variant of the fused op.  It has NO
+ *      counterpart in the reference; it was added for callers that
+ *      cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same tensors and attributes as spaSparsePagedFusionAttentionGetWorkspaceSize (same validation, same
+ * kernel, default select options, no softmax LSE), launched at once on `stream`: the caller passes inputs
+ * and outputs only.  The workspace is a file-scope `static __device__` array of SPA_STATIC_SCRATCH_BYTES
+ * inside the library -- every GPU that loads the library holds that much device memory until the process
+ * exits -- and the plan lives on the stack: the call performs no cudaMalloc / cudaFree and no host or
+ * library allocation.  A problem whose workspace exceeds the array (B*Nkv work items x (page entries +
+ * 9 fp32 partials) + exact-score scratch: BASELINE configs c2 / c3 / c4 need 9.9 / 25.1 / 31.1 MB) is
+ * refused with SPA_ERR_WORKSPACE and a message naming both sizes; use the two-phase entry points then.
+ * All calls on a device share the one array, which keeps the previous call's contents: the words that
+ * must start at zero are cleared on `stream` in front of every launch, everything else is written before
+ * it is read.  Calls that OVERLAP on the GPU (two streams, two host threads, a graph replay next to an
+ * eager call) race on the array -- serialise them on one stream.                                      */
+#define SPA_STATIC_SCRATCH_BYTES (32u << 20)
+SPA_API uint64_t spaStaticScratchBytes(void);
+SPA_API int spaSparsePagedFusionAttentionStatic(
+    const spaTensor *query, const spaTensor *key, const spaTensor *value,
+    const spaTensor *pseShift, const spaTensor *attenMask, const spaTensor *actualSeqLengths,
+    const spaTensor *dequantScale1, const spaTensor *quantScale1, const spaTensor *dequantScale2,
+    const spaTensor *quantScale2, const spaTensor *quantOffset2,
+    const spaTensor *antiquantScale, const spaTensor *antiquantOffset,
+    const spaTensor *blocktable, const spaTensor *kvPaddingSize,
+    const spaTensor *l1Cent, const spaTensor *blockIds, const spaTensor *totalSeqLen,
+    int64_t numHeads, double scaleValue, const char *inputLayout, int64_t numKeyValueHeads,
+    int64_t blockSize, int64_t innerPrecise, int64_t topK,
+    const spaTensor *blockPosition, const spaTensor *pagePositionLength,
+    const spaTensor *maxPagePositionLength,
+    const spaTensor *attentionOut, spaStream stream);
+
 /* ---- AssignPageClusters: centroid maintenance, the step BEFORE the chain.  The reference
  *      consumes blockIds [Nkv, kvPageLen] but never produces them (tests/cent_select.py:49-50 draws them at
  *      random), so there is no aclnn interface to cite; the two-phase shape is the same.
