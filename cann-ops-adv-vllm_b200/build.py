@@ -1,4 +1,5 @@
-"""In-tree build of the two native artefacts (no JIT cache, so the .so files travel with the repo):
+"""In-tree build of the two native artefacts (no JIT cache: the .so files are git-ignored but travel with the
+gpurun snapshot of the working tree):
 
   libspa_b200.so     hand-written sm_100a CUDA kernels + the C ABI (include/spa_b200.h); nvcc only,
                      no torch -- loadable from C, ctypes or another framework.

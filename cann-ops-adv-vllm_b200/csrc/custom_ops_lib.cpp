@@ -434,6 +434,7 @@ at::Tensor incre_flash_attention_v4(
                 "incre_flash_attention_v4: only the paged KV layout (blocktable [B, maxBlocks]) is supported");
     c10::cuda::CUDAGuard guard(query.device());
     const int64_t B = query.size(0), maxP = blocktable.size(1);
+    if (num_key_value_heads <= 0) num_key_value_heads = num_heads;      // the reference's default: 0 = MHA
     at::Tensor ident = at::arange(maxP, blocktable.options().dtype(at::kInt))
                            .view({1, 1, maxP}).expand({B, num_key_value_heads, maxP}).contiguous();
     return sparse_paged_attention(query, key_list, value_list, pse_shift, attention_mask, actual_seq_lengths,

@@ -59,7 +59,14 @@ __device__ __noinline__ void peer_exchange_flags(const ChainParams &p) {
             unsigned v;
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p.sig_local + p.peer_rank[i]) : "memory");
             if ((int)(v - e) >= 0) break;
-            if (globaltimer_ns() - t0 > 2000000000ull) { p.sig_local[kSigError] = e; return; }   // a peer never launched
+            if (globaltimer_ns() - t0 > 2000000000ull) {
+                // a peer did not launch within 2 s: the gathered buffer is incomplete and the lock-step that makes
+                // the double buffer safe is broken.  Fail LOUDLY: leave the marker for the host, then trap -- the
+                // stream's next synchronisation returns an error instead of a consumer reading stale rows.
+                p.sig_local[kSigError] = e;
+                asm volatile("fence.acq_rel.sys;" ::: "memory");
+                __trap();
+            }
             __nanosleep(64);
         }
     }
@@ -110,6 +117,14 @@ __global__ void __launch_bounds__(kThreads, 1) spa_select_kernel(const __grid_co
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = aligned_smem(smem_raw);
     select_phase<QT, FLAGS>(p, &tmC, smem, nullptr);
+}
+
+// Test hook (spaDebugHoldSMs): CTAs that claim a whole SM each (shared memory) and spin for a given time.
+__global__ void spa_hold_sm_kernel(unsigned long long ns) {
+    extern __shared__ unsigned char hold_smem[];
+    const unsigned long long t0 = globaltimer_ns();
+    if (threadIdx.x == 0) hold_smem[0] = 1;
+    while (globaltimer_ns() - t0 < ns) __nanosleep(1000);
 }
 
 __global__ void spa_max_ppl_kernel(const __grid_constant__ ChainParams p) {
@@ -201,6 +216,17 @@ static int dev_info(DevInfo *d) {
     return SPA_OK;
 }
 
+
+// Raise a kernel's dynamic shared-memory limit to everything the device allows next to the kernel's static
+// shared memory.  Done at plan time with the DEVICE's maximum rather than the plan's need: the attribute is
+// global to the function, so plans with different needs (other threads, other executors) must never lower
+// it under each other's launches.
+static int raise_smem_limit(const void *func, int optin) {
+    cudaFuncAttributes fa;
+    CUDA_TRY(cudaFuncGetAttributes(&fa, func));
+    CUDA_TRY(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes));
+    return SPA_OK;
+}
 
 // ---- query: [B,Nq,D] or [B,Nq,1,D]
 static int parse_query(const spaTensor *q, const char *name, int *B, int *Nq, long long *sb,
@@ -566,6 +592,9 @@ int spaAssignPageClustersGetWorkspaceSize(const spaTensor *key, const spaTensor 
         if (S.total > d.smem_optin) { delete e; return fail(SPA_ERR_UNSUPPORTED, "clusters %d need %d bytes of shared memory", C, S.total); }
         const int per_sm = std::max(1, std::min(4, (d.smem_optin - 1024) / (S.total + 1024)));
         e->grid = (int)std::min<int64_t>(units, (int64_t)d.sms * per_sm);
+        void (*kern)(AssignParams) = e->q_bf16 ? (i8 ? spa_assign_kernel<__nv_bfloat16, true> : spa_assign_kernel<__nv_bfloat16, false>)
+                                               : (i8 ? spa_assign_kernel<__half, true> : spa_assign_kernel<__half, false>);
+        if ((rc = raise_smem_limit((const void *)kern, d.smem_optin))) { delete e; return rc; }
     }
     *executor = e;
     return SPA_OK;
@@ -577,8 +606,7 @@ int spaAssignPageClusters(void *, uint64_t, spaExecutor *e, spaStream stream_) {
     const AssignSmem S(e->ap.C, e->q_bf16 ? 3 : 2);
     void (*kern)(AssignParams) = e->q_bf16 ? (e->kv_i8 ? spa_assign_kernel<__nv_bfloat16, true> : spa_assign_kernel<__nv_bfloat16, false>)
                                            : (e->kv_i8 ? spa_assign_kernel<__half, true> : spa_assign_kernel<__half, false>);
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total));
-    kern<<<e->grid, kAssignThreads, S.total, stream>>>(e->ap);
+    kern<<<e->grid, kAssignThreads, S.total, stream>>>(e->ap);       // (smem limit raised once, at plan time)
     CUDA_TRY(cudaGetLastError());
     return SPA_OK;
 }
@@ -600,6 +628,9 @@ static int finish_select_plan(spaExecutor *e, uint64_t *ws, spaExecutor **out) {
         if (rc) { delete e; return rc; }
     }
     e->p.smem_bytes = bytes + 1024;
+    if (SelectKernel k = select_kernel_for(e->q_bf16, e->flags)) {
+        if ((rc = raise_smem_limit((const void *)k, d.smem_optin))) { delete e; return rc; }
+    }
     const int ngroups = kConsumerWarps / e->p.sel_gw;
     e->grid = std::max(1, std::min((e->p.items + ngroups - 1) / ngroups, 8 * d.sms));
     // exact-score scratch for the rare case of more than kXCap near-ties around the k-th score
@@ -618,8 +649,7 @@ static int launch_select(void *workspace, uint64_t wsSize, spaExecutor *e, cudaS
     p.exact_scratch = (double *)workspace;
     SelectKernel k = select_kernel_for(e->q_bf16, e->flags);
     if (!k) return fail(SPA_ERR_ARG, "no selection kernel for flags %d", e->flags);
-    CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
-    k<<<e->grid, kThreads, p.smem_bytes, stream>>>(p, e->tmC);
+    k<<<e->grid, kThreads, p.smem_bytes, stream>>>(p, e->tmC);       // (smem limit raised once, in finish_select_plan)
     CUDA_TRY(cudaGetLastError());
     if (e->op == OP_CENT_SELECT) {
         spa_max_ppl_kernel<<<std::max(1, p.B), 32, 0, stream>>>(p);
@@ -884,7 +914,7 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     p.smem_bytes = std::max(attn_bytes, sel_bytes) + 1024;
     if (p.smem_bytes > d.smem_optin) return fail(SPA_ERR_UNSUPPORTED, "shared memory need %d > %d", p.smem_bytes, d.smem_optin);
     ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
+    if ((rc = raise_smem_limit((const void *)kern, d.smem_optin))) return rc;
     int occ = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, p.smem_bytes));
     if (occ < 1) return fail(SPA_ERR_CUDA, "chain kernel does not fit on an SM (smem %d)", p.smem_bytes);
@@ -925,13 +955,16 @@ static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaSt
     p.item_ppl = (int *)(w + e->off_ippl);
     p.part_o = (float *)(w + e->off_po); p.part_ml = (float *)(w + e->off_pml);
     p.exact_scratch = (double *)(w + e->off_xs);
-    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem_bytes));
+    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);   // (smem limit raised once, in plan_attention)
     // queue words start at zero and the kernel leaves them at zero again, but the workspace is the
-    // caller's scratch: clear it unless the caller vouches for it (spaExecutorSetPersistentWorkspace)
+    // caller's scratch: clear it unless the caller vouches for it (spaExecutorSetPersistentWorkspace).
+    // "Known clean" is only recorded for a clear that really executes: under stream capture the memset is
+    // merely recorded into the graph (it then runs with every replay), so the flag stays as it was.
     if (!e->persistent_ws || e->clean_ws != workspace) {
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        CUDA_TRY(cudaStreamIsCapturing(stream, &cap));
         CUDA_TRY(cudaMemsetAsync(p.ctrl, 0, e->ctrl_bytes, stream));
-        e->clean_ws = e->persistent_ws ? workspace : nullptr;
+        if (cap == cudaStreamCaptureStatusNone) e->clean_ws = e->persistent_ws ? workspace : nullptr;
     }
     // One CTA per SM, launched cooperatively: there is no grid-wide barrier, but CTAs wait for words that other
     // CTAs publish after their own selection, so all of them must be co-resident.  The cooperative launch makes
@@ -1056,6 +1089,18 @@ static int static_scratch_address(void **ptr) {
 }
 
 uint64_t spaStaticScratchBytes(void) { return SPA_STATIC_SCRATCH_BYTES; }
+
+int spaDebugHoldSMs(int numSMs, uint64_t nanoseconds, spaStream stream) {
+    if (numSMs <= 0) return SPA_OK;
+    DevInfo d;
+    int rc = dev_info(&d);
+    if (rc) return rc;
+    const int smem = d.smem_optin - 4096;               // more than half an SM: one such CTA per SM
+    if ((rc = raise_smem_limit((const void *)spa_hold_sm_kernel, d.smem_optin))) return rc;
+    spa_hold_sm_kernel<<<numSMs, 32, smem, (cudaStream_t)stream>>>((unsigned long long)nanoseconds);
+    CUDA_TRY(cudaGetLastError());
+    return SPA_OK;
+}
 
 int spaSparsePagedFusionAttentionStatic(
     const spaTensor *query, const spaTensor *key, const spaTensor *value, const spaTensor *pseShift,

@@ -665,7 +665,8 @@ __device__ __noinline__ int warp_emit_union(const ChainParams &p, int item, cons
     int base = 0;
     for (int i0 = 0; i0 < pl; i0 += 32) {
         const int i = i0 + lane;
-        const unsigned m = (i < pl) ? pm[i] : 0u;
+        unsigned m = (i < pl) ? pm[i] : 0u;
+        if (m != 0u && (unsigned)phys[i] >= (unsigned)p.num_blocks) m = 0u;      // block id outside the pool: skipped
         const unsigned mt = (m >> 16) & m & 0xffffu, mf = m & 0xffffu & ~mt;
         const unsigned bf = __ballot_sync(0xffffffffu, mf != 0u), bt = __ballot_sync(0xffffffffu, mt != 0u);
         if (mf) st_relaxed_u64(q + base + __popc(bf & lt), queue_entry(phys[i], mf, false, item, kBS));
@@ -856,10 +857,14 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
     for (int ch = G.warp; ch < nch; ch += G.gw) {
         const int i = ch * 32 + lane;
         const unsigned m = (i < pl) ? pm[i] : 0u;
+        // union (what is streamed): only pages whose block_table entry names a block of the pool -- a negative /
+        // padding / out-of-range id is skipped, not read (include/spa_b200.h, "invalid block ids"); the per-head
+        // position lists keep the golden's semantics and list the page all the same
+        const bool inpool = !(FLAGS & kSelUnion) || (i < pl && (unsigned)physS[i] < (unsigned)p.num_blocks);
         int mine = 0;
 #pragma unroll 1
         for (int h = 0; h <= g; ++h) {
-            const bool on = (h < g) ? ((m >> h) & 1u) : ((m & 0xffffu) != 0u);
+            const bool on = (h < g) ? ((m >> h) & 1u) : ((m & 0xffffu) != 0u && inpool);
             const int c = __popc(__ballot_sync(0xffffffffu, on));
             if (lane == h) mine = c;
         }
@@ -912,7 +917,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
                 if (on && pp0) pp0[(size_t)h * p.MP + cnt[ch * KG1 + h] + __popc(bal & lt)] = i;
             }
             if (FLAGS & kSelUnion) {
-                const bool on = (m & 0xffffu) != 0u;
+                const bool on = (m & 0xffffu) != 0u && (unsigned)physS[i < pl ? i : 0] < (unsigned)p.num_blocks;
                 const unsigned bal = __ballot_sync(0xffffffffu, on);
                 if (on) st_relaxed_u64(qent + cnt[ch * KG1 + g] + __popc(bal & lt), queue_entry(physS[i], m, (m >> 16) != 0u, item, max(1, tail_cnt)));
             }

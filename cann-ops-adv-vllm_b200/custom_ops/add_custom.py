@@ -86,7 +86,7 @@ def sparse_paged_attention(query: torch.Tensor,
     """Paged flash-decode over the pages listed in `blockposition` (add_custom.py:41-75).
 
     `softmax_lse`: optional caller-allocated float32 [B, Nq], filled with ln(sum exp(scale * q.k)) per row
-    (the reference kernels' softmaxLse output); fp16/bf16 KV only."""
+    (the reference kernels' softmaxLse output); fp16/bf16 and int8 KV."""
     actual_seq_lengths = _tensor(actual_seq_lengths, torch.int64, query.device)
     return custom_ops_lib.sparse_paged_attention_ex(
         query, [key], [value], pse_shift, attention_mask, actual_seq_lengths,

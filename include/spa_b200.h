@@ -150,7 +150,14 @@ SPA_API int spaCentSelect(void *workspace, uint64_t workspaceSize, spaExecutor *
  *      1-element tensor lists, add_custom.py:70-75).
  * actualSeqLengths: DEVICE int64 [B] or [1] (the reference copies it to the host,
  *      add_custom.cpp:105-118; here it is read on device, no sync).
- * blockPosition [B, Nkv or Nq, MP] int32, 0x7fffffff-terminated.
+ * blockPosition [B, Nkv or Nq, MP] int32, 0x7fffffff-terminated.  A logical page listed more than once in a
+ *      row is attended ONCE (the reference walks the slots and would weigh it twice; no reference test
+ *      repeats a page).
+ * Invalid block ids (both attention ops): a selected logical page whose blocktable entry is negative or
+ *      >= the pool's block count (padding such as -1) is SKIPPED -- it contributes no tokens to the
+ *      softmax; it is never read.  blockPosition / pagePositionLength of the fused op still list it, as the
+ *      reference golden does (tests/utils.py:57-80 clamps the table value for the block_ids lookup only).
+ *      At most 2^24 blocks per pool.
  * pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2,
  * kvPaddingSize must be absent (SPA_ERR_UNSUPPORTED otherwise).                                 */
 SPA_API int spaSparsePagedAttentionGetWorkspaceSize(
@@ -172,6 +179,11 @@ SPA_API int spaSparsePagedAttention(void *workspace, uint64_t workspaceSize, spa
  *      the aclnn prototype: inputs, attrs, the three aux outputs, attentionOut.
  * One launch: CentSelect (writes blockPosition [B,Nq,MP], pagePositionLength [B,Nq,8],
  * maxPagePositionLength [B,8] in place) then attention over the selected pages.
+ * Exactness of the selection: scores are defined by EXACT arithmetic (fp16/bf16 products summed without
+ * rounding; ties -> lowest index), which float64 accumulation delivers while, per (head, cluster) dot
+ * product, the largest and the smallest non-zero |q_d * cent_d| lie within 2^40 of each other (always true
+ * for fp16; for bf16 it excludes tables that mix magnitudes like 1e-30 and 1e+3 in one row).  Outside that
+ * range two scores closer than float64 rounding of the largest term may be ordered either way.
  * topK: reference tiling constant (cent_select: 64).  actualSeqLengths is accepted and ignored
  * (the reference kernel substitutes the on-device maxPagePositionLength,
  * sparse_paged_fusion_attention.cpp:68).                                                        */
@@ -265,6 +277,12 @@ SPA_API int spaAssignPageClusters(void *workspace, uint64_t workspaceSize, spaEx
  *     consumed their gathered buffer must alternate between two buffers (two executors): a rank cannot
  *     finish launch t before every peer has finished launch t, so buffer t%2 is never overwritten while a
  *     peer still reads it.   world <= 1 or gatheredOut == NULL switches peer output off.                   */
+/* Test hook: occupy `numSMs` SMs (one CTA each, nearly all of the SM's shared memory) for `nanoseconds` on
+ * `stream`.  Used by the tests to run the chain kernel while part of the device is unavailable: the chain
+ * kernel is launched cooperatively (all its CTAs must be co-resident), so it starts when the SMs are free
+ * again instead of spinning on a partial grid.  No reference counterpart.                                  */
+SPA_API int spaDebugHoldSMs(int numSMs, uint64_t nanoseconds, spaStream stream);
+
 #define SPA_IPC_HANDLE_BYTES 64
 #define SPA_MAX_PEERS 8
 SPA_API int spaPeerBufferCreate(uint64_t bytes, void **devPtr, unsigned char *ipcHandle);

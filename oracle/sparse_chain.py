@@ -13,7 +13,8 @@ Parity status
   `tests/test_oracle_golden.py` checks this restatement against them bit-for-bit.
 * Attention: the reference ships NO torch/numpy attention golden (only constant-value known-answer
   tests, `tests/ifa_v5_case.py:584-765`).  The restatement below follows the kernel sources and is
-  pinned only by those known-answer vectors (`tests/golden/kat_*.npz`) plus a float64 cross-check;
+  pinned only by those known-answer vectors (restated in tests/test_gpu_parity.py::test_attention_known_answer)
+  plus a float64 cross-check;
   beyond that it is "parity unpinned" and the north-star tolerances (1e-3 fp16, 2e-2 bf16/int8)
   define agreement.
 """
@@ -228,16 +229,14 @@ def attend_lists(
             pages = torch.tensor([e[0] for e in ent], dtype=torch.int64)
             ntok = torch.tensor([e[1] for e in ent], dtype=torch.int64)
             phys = bt[b, pages]
-            ok = (phys >= 0) & (phys < nblk)          # out-of-pool blocks read as zeros (TMA OOB fill)
+            ok = (phys >= 0) & (phys < nblk)          # a block id outside the pool is skipped (include/spa_b200.h)
             physc = phys.clamp(0, nblk - 1)
             Kp = K[physc, :, n2, :].to(ft)            # [n, bs, D]
             Vp = V[physc, :, n2, :].to(ft)
-            Kp = Kp * ok.view(-1, 1, 1).to(ft)
-            Vp = Vp * ok.view(-1, 1, 1).to(ft)
             if is_i8:
                 Kp = (Kp + of[0, n2].to(ft)) * sc[0, n2].to(ft)
                 Vp = (Vp + of[1, n2].to(ft)) * sc[1, n2].to(ft)
-            tokmask = torch.arange(block_size).view(1, -1) < ntok.view(-1, 1)     # [n, bs]
+            tokmask = (torch.arange(block_size).view(1, -1) < ntok.view(-1, 1)) & ok.view(-1, 1)   # [n, bs]
             Kf = Kp.reshape(-1, D)
             Vf = Vp.reshape(-1, D)
             s = (Kf @ q[b, hq].to(ft)) * float(scale_value)
