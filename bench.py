@@ -17,15 +17,26 @@ on the selected-KV bytes).  Prints ONE JSON line on rank 0.
             in device memory in the reference too) and are not per-step inputs.
   roofline  algorithmic bytes of one launch (union-of-group selected K+V page slices +
             centroids + index tensors + q/out, computed from the selection the kernel produced)
-            / CUDA-event duration of that launch, against MEASURED_PEAKS.json hbm_gbs.
-  cpu_baseline  the CPU oracle (port of the reference golden chain + attention restatement) timed
-            on this box's host cores on a bounded sample (first sequences of the same workload).
+            / CUDA-event duration of that launch, against MEASURED_PEAKS.json hbm_gbs.  `traffic` is
+            the ncu-measured DRAM bytes of one launch (profiles/ncu_traffic.json), reported only while
+            that capture belongs to the kernel sources being timed (content hash), else null.
+  cpu_baseline  the CPU oracle (port of the reference golden chain as written + attention
+            restatement) timed on this box's host cores on the same workload (whole batch at c1/c2,
+            else a bounded sample); cpu_baseline_vectorised = the same chain with batched torch ops
+            (oracle/fast_chain.py), the "fair CPU" number of BASELINE.md section 3.
+  extra_workloads (N=1, default run)  the same measurement for BASELINE configs[2] (c3: int8 KV),
+            configs[3] (c4: 70B shape) and c2 with randn centroids (independent heads: larger union).
+  strong_c4 (N>1)  STRONG scaling of configs[3] (c4, B=32 fixed, KV heads split over the ranks):
+            ms/step at N, at N=1 (rank 0 alone, same run), speed-up and efficiency.
+  gather_verified (N>1)  the fused peer-store all-gather compared, outside the timed region, bit for
+            bit with an NCCL all-gather of the same shards and with the oracle on one sequence; the
+            run fails if it differs.
 
 Multi-GPU (torchrun, one rank per GPU): KV-head tensor parallelism -- rank r owns KV heads
 [r*Nkv/N, (r+1)*Nkv/N) with their query heads, centroids, block_ids and a rank-local KV pool; the
-only collective is the NCCL all-gather of attention_out.  Default scaling is "weak": the batch
-grows with N (B = 16*N) so the bytes streamed per GPU stay fixed; `--scaling strong` keeps the
-global workload fixed (BASELINE configs[3]: c4 on 2/4/8 GPUs).
+only exchange is the all-gather of attention_out, fused into the launch (NVLink peer stores) or by
+NCCL (--gather nccl).  Default scaling is "weak": the batch grows with N (B = 16*N) so the bytes
+streamed per GPU stay fixed; `--scaling strong` keeps the global workload fixed.
 """
 import argparse
 import json
@@ -37,7 +48,8 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-for _p in (ROOT, os.path.join(ROOT, "cann-ops-adv-vllm_b200")):
+# SPA_PKG_DIR: another build of the package (same-box A/B of two kernel builds, tools/gpu_batch.sh)
+for _p in (ROOT, os.environ.get("SPA_PKG_DIR") or os.path.join(ROOT, "cann-ops-adv-vllm_b200")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
@@ -45,8 +57,36 @@ import torch  # noqa: E402
 
 BS = 128
 D = 128
-# DRAM bytes of one chain-kernel launch from the committed ncu capture (read 541,532,672 + write 6,386,432)
-NCU_TRAFFIC = {"c2": 547919104}
+
+
+def kernel_source_sha():
+    """Content hash of the kernel sources + the C ABI header: identifies the build an ncu capture belongs to
+    (git is not available on the GPU box: .git does not travel with the snapshot)."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "cann-ops-adv-vllm_b200", "csrc", "*.cu*"))) + \
+            [os.path.join(ROOT, "include", "spa_b200.h")]:
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE chain-kernel launch from the committed `ncu --set full`
+    capture (profiles/ncu_traffic.json, written by tools/ncu_traffic.py next to the summary it was read from).
+    Reported only while the capture belongs to the kernel sources being timed; otherwise null."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)
+    except (OSError, ValueError):
+        return None, "no capture committed (profiles/ncu_traffic.json)"
+    rec = t.get("workloads", {}).get(workload)
+    if rec is None:
+        return None, f"no capture of {workload}"
+    if rec.get("src_sha") != kernel_source_sha():
+        return None, f"capture {rec.get('summary')} belongs to kernel sources {rec.get('src_sha')}, not the ones timed"
+    return int(rec["dram_read"]) + int(rec["dram_write"]), f"ncu --set full, one launch ({rec.get('summary')})"
 
 WORKLOADS = {
     # BASELINE.json configs[0..3]
@@ -76,7 +116,7 @@ def qdtype(w):
 # synthetic inputs: generated on the device, seeded; block_table is a per-sequence
 # permutation of distinct physical pages so aliasing does not inflate L2 hits
 # ------------------------------------------------------------------------------------------------
-def make_inputs(w, B, rank, world, device, seed=1234, kv_layout="bsnd"):
+def make_inputs(w, B, rank, world, device, seed=1234, kv_layout="bsnd", cent_dist="rand"):
     """kv_layout: "bsnd" = vLLM pool [blocks, bs, Nkv, D] (primary, tests/ifa_v5_case.py:608-610);
     "bnsd" = [blocks, Nkv, bs, D] (the reference's BNSD-paged KAT layout, tests/ifa_v5_case.py:36)."""
     Nq, Nkv, S, C = w["Nq"], w["Nkv"], w["S"], w["C"]
@@ -91,7 +131,9 @@ def make_inputs(w, B, rank, world, device, seed=1234, kv_layout="bsnd"):
     block_table = torch.randperm(pages, generator=g_common, device=device).to(torch.int32).view(B, P)
     seq = torch.full((B,), S, dtype=torch.int32, device=device)
     q = torch.rand(B, nq, D, generator=g_rank, device=device).to(qd)
-    l1 = torch.rand(nkv, C, D, generator=g_rank, device=device).to(qd)
+    # "rand": selection tests of the reference (tests/cent_select.py:49); "randn": its fused test (fused_ifa_v5_case.py:55)
+    # -- with zero-mean centroids the heads of a GQA group rank the clusters independently (larger union)
+    l1 = (torch.rand if cent_dist == "rand" else torch.randn)(nkv, C, D, generator=g_rank, device=device).to(qd)
     block_ids = torch.randint(0, C, (nkv, pages), generator=g_rank, device=device, dtype=torch.int32)
     pool_shape = (pages, BS, nkv, D) if kv_layout == "bsnd" else (pages, nkv, BS, D)
     if w["kv"] == "i8":
@@ -226,32 +268,275 @@ def cpu_sample(inp, nseq):
     return c
 
 
-def run_oracle(c, inp):
+def run_oracle(c, inp, fast=False):
     from oracle import sparse_chain as oc
     i8 = c["key"].dtype == torch.int8
+    if fast:
+        from oracle import fast_chain
+        return fast_chain.fused_chain(
+            c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"], c["seq"], inp["Nq"],
+            inp["scale"], inp["Nkv"], BS, inp["k"], inp["MP"], c["aq_scale"] if i8 else None,
+            c["aq_offset"] if i8 else None)
     return oc.sparse_paged_fusion_attention(
         c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"], c["seq"], inp["Nq"],
         inp["scale"], inp["Nkv"], BS, inp["k"], inp["MP"], c["aq_scale"] if i8 else None,
         c["aq_offset"] if i8 else None)
 
 
-def time_cpu_baseline(inp, budget_s=15.0, nseq=1):
+def cpu_nseq(w):
+    """Sequences of the workload the CPU legs run per step: the whole batch where the host copy of their pages
+    stays modest (c1, c2: <= 2 GiB), else a bounded sample."""
+    P = (w["S"] + BS - 1) // BS
+    page_bytes = BS * w["Nkv"] * D * 2 * (1 if w["kv"] == "i8" else 2)
+    return max(1, min(w["B"], (2 << 30) // (P * page_bytes)))
+
+
+def time_cpu_baseline(inp, w, budget_s=12.0):
+    """The oracle port (reference golden as written: Python loops) and the vectorised variant, on the host cores."""
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    nseq = cpu_nseq(w)
     c = cpu_sample(inp, nseq)
-    best = float("inf")
-    t_all = time.perf_counter()
-    reps = 0
-    while reps < 3 or (time.perf_counter() - t_all < budget_s and reps < 10):
-        t0 = time.perf_counter()
-        run_oracle(c, inp)
-        best = min(best, time.perf_counter() - t0)
-        reps += 1
-        if time.perf_counter() - t_all > 2 * budget_s:
-            break
-    return {"value": nseq / best, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"first {nseq} of {inp['B']} sequences of the workload (all {inp['Nq']} q heads), "
-                      f"oracle/sparse_chain.py fused chain, best of {reps}, torch threads={cores}"}, c
+    res = {}
+    for fast in (False, True):
+        best, reps, t_all = float("inf"), 0, time.perf_counter()
+        while reps < 2 or (time.perf_counter() - t_all < budget_s and reps < 8):
+            t0 = time.perf_counter()
+            run_oracle(c, inp, fast)
+            best = min(best, time.perf_counter() - t0)
+            reps += 1
+        what = "oracle/fast_chain.py (vectorised torch, loops over B*Nkv items only)" if fast else \
+            "oracle/sparse_chain.py (the reference golden as written: Python loops over B*Nq rows)"
+        res[fast] = {"value": nseq / best, "unit": UNIT, "cores": cores, "kind": "port",
+                     "sample": f"{'all' if nseq == inp['B'] else 'first'} {nseq} of {inp['B']} sequences of the workload "
+                               f"(all {inp['Nq']} q heads), fused chain by {what}, best of {reps}, torch threads={cores}"}
+    return res[False], res[True]
+
+
+# ------------------------------------------------------------------------------------------------
+def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="rand", do_e2e=True, verify=False,
+                   sample_clocks=True):
+    """Time `steps` fused decode steps of workload `name` on the ranks of ctx (device-resident, then end to end).
+    Returns the measurement record on rank 0 of ctx, None elsewhere."""
+    import custom_ops
+    rank, world, dev, dist = ctx["rank"], ctx["world"], ctx["dev"], ctx["dist"]
+    w = WORKLOADS[name]
+    B = w["B"] * world if scaling == "weak" else w["B"]
+    inp = make_inputs(w, B, rank, world, dev, kv_layout=args.kv_layout, cent_dist=cent_dist)
+    nq, nkv, qd = inp["Nq"], inp["Nkv"], inp["qd"]
+    bp = torch.empty(B, nq, inp["MP"], dtype=torch.int32, device=dev)
+    ppl = torch.empty(B, nq, 8, dtype=torch.int32, device=dev)
+    mppl = torch.empty(B, 8, dtype=torch.int64, device=dev)
+    out = torch.empty(B, nq, D, dtype=qd, device=dev)
+
+    # The step's inputs are staged the way a serving engine stages them: ONE pinned host blob (query | block_table |
+    # seq_len, 256-byte aligned sections) -> one H2D copy per step into a device blob the op's tensors are views of.
+    def _sec(n):
+        return (n + 255) // 256 * 256
+    nb_q, nb_bt, nb_seq = inp["q"].numel() * inp["q"].element_size(), inp["block_table"].numel() * 4, inp["seq"].numel() * 4
+    o_bt, o_seq, nb_all = _sec(nb_q), _sec(nb_q) + _sec(nb_bt), _sec(nb_q) + _sec(nb_bt) + _sec(nb_seq)
+    hblob = torch.zeros(nb_all, dtype=torch.uint8).pin_memory()
+    dblob = torch.zeros(nb_all, dtype=torch.uint8, device=dev)
+    hblob[:nb_q].view(qd).view(inp["q"].shape).copy_(inp["q"])
+    hblob[o_bt:o_bt + nb_bt].view(torch.int32).view(inp["block_table"].shape).copy_(inp["block_table"])
+    hblob[o_seq:o_seq + nb_seq].view(torch.int32).view(inp["seq"].shape).copy_(inp["seq"])
+    sq = dblob[:nb_q].view(qd).view(inp["q"].shape)
+    sbt = dblob[o_bt:o_bt + nb_bt].view(torch.int32).view(inp["block_table"].shape)
+    sseq = dblob[o_seq:o_seq + nb_seq].view(torch.int32).view(inp["seq"].shape)
+    dblob.copy_(hblob)
+    gather = out_full = None
+    i8 = w["kv"] == "i8"
+    peer = world > 1 and args.gather == "peer"
+    aq = dict(antiquant_scale=inp["aq_scale"] if i8 else None, antiquant_offset=inp["aq_offset"] if i8 else None)
+    if world > 1:
+        from kvhead_tp import HeadGather, head_shard
+        gather = HeadGather(out.shape, qd, dev)                      # NCCL all-gather of the output shards
+        out_full = torch.empty(B, nq * world, D, dtype=qd, device=dev)
+    if peer:
+        # the launch itself delivers every rank's rows to every rank (peer stores + flag exchange)
+        from peer_gather import TPFusedDecode
+        shard = head_shard(rank, world, nq * world, nkv * world)
+        plan = TPFusedDecode(shard, nq * world, sq, inp["key"], inp["value"], sbt, inp["l1"], inp["block_ids"], sseq,
+                             bp, ppl, mppl, inp["scale"], BS, k=inp["k"], **aq)
+    else:
+        plan = custom_ops.FusedDecodePlan(inp["q"], inp["key"], inp["value"], inp["block_table"], inp["l1"],
+                                          inp["block_ids"], inp["seq"], bp, ppl, mppl, out, nq, inp["scale"], nkv, BS,
+                                          k=inp["k"], **aq)
+    flush = None if args.no_flush else L2Flush(dev)
+
+    def step():
+        r = plan.launch()
+        if world > 1 and args.gather == "nccl":
+            return gather(out, out_full)
+        return r
+
+    # N>1: the ranks are coupled by the output exchange at the end of every step, so a rank whose L2 flush ran a few
+    # microseconds longer makes all the others wait inside THEIR timed region.  A one-element all-reduce after the
+    # flush (outside the timed region) lines the ranks up again, as the collective in front of the attention does
+    # in a tensor-parallel decoder layer.
+    align_buf = torch.zeros(1, device=dev) if world > 1 else None
+
+    def pre_step():
+        if flush is not None:
+            flush()
+        if align_buf is not None and not args.no_align:
+            dist.all_reduce(align_buf)
+
+    graph = None
+    if args.graph and peer:
+        raise SystemExit("--graph with --gather peer: capture both plans of TPFusedDecode yourself (alternating buffers); use --gather nccl here")
+    if args.graph:
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            step()
+        torch.cuda.current_stream().wait_stream(s)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            step()
+
+    def run_step():
+        return graph.replay() if graph is not None else step()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        pre_step()
+        run_step()
+    barrier()
+
+    # ---------------- N>1: is the gathered output right?  (outside the timed region) ----------------
+    gather_verified = None
+    if verify and world > 1:
+        got = step().clone()                                         # gathered [B, Nq_total, D] of this rank
+        torch.cuda.synchronize()
+        lo = rank * nq
+        mine = got[:, lo:lo + nq].contiguous()
+        ref_full = gather(mine, torch.empty_like(got))               # the same shards through NCCL
+        ok = torch.equal(got, ref_full)                              # bit for bit: the exchange moved every row
+        c1 = cpu_sample(inp, 1)                                      # this rank's heads of sequence 0 vs the oracle
+        wo = run_oracle(c1, inp)[0].float()
+        tol = 2e-2 if (i8 or w["q"] == "bf16") else 1e-3
+        ok = ok and bool(((mine[:1].float().cpu() - wo).abs() <= tol + tol * wo.abs()).all())
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        gather_verified = bool(flag.item())
+        barrier()
+
+    # ---------------- device-resident timing ----------------
+    ab = algorithmic_bytes(inp, bp, ppl)
+    sampler = ClockSampler(ctx["local_rank"]) if (rank == 0 and sample_clocks) else None
+    if sampler:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    barrier()
+    xch0 = (plan.out.exchange_ns(), plan.out.exchange_send_ns()) if peer else (0, 0)
+    for s0, s1 in ev:
+        pre_step()
+        s0.record()
+        run_step()
+        s1.record()
+    barrier()
+    xch_us = None
+    if peer:
+        mine = torch.tensor([(plan.out.exchange_ns() - xch0[0]) / steps / 1e3,
+                             (plan.out.exchange_send_ns() - xch0[1]) / steps / 1e3], dtype=torch.float64, device=dev)
+        allx = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allx, mine)
+        xch_us = {"total_per_rank": [round(x[0].item(), 2) for x in allx],
+                  "fence_and_flags_per_rank": [round(x[1].item(), 2) for x in allx]}
+    times = [a.elapsed_time(b) for a, b in ev]                      # ms
+    total_ms = torch.tensor([sum(times)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    ms_per_step = total_ms.item() / steps
+    st = sorted(times)
+
+    # ---------------- end-to-end through the reference-facing call ----------------
+    e2e = None
+    if do_e2e:
+        # N>1: a tensor-parallel engine consumes the gathered output on the DEVICE; what returns to the host here
+        # is this rank's shard of it (the whole-job D2H volume is then one full output, not N of them)
+        hout = torch.empty(B, nq, D, dtype=qd).pin_memory()
+        dshard = torch.empty(B, nq, D, dtype=qd, device=dev) if world > 1 else None
+        e = torch.empty(0, dtype=qd, device=dev)
+        e64 = torch.empty(0, dtype=torch.int64, device=dev)
+
+        def e2e_step():
+            dblob.copy_(hblob, non_blocking=True)                    # query | block_table | seq_len: one H2D copy
+            if peer:
+                # same public surface as the TP serving step: the plan is bound to views of dblob, the launch
+                # returns the gathered output of all ranks
+                full = plan.launch()
+                dshard.copy_(full[:, rank * nq:(rank + 1) * nq])
+                hout.copy_(dshard, non_blocking=True)
+                return
+            o, _, _ = custom_ops.sparse_paged_fusion_attention(
+                sq, inp["key"], inp["value"], e, e, e64, e, e, e, e, e, inp["aq_scale"], inp["aq_offset"], sbt, e64,
+                inp["l1"], inp["block_ids"], sseq, bp, ppl, mppl, nq, inp["scale"], "BNSD", nkv, BS, 1, k=inp["k"])
+            if world > 1 and args.gather == "nccl":
+                gather(o, out_full)
+            hout.copy_(o, non_blocking=True)
+
+        for _ in range(warmup):
+            e2e_step()
+        barrier()
+        ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for s0, s1 in ev2:
+            pre_step()
+            s0.record()
+            e2e_step()
+            s1.record()
+            s1.synchronize()                                         # the caller consumes hout every step
+        barrier()
+        tot2 = torch.tensor([sum(a.elapsed_time(b) for a, b in ev2)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tot2, op=dist.ReduceOp.MAX)
+        e2e_ms = tot2.item() / steps
+        e2e = {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": nb_all,
+               "d2h_bytes_per_step": hout.numel() * hout.element_size(), "ms_per_step": e2e_ms,
+               "api": ("peer_gather.TPFusedDecode.launch (gathered output stays on the device; each rank returns its "
+                       "own shard to the host; bytes are per rank)") if peer else
+                      "custom_ops.sparse_paged_fusion_attention" + (" + kvhead_tp.HeadGather (NCCL); each rank returns its own shard; bytes are per rank" if world > 1 else "")}
+    clocks = sampler.stop() if sampler else None
+    if peer and plan.out.timed_out():
+        raise SystemExit(f"rank {rank}: a flag exchange of the fused output gather timed out (a peer did not launch)")
+
+    agg = torch.tensor([ab["bytes_alg"], ab["bytes_kv_union"], ab["bytes_logical"], ab["bytes_dense"]],
+                       dtype=torch.float64, device=dev)             # whole job
+    if world > 1:
+        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+    rec = None
+    if rank == 0:
+        achieved = ab["bytes_alg"] / (ms_per_step * 1e-3) / 1e9      # per-GPU kernel (rank 0's launch)
+        traffic, traffic_src = measured_traffic(name) if (world == 1 and cent_dist == "rand") else (None, "not captured for this configuration")
+        rec = {
+            "workload": name, "B": B, "ms_per_step": ms_per_step, "value": B / (ms_per_step * 1e-3),
+            "achieved_hbm_gbs_selected_kv": agg[1].item() / (ms_per_step * 1e-3) / 1e9,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": ctx["hbm_peak"], "unit": "GB/s",
+                         "frac": achieved / ctx["hbm_peak"], "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": ctx["peak_src"],
+                         "kernel": "spa_chain_kernel (fused: select + flash-decode + combine)",
+                         "bytes_alg_per_launch": ab["bytes_alg"], "bytes_kv_union": ab["bytes_kv_union"],
+                         "bytes_logical_per_q_head": ab["bytes_logical"], "bytes_dense": ab["bytes_dense"],
+                         "union_pages": ab["union_pages"], "selected_pages": ab["selected_pages"],
+                         "union_over_selected": ab["union_pages"] / max(1, ab["selected_pages"])},
+            "timing": {"min_ms": st[0], "median_ms": st[len(st) // 2], "p90_ms": st[int(len(st) * 0.9)], "max_ms": st[-1]},
+            "e2e": e2e, "launches_per_step": plan.num_launches, "tp_flag_exchange_us_per_step": xch_us,
+            "clocks": clocks, "gather_verified": gather_verified, "cent_dist": cent_dist,
+            "l2": ("flushed before every timed step (256 MiB write + 256 MiB read of a second buffer, so L2 holds clean lines); " if flush is not None else "not flushed; ") +
+                  f"per-step read set {ab['bytes_kv_union'] / 2**20:.0f} MiB > 126 MB L2" +
+                  ("; ranks aligned by a 1-element all-reduce before each timed step (outside the timed region)" if world > 1 and not args.no_align else ""),
+            "launch": "cuda graph replay" if graph is not None else ("TPFusedDecode.launch()" if peer else "FusedDecodePlan.launch()"),
+            "_inp": inp,
+        }
+    if peer:
+        plan.close()
+    return rec
 
 
 # ------------------------------------------------------------------------------------------------
@@ -263,8 +548,12 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--cent-dist", default="rand", choices=["rand", "randn"],
+                    help="centroid distribution: rand = U[0,1) (tests/cent_select.py:49), randn (fused_ifa_v5_case.py:55)")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true",
+                    help="main workload only: no extra_workloads (N=1) / strong_c4 (N>1) records")
     ap.add_argument("--no-align", action="store_true", help="N>1: no rank-aligning all-reduce before the timed steps")
     ap.add_argument("--graph", action="store_true", help="replay the step from a CUDA graph")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl", "none"],
@@ -293,248 +582,125 @@ def main():
         return reference_arm(args, w)
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback exists)"
-    import custom_ops
+    import custom_ops  # noqa: F401  (fails loudly if the extension is not built)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    dist = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
-    B = w["B"] * world if args.scaling == "weak" else w["B"]
-    inp = make_inputs(w, B, rank, world, dev, kv_layout=args.kv_layout)
-    nq, nkv = inp["Nq"], inp["Nkv"]
-    qd = inp["qd"]
+    ctx = dict(rank=rank, local_rank=local_rank, world=world, dev=dev, dist=dist, hbm_peak=hbm_peak, peak_src=peak_src)
+    solo = dict(ctx, rank=0, world=1, dist=None)                    # one rank on its own (no collectives)
 
-    bp = torch.empty(B, nq, inp["MP"], dtype=torch.int32, device=dev)
-    ppl = torch.empty(B, nq, 8, dtype=torch.int32, device=dev)
-    mppl = torch.empty(B, 8, dtype=torch.int64, device=dev)
-    out = torch.empty(B, nq, D, dtype=qd, device=dev)
-    # The step's inputs are staged the way a serving engine stages them: ONE pinned host blob (query | block_table |
-    # seq_len, 256-byte aligned sections) -> one H2D copy per step into a device blob the op's tensors are views of.
-    def _sec(n):
-        return (n + 255) // 256 * 256
-    nb_q, nb_bt, nb_seq = inp["q"].numel() * inp["q"].element_size(), inp["block_table"].numel() * 4, inp["seq"].numel() * 4
-    o_bt, o_seq, nb_all = _sec(nb_q), _sec(nb_q) + _sec(nb_bt), _sec(nb_q) + _sec(nb_bt) + _sec(nb_seq)
-    hblob = torch.zeros(nb_all, dtype=torch.uint8).pin_memory()
-    dblob = torch.zeros(nb_all, dtype=torch.uint8, device=dev)
-    hq = hblob[:nb_q].view(qd).view(inp["q"].shape)
-    hbt = hblob[o_bt:o_bt + nb_bt].view(torch.int32).view(inp["block_table"].shape)
-    hseq = hblob[o_seq:o_seq + nb_seq].view(torch.int32).view(inp["seq"].shape)
-    hq.copy_(inp["q"]); hbt.copy_(inp["block_table"]); hseq.copy_(inp["seq"])
-    sq = dblob[:nb_q].view(qd).view(inp["q"].shape)
-    sbt = dblob[o_bt:o_bt + nb_bt].view(torch.int32).view(inp["block_table"].shape)
-    sseq = dblob[o_seq:o_seq + nb_seq].view(torch.int32).view(inp["seq"].shape)
-    dblob.copy_(hblob)
-    gather = out_full = None
-    i8 = w["kv"] == "i8"
-    peer = world > 1 and args.gather == "peer"
-    if world > 1:
-        from kvhead_tp import HeadGather, head_shard
-        gather = HeadGather(out.shape, qd, dev)                      # NCCL all-gather of the output shards
-        out_full = torch.empty(B, nq * world, D, dtype=qd, device=dev)
-    if peer:
-        # the launch itself delivers every rank's rows to every rank (peer stores + flag exchange)
-        from peer_gather import TPFusedDecode
-        plan = TPFusedDecode(head_shard(rank, world, nq * world, nkv * world), nq * world, sq, inp["key"],
-                             inp["value"], sbt, inp["l1"], inp["block_ids"], sseq, bp, ppl, mppl,
-                             inp["scale"], BS, k=inp["k"], antiquant_scale=inp["aq_scale"] if i8 else None,
-                             antiquant_offset=inp["aq_offset"] if i8 else None)
-    else:
-        plan = custom_ops.FusedDecodePlan(
-            inp["q"], inp["key"], inp["value"], inp["block_table"], inp["l1"], inp["block_ids"], inp["seq"],
-            bp, ppl, mppl, out, nq, inp["scale"], nkv, BS, k=inp["k"],
-            antiquant_scale=inp["aq_scale"] if i8 else None, antiquant_offset=inp["aq_offset"] if i8 else None)
-    launches_per_step = plan.num_launches
-    flush = None if args.no_flush else L2Flush(dev)
-
-    def step():
-        plan.launch()
-        if world > 1 and args.gather == "nccl":
-            gather(out, out_full)
-
-    # N>1: the ranks are coupled by the output exchange at the end of every step, so a rank whose L2 flush
-    # ran a few microseconds longer makes all the others wait inside THEIR timed region.  A one-element
-    # all-reduce after the flush (outside the timed region) lines the ranks up again, as the collective in
-    # front of the attention does in a tensor-parallel decoder layer.
-    align_buf = torch.zeros(1, device=dev) if world > 1 else None
-
-    def pre_step():
-        if flush is not None:
-            flush()
-        if align_buf is not None and not args.no_align:
-            dist.all_reduce(align_buf)
-
-    graph = None
-    if args.graph and peer:
-        raise SystemExit("--graph with --gather peer: capture both plans of TPFusedDecode yourself (alternating buffers); use --gather nccl here")
-    if args.graph:
-        s = torch.cuda.Stream()
-        s.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(s):
-            step()
-        torch.cuda.current_stream().wait_stream(s)
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            step()
-
-    def run_step():
-        if graph is not None:
-            graph.replay()
-        else:
-            step()
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    # ---------------- device-resident timing ----------------
-    for _ in range(args.warmup):
-        pre_step()
-        run_step()
-    barrier()
-    ab = algorithmic_bytes(inp, bp, ppl)
-    sampler = ClockSampler(local_rank)
+    main_rec = bench_workload(args, args.workload, ctx, args.steps, args.warmup, scaling=args.scaling,
+                              cent_dist=args.cent_dist, verify=(world > 1 and args.gather != "none"))
+    cpu = cpu_fair = None
     if rank == 0:
-        sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    barrier()
-    xch0 = (plan.out.exchange_ns(), plan.out.exchange_send_ns()) if peer else (0, 0)
-    for s0, s1 in ev:
-        pre_step()
-        s0.record()
-        run_step()
-        s1.record()
-    barrier()
-    xch_us = None
-    if peer:
-        mine = torch.tensor([(plan.out.exchange_ns() - xch0[0]) / args.steps / 1e3,
-                             (plan.out.exchange_send_ns() - xch0[1]) / args.steps / 1e3], dtype=torch.float64, device=dev)
-        allx = [torch.zeros_like(mine) for _ in range(world)]
-        dist.all_gather(allx, mine)
-        xch_us = {"total_per_rank": [round(x[0].item(), 2) for x in allx], "fence_and_flags_per_rank": [round(x[1].item(), 2) for x in allx]}
-    times = [a.elapsed_time(b) for a, b in ev]                      # ms
-    total_ms = torch.tensor([sum(times)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
-    ms_per_step = total_ms.item() / args.steps
-    st = sorted(times)
-
-    # ---------------- end-to-end through the reference-facing call ----------------
-    hout = torch.empty(B, nq * world, D, dtype=qd).pin_memory() if world > 1 else torch.empty(B, nq, D, dtype=qd).pin_memory()
-    e = torch.empty(0, dtype=qd, device=dev)
-    e64 = torch.empty(0, dtype=torch.int64, device=dev)
-    h2d = nb_all
-    d2h = hout.numel() * hout.element_size()
-
-    def e2e_step_peer():
-        # same public surface as the TP serving step: inputs land in the plan's bound tensors, the launch
-        # returns the gathered output of all ranks
-        dblob.copy_(hblob, non_blocking=True)                       # the plan is bound to views of dblob
-        hout.copy_(plan.launch(), non_blocking=True)
-
-    def e2e_step():
-        if peer:
-            return e2e_step_peer()
-        dblob.copy_(hblob, non_blocking=True)
-        dq, dbt, dseq = sq, sbt, sseq
-        o, _, _ = custom_ops.sparse_paged_fusion_attention(
-            dq, inp["key"], inp["value"], e, e, e64, e, e, e, e, e, inp["aq_scale"], inp["aq_offset"], dbt, e64,
-            inp["l1"], inp["block_ids"], dseq, bp, ppl, mppl, nq, inp["scale"], "BNSD", nkv, BS, 1, k=inp["k"])
-        if world > 1:
-            hout.copy_(gather(o, out_full), non_blocking=True)
-        else:
-            hout.copy_(o, non_blocking=True)
-
-    for _ in range(args.warmup):
-        e2e_step()
-    barrier()
-    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    for s0, s1 in ev2:
-        pre_step()
-        s0.record()
-        e2e_step()
-        s1.record()
-        s1.synchronize()                                            # the caller consumes hout every step
-    barrier()
-    t2 = [a.elapsed_time(b) for a, b in ev2]
-    tot2 = torch.tensor([sum(t2)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tot2, op=dist.ReduceOp.MAX)
-    e2e_ms = tot2.item() / args.steps
-    clocks = sampler.stop() if rank == 0 else None
-    if peer and plan.out.timed_out():
-        raise SystemExit(f"rank {rank}: a flag exchange of the fused output gather timed out (a peer did not launch)")
-
-    # sum the per-rank algorithmic bytes (whole job)
-    agg = torch.tensor([ab["bytes_alg"], ab["bytes_kv_union"], ab["bytes_logical"], ab["bytes_dense"]],
-                       dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
-
-    if rank == 0:
-        cpu = None
+        inp = main_rec.pop("_inp")
         if world == 1 and not args.no_cpu_baseline:
-            cpu, _ = time_cpu_baseline(inp)
-        tokens_per_s = B / (ms_per_step * 1e-3)
-        achieved = ab["bytes_alg"] / (ms_per_step * 1e-3) / 1e9      # per-GPU kernel (rank 0's launch)
+            cpu, cpu_fair = time_cpu_baseline(inp, w)
+        del inp
+    torch.cuda.empty_cache()
+
+    def brief(r):
+        r.pop("_inp", None)
+        return {"workload": WORKLOADS[r["workload"]]["desc"], "global_batch": r["B"], "cent_dist": r["cent_dist"],
+                "ms_per_step": r["ms_per_step"], "value": r["value"], "unit": UNIT, "roofline": r["roofline"],
+                "e2e": r["e2e"], "clocks": r["clocks"], "timing": r["timing"]}
+
+    # ---- N=1: the other single-GPU BASELINE configs and the randn-centroid variant, in the same line, so that
+    # their numbers are driver-visible too (each is one more fused launch per step, timed exactly like the headline)
+    extra = None
+    if world == 1 and not args.no_extra and args.workload == "c2" and args.cent_dist == "rand":
+        extra = {}
+        xs = max(10, min(args.steps, 30))
+        for nm, cd in (("c3", "rand"), ("c4", "rand"), ("c2", "randn")):
+            r = bench_workload(args, nm, ctx, xs, args.warmup, cent_dist=cd)
+            extra[nm if cd == "rand" else f"{nm}_{cd}"] = dict(brief(r), steps=xs)
+            del r
+            torch.cuda.empty_cache()
+
+    # ---- N>1: STRONG scaling of BASELINE configs[3] (c4, B = 32 fixed, KV heads split over the ranks) next to the
+    # weak-scaling headline: rank 0 first times the whole problem alone, then all ranks time their shards
+    strong = None
+    if world > 1 and not args.no_extra and args.scaling == "weak" and WORKLOADS["c4"]["Nkv"] % world == 0:
+        xs = max(10, min(args.steps, 30))
+        n1 = None
+        if rank == 0:
+            r1 = bench_workload(args, "c4", solo, xs, args.warmup, do_e2e=False, sample_clocks=False)
+            n1 = r1["ms_per_step"]
+            del r1
+            torch.cuda.empty_cache()
+        dist.barrier()
+        rN = bench_workload(args, "c4", ctx, xs, args.warmup, scaling="strong", do_e2e=False, sample_clocks=False,
+                            verify=args.gather != "none")
+        if rank == 0:
+            rN.pop("_inp", None)
+            strong = {"workload": WORKLOADS["c4"]["desc"], "global_batch": rN["B"], "n_gpus": world, "steps": xs,
+                      "ms_per_step": rN["ms_per_step"], "n1_ms_per_step": n1, "speedup_vs_n1": n1 / rN["ms_per_step"],
+                      "efficiency": n1 / rN["ms_per_step"] / world, "value": rN["value"], "unit": UNIT,
+                      "roofline_frac_per_gpu": rN["roofline"]["frac"], "gather_verified": rN["gather_verified"],
+                      "tp_flag_exchange_us_per_step": rN["tp_flag_exchange_us_per_step"],
+                      "n1_measured": "rank 0 alone, same run, same kernel, whole c4 problem on one GPU"}
+        torch.cuda.empty_cache()
+
+    if rank == 0:
+        r = main_rec
+        peer = world > 1 and args.gather == "peer"
         line = {
-            "metric": METRIC, "value": tokens_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f16" if w["q"] == "f16" else "bf16",
             "data": "synthetic (seeded torch.rand/randint on device; block_table = random permutation of distinct pages)",
-            "config": {"workload": f"{args.workload}: {w['desc']}", "global_batch": B, "q_heads": w["Nq"],
+            "config": {"workload": f"{args.workload}: {w['desc']}", "global_batch": r["B"], "q_heads": w["Nq"],
                        "kv_heads": w["Nkv"], "head_dim": D, "seq_len": w["S"], "block_size": BS, "clusters": w["C"],
-                       "top_k": w["k"], "kv_dtype": w["kv"], "q_dtype": w["q"],
+                       "top_k": w["k"], "kv_dtype": w["kv"], "q_dtype": w["q"], "cent_dist": args.cent_dist,
                        "kv_layout": "[blocks,bs,Nkv,D]" if args.kv_layout == "bsnd" else "[blocks,Nkv,bs,D]",
                        "parallelism": (f"kv-head tp{world}, output all-gather " + ("fused into the launch (NVLink peer stores)" if peer else "by NCCL")) if world > 1 else "single gpu",
-                       "l2": ("flushed before every timed step (256 MiB write + 256 MiB read of a second buffer, so L2 holds clean lines); " if flush is not None else "not flushed; ") +
-                             f"per-step read set {ab['bytes_kv_union'] / 2**20:.0f} MiB > 126 MB L2" +
-                             ("; ranks aligned by a 1-element all-reduce before each timed step (outside the timed region)" if world > 1 and not args.no_align else ""),
-                       "launch": "cuda graph replay" if graph is not None else "FusedDecodePlan.launch()"},
-            "achieved_hbm_gbs_selected_kv": agg[1].item() / (ms_per_step * 1e-3) / 1e9,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC.get(args.workload) if world == 1 else None,
-                         "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch (profiles/r01_ncu_full_c2_summary.txt)" if world == 1 and args.workload in NCU_TRAFFIC else None,
-                         "peak_source": peak_src,
-                         "kernel": "spa_chain_kernel (fused: select + flash-decode + combine)",
-                         "bytes_alg_per_launch": ab["bytes_alg"], "bytes_kv_union": ab["bytes_kv_union"],
-                         "bytes_logical_per_q_head": ab["bytes_logical"], "bytes_dense": ab["bytes_dense"],
-                         "union_pages": ab["union_pages"], "selected_pages": ab["selected_pages"]},
-            "timing": {"min_ms": st[0], "median_ms": st[len(st) // 2], "p90_ms": st[int(len(st) * 0.9)],
-                       "max_ms": st[-1]},
-            "e2e": {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
-                    "api": "peer_gather.TPFusedDecode.launch" if peer else "custom_ops.sparse_paged_fusion_attention"},
-            "gpu_launches": launches_per_step * args.steps,
-            "tp_flag_exchange_us_per_step": xch_us,
-            "clocks": clocks,
+                       "l2": r["l2"], "launch": r["launch"]},
+            "achieved_hbm_gbs_selected_kv": r["achieved_hbm_gbs_selected_kv"],
+            "roofline": r["roofline"], "timing": r["timing"], "e2e": r["e2e"],
+            "gpu_launches": r["launches_per_step"] * args.steps,
+            "tp_flag_exchange_us_per_step": r["tp_flag_exchange_us_per_step"],
+            "clocks": r["clocks"], "kernel_src_sha": kernel_source_sha(),
         }
+        if world > 1:
+            line["gather_verified"] = r["gather_verified"]
         if cpu is not None:
             line["cpu_baseline"] = cpu
+            line["cpu_baseline_vectorised"] = cpu_fair
+        if extra is not None:
+            line["extra_workloads"] = extra
+        if strong is not None:
+            line["strong_c4"] = strong
         print(json.dumps(line), flush=True)
+    bad = world > 1 and rank == 0 and (main_rec["gather_verified"] is False or (strong and strong["gather_verified"] is False))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if bad:
+        raise SystemExit("gathered output differs from the NCCL gather / the oracle: run REJECTED")
     return 0
 
 
 def reference_arm(args, w):
-    """The reference's CPU implementation of the path (its torch golden for the selection + the CPU
-    restatement of the attention kernel), i.e. the oracle port, on this box's host cores."""
+    """The reference's CPU implementation of the path (its torch golden for the selection + the CPU restatement of
+    the attention kernel), i.e. the oracle port as the reference wrote it (Python loops), on this box's host cores,
+    on the b200 arm's config: the whole batch where the host copy of the pages stays modest (c1, c2), else a
+    bounded sample.  The reference's kernels are AscendC and cannot be built here."""
     dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    nseq = 1
+    nseq = cpu_nseq(w)
     # inputs: same generator as the b200 arm when a GPU is present, else a CPU-generated sample
     if dev.type == "cuda":
-        inp = make_inputs(w, w["B"], 0, 1, dev)
-        c = cpu_sample(inp, nseq)
+        inp = make_inputs(w, w["B"], 0, 1, dev, cent_dist=args.cent_dist)
     else:
         small = dict(w); small["B"] = nseq
-        inp = make_inputs(small, nseq, 0, 1, dev)
-        c = cpu_sample(inp, nseq)
-    for _ in range(min(args.warmup, 3)):
+        inp = make_inputs(small, nseq, 0, 1, dev, cent_dist=args.cent_dist)
+    c = cpu_sample(inp, nseq)
+    warm = min(args.warmup, 3)
+    for _ in range(warm):
         run_oracle(c, inp)
     steps = max(1, min(args.steps, 20))
     t0 = time.perf_counter()
@@ -542,14 +708,20 @@ def reference_arm(args, w):
         run_oracle(c, inp)
     dt = (time.perf_counter() - t0) / steps
     v = nseq / dt
-    sample = (f"each step = first {nseq} of {w['B']} sequences of the workload (all {w['Nq']} q heads); "
-              f"oracle/sparse_chain.py fused chain; torch threads={cores}")
+    t1 = time.perf_counter()
+    run_oracle(c, inp, fast=True)
+    vfast = nseq / (time.perf_counter() - t1)
+    sample = (f"each step = {'all' if nseq == w['B'] else 'the first'} {nseq} of {w['B']} sequences of the workload (all {w['Nq']} q heads); "
+              f"oracle/sparse_chain.py fused chain (reference golden as written); torch threads={cores}")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-            "warmup": min(args.warmup, 3), "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f16" if w["q"] == "f16" else "bf16",
             "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {w['desc']}", "sample": sample},
+            "config": {"workload": f"{args.workload}: {w['desc']}", "global_batch": nseq, "sample": sample,
+                       "cent_dist": args.cent_dist},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "cpu_baseline_vectorised": {"value": vfast, "unit": UNIT, "cores": cores, "kind": "port",
+                                        "sample": "same sequences, oracle/fast_chain.py (vectorised torch), one pass"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
     return 0

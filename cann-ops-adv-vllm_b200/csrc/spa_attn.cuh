@@ -26,9 +26,11 @@ constexpr int kMailSlots = 4;                           // flush -> post-warp me
 constexpr int kPostWarp = kConsumerWarps + 1;           // warp 8: TMA producer, warps 9..11: partial bookkeeping + combine
 
 struct AttnSmem {
-    int stages, mbuf, wml, meta, bars, mail, total;
+    int stages, mbuf, wml, meta, bars, mail, qst, total;
     __host__ __device__ static inline int align(int x, int a) { return (x + a - 1) / a * a; }
-    __host__ __device__ AttnSmem(int nstages, int stage_bytes, int nt_tiles) {
+    // one of the two query staging buffers: g rows of kQStageStride halves + the kv head's K antiquant scales
+    __host__ __device__ static inline int qstage_bytes(int g) { return g * kQStageStride * 2 + kD * 2; }
+    __host__ __device__ AttnSmem(int nstages, int stage_bytes, int nt_tiles, int g_staged) {
         int o = 0;
         stages = o;   o = align(o + nstages * stage_bytes, 1024);
         mbuf = o;     o = align(o + kConsumerWarps * kMergeWarpFloats * 4, 16);   // 8 heads x 64 dims per warp
@@ -36,6 +38,7 @@ struct AttnSmem {
         meta = o;     o = align(o + nstages * 16, 16);
         bars = o;     o = align(o + (nstages * 2 + kPostWarps * kMailSlots * 2) * 8, 16);
         mail = o;     o = align(o + kPostWarps * kMailSlots * 32, 16);
+        qst = o;      o = align(o + 2 * qstage_bytes(g_staged), 16);      // g_staged == 0: no staging
         total = o;
     }
 };
@@ -405,7 +408,8 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     for (int pp = 0; pp < PP; ++pp)
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) s[pp][nt][0] = s[pp][nt][1] = s[pp][nt][2] = s[pp][nt][3] = 0.f;
-    if (!KVI8) {
+    if (p.dbg_skip & 1) {
+    } else if (!KVI8) {
 #pragma unroll
         for (int k8 = 0; k8 < 8; ++k8) {
             const int chunk = (k8 & 3) * 2 + a_chk;
@@ -463,6 +467,12 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     uint32_t pb[PP][NT][2];                      // P^T as B fragments (after transpose)
     float alpha[NT][2];
     bool moved = false;
+    if (p.dbg_skip & 4) {
+#pragma unroll
+        for (int pp = 0; pp < PP; ++pp)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) { pb[pp][nt][0] = __float_as_uint(s[pp][nt][0]); pb[pp][nt][1] = __float_as_uint(s[pp][nt][1]); alpha[nt][0] = alpha[nt][1] = 1.f; }
+    } else
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
         float pr[PP][4];
@@ -530,7 +540,8 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     // ------------------------------ V: O^T += V^T P^T ------------------------------
 #pragma unroll
     for (int pp = 0; pp < PP; ++pp) mbar_wait(&full[vs[pp]], vph[pp]);
-    if (!KVI8) {
+    if (p.dbg_skip & 2) {
+    } else if (!KVI8) {
 #pragma unroll
         for (int mt = 0; mt < 8; ++mt) {
             const int chunk = (mt & 3) * 2 + v_chk;
@@ -579,7 +590,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
 template <typename QT, bool KVI8, int NT>
 __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, const CUtensorMap *tmV,
                                 unsigned char *smem, PubState *pub) {
-    AttnSmem L(p.nstages, p.stage_bytes, NT);
+    AttnSmem L(p.nstages, p.stage_bytes, NT, p.q_stage ? p.g : 0);
     unsigned char *stage_base = smem + L.stages;
     float *mbuf = reinterpret_cast<float *>(smem + L.mbuf);
     float *wml = reinterpret_cast<float *>(smem + L.wml);
@@ -623,6 +634,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         const int nown = pub->n_own;
         int oi = 0;
         int rf = 0, rn = 0, rpid = 0;                                      // current run: flat[rf, rf + rn), its partial id
+        bool rfirst = false;                                               // the next chunk handed out starts a run
         int nf = 0, claim_idx = 0;                                         // claim in flight (lane 0) / claimed index
         unsigned long long dv = 0ull;                                      // descriptor word of claim_idx as last loaded (lane 0)
         int cst = 0;                                                       // claim state: 0 none, 1 atomic in flight, 2 descriptor loading
@@ -643,9 +655,9 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         };
         // next chunk (<= 32 entries of one run) -> cf, cn, last (it ends its run).  Returns 1: got one, 0: the queue
         // is exhausted, -1 (only with block == false): the next run is not known yet -- issue what you have first
-        auto next_chunk = [&](int &cf, int &cn, int &cpid, bool &last, bool block) -> int {
+        auto next_chunk = [&](int &cf, int &cn, int &cpid, bool &rstart, bool &last, bool block) -> int {
             while (rn == 0) {
-                if (oi < nown) { rf = pub->own_item[oi] * p.qstride; rn = pub->own_len[oi]; rpid = 0; ++oi; ++t_runs; continue; }
+                if (oi < nown) { rf = pub->own_item[oi] * p.qstride; rn = pub->own_len[oi]; rpid = 0; rfirst = true; ++oi; ++t_runs; continue; }
                 if (!more) return 0;
                 if (!block) return -1;
                 if (cst == 0) { if (lane == 0) nf = atomicAdd(p.ctrl + Ctrl::kHead, 1); cst = 1; }
@@ -679,22 +691,31 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                 rf = (int)((d >> 48) & (kMaxItems - 1)) * p.qstride + (int)(unsigned)d;
                 rn = (int)((d >> 32) & 0xffffu);
                 rpid = 1 + claim_idx / p.items;
+                rfirst = true;
                 ++t_runs;
             }
-            cf = rf; cn = min(32, rn); cpid = rpid;
+            cf = rf; cn = min(32, rn); cpid = rpid; rstart = rfirst;
+            rfirst = false;
             rf += cn; rn -= cn;
             last = rn == 0;
             return 1;
         };
         int cf = 0, cn = 0, cpid = 0;
-        bool last = false;
-        int ok = next_chunk(cf, cn, cpid, last, true);
+        bool rstart = false, last = false;
+        int ok = next_chunk(cf, cn, cpid, rstart, last, true);
+        // query staging (lane 0): run r's rows go to buffer r & 1.  A buffer is free again once the first stage of
+        // the run that used it has been released by the consumers (they read the rows before they release it)
+        int qrun = 0, pg = 0;
+        int qstg0 = 0, qstg1 = 0, qpg0 = -(1 << 20), qpg1 = -(1 << 20);      // per buffer: first stage / page count of its last user
+        uint32_t qph0 = 0u, qph1 = 0u;
+        unsigned char *qst_base = smem + L.qst;
+        const int qst_bytes = AttnSmem::qstage_bytes(p.g);
         unsigned long long ent = (ok == 1 && lane < cn) ? ld_relaxed_u64(p.flat + cf + lane) : 0ull;
         while (ok == 1) {
             // entries of the following chunk travel while this chunk is issued
             int cf2 = 0, cn2 = 0, cpid2 = 0;
-            bool last2 = false;
-            int ok2 = next_chunk(cf2, cn2, cpid2, last2, false);
+            bool rstart2 = false, last2 = false;
+            int ok2 = next_chunk(cf2, cn2, cpid2, rstart2, last2, false);
             unsigned long long ent2 = (ok2 == 1 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
             if (lane < cn) ent = take_entry(p, cf + lane, ent);
             t_pages += cn;
@@ -710,8 +731,11 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     const unsigned hi = (unsigned)(e >> 32), lo = (unsigned)e;
                     const int ph = (int)(lo & 0xffffffu), item = (int)((hi >> 16) & (kMaxItems - 1));
                     const int n2 = item % p.Nkv;
-                    // stage header: head mask | tail flag << 16 | pair flag << 17, item, partial id of the run, tokens on a tail page
-                    const int4 md = make_int4((int)(hi & 0xffffu) | (int)(((hi >> 30) & 1u) << 16) | (first ? (1 << 17) : 0),
+                    // stage header: head mask | tail flag << 16 | pair flag << 17 | query buffer << 18, item, partial id
+                    // of the run, tokens on a tail page
+                    const bool stage_q = p.q_stage && rstart && j == 0;
+                    const int qi = qrun & 1;
+                    const int4 md = make_int4((int)(hi & 0xffffu) | (int)(((hi >> 30) & 1u) << 16) | (first ? (1 << 17) : 0) | (qi << 18),
                                               item, cpid, (int)((lo >> 24) & 0x7fu) + 1);
                     int c[4];
                     c[1] = (p.ax_head == 1) ? n2 : (p.ax_blk == 1 ? ph : 0);
@@ -721,7 +745,15 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     for (int kv = 0; kv < 2; ++kv) {
                         mbar_wait(&empty[stage], phase ^ 1u);
                         metaS[stage] = md;
-                        mbar_expect_tx(&full[stage], (uint32_t)p.stage_bytes);
+                        uint32_t tx = (uint32_t)p.stage_bytes;
+                        const bool with_q = stage_q && kv == 0;
+                        const bool with_s = with_q && KVI8 && !p.aq_per_tensor;
+                        if (with_q) {
+                            // the rows of this run travel with its first K page and complete on the same barrier
+                            if (2 * (pg - (qi ? qpg1 : qpg0)) <= nstages) mbar_wait(&empty[qi ? qstg1 : qstg0], qi ? qph1 : qph0);
+                            tx += (uint32_t)(p.g * kD * 2) + (with_s ? (uint32_t)(kD * 2) : 0u);
+                        }
+                        mbar_expect_tx(&full[stage], tx);
                         unsigned char *dst = stage_base + (size_t)stage * p.stage_bytes;
                         const CUtensorMap *tm = kv ? tmV : tmK;
                         if (KVI8) {
@@ -730,16 +762,29 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                             tma_load_4d(dst, tm, &full[stage], 0, c[1], c[2], c[3]);
                             tma_load_4d(dst + p.stage_bytes / 2, tm, &full[stage], 64, c[1], c[2], c[3]);
                         }
+                        if (with_q) {
+                            unsigned char *qd = qst_base + (size_t)qi * qst_bytes;
+                            const unsigned short *qrow = reinterpret_cast<const unsigned short *>(p.q) + (size_t)(item / p.Nkv) * p.q_sb +
+                                                         (size_t)(n2 * p.g) * p.q_sh;
+                            for (int h = 0; h < p.g; ++h)
+                                bulk_load(qd + (size_t)h * kQStageStride * 2, qrow + (size_t)h * p.q_sh, kD * 2, &full[stage]);
+                            if (with_s)
+                                bulk_load(qd + (size_t)p.g * kQStageStride * 2,
+                                          reinterpret_cast<const unsigned short *>(p.aq_scale) + (size_t)n2 * kD, kD * 2, &full[stage]);
+                            if (qi) { qstg1 = stage; qph1 = phase; qpg1 = pg; } else { qstg0 = stage; qph0 = phase; qpg0 = pg; }
+                            ++qrun;
+                        }
                         if (++stage == nstages) { stage = 0; phase ^= 1u; }
                     }
+                    ++pg;
                 }
             }
             __syncwarp();
             if (ok2 < 0) {
-                ok2 = next_chunk(cf2, cn2, cpid2, last2, true);
+                ok2 = next_chunk(cf2, cn2, cpid2, rstart2, last2, true);
                 ent2 = (ok2 == 1 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
             }
-            ok = ok2; cf = cf2; cn = cn2; cpid = cpid2; last = last2; ent = ent2;
+            ok = ok2; cf = cf2; cn = cn2; cpid = cpid2; rstart = rstart2; last = last2; ent = ent2;
         }
         if (lane == 0 && cst == 1) pub->priv_used = nf;  // a claim in flight has landed before this CTA reports "finished"
         if (lane == 0) { unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid)); trace_put(p, 12, smid); }
@@ -786,11 +831,23 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             cur = md.y; cnt = 0; pid = md.z;
             rec = ld_relaxed_u64(p.item_info + cur);             // first used at the flush
             const int b = cur / p.Nkv, n2 = cur % p.Nkv;
+            // The item's query rows (and K scales): staged in shared memory by the producer together with this
+            // run's first K page (the stage barrier just passed covers them), else read from global memory --
+            // a round trip of microseconds under a saturated HBM, per segment and warp (ncu, c3: 23 % of all
+            // stall samples sat on these loads before the staging).
+            const unsigned short *qbase = qg + (size_t)b * p.q_sb + (size_t)(n2 * p.g) * p.q_sh;
+            size_t qstride = (size_t)p.q_sh;
+            const unsigned short *sk_staged = nullptr;
+            if (p.q_stage) {
+                qbase = reinterpret_cast<const unsigned short *>(smem + L.qst + (size_t)((md.x >> 18) & 1) * AttnSmem::qstage_bytes(p.g));
+                qstride = kQStageStride;
+                sk_staged = qbase + (size_t)p.g * kQStageStride;
+            }
             // ---- Q fragments (B operand of S^T = K Q^T): b0 = Q[head][d0,d0+1], b1 = Q[head][d0+8,+9]
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
                 const int h = nt * 8 + gid;
-                const unsigned short *qrow = qg + (size_t)b * p.q_sb + (size_t)(n2 * p.g + h) * p.q_sh;
+                const unsigned short *qrow = qbase + (size_t)h * qstride;
                 if (!KVI8) {
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks) {
@@ -810,8 +867,8 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     // (:2146-2155).  q*scale_k is brought to [1, 2) per head by a power of two (exact), then split
                     // into two int8 digits (split_digits: 2^-16 of the head's range, finer than the fp16 rounding
                     // of the non-quantised path); the factor returns to the logits in fp32 (hsc).
-                    const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) +
-                                               (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
+                    const unsigned short *sk = (sk_staged != nullptr && !p.aq_per_tensor) ? sk_staged
+                                               : reinterpret_cast<const unsigned short *>(p.aq_scale) + (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
                     auto qs4 = [&](int ks, float (&f)[4]) {
                         const int d0 = ks * 16 + tig * 4;
                         const uint2 qv = *reinterpret_cast<const uint2 *>(qrow + d0);

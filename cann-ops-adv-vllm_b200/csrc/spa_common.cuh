@@ -92,11 +92,14 @@ struct ChainParams {
     int claim_lead;                                      // a chunk is claimed when the current run has this many pages left to issue
     int small_pages;                                     // a CTA keeps its own items whole while they add up to <= this many pages (0 = off)
     int pair_pages;                                      // consumers take two pages of an item per step (needs >= 4 stages)
+    int q_stage;                                         // the producer stages each run's query rows (and K scales) in shared memory
     // ---- optional phase trace: [gridDim.x, kTraceSlots] globaltimer ns (null = off)
     unsigned long long *trace;
     int dbg;                                             // trace-only experiments (env SPA_DBG_REPEAT)
+    int dbg_skip;                                        // diagnostics (env SPA_DBG_SKIP): 1 skip the K matmul, 2 the V matmul, 4 the softmax -- WRONG RESULTS
 };
 constexpr int kTraceSlots = 32;
+constexpr int kQStageStride = kD + 8;                    // halves per staged query row: +16 B keeps the 8 rows of a fragment load on distinct banks
 
 enum Mode : int {
     kModeFused = 0,        // scores + topk + select + attention
@@ -267,6 +270,12 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, u
         " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
         "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+// 1-D bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP); 16-byte aligned, size multiple of 16
+__device__ __forceinline__ void bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
 }
 // 4-byte asynchronous global -> shared copy (SASS: LDGSTS): gathers that must not hold registers
 __device__ __forceinline__ void cp_async_4(void *dst, const void *src) {

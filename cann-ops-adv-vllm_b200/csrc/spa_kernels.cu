@@ -898,14 +898,20 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     if (p.num_blocks > kMaxBlocks) return fail(SPA_ERR_UNSUPPORTED, "more than %d KV blocks", kMaxBlocks);
     p.stage_bytes = e->kv_i8 ? 16384 : 32768;
     const int budget = d.smem_optin - 1024 - 512;     // 1 KiB alignment slack + the kernels' static shared memory
+    // the producer stages every run's query rows (and the K scales) in shared memory ahead of the consumers
+    // (bulk copies: 16-byte aligned rows); otherwise the consumers read them from global memory per segment
+    p.q_stage = (reinterpret_cast<uintptr_t>(p.q) % 16 == 0) && p.q_sb % 8 == 0 && p.q_sh % 8 == 0 &&
+                (!e->kv_i8 || p.aq_per_tensor || reinterpret_cast<uintptr_t>(p.aq_scale) % 16 == 0);
+    if (const char *s = getenv("SPA_Q_STAGE")) p.q_stage = p.q_stage && atoi(s) != 0;
+    if (const char *s = getenv("SPA_DBG_SKIP")) p.dbg_skip = atoi(s);      // bound-finding experiments only: results are wrong
     int nst = e->kv_i8 ? 12 : 6;
     for (; nst >= 2; --nst)
-        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles).total <= budget) break;
+        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.q_stage ? p.g : 0).total <= budget) break;
     if (nst < 2) return fail(SPA_ERR_UNSUPPORTED, "attention working set exceeds shared memory");
     p.nstages = nst;
     p.pair_pages = nst >= 4;
     if (const char *s = getenv("SPA_PAIR")) p.pair_pages = p.pair_pages && atoi(s) != 0;
-    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles).total;
+    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.q_stage ? p.g : 0).total;
     int sel_bytes = p.maxP * 4;
     if (p.mode == kModeFused) {
         if ((rc = plan_select_smem(&p, kSelScores | kSelSelect | kSelUnion, d.sms, budget - 1024, &sel_bytes))) return rc;

@@ -60,7 +60,8 @@ struct HeadRec {
     unsigned kmin, kmax;                 // key range of the approximate scores
     int ncand;                           // candidates collected
     float l1;                            // ||q_h||_1
-    float lo_val, hi_val, band;          // edges of the bin of the k-th largest, 2*eps
+    float lo, inv, band;                 // histogram: bin(x) = floor(x * inv + lo) (lo = -min * inv); 2*eps
+    int bstar;                           // bin of the k-th largest approximate score
     int total;                           // selected pages (compaction)
 };
 
@@ -329,22 +330,31 @@ __device__ __noinline__ void exact_scores(const CentSrc cent_rows, const unsigne
 }
 
 // ---- TopK, step 1 (group): histogram of the order-preserving keys of every head ----------------
-__device__ __forceinline__ int key_shift(unsigned kmin, unsigned kmax) {
-    const int bits = 32 - __clz(kmax - kmin);                     // kmax - kmin < 2^bits
-    return max(0, bits - 10);                                     // 10 = log2(kSelBins)
+// Histogram bins are LINEAR in the score: bin(x) = floor((x - lo) * inv) with lo = the head's smallest score and
+// inv = bins / range.  (Bins cut in the bit space of the float keys are very uneven when the scores straddle
+// zero -- zero-mean centroids, fused_ifa_v5_case.py:55 -- and left ~50 candidates per head in the bin of the k-th
+// score: c2 with randn centroids ran 12 us behind rand.)  sel_bin() is monotone non-decreasing in x, which is all
+// the classification needs: bin(x) > bin(y) implies x > y.  Below the range: negative.
+// (one FMA -- a single rounding, hence monotone -- and a floor conversion; c0 = -lo * inv)
+__device__ __forceinline__ int sel_bin(float x, float c0, float inv) {
+    return min(kSelBins - 1, __float2int_rd(fmaf(x, inv, c0)));
+}
+__device__ __forceinline__ void sel_bin_scale(unsigned kmin, unsigned kmax, float &c0, float &inv) {
+    const float lo = key_float(kmin);
+    const float range = key_float(kmax) - lo;
+    inv = (range > 0.f && range < INFINITY) ? (float)kSelBins / range : 0.f;
+    c0 = -lo * inv;
 }
 __device__ __forceinline__ void topk_hist(const ChainParams &p, const float *sc, int scs, unsigned *hist,
                                           const HeadRec *hd, const Grp &G) {
     // four heads per pass: four independent load -> key -> atomic chains per thread
 #pragma unroll 1
     for (int h0 = 0; h0 < p.g; h0 += 4) {
-        unsigned lo[4];
-        int shift[4];
+        float lo[4], inv[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int h = min(h0 + u, p.g - 1);
-            lo[u] = hd[h].kmin;
-            shift[u] = key_shift(lo[u], hd[h].kmax);
+            sel_bin_scale(hd[h].kmin, hd[h].kmax, lo[u], inv[u]);
         }
         const int nh = min(4, p.g - h0);
 #pragma unroll 2
@@ -354,7 +364,7 @@ __device__ __forceinline__ void topk_hist(const ChainParams &p, const float *sc,
             for (int u = 0; u < 4; ++u) a[u] = sc[min(h0 + u, p.g - 1) * scs + c];
 #pragma unroll
             for (int u = 0; u < 4; ++u)
-                if (u < nh) atomicAdd(&hist[(h0 + u) * kSelBins + ((float_key(a[u]) - lo[u]) >> shift[u])], 1u);
+                if (u < nh) atomicAdd(&hist[(h0 + u) * kSelBins + max(0, sel_bin(a[u], lo[u], inv[u]))], 1u);
         }
     }
 }
@@ -389,12 +399,8 @@ __device__ __forceinline__ void topk_bin(const ChainParams &p, const unsigned *h
     const int lb = 31 - __clz(__ballot_sync(0xffffffffu, above_blk + suf2 >= k));
     const int bstar = ls * 32 + lb;
     if (lane == 0) {
-        const unsigned lo = r->kmin;
-        const int shift = key_shift(lo, r->kmax);
-        const unsigned long long lo_key = (unsigned long long)lo + ((unsigned long long)bstar << shift);
-        const unsigned long long hi_key = lo_key + (1ull << shift);
-        r->lo_val = key_float((uint32_t)lo_key);
-        r->hi_val = (hi_key >= 0xFF800000ull) ? INFINITY : key_float((uint32_t)hi_key);
+        sel_bin_scale(r->kmin, r->kmax, r->lo, r->inv);
+        r->bstar = bstar;
         r->band = ldexpf(r->l1 * maxabs, -15) * 1.0625f;                   // 2 * eps
     }
 }
@@ -408,11 +414,12 @@ __device__ __forceinline__ void topk_classify(const ChainParams &p, const float 
     // one bitmap word per head: ballots, no per-lane atomics.
 #pragma unroll 1
     for (int h0 = 0; h0 < p.g; h0 += 4) {
-        float lo_val[4], hi_val[4], band[4];
+        float lo[4], inv[4], band[4];
+        int bstar[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int h = min(h0 + u, p.g - 1);
-            lo_val[u] = hd[h].lo_val; hi_val[u] = hd[h].hi_val; band[u] = hd[h].band;
+            lo[u] = hd[h].lo; inv[u] = hd[h].inv; band[u] = hd[h].band; bstar[u] = hd[h].bstar;
         }
         const int nh = min(4, p.g - h0);
 #pragma unroll 1
@@ -423,8 +430,10 @@ __device__ __forceinline__ void topk_classify(const ChainParams &p, const float 
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const float a = (c < p.C) ? sc[min(h0 + u, p.g - 1) * scs + c] : -INFINITY;
-                const bool in = (c < p.C) && (a - band[u] >= hi_val[u]);
-                cd[u] = (c < p.C) && !in && (a + band[u] >= lo_val[u]);
+                // above every score of the k-th score's bin even after the error band: certainly selected;
+                // able to reach that bin: candidate
+                const bool in = (c < p.C) && sel_bin(a - band[u], lo[u], inv[u]) > bstar[u];
+                cd[u] = (c < p.C) && !in && sel_bin(a + band[u], lo[u], inv[u]) >= bstar[u];
                 bin[u] = __ballot_sync(0xffffffffu, in);
                 bcd[u] = __ballot_sync(0xffffffffu, cd[u]);
             }

@@ -16,7 +16,7 @@ def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "c2"
     w = bench.WORKLOADS[name]
     dev = torch.device("cuda", 0)
-    inp = bench.make_inputs(w, w["B"], 0, 1, dev)
+    inp = bench.make_inputs(w, w["B"], 0, 1, dev, cent_dist=os.environ.get("CENT_DIST", "rand"))
     B, nq, nkv = inp["B"], inp["Nq"], inp["Nkv"]
     bp = torch.empty(B, nq, inp["MP"], dtype=torch.int32, device=dev)
     ppl = torch.empty(B, nq, 8, dtype=torch.int32, device=dev)

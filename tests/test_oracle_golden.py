@@ -132,3 +132,24 @@ def test_assign_page_clusters_oracle_agrees_with_plain_float64():
         assert torch.allclose(mean[i].double(), pooled / nt, rtol=1e-5, atol=1e-6)
     untouched = [p for p in range(blocks) if p not in ids.tolist()]
     assert bool((out[:, untouched] == -7).all())
+
+
+@pytest.mark.parametrize("int8", [False, True])
+def test_vectorised_cpu_baseline_agrees_with_the_loop_oracle(int8):
+    """oracle/fast_chain.py (the "fair CPU" baseline bench.py reports beside the loop port) computes the same
+    chain: selection identical (tie-free seeded case), attention within the oracle-vs-kernel tolerance."""
+    from cases import make_case
+    from oracle import fast_chain
+    qd = torch.bfloat16 if int8 else torch.float16
+    c = make_case(99, 3, 16, 4, 64, 3000, kv_pages=40, ragged=True, qdtype=qd, kv_int8=int8)
+    c["seq"][2] = 0
+    want = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"],
+                                            c["seq"], 16, c["scale"], 4, 128, 8, 256,
+                                            c["aq_scale"] if int8 else None, c["aq_offset"] if int8 else None)
+    got = fast_chain.fused_chain(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"], c["seq"],
+                                 16, c["scale"], 4, 128, 8, 256, c["aq_scale"] if int8 else None,
+                                 c["aq_offset"] if int8 else None)
+    assert torch.equal(got[1], want[1]) and torch.equal(got[2], want[2]) and torch.equal(got[3], want[3])
+    tol = 2e-2 if int8 else 1e-3
+    err = (got[0].float() - want[0].float()).abs()
+    assert bool((err <= tol + tol * want[0].float().abs()).all()), err.max().item()
