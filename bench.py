@@ -315,14 +315,15 @@ def time_cpu_baseline(inp, w, budget_s=12.0):
 
 # ------------------------------------------------------------------------------------------------
 def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="rand", do_e2e=True, verify=False,
-                   sample_clocks=True):
+                   sample_clocks=True, kv_layout=None):
     """Time `steps` fused decode steps of workload `name` on the ranks of ctx (device-resident, then end to end).
     Returns the measurement record on rank 0 of ctx, None elsewhere."""
     import custom_ops
     rank, world, dev, dist = ctx["rank"], ctx["world"], ctx["dev"], ctx["dist"]
     w = WORKLOADS[name]
     B = w["B"] * world if scaling == "weak" else w["B"]
-    inp = make_inputs(w, B, rank, world, dev, kv_layout=args.kv_layout, cent_dist=cent_dist)
+    kv_layout = kv_layout or args.kv_layout
+    inp = make_inputs(w, B, rank, world, dev, kv_layout=kv_layout, cent_dist=cent_dist)
     nq, nkv, qd = inp["Nq"], inp["Nkv"], inp["qd"]
     bp = torch.empty(B, nq, inp["MP"], dtype=torch.int32, device=dev)
     ppl = torch.empty(B, nq, 8, dtype=torch.int32, device=dev)
@@ -528,6 +529,7 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
             "timing": {"min_ms": st[0], "median_ms": st[len(st) // 2], "p90_ms": st[int(len(st) * 0.9)], "max_ms": st[-1]},
             "e2e": e2e, "launches_per_step": plan.num_launches, "tp_flag_exchange_us_per_step": xch_us,
             "clocks": clocks, "gather_verified": gather_verified, "cent_dist": cent_dist,
+            "kv_layout": "[blocks,bs,Nkv,D]" if kv_layout == "bsnd" else "[blocks,Nkv,bs,D]",
             "l2": ("flushed before every timed step (256 MiB write + 256 MiB read of a second buffer, so L2 holds clean lines); " if flush is not None else "not flushed; ") +
                   f"per-step read set {ab['bytes_kv_union'] / 2**20:.0f} MiB > 126 MB L2" +
                   ("; ranks aligned by a 1-element all-reduce before each timed step (outside the timed region)" if world > 1 and not args.no_align else ""),
@@ -605,6 +607,7 @@ def main():
     def brief(r):
         r.pop("_inp", None)
         return {"workload": WORKLOADS[r["workload"]]["desc"], "global_batch": r["B"], "cent_dist": r["cent_dist"],
+                "kv_layout": r["kv_layout"],
                 "ms_per_step": r["ms_per_step"], "value": r["value"], "unit": UNIT, "roofline": r["roofline"],
                 "e2e": r["e2e"], "clocks": r["clocks"], "timing": r["timing"]}
 
@@ -614,9 +617,10 @@ def main():
     if world == 1 and not args.no_extra and args.workload == "c2" and args.cent_dist == "rand":
         extra = {}
         xs = max(10, min(args.steps, 30))
-        for nm, cd in (("c3", "rand"), ("c4", "rand"), ("c2", "randn")):
-            r = bench_workload(args, nm, ctx, xs, args.warmup, cent_dist=cd)
-            extra[nm if cd == "rand" else f"{nm}_{cd}"] = dict(brief(r), steps=xs)
+        # (c3_bnsd: int8 KV with contiguous page-head slices -- in the vLLM layout an int8 row is 128 B at a 1 KiB stride)
+        for nm, cd, lay in (("c3", "rand", None), ("c4", "rand", None), ("c2", "randn", None), ("c3", "rand", "bnsd")):
+            r = bench_workload(args, nm, ctx, xs, args.warmup, cent_dist=cd, kv_layout=lay)
+            extra[nm + ("" if cd == "rand" else f"_{cd}") + (f"_{lay}" if lay else "")] = dict(brief(r), steps=xs)
             del r
             torch.cuda.empty_cache()
 

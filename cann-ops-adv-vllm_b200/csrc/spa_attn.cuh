@@ -408,8 +408,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     for (int pp = 0; pp < PP; ++pp)
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) s[pp][nt][0] = s[pp][nt][1] = s[pp][nt][2] = s[pp][nt][3] = 0.f;
-    if (p.dbg_skip & 1) {
-    } else if (!KVI8) {
+    if (!KVI8) {
 #pragma unroll
         for (int k8 = 0; k8 < 8; ++k8) {
             const int chunk = (k8 & 3) * 2 + a_chk;
@@ -467,12 +466,6 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     uint32_t pb[PP][NT][2];                      // P^T as B fragments (after transpose)
     float alpha[NT][2];
     bool moved = false;
-    if (p.dbg_skip & 4) {
-#pragma unroll
-        for (int pp = 0; pp < PP; ++pp)
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) { pb[pp][nt][0] = __float_as_uint(s[pp][nt][0]); pb[pp][nt][1] = __float_as_uint(s[pp][nt][1]); alpha[nt][0] = alpha[nt][1] = 1.f; }
-    } else
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
         float pr[PP][4];
@@ -540,8 +533,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     // ------------------------------ V: O^T += V^T P^T ------------------------------
 #pragma unroll
     for (int pp = 0; pp < PP; ++pp) mbar_wait(&full[vs[pp]], vph[pp]);
-    if (p.dbg_skip & 2) {
-    } else if (!KVI8) {
+    if (!KVI8) {
 #pragma unroll
         for (int mt = 0; mt < 8; ++mt) {
             const int chunk = (mt & 3) * 2 + v_chk;
@@ -590,7 +582,10 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
 template <typename QT, bool KVI8, int NT>
 __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, const CUtensorMap *tmV,
                                 unsigned char *smem, PubState *pub) {
-    AttnSmem L(p.nstages, p.stage_bytes, NT, p.q_stage ? p.g : 0);
+    // query staging is compiled into the int8 kernels only: the fp16 stream gains nothing from it (its pages are
+    // twice as long) and the extra live state cost the fp16 kernels 1-2 us (same-box A/B, c2 / c4)
+    const bool q_stage = KVI8 && p.q_stage;
+    AttnSmem L(p.nstages, p.stage_bytes, NT, q_stage ? p.g : 0);
     unsigned char *stage_base = smem + L.stages;
     float *mbuf = reinterpret_cast<float *>(smem + L.mbuf);
     float *wml = reinterpret_cast<float *>(smem + L.wml);
@@ -605,6 +600,15 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     const int nstages = p.nstages;
 
     __syncthreads();                                  // phase A of every warp group is done with the shared memory
+    if (p.bs < kBS) {
+        // pages shorter than the 128-row stage image (block_size 16 / 32 / 64): TMA fills the first bs rows of a
+        // stage, the other rows are never written again -- zero them once, so that the matmuls meet finite values
+        // there (their tokens are masked, but 0 x NaN would poison the P.V sums)
+        uint4 *z = reinterpret_cast<uint4 *>(stage_base);
+        for (int i = tid; i < nstages * p.stage_bytes / 16; i += blockDim.x) z[i] = make_uint4(0u, 0u, 0u, 0u);
+        fence_proxy_async();
+        __syncthreads();
+    }
     if (tid == 0) {
         for (int s = 0; s < nstages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kConsumerWarps); }
         for (int s = 0; s < kPostWarps * kMailSlots; ++s) { mbar_init(&mfull[s], 1); mbar_init(&mempty[s], 1); }
@@ -733,7 +737,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     const int n2 = item % p.Nkv;
                     // stage header: head mask | tail flag << 16 | pair flag << 17 | query buffer << 18, item, partial id
                     // of the run, tokens on a tail page
-                    const bool stage_q = p.q_stage && rstart && j == 0;
+                    const bool stage_q = q_stage && rstart && j == 0;
                     const int qi = qrun & 1;
                     const int4 md = make_int4((int)(hi & 0xffffu) | (int)(((hi >> 30) & 1u) << 16) | (first ? (1 << 17) : 0) | (qi << 18),
                                               item, cpid, (int)((lo >> 24) & 0x7fu) + 1);
@@ -745,7 +749,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     for (int kv = 0; kv < 2; ++kv) {
                         mbar_wait(&empty[stage], phase ^ 1u);
                         metaS[stage] = md;
-                        uint32_t tx = (uint32_t)p.stage_bytes;
+                        uint32_t tx = (uint32_t)p.page_tx;
                         const bool with_q = stage_q && kv == 0;
                         const bool with_s = with_q && KVI8 && !p.aq_per_tensor;
                         if (with_q) {
@@ -838,7 +842,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             const unsigned short *qbase = qg + (size_t)b * p.q_sb + (size_t)(n2 * p.g) * p.q_sh;
             size_t qstride = (size_t)p.q_sh;
             const unsigned short *sk_staged = nullptr;
-            if (p.q_stage) {
+            if (q_stage) {
                 qbase = reinterpret_cast<const unsigned short *>(smem + L.qst + (size_t)((md.x >> 18) & 1) * AttnSmem::qstage_bytes(p.g));
                 qstride = kQStageStride;
                 sk_staged = qbase + (size_t)p.g * kQStageStride;
@@ -942,7 +946,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             mbar_wait(&full[st[2]], ph[2]);
             const int4 md1 = metaS[st[2]];
             const unsigned metas[2] = {meta, (unsigned)md1.x & 0xffffu};
-            const int tails[2] = {tail_page ? tail_cnt : kBS, ((md1.x >> 16) & 1) ? md1.w : kBS};
+            const int tails[2] = {tail_page ? tail_cnt : p.bs, ((md1.x >> 16) & 1) ? md1.w : p.bs};
             const int ks[2] = {st[0], st[2]}, vs[2] = {st[1], st[3]};
             const uint32_t vph[2] = {ph[1], ph[3]};
             cnt += 2;
@@ -953,7 +957,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             int st1 = stage + 1; uint32_t ph1 = phase;
             if (st1 == nstages) { st1 = 0; ph1 ^= 1u; }
             const unsigned metas[1] = {meta};
-            const int tails[1] = {tail_page ? tail_cnt : kBS};
+            const int tails[1] = {tail_page ? tail_cnt : p.bs};
             const int ks[1] = {stage}, vs[1] = {st1};
             const uint32_t vph[1] = {ph1};
             cnt += 1;

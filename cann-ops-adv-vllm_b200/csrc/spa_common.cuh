@@ -31,7 +31,7 @@ struct ChainParams {
     int MP;                          // max_page_num = page_position.shape[2]
     int maxP;                        // block_table.shape[1]
     int kvPageLen;                   // block_ids.shape[1]
-    int bs;                          // block size (tokens per page) == kBS
+    int bs;                          // block size (tokens per page): 128, or 16 / 32 / 64 (a stage then holds a partly filled image)
     int items;                       // B * Nkv work items (b, kv head)
     // ---- selection inputs
     const void *q;       long long q_sb, q_sh;          // element strides (batch, head); D contiguous
@@ -83,7 +83,8 @@ struct ChainParams {
     int sel_group_bytes;                                 // smem bytes of one selection group
     int sel_ns;                                          // centroid-tile stages per selection group
     int nstages;                                         // pipeline stages
-    int stage_bytes;
+    int stage_bytes;                                     // ring stride: one 128-row K or V image
+    int page_tx;                                         // bytes TMA delivers per K or V page: bs * D * sizeof(kv)
     int smem_bytes;
     int mode;                                            // see Mode
     int static_pct;                                      // share of a CTA's fair share it keeps of its OWN items (streamed first), percent
@@ -96,7 +97,6 @@ struct ChainParams {
     // ---- optional phase trace: [gridDim.x, kTraceSlots] globaltimer ns (null = off)
     unsigned long long *trace;
     int dbg;                                             // trace-only experiments (env SPA_DBG_REPEAT)
-    int dbg_skip;                                        // diagnostics (env SPA_DBG_SKIP): 1 skip the K matmul, 2 the V matmul, 4 the softmax -- WRONG RESULTS
 };
 constexpr int kTraceSlots = 32;
 constexpr int kQStageStride = kD + 8;                    // halves per staged query row: +16 B keeps the 8 rows of a fragment load on distinct banks

@@ -678,7 +678,7 @@ __device__ __noinline__ int warp_emit_union(const ChainParams &p, int item, cons
         if (m != 0u && (unsigned)phys[i] >= (unsigned)p.num_blocks) m = 0u;      // block id outside the pool: skipped
         const unsigned mt = (m >> 16) & m & 0xffffu, mf = m & 0xffffu & ~mt;
         const unsigned bf = __ballot_sync(0xffffffffu, mf != 0u), bt = __ballot_sync(0xffffffffu, mt != 0u);
-        if (mf) st_relaxed_u64(q + base + __popc(bf & lt), queue_entry(phys[i], mf, false, item, kBS));
+        if (mf) st_relaxed_u64(q + base + __popc(bf & lt), queue_entry(phys[i], mf, false, item, p.bs));
         if (mt) st_relaxed_u64(q + base + __popc(bf) + __popc(bt & lt), queue_entry(phys[i], mt, true, item, max(1, tail_cnt)));
         base += __popc(bf) + __popc(bt);
     }

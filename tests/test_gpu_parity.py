@@ -233,13 +233,17 @@ def build_kat(num_heads, block_size, total_kv, sel_tokens, layout, batch=1, head
     return q, key, value, bt, bp, asl, expect
 
 
-@pytest.mark.parametrize("layout,delta", [("vllm", 0.0), ("vllm", 0.001), ("bnsd", 0.001)])
-def test_attention_known_answer(ops, layout, delta):
+@pytest.mark.parametrize("layout,delta,bs,sel", [("vllm", 0.0, 128, 10 * 1024), ("vllm", 0.001, 128, 10 * 1024),
+                                                 ("bnsd", 0.001, 128, 10 * 1024),
+                                                 # tests/ifa_v5_case.py:12-191 as written: BNSD-paged pool, block 16, 256 pages per head
+                                                 ("bnsd", 0.0, 16, 4 * 1024), ("bnsd", 0.001, 16, 4 * 1024)])
+def test_attention_known_answer(ops, layout, delta, bs, sel):
     H = 32
-    q, key, value, bt, bp, asl, expect = build_kat(H, 128, 32 * 1024, 10 * 1024, layout, head_delta=delta)
+    q, key, value, bt, bp, asl, expect = build_kat(H, bs, 32 * 1024, sel, layout, head_delta=delta)
     e = torch.empty(0, device=DEV)
+    scale = np.float32(1.0) if bs == 128 else np.float32(1.0 / np.sqrt(128.0))      # :41 / ifa_v5_case.py:730
     out = ops.sparse_paged_attention(q.to(DEV), key.to(DEV), value.to(DEV), e, e, asl.to(DEV), e, e, e, e, e, e, e,
-                                     bt.to(DEV), e, bp.to(DEV), H, np.float32(1.0), "BNSD", H, 128, 1)
+                                     bt.to(DEV), e, bp.to(DEV), H, scale, "BNSD", H, bs, 1)
     out = out.cpu()
     assert out.shape == q.shape and out.dtype == torch.float16
     assert not ((out.float() - 9.9).abs() < 1.0).any()            # ifa_v5_case.py:176-178 pass criterion
@@ -392,7 +396,7 @@ def test_unsupported_arguments_raise(ops):
     with pytest.raises(RuntimeError, match="num_heads"):
         call(heads=16)
     with pytest.raises(RuntimeError, match="block_size"):
-        call(bs=64)
+        call(bs=48)
     with pytest.raises(RuntimeError, match="CUDA"):
         ops.compute_cent(c["q"], c["l1"])
     with pytest.raises(RuntimeError, match="exceeds cluster count"):
@@ -923,3 +927,29 @@ print("OK ms_behind_holder=%.1f" % ev0.elapsed_time(ev1))
                        timeout=240)
     assert r.returncode == 0 and "OK" in r.stdout, f"SPA_COOP={coop}: rc={r.returncode}\n{r.stdout[-2000:]}\n{r.stderr[-3000:]}"
     print(f"SPA_COOP={coop}: {r.stdout.strip().splitlines()[-1]}")
+
+
+@pytest.mark.parametrize("bs", [16, 32, 64])
+@pytest.mark.parametrize("int8", [False, True])
+def test_block_sizes_below_128(ops, bs, int8):
+    """block_size 16 / 32 / 64 (the reference's sweep script varies it, sparse_paged_fusion_attention/op_eval/run.sh:26-48):
+    fused op and the separate chain against the oracle, ragged contexts (partial last page)."""
+    B, Nq, Nkv, C, S, k = 3, 16, 4, 64, 40 * bs + 5, 8
+    qd = torch.bfloat16 if int8 else torch.float16
+    tol = 2e-2 if int8 else 1e-3
+    c = make_case(4000 + bs, B, Nq, Nkv, C, S, kv_pages=3 * 48 + 7, bs=bs, ragged=True, permute_table=True, qdtype=qd,
+                  kv_int8=int8)
+    g = to_device(c, DEV)
+    aq = (c["aq_scale"], c["aq_offset"]) if int8 else (None, None)
+    want = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"],
+                                            c["seq"], Nq, c["scale"], Nkv, bs, k, 256, *aq)
+    out, bp, ppl, mppl, _ = fused_call(ops, g, k)
+    assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2]) and torch.equal(mppl.cpu(), want[3])
+    assert_close(out, want[0], tol, f"fused, block_size {bs}")
+    pp, ppl2, mppl2 = ops.cent_select(g["q"], g["l1"], g["block_ids"], g["block_table"], g["seq"], k=k, block_size=bs)
+    assert torch.equal(pp, bp) and torch.equal(mppl2, mppl)
+    asl = mppl2[:, 0].contiguous()
+    out_s = attn_call(ops, g, pp, asl)
+    want_s = oc.sparse_paged_attention(c["q"], c["key"], c["value"], asl.cpu(), c["block_table"], pp.cpu(), Nq, c["scale"],
+                                       Nkv, bs, *aq)
+    assert_close(out_s, want_s, tol, f"separate, block_size {bs}")
