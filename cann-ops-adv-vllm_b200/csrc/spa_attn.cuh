@@ -139,11 +139,11 @@ __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, i
 template <typename QT, bool KVI8, int NT>
 __device__ void combine_item_warp(const ChainParams &p, int item, unsigned bits) {
     constexpr int HP = NT * 8;
-    constexpr int NP = kMaxChunks + 1;
+    constexpr int NB = 8;                                     // partials per round of O-row loads
     const int lane = lane_id();
     const int b = item / p.Nkv, n2 = item % p.Nkv, g = p.g;
-    const int n = __popc(bits);
-    // lane j < n holds the j-th partial: its slot and, head by head, its (m, l)
+    const int n = __popc(bits);                               // <= kMaxChunks + 1 = 16
+    // lane j < n holds the j-th partial: its slot and, per round of heads, its (m, l)
     int slot = -1;
     {
         unsigned rest = bits;
@@ -153,50 +153,53 @@ __device__ void combine_item_warp(const ChainParams &p, int item, unsigned bits)
             if (lane == j) slot = item * p.pslots + pid;
         }
     }
-    float2 ml[HP];
-#pragma unroll
-    for (int h = 0; h < HP; ++h)
-        ml[h] = (slot >= 0 && h < g) ? __ldcg(reinterpret_cast<const float2 *>(p.part_ml + ((size_t)slot * HP + h) * 2))
-                                     : make_float2(-INFINITY, 0.f);
-    int sj[NP];
-#pragma unroll
-    for (int u = 0; u < NP; ++u) sj[u] = __shfl_sync(0xffffffffu, slot, min(u, n - 1));
 #pragma unroll 1
     for (int h0 = 0; h0 < g; h0 += 2) {
         const int nh = min(2, g - h0);
-        float4 v[2][NP];
+        float2 me[2];
 #pragma unroll
-        for (int u = 0; u < NP; ++u)
-#pragma unroll
-            for (int e = 0; e < 2; ++e)
-                if (u < n) v[e][u] = __ldcg(reinterpret_cast<const float4 *>(p.part_o + ((size_t)sj[u] * HP + h0 + min(e, nh - 1)) * kD) + lane);
-        float M[2], Ls[2], w[2];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            float2 me = make_float2(-INFINITY, 0.f);
-#pragma unroll
-            for (int h = 0; h < HP; ++h) if (h == h0 + e) me = ml[h];
-            float cm = me.x;
-#pragma unroll
-            for (int o = 16; o; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
-            M[e] = cm;
-            w[e] = (me.x == -INFINITY) ? 0.f : fast_exp2(me.x - cm);
-            float L = me.y * w[e];
-#pragma unroll
-            for (int o = 16; o; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
-            Ls[e] = L;
-        }
+        for (int e = 0; e < 2; ++e)
+            me[e] = (slot >= 0 && e < nh) ? __ldcg(reinterpret_cast<const float2 *>(p.part_ml + ((size_t)slot * HP + h0 + e) * 2))
+                                          : make_float2(-INFINITY, 0.f);
         float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+        float M[2] = {0.f, 0.f}, Ls[2] = {0.f, 0.f}, w[2] = {0.f, 0.f};
+#pragma unroll 1
+        for (int u0 = 0; u0 < n; u0 += NB) {
+            // one round of independent L2 loads: the O rows of two heads x up to eight partials (with the (m, l)
+            // loads above in the first round)
+            float4 v[2][NB];
 #pragma unroll
-        for (int u = 0; u < NP; ++u)
+            for (int u = 0; u < NB; ++u) {
+                const int sj = __shfl_sync(0xffffffffu, slot, min(u0 + u, n - 1));
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const float we = __shfl_sync(0xffffffffu, w[e], min(u, n - 1));
-                if (u < n) {
-                    acc[e][0] += v[e][u].x * we; acc[e][1] += v[e][u].y * we;
-                    acc[e][2] += v[e][u].z * we; acc[e][3] += v[e][u].w * we;
+                for (int e = 0; e < 2; ++e)
+                    if (u0 + u < n) v[e][u] = __ldcg(reinterpret_cast<const float4 *>(p.part_o + ((size_t)sj * HP + h0 + min(e, nh - 1)) * kD) + lane);
+            }
+            if (u0 == 0) {
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    float cm = me[e].x;
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+                    M[e] = cm;
+                    w[e] = (me[e].x == -INFINITY) ? 0.f : fast_exp2(me[e].x - cm);
+                    float L = me[e].y * w[e];
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
+                    Ls[e] = L;
                 }
             }
+#pragma unroll
+            for (int u = 0; u < NB; ++u)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const float we = __shfl_sync(0xffffffffu, w[e], min(u0 + u, n - 1));
+                    if (u0 + u < n) {
+                        acc[e][0] += v[e][u].x * we; acc[e][1] += v[e][u].y * we;
+                        acc[e][2] += v[e][u].z * we; acc[e][3] += v[e][u].w * we;
+                    }
+                }
+        }
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
             if (e < nh) write_out_vals<QT, KVI8, 4>(p, b, n2, h0 + e, lane * 4, acc[e], Ls[e]);
@@ -250,7 +253,7 @@ __device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t 
         int old = 0;
         if (lane == 0) {
             __threadfence();
-            old = atomicAdd(p.ctrl + Ctrl::pages_done(item), cnt | (1 << (16 + pid)));
+            old = atomicAdd(p.ctrl + Ctrl::pages_done(item), (int)((unsigned)cnt | (1u << (16 + pid))));
         }
         old = __shfl_sync(0xffffffffu, old, 0);
         if ((old & 0xffff) + cnt == len) {

@@ -146,7 +146,7 @@ __host__ __device__ __forceinline__ unsigned long long item_record(int len, int 
 __host__ __device__ __forceinline__ int record_len(unsigned long long r) { return (int)((r >> 28) & 0xffffff); }
 __host__ __device__ __forceinline__ int record_tail(unsigned long long r) { return (int)((r >> 52) & 0xff); }
 // Chunk of an item's pages offered to every CTA: valid | item (14 bits) | pages (16 bits) | first entry (32 bits)
-constexpr int kMaxChunks = 8;         // chunks one item is cut into at most
+constexpr int kMaxChunks = 15;        // chunks one item is cut into at most (partial ids 0..15 share a 16-bit field)
 constexpr int kMaxOwn = 8;            // own items a CTA keeps a private prefix of
 __host__ __device__ __forceinline__ unsigned long long chunk_desc(int item, int start, int n) {
     return (1ull << 63) | ((unsigned long long)(item & (kMaxItems - 1)) << 48) | ((unsigned long long)(n & 0xffff) << 32) |

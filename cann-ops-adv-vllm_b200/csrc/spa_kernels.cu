@@ -896,7 +896,8 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     p.qstride = p.maxP * (p.mode == kModeAttnOnly ? 2 : 1);     // x2: a page may be listed twice (split tail entries)
     // Partials: fixed slots, one for the owner's prefix and one per chunk of every item; chunks are not smaller
     // than 1/32 of a CTA's fair share (publish_item), so with very many items an item is never cut more than once
-    p.pslots = ((long long)p.items >= 32ll * d.sms) ? 2 : kMaxChunks + 1;
+    // few items (tensor-parallel shards): up to 15 chunks each, so that the idle CTAs get even shares of long items
+    p.pslots = ((long long)p.items >= 32ll * d.sms) ? 2 : (p.items <= d.sms ? kMaxChunks + 1 : 9);
     if (p.qstride >= 65536) return fail(SPA_ERR_UNSUPPORTED, "more than 65535 page entries per work item");
     if (p.num_blocks > kMaxBlocks) return fail(SPA_ERR_UNSUPPORTED, "more than %d KV blocks", kMaxBlocks);
     p.stage_bytes = e->kv_i8 ? 16384 : 32768;

@@ -579,8 +579,8 @@ __device__ __noinline__ int warp_compact_bit(unsigned *pm, int pl, int bit, int 
 //     fair share of the launch, estimated from this item -- and starts streaming it as soon as its own selection
 //     is over, while other CTAs are still selecting (the reference separates the phases with SyncAll,
 //     sparse_paged_fusion_attention.cpp:56-76);
-//   * the rest [S, ulen) is cut into chunks of HALVING size (between 1/8 and 1/32 of a CTA's fair share, at most
-//     kMaxChunks): chunk j of item i is descriptor desc[j * items + i], and CTAs claim descriptors in index
+//   * the rest [S, ulen) is cut into chunks of HALVING size (between 1/8 and 1/32 of a CTA's fair share -- larger when
+//     an item is so long that its pslots - 1 chunks would not cover it otherwise): chunk j of item i is descriptor desc[j * items + i], and CTAs claim descriptors in index
 //     order, so all the large chunks go first and the launch ends on the small ones (guided self-scheduling
 //     without knowing the total).  No reservation: the slot is fixed;
 //   * one release-add reports the item (high half of the kTail word) after an atomicMax of its chunk count
@@ -612,7 +612,9 @@ __device__ __noinline__ void publish_item(const ChainParams &p, PubState *pub, i
         int at = S, left = ulen - S;
         while (left > 0) {
             int c = max(min_chunk, min((left * p.chunk_num) / p.chunk_den, max_chunk));
-            if (nch == p.pslots - 2 || left - c < min_chunk) c = left;
+            const int slots_left = p.pslots - 1 - nch;                 // chunks this item may still be cut into
+            c = max(c, (left + slots_left - 1) / slots_left);          // ... must cover what is left (few, long items)
+            if (slots_left == 1 || left - c < min_chunk) c = left;
             st_relaxed_u64(p.desc + (size_t)nch * p.items + item, chunk_desc(item, at, c));
             at += c; left -= c; ++nch;
         }

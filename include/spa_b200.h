@@ -212,7 +212,7 @@ SPA_API int spaSparsePagedFusionAttention(void *workspace, uint64_t workspaceSiz
  * inside the library -- every GPU that loads the library holds that much device memory until the process
  * exits -- and the plan lives on the stack: the call performs no cudaMalloc / cudaFree and no host or
  * library allocation.  A problem whose workspace exceeds the array (B*Nkv work items x (page entries +
- * 9 fp32 partials) + exact-score scratch: BASELINE configs c2 / c3 / c4 need 9.9 / 25.1 / 31.1 MB) is
+ * 9 or 16 fp32 partials) + exact-score scratch: BASELINE configs c2 / c3 / c4 need 13.7 / 25.1 / 31.1 MB) is
  * refused with SPA_ERR_WORKSPACE and a message naming both sizes; use the two-phase entry points then.
  * All calls on a device share the one array, which keeps the previous call's contents: the words that
  * must start at zero are cleared on `stream` in front of every launch, everything else is written before

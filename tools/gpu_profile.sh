@@ -14,3 +14,6 @@ for wl in c2 c3 c4; do
   echo "ncu full $wl rc=$?"
 done
 ls -la $O | grep p_
+for wl in c2 c3 c4; do timeout -k 10 300 python tests/gpu_phase_trace.py $wl > $O/p_trace_$wl.txt 2>&1; done
+timeout -k 10 900 python tools/sweep.py > $O/p_sweep.md 2> $O/p_sweep.err; echo "sweep rc=$?"
+timeout -k 10 300 python tools/bench_assign.py > $O/p_assign.json 2>&1; echo "assign rc=$?"
