@@ -151,7 +151,7 @@ def test_attention_rejects_unsupported_ifa_features_without_gpu(lib):
     assert call(kvpad=extra) == SPA_ERR_UNSUPPORTED
     assert call(heads=16) == SPA_ERR_SHAPE and b"num_heads" in lib.spaGetLastError()
     assert call(layout=b"XYZ") == SPA_ERR_ARG
-    assert call(bs=64) == SPA_ERR_UNSUPPORTED
+    assert call(bs=48) == SPA_ERR_UNSUPPORTED
     assert call(kvh=5) == SPA_ERR_SHAPE
 
 
