@@ -385,8 +385,8 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
 
     graph = None
     if args.graph and peer:
-        raise SystemExit("--graph with --gather peer: capture both plans of TPFusedDecode yourself (alternating buffers); use --gather nccl here")
-    if args.graph:
+        plan.capture()                                               # one graph per gathered buffer, replayed alternately
+    elif args.graph:
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
@@ -397,6 +397,8 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
             step()
 
     def run_step():
+        if args.graph and peer:
+            return plan.replay()
         return graph.replay() if graph is not None else step()
 
     def barrier():
@@ -533,7 +535,7 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
             "l2": ("flushed before every timed step (256 MiB write + 256 MiB read of a second buffer, so L2 holds clean lines); " if flush is not None else "not flushed; ") +
                   f"per-step read set {ab['bytes_kv_union'] / 2**20:.0f} MiB > 126 MB L2" +
                   ("; ranks aligned by a 1-element all-reduce before each timed step (outside the timed region)" if world > 1 and not args.no_align else ""),
-            "launch": "cuda graph replay" if graph is not None else ("TPFusedDecode.launch()" if peer else "FusedDecodePlan.launch()"),
+            "launch": "cuda graph replay" if (graph is not None or (args.graph and peer)) else ("TPFusedDecode.launch()" if peer else "FusedDecodePlan.launch()"),
             "_inp": inp,
         }
     if peer:

@@ -750,23 +750,28 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             for (int i = G.tid; i < total; i += G.gt) base[i] = kSentinel;
         }
     }
-    if (DP) cp_async_wait_all();
-    grp_sync(G);
-    trace_clk(p, 17);
-    if (DP) {
+    // c[i] = block_ids[n2, block_table[b, i]] (select_position.cpp:97-115), asynchronously into smem; the table
+    // value is clamped as the golden does (tests/utils.py:62).  Needs the block_table row (a cold HBM round trip):
+    // with scores to compute, that wait and the gather are issued AFTER the score loop -- the scores do not depend
+    // on them, the row has long landed by then, and the gather hides under the TopK stages.  Page i is copied and
+    // gathered by the same thread, so a thread only waits for its own copies.
+    auto issue_gather = [&]() {
+        cp_async_wait_all();
         pl = max(0, min((seq + p.bs - 1) / p.bs, p.maxP));
         rem = (pl > 0) ? seq - (pl - 1) * p.bs : 0;               // tokens on the last page
         has_tail = (pl > 0) && (rem < p.bs);
-        // c[i] = block_ids[n2, block_table[b, i]] (select_position.cpp:97-115), asynchronously into smem;
-        // the table value is clamped as the golden does (tests/utils.py:62)
         for (int i = G.tid; i < pl; i += G.gt) cp_async_4(&cS[i], bid + max(0, min(physS[i], p.kvPageLen - 1)));
-    }
+    };
+    if (DP && !DS) issue_gather();
+    grp_sync(G);
+    trace_clk(p, 17);
     trace_mark(p, 8);
 
     const unsigned short *q = reinterpret_cast<const unsigned short *>(p.q);
     if (DS) {
         score_item<QT>(p, tmC, b, n2, sc, L.scs, hd, misc, R, tcount, G, qf);
         trace_clk(p, 20);
+        if (DP) issue_gather();
         grp_sync(G);
         trace_clk(p, 21);
         trace_mark(p, 9);

@@ -117,7 +117,7 @@ class SparseDecodeBackend:
             out = plan.launch()
             return out if self.world > 1 else self.attention_out[:B]
         if self.world > 1:
-            raise NotImplementedError("graph replay under tensor parallelism: capture both buffers of TPFusedDecode")
+            return plan.replay()                                # one captured graph per gathered buffer (peer_gather.py)
         entry = self._graphs.get(B)
         if entry is None:
             side = torch.cuda.Stream(self.device)

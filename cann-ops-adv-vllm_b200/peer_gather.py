@@ -110,6 +110,7 @@ class TPFusedDecode:
             self.out.attach(plan, i)
             self.plans.append(plan)
         self.step = 0
+        self.graphs = None
 
     @property
     def num_launches(self) -> int:
@@ -121,6 +122,39 @@ class TPFusedDecode:
         self.plans[i].launch()
         return self.out.gathered(i)
 
+    def capture(self) -> None:
+        """Capture one CUDA graph per gathered buffer (the launch count of the flag exchange lives in the signal
+        block on the device, so a captured launch replays correctly); `replay()` then alternates between them
+        exactly as `launch()` alternates between the plans.  Collective in the sense that EVERY rank must call it at
+        the same point: both plans are launched once eagerly first (workspace clear outside the capture)."""
+        if self.graphs is not None:
+            return
+        dev = self.out.device
+        cur = torch.cuda.current_stream(dev)
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            self.launch()
+            self.launch()
+        cur.wait_stream(side)
+        graphs = []
+        for i in range(2):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.plans[i].launch()
+            graphs.append(g)
+        self.graphs = graphs
+
+    def replay(self) -> torch.Tensor:
+        """`launch()` from the captured graphs."""
+        if self.graphs is None:
+            self.capture()
+        i = self.step & 1
+        self.step += 1
+        self.graphs[i].replay()
+        return self.out.gathered(i)
+
     def close(self) -> None:
+        self.graphs = None
         self.plans = []
         self.out.close()

@@ -83,9 +83,11 @@ def main():
     be = SparseDecodeBackend(Nq, Nkv, 128, 128, k, max_batch=4, max_blocks_per_seq=S // 128, dtype=torch.float16,
                              device=dev, scale=c["scale"], tensor_parallel=True)
     be.bind_cache(loc["key"].to(dev), loc["value"].to(dev), loc["l1_cent"].to(dev), loc["block_ids"].to(dev))
-    for it, Bs in enumerate([3, 2, 3, 3]):
+    # the second half of the steps replays the launches from CUDA graphs (one per gathered buffer, alternating)
+    for it, Bs in enumerate([3, 2, 3, 3, 3, 2, 3, 3, 2]):
         q_full = torch.rand(Bs, Nq, 128, generator=torch.Generator().manual_seed(500 + it)).half()
-        got = be.forward_decode(q_full[:, sh.q_lo:sh.q_hi].to(dev), c["block_table"][:Bs].to(dev), c["seq"][:Bs].to(dev))
+        got = be.forward_decode(q_full[:, sh.q_lo:sh.q_hi].to(dev), c["block_table"][:Bs].to(dev), c["seq"][:Bs].to(dev),
+                                use_graph=it >= 4)
         torch.cuda.synchronize()
         if rank == 0:
             want = oc.sparse_paged_fusion_attention(q_full, c["key"], c["value"], c["block_table"][:Bs], c["l1"],
@@ -93,7 +95,7 @@ def main():
             err = (got.float().cpu() - want.float()).abs()
             if got.shape != want.shape or not bool((err <= 1e-3 + 1e-3 * want.float().abs()).all()):
                 ok = False
-                print(f"backend TP step {it} B={Bs}: max err {err.max().item():.3e}", flush=True)
+                print(f"backend TP step {it} B={Bs} graph={it >= 4}: max err {err.max().item():.3e}", flush=True)
         dist.barrier()
     be.close()
     flag = torch.tensor([0 if ok else 1], device=dev)
