@@ -96,6 +96,8 @@ WORKLOADS = {
                desc="Llama-3-8B decode: B=16 32Q/8KV D=128 seq 32k C=512 top-k=64 fp16 KV, fused"),
     "c3": dict(B=64, Nq=32, Nkv=8, S=32768, C=512, k=64, q="bf16", kv="i8",
                desc="Llama-3-8B decode, int8 KV (antiquant), bf16 query: B=64 seq 32k C=512 top-k=64, fused"),
+    "c3_fp8": dict(B=64, Nq=32, Nkv=8, S=32768, C=512, k=64, q="bf16", kv="f8",
+                   desc="c3 with FP8 (e4m3) KV pages instead of int8 + antiquant: B=64 seq 32k C=512 top-k=64, bf16 query, fused"),
     "c4": dict(B=32, Nq=64, Nkv=8, S=131072, C=2048, k=128, q="f16", kv="f16",
                desc="Llama-3-70B decode: B=32 64Q/8KV D=128 seq 128k C=2048 top-k=128 fp16 KV, fused"),
     # corners of the configs[4] sweep (tools/sweep.py), for traces
@@ -136,7 +138,12 @@ def make_inputs(w, B, rank, world, device, seed=1234, kv_layout="bsnd", cent_dis
     l1 = (torch.rand if cent_dist == "rand" else torch.randn)(nkv, C, D, generator=g_rank, device=device).to(qd)
     block_ids = torch.randint(0, C, (nkv, pages), generator=g_rank, device=device, dtype=torch.int32)
     pool_shape = (pages, BS, nkv, D) if kv_layout == "bsnd" else (pages, nkv, BS, D)
-    if w["kv"] == "i8":
+    if w["kv"] == "f8":
+        key = torch.empty(pool_shape, dtype=torch.float8_e4m3fn, device=device)
+        value = torch.empty_like(key)
+        aq_scale = torch.empty(0, dtype=qd, device=device)
+        aq_offset = torch.empty(0, dtype=qd, device=device)
+    elif w["kv"] == "i8":
         key = torch.empty(pool_shape, dtype=torch.int8, device=device)
         value = torch.empty_like(key)
         aq_scale = (torch.rand(2, nkv, D, generator=g_rank, device=device) * 0.02 + 0.005).to(qd)
@@ -150,7 +157,9 @@ def make_inputs(w, B, rank, world, device, seed=1234, kv_layout="bsnd", cent_dis
     for t in (key, value):
         for p0 in range(0, pages, chunk):
             n = min(chunk, pages - p0)
-            if w["kv"] == "i8":
+            if w["kv"] == "f8":
+                t[p0:p0 + n] = torch.randn((n,) + pool_shape[1:], generator=g_rank, device=device).to(torch.float8_e4m3fn)
+            elif w["kv"] == "i8":
                 t[p0:p0 + n] = torch.randint(-128, 128, (n,) + pool_shape[1:], generator=g_rank, device=device,
                                              dtype=torch.int8)
             else:
@@ -177,7 +186,7 @@ def algorithmic_bytes(inp, page_position, page_position_length):
     bytes_kv = union_pages * page_bytes
     bytes_sel = (nkv * inp["C"] * D * q_elem + nkv * B * P * 4 + B * P * 4 + B * nq * (MP + 8) * 4 + B * 8 * 8)
     bytes_io = 2 * B * nq * D * q_elem
-    if kv_elem == 1:
+    if kv_elem == 1 and inp["aq_scale"].numel():
         bytes_sel += 2 * 2 * nkv * D * q_elem
     return dict(bytes_alg=bytes_kv + bytes_sel + bytes_io, bytes_kv_union=bytes_kv,
                 bytes_logical=selected * page_bytes, union_pages=union_pages, selected_pages=selected,
@@ -287,7 +296,7 @@ def cpu_nseq(w):
     """Sequences of the workload the CPU legs run per step: the whole batch where the host copy of their pages
     stays modest (c1, c2: <= 2 GiB), else a bounded sample."""
     P = (w["S"] + BS - 1) // BS
-    page_bytes = BS * w["Nkv"] * D * 2 * (1 if w["kv"] == "i8" else 2)
+    page_bytes = BS * w["Nkv"] * D * 2 * (1 if w["kv"] in ("i8", "f8") else 2)
     return max(1, min(w["B"], (2 << 30) // (P * page_bytes)))
 
 
@@ -423,7 +432,7 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
         ok = torch.equal(got, ref_full)                              # bit for bit: the exchange moved every row
         c1 = cpu_sample(inp, 1)                                      # this rank's heads of sequence 0 vs the oracle
         wo = run_oracle(c1, inp)[0].float()
-        tol = 2e-2 if (i8 or w["q"] == "bf16") else 1e-3
+        tol = 2e-2 if (w["kv"] != "f16" or w["q"] == "bf16") else 1e-3
         ok = ok and bool(((mine[:1].float().cpu() - wo).abs() <= tol + tol * wo.abs()).all())
         flag = torch.tensor([1 if ok else 0], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
@@ -620,7 +629,8 @@ def main():
         extra = {}
         xs = max(10, min(args.steps, 30))
         # (c3_bnsd: int8 KV with contiguous page-head slices -- in the vLLM layout an int8 row is 128 B at a 1 KiB stride)
-        for nm, cd, lay in (("c3", "rand", None), ("c4", "rand", None), ("c2", "randn", None), ("c3", "rand", "bnsd")):
+        for nm, cd, lay in (("c3", "rand", None), ("c4", "rand", None), ("c2", "randn", None), ("c3", "rand", "bnsd"),
+                            ("c3_fp8", "rand", None)):
             r = bench_workload(args, nm, ctx, xs, args.warmup, cent_dist=cd, kv_layout=lay)
             extra[nm + ("" if cd == "rand" else f"_{cd}") + (f"_{lay}" if lay else "")] = dict(brief(r), steps=xs)
             del r

@@ -33,6 +33,7 @@ int to_spa_dtype(at::ScalarType t) {
         case at::kBFloat16: return SPA_BF16;
         case at::kFloat: return SPA_F32;
         case at::kChar: return SPA_I8;
+        case at::kFloat8_e4m3fn: return SPA_F8E4M3;
         case at::kInt: return SPA_I32;
         case at::kLong: return SPA_I64;
         default: TORCH_CHECK(false, "Unsupported tensor dtype");   // add_custom.cpp:69

@@ -44,30 +44,32 @@ struct AttnSmem {
 };
 
 // head-dim index held by accumulator register r of m-tile mt (rows gid / gid+8 of the mma tile)
-template <bool KVI8>
+template <int KVK>
 __device__ __forceinline__ int o_dim(int mt, int gid, int r) {
-    return KVI8 ? mt * 16 + 2 * gid + (r >> 1) : mt * 16 + gid + (r >> 1) * 8;
+    return KVK != 0 ? mt * 16 + 2 * gid + (r >> 1) : mt * 16 + gid + (r >> 1) * 8;      // 8-bit V pages: see consume_pages
 }
 
 // normalise NV consecutive head dims d0.. of one output row, V antiquant, store
-template <typename QT, bool KVI8, int NV>
+template <typename QT, int KVK, int NV>
 __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int n2, int h, int d0, const float (&acc)[NV],
                                                float Lsum) {
     const float inv = (Lsum > 0.f) ? 1.f / Lsum : 0.f;
     float r[NV];
 #pragma unroll
     for (int e = 0; e < NV; ++e) r[e] = acc[e] * inv;
-    if (KVI8 && Lsum > 0.f) {
-        // V dequant applied once to the normalised sum: (O + offset_v) * scale_v (…_Us2.h:3655-3670)
-        const unsigned short *sv = reinterpret_cast<const unsigned short *>(p.aq_scale) +
-                                   (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD);
+    if (KVK != 0 && Lsum > 0.f) {
+        // V dequant applied once to the normalised sum: (O + offset_v) * scale_v (…_Us2.h:3655-3670).  int8 pages
+        // entered the matmul biased by 1152 (see consume_pages); FP8 pages need no scale at all (absent = 1)
+        const unsigned short *sv = p.aq_scale ? reinterpret_cast<const unsigned short *>(p.aq_scale) +
+                                   (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD) : nullptr;
         const unsigned short *ov = p.aq_offset ? reinterpret_cast<const unsigned short *>(p.aq_offset) +
                                    (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD) : nullptr;
 #pragma unroll
         for (int e = 0; e < NV; ++e) {
             const int d = p.aq_per_tensor ? 0 : d0 + e;
             const float off = ov ? QTraits<QT>::to_float(ov[d]) : 0.f;
-            r[e] = ((r[e] - kI8Bias) + off) * QTraits<QT>::to_float(sv[d]);      // O'/l - 1152 = O/l, see consume_pages
+            const float scl = sv ? QTraits<QT>::to_float(sv[d]) : 1.f;
+            r[e] = ((KVK == 1 ? r[e] - kI8Bias : r[e]) + off) * scl;             // int8: O'/l - 1152 = O/l
         }
     }
     const size_t off = (size_t)b * p.out_sb + (size_t)(n2 * p.g + h) * p.out_sh + d0;
@@ -93,38 +95,42 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
 // matmul as k instead of k + offset_k, with q*scale_k split into two int8 digits after a power-of-two
 // normalisation (see the Q fragments in attention_phase) -- which the softmax never sees but its log-sum
 // does: it is rebuilt here from the same quantised operands, 4 head dims per lane.
-template <typename QT, bool KVI8>
+template <typename QT, int KVK>
 __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, int h, float m2, float lsum) {
     const int lane = lane_id();
     float shift = 0.f;
-    if (KVI8) {
+    if (KVK != 0) {
         const unsigned short *qrow = reinterpret_cast<const unsigned short *>(p.q) + (size_t)b * p.q_sb +
                                      (size_t)(n2 * p.g + h) * p.q_sh + lane * 4;
-        const unsigned short *sk = reinterpret_cast<const unsigned short *>(p.aq_scale) + (p.aq_per_tensor ? 0 : (size_t)n2 * kD + lane * 4);
+        const unsigned short *sk = p.aq_scale ? reinterpret_cast<const unsigned short *>(p.aq_scale) + (p.aq_per_tensor ? 0 : (size_t)n2 * kD + lane * 4) : nullptr;
         const unsigned short *ok = p.aq_offset ? reinterpret_cast<const unsigned short *>(p.aq_offset) +
                                    (p.aq_per_tensor ? 0 : (size_t)n2 * kD + lane * 4) : nullptr;
         float f[4], off[4], amax = 0.f;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             const int j = p.aq_per_tensor ? 0 : e;
-            f[e] = QTraits<QT>::to_float(qrow[e]) * QTraits<QT>::to_float(sk[j]);
+            f[e] = QTraits<QT>::to_float(qrow[e]) * (sk ? QTraits<QT>::to_float(sk[j]) : 1.f);
             off[e] = ok ? QTraits<QT>::to_float(ok[j]) : 0.f;
             amax = fmaxf(amax, fabsf(f[e]));
         }
 #pragma unroll
         for (int o = 16; o; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
         const uint32_t ex = min(max((__float_as_uint(amax) >> 23) & 0xffu, 1u), 253u);
-        const float up = __uint_as_float((254u - ex) << 23) * kQDigitRange, down = __uint_as_float(ex << 23);
+        const float up = __uint_as_float((254u - ex) << 23) * (KVK == 1 ? kQDigitRange : 1.f), down = __uint_as_float(ex << 23);
         float sum = 0.f;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            int d1, d2;
-            split_digits(f[e] * up, d1, d2);
-            sum += ((float)d1 + (float)d2 * (1.f / kQDigit2)) * off[e];
+            if (KVK == 1) {
+                int d1, d2;
+                split_digits(f[e] * up, d1, d2);
+                sum += ((float)d1 + (float)d2 * (1.f / kQDigit2)) * off[e];
+            } else {
+                sum += __half2float(__float2half_rn(f[e] * up)) * off[e];      // FP8: Q enters as fp16(q * scale_k * 2^n)
+            }
         }
 #pragma unroll
         for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        shift = p.scale_log2 * down * (1.f / kQDigitRange) * sum;
+        shift = p.scale_log2 * down * (KVK == 1 ? 1.f / kQDigitRange : 1.f) * sum;
     }
     if (lane == 0)
         p.lse[(size_t)b * p.lse_sb + (size_t)(n2 * p.g + h) * p.lse_sh] =
@@ -136,7 +142,7 @@ __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, i
 // word that counts the item's finished pages also collects one bit per partial (see post_warp_loop), so the
 // last arriver knows the slots without searching.  Latency-bound (everything sits in L2): (m, l) of every
 // partial and head in one round of loads, then the O rows of two heads x all partials per round trip.
-template <typename QT, bool KVI8, int NT>
+template <typename QT, int KVK, int NT>
 __device__ void combine_item_warp(const ChainParams &p, int item, unsigned bits) {
     constexpr int HP = NT * 8;
     constexpr int NB = 8;                                     // partials per round of O-row loads
@@ -202,8 +208,8 @@ __device__ void combine_item_warp(const ChainParams &p, int item, unsigned bits)
         }
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-            if (e < nh) write_out_vals<QT, KVI8, 4>(p, b, n2, h0 + e, lane * 4, acc[e], Ls[e]);
-            if (e < nh && p.lse != nullptr) write_lse<QT, KVI8>(p, b, n2, h0 + e, M[e], Ls[e]);
+            if (e < nh) write_out_vals<QT, KVK, 4>(p, b, n2, h0 + e, lane * 4, acc[e], Ls[e]);
+            if (e < nh && p.lse != nullptr) write_lse<QT, KVK>(p, b, n2, h0 + e, M[e], Ls[e]);
         }
     }
     if (lane == 0) { p.item_info[item] = 0ull; p.ctrl[Ctrl::pages_done(item)] = 0; }
@@ -236,7 +242,7 @@ __device__ __noinline__ void max_ppl_poll(const ChainParams &p) {
     }
 }
 
-template <typename QT, bool KVI8, int NT>
+template <typename QT, int KVK, int NT>
 __device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t *mfull, uint64_t *mempty) {
     const int lane = lane_id();
     int mi = 0;
@@ -259,7 +265,7 @@ __device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t 
         if ((old & 0xffff) + cnt == len) {
             __threadfence();
             const unsigned long long tc0 = (p.dbg && lane == 0) ? globaltimer_ns() : 0ull;
-            combine_item_warp<QT, KVI8, NT>(p, item, ((unsigned)old >> 16) | (1u << pid));
+            combine_item_warp<QT, KVK, NT>(p, item, ((unsigned)old >> 16) | (1u << pid));
             if (p.dbg && lane == 0 && p.trace) {
                 p.trace[(size_t)blockIdx.x * kTraceSlots + 10] += 1;
                 p.trace[(size_t)blockIdx.x * kTraceSlots + 11] += globaltimer_ns() - tc0;
@@ -284,7 +290,7 @@ __device__ __forceinline__ void post_message(int4 *mail, uint64_t *mfull, uint64
 
 // ---- segment flush: merge the 8 warps' running states of `item`; either finish the item (all of its
 // pages were in this segment) or leave a partial and tell the post warp.  All consumers.
-template <typename QT, bool KVI8, int NT>
+template <typename QT, int KVK, int NT>
 __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, int pid, int cnt,
                                               unsigned long long rec, float (&o)[NT][8][4],
                                               float (&m_run)[NT][2], float (&l_run)[NT][2], float *mbuf,
@@ -349,7 +355,7 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
             for (int mt = half * 4; mt < half * 4 + 4; ++mt)
 #pragma unroll
                 for (int r = 0; r < 4; ++r)
-                    mine[(tig * 2 + (r & 1)) * kMergeHeadStride + o_dim<KVI8>(mt, gid, r) - half * kMergeHalf] = o[nt][mt][r];
+                    mine[(tig * 2 + (r & 1)) * kMergeHeadStride + o_dim<KVK>(mt, gid, r) - half * kMergeHalf] = o[nt][mt][r];
             named_bar_sync(1, kAll);
             // dims half*64 + 2*lane, +1 of head h: sum over the 8 warps
             float acc[2] = {0.f, 0.f};
@@ -360,7 +366,7 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
             }
             const int d0 = half * kMergeHalf + lane * 2;
             if (whole) {
-                if (h < p.g) write_out_vals<QT, KVI8, 2>(p, b, n2, h, d0, acc, Ls);
+                if (h < p.g) write_out_vals<QT, KVK, 2>(p, b, n2, h, d0, acc, Ls);
             } else {
                 *reinterpret_cast<float2 *>(p.part_o + ((size_t)slot * HP + h) * kD + d0) = make_float2(acc[0], acc[1]);
             }
@@ -389,14 +395,14 @@ __device__ __forceinline__ unsigned long long take_entry(const ChainParams &p, i
 // O^T += V^T P^T.  With PP = 2 the two pages' chains are interleaved instruction by instruction, the
 // running max is reduced once over both and O is rescaled once (and only when some max moved).
 // ks/vs: ring stages of the K and V tiles (K full barriers already passed), vph: parities of the V stages.
-template <typename QT, bool KVI8, int NT, int PP>
+template <typename QT, int KVK, int NT, int PP>
 __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t stage_u32, const int (&ks)[PP],
                                               const int (&vs)[PP], const uint32_t (&vph)[PP],
                                               const unsigned (&metas)[PP], const int (&tails)[PP],
                                               const uint32_t (&qf)[NT][8][2], float (&o)[NT][8][4],
                                               float (&m_run)[NT][2], float (&l_run)[NT][2],
                                               const float (&hsc)[NT][2], uint64_t *full, uint64_t *empty) {
-    using MT = typename MmaType<QT, KVI8>::type;
+    using MT = typename MmaType<QT, KVK>::type;
     const int lane = lane_id(), warp = warp_id(), gid = lane >> 2, tig = lane & 3;
     const int t0 = warp * 16;                       // this warp's 16 tokens of every page
     // ldmatrix lane offsets (128B-swizzled tile: row r, 16B chunk c stored at chunk c ^ (r & 7))
@@ -411,7 +417,30 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     for (int pp = 0; pp < PP; ++pp)
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) s[pp][nt][0] = s[pp][nt][1] = s[pp][nt][2] = s[pp][nt][3] = 0.f;
-    if (!KVI8) {
+    if (KVK == kKvF8) {
+        // FP8 (e4m3) page: [128 tokens][128 B], the same shared-memory image as an int8 page.  One ldmatrix.x4 covers
+        // 16 tokens x 32 d; a register holds 4 consecutive d of one token, so after the (exact) conversion to fp16
+        // pairs k-slot (2 tig + e) of an fp16 mma is d = 4 tig + e and slot (2 tig + 8 + e) is d = 4 tig + 2 + e --
+        // the same permutation on the Q fragments (see there); two m16n8k16 mmas per 32 d.
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int chunk = j * 2 + a_chk;
+            const uint32_t off = a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
+#pragma unroll
+            for (int pp = 0; pp < PP; ++pp) {
+                uint32_t r0, r1, r2, r3;
+                ldmatrix_x4(r0, r1, r2, r3, stage_u32 + (uint32_t)ks[pp] * p.stage_bytes + off);
+                const uint32_t k00 = cvt_e4m3x2_f16x2(r0), k01 = cvt_e4m3x2_f16x2(r1), k02 = cvt_e4m3x2_f16x2(r0 >> 16),
+                               k03 = cvt_e4m3x2_f16x2(r1 >> 16), k10 = cvt_e4m3x2_f16x2(r2), k11 = cvt_e4m3x2_f16x2(r3),
+                               k12 = cvt_e4m3x2_f16x2(r2 >> 16), k13 = cvt_e4m3x2_f16x2(r3 >> 16);
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    mma_16816<MT>(s[pp][nt], k00, k01, k02, k03, qf[nt][2 * j][0], qf[nt][2 * j][1]);
+                    mma_16816<MT>(s[pp][nt], k10, k11, k12, k13, qf[nt][2 * j + 1][0], qf[nt][2 * j + 1][1]);
+                }
+            }
+        }
+    } else if (KVK == kKvSame) {
 #pragma unroll
         for (int k8 = 0; k8 < 8; ++k8) {
             const int chunk = (k8 & 3) * 2 + a_chk;
@@ -475,7 +504,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
             const int h = nt * 8 + tig * 2 + e;
-            const float sc2 = KVI8 ? hsc[nt][e] : p.scale_log2;
+            const float sc2 = KVK != kKvSame ? hsc[nt][e] : p.scale_log2;
             float x[PP][2];
             float mx = -INFINITY;
 #pragma unroll
@@ -497,7 +526,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
             for (int pp = 0; pp < PP; ++pp) {
                 const float p0 = fast_exp2(x[pp][0] - m_use);
                 const float p1 = fast_exp2(x[pp][1] - m_use);
-                if (!KVI8) psum += p0 + p1;              // int8 KV: l is summed from the ROUNDED P below
+                if (KVK != kKvI8) psum += p0 + p1;       // int8 KV: l is summed from the ROUNDED P below
                 pr[pp][e] = p0; pr[pp][2 + e] = p1;
             }
             l_run[nt][e] = l_run[nt][e] * alpha[nt][e] + psum;
@@ -509,7 +538,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
         for (int pp = 0; pp < PP; ++pp) {
             const uint32_t pk0 = QTraits<MT>::pack2(pr[pp][0], pr[pp][1]);
             const uint32_t pk1 = QTraits<MT>::pack2(pr[pp][2], pr[pp][3]);
-            if (KVI8) {
+            if (KVK == kKvI8) {
                 // V enters the matmul as 1152 + v: O' = O + 1152 * sum(P16).  With l = sum(P16) -- the very
                 // values the tensor cores multiply by -- the constant leaves as O'/l - 1152 in write_out_vals.
                 // (l differs from the fp32 sum of the unrounded p by < 2^-12 relative.)
@@ -536,7 +565,31 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     // ------------------------------ V: O^T += V^T P^T ------------------------------
 #pragma unroll
     for (int pp = 0; pp < PP; ++pp) mbar_wait(&full[vs[pp]], vph[pp]);
-    if (!KVI8) {
+    if (KVK == kKvF8) {
+        // FP8 page, transposed 8x8 b16 loads as for int8 (below): a register holds V[tok 2tig][d, d+1] and
+        // V[tok 2tig+1][d, d+1]; converted pairwise (exact) and regrouped into (tok, tok+1) pairs per d
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int chunk = j * 2 + a_chk;
+            const uint32_t off = a_row * 128 + ((chunk ^ (a_row & 7)) << 4);
+#pragma unroll
+            for (int pp = 0; pp < PP; ++pp) {
+                uint32_t r[4], va[4], vb[4];
+                ldmatrix_x4_trans(r[0], r[1], r[2], r[3], stage_u32 + (uint32_t)vs[pp] * p.stage_bytes + off);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t x = cvt_e4m3x2_f16x2(r[i]), y = cvt_e4m3x2_f16x2(r[i] >> 16);
+                    va[i] = prmt(x, y, 0x5410u);          // {V[t][d],   V[t+1][d]}
+                    vb[i] = prmt(x, y, 0x7632u);          // {V[t][d+1], V[t+1][d+1]}
+                }
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    mma_16816<MT>(o[nt][2 * j], va[0], vb[0], va[1], vb[1], pb[pp][nt][0], pb[pp][nt][1]);
+                    mma_16816<MT>(o[nt][2 * j + 1], va[2], vb[2], va[3], vb[3], pb[pp][nt][0], pb[pp][nt][1]);
+                }
+            }
+        }
+    } else if (KVK == kKvSame) {
 #pragma unroll
         for (int mt = 0; mt < 8; ++mt) {
             const int chunk = (mt & 3) * 2 + v_chk;
@@ -582,12 +635,12 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     }
 }
 
-template <typename QT, bool KVI8, int NT>
+template <typename QT, int KVK, int NT>
 __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, const CUtensorMap *tmV,
                                 unsigned char *smem, PubState *pub) {
     // query staging is compiled into the int8 kernels only: the fp16 stream gains nothing from it (its pages are
     // twice as long) and the extra live state cost the fp16 kernels 1-2 us (same-box A/B, c2 / c4)
-    const bool q_stage = KVI8 && p.q_stage;
+    const bool q_stage = KVK != kKvSame && p.q_stage;
     AttnSmem L(p.nstages, p.stage_bytes, NT, q_stage ? p.g : 0);
     unsigned char *stage_base = smem + L.stages;
     float *mbuf = reinterpret_cast<float *>(smem + L.mbuf);
@@ -626,7 +679,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     if (warp >= kPostWarp) {
         const int pw = warp - kPostWarp;
         if (pw == 0 && p.mode == kModeFused && p.max_ppl != nullptr) max_ppl_poll(p);
-        post_warp_loop<QT, KVI8, NT>(p, mail + pw * kMailSlots * 2, mfull + pw * kMailSlots, mempty + pw * kMailSlots);
+        post_warp_loop<QT, KVK, NT>(p, mail + pw * kMailSlots * 2, mfull + pw * kMailSlots, mempty + pw * kMailSlots);
         return;
     }
     if (warp == kConsumerWarps) {
@@ -754,7 +807,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                         metaS[stage] = md;
                         uint32_t tx = (uint32_t)p.page_tx;
                         const bool with_q = stage_q && kv == 0;
-                        const bool with_s = with_q && KVI8 && !p.aq_per_tensor;
+                        const bool with_s = with_q && !p.aq_per_tensor && p.aq_scale != nullptr;
                         if (with_q) {
                             // the rows of this run travel with its first K page and complete on the same barrier
                             if (2 * (pg - (qi ? qpg1 : qpg0)) <= nstages) mbar_wait(&empty[qi ? qstg1 : qstg0], qi ? qph1 : qph0);
@@ -763,7 +816,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                         mbar_expect_tx(&full[stage], tx);
                         unsigned char *dst = stage_base + (size_t)stage * p.stage_bytes;
                         const CUtensorMap *tm = kv ? tmV : tmK;
-                        if (KVI8) {
+                        if (KVK != kKvSame) {
                             tma_load_4d(dst, tm, &full[stage], 0, c[1], c[2], c[3]);
                         } else {
                             tma_load_4d(dst, tm, &full[stage], 0, c[1], c[2], c[3]);
@@ -815,7 +868,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     const int v_chk = (lane >> 3) & 1;
 
     // running state of the current segment: O^T[d][head] fragments, m (log2 domain), l (thread-partial)
-    using MT = typename MmaType<QT, KVI8>::type;     // element type of the tensor-core operands
+    using MT = typename MmaType<QT, KVK>::type;     // element type of the tensor-core operands
     uint32_t qf[NT][8][2];
     float o[NT][8][4];
     float m_run[NT][2], l_run[NT][2];
@@ -832,7 +885,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         const int tail_cnt = md.w;
         if (md.y != cur) {
             if (p.dbg && tid == 0 && md.y < 0) { trace_put(p, 10, 0); trace_put(p, 11, 0); trace_put(p, 8, globaltimer_ns()); }
-            if (cur >= 0) flush_segment<QT, KVI8, NT>(p, cur, pid, cnt, rec, o, m_run, l_run, mbuf, wml, mail, mfull, mempty, mi, mph);
+            if (cur >= 0) flush_segment<QT, KVK, NT>(p, cur, pid, cnt, rec, o, m_run, l_run, mbuf, wml, mail, mfull, mempty, mi, mph);
             if (p.dbg && tid == 0 && md.y < 0) trace_put(p, 9, globaltimer_ns());
             if (md.y < 0) break;
             cur = md.y; cnt = 0; pid = md.z;
@@ -855,7 +908,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             for (int nt = 0; nt < NT; ++nt) {
                 const int h = nt * 8 + gid;
                 const unsigned short *qrow = qbase + (size_t)h * qstride;
-                if (!KVI8) {
+                if (KVK == kKvSame) {
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks) {
                         const int d0 = ks * 16 + tig * 2;
@@ -874,13 +927,18 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     // (:2146-2155).  q*scale_k is brought to [1, 2) per head by a power of two (exact), then split
                     // into two int8 digits (split_digits: 2^-16 of the head's range, finer than the fp16 rounding
                     // of the non-quantised path); the factor returns to the logits in fp32 (hsc).
-                    const unsigned short *sk = (sk_staged != nullptr && !p.aq_per_tensor) ? sk_staged
+                    // FP8 (e4m3) KV: the same folding, but K is converted to fp16 (exact) and Q enters as
+                    // fp16(q * scale_k * 2^n) in the k-slot permutation of the converted fragments: b0 = Q[h][16ks +
+                    // 4tig, +1], b1 = Q[h][16ks + 4tig + 2, +3].  Scales are optional for FP8 (absent = 1).
+                    const unsigned short *sk = (p.aq_scale == nullptr) ? nullptr
+                                               : (sk_staged != nullptr && !p.aq_per_tensor) ? sk_staged
                                                : reinterpret_cast<const unsigned short *>(p.aq_scale) + (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
                     auto qs4 = [&](int ks, float (&f)[4]) {
                         const int d0 = ks * 16 + tig * 4;
                         const uint2 qv = *reinterpret_cast<const uint2 *>(qrow + d0);
                         uint2 sv;
-                        if (p.aq_per_tensor) sv.x = sv.y = (uint32_t)sk[0] * 0x10001u;
+                        if (sk == nullptr) sv.x = sv.y = (uint32_t)QTraits<QT>::from_float(1.f) * 0x10001u;
+                        else if (p.aq_per_tensor) sv.x = sv.y = (uint32_t)sk[0] * 0x10001u;
                         else sv = *reinterpret_cast<const uint2 *>(sk + d0);
                         f[0] = QTraits<QT>::to_float(qv.x & 0xffff) * QTraits<QT>::to_float(sv.x & 0xffff);
                         f[1] = QTraits<QT>::to_float(qv.x >> 16) * QTraits<QT>::to_float(sv.x >> 16);
@@ -899,29 +957,39 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
                     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
                     const uint32_t ex = min(max((__float_as_uint(amax) >> 23) & 0xffu, 1u), 253u);
-                    const float up = __uint_as_float((254u - ex) << 23) * kQDigitRange;     // amax -> [63.5, 127)
+                    const float up = __uint_as_float((254u - ex) << 23) * (KVK == kKvI8 ? kQDigitRange : 1.f);   // int8: amax -> [63.5, 127); FP8: [1, 2)
                     const float down = __uint_as_float(ex << 23);                          // inverse of the power of two
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks) {
-                        // ks = 2j: the b0 quad of k-step j, ks = 2j + 1: its b1 quad; digit 1 -> qf[2j], digit 2 -> qf[2j+1]
                         uint32_t v1 = 0, v2 = 0;
                         if (h < p.g) {
                             float f[4];
                             qs4(ks, f);
+                            if (KVK == kKvI8) {
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                int d1, d2;
-                                split_digits(f[e] * up, d1, d2);
-                                v1 |= ((uint32_t)d1 & 0xffu) << (8 * e);
-                                v2 |= ((uint32_t)d2 & 0xffu) << (8 * e);
+                                for (int e = 0; e < 4; ++e) {
+                                    int d1, d2;
+                                    split_digits(f[e] * up, d1, d2);
+                                    v1 |= ((uint32_t)d1 & 0xffu) << (8 * e);
+                                    v2 |= ((uint32_t)d2 & 0xffu) << (8 * e);
+                                }
+                            } else {
+                                v1 = QTraits<MT>::pack2(f[0] * up, f[1] * up);
+                                v2 = QTraits<MT>::pack2(f[2] * up, f[3] * up);
                             }
                         }
-                        qf[nt][(ks & ~1)][ks & 1] = v1; qf[nt][(ks & ~1) + 1][ks & 1] = v2;
+                        if (KVK == kKvI8) {
+                            // ks = 2j: the b0 quad of k-step j, ks = 2j + 1: its b1 quad; digit 1 -> qf[2j], digit 2 -> qf[2j+1]
+                            qf[nt][(ks & ~1)][ks & 1] = v1; qf[nt][(ks & ~1) + 1][ks & 1] = v2;
+                        } else {
+                            qf[nt][ks][0] = v1; qf[nt][ks][1] = v2;
+                        }
                     }
                     // the softmax holds head nt*8 + 2*tig + e: fetch that head's factor
 #pragma unroll
                     for (int e = 0; e < 2; ++e)
-                        hsc[nt][e] = p.scale_log2 * (1.f / (kQDigitRange * kQDigit2)) * __shfl_sync(0xffffffffu, down, (tig * 2 + e) * 4);
+                        hsc[nt][e] = p.scale_log2 * (KVK == kKvI8 ? 1.f / (kQDigitRange * kQDigit2) : 1.f) *
+                                     __shfl_sync(0xffffffffu, down, (tig * 2 + e) * 4);
                 }
             }
             // ---- running state: O^T[d][head] fragments, m (log2 domain), l (thread-partial)
@@ -953,7 +1021,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             const int ks[2] = {st[0], st[2]}, vs[2] = {st[1], st[3]};
             const uint32_t vph[2] = {ph[1], ph[3]};
             cnt += 2;
-            consume_pages<QT, KVI8, NT, 2>(p, stage_u32, ks, vs, vph, metas, tails, qf, o, m_run, l_run, hsc, full, empty);
+            consume_pages<QT, KVK, NT, 2>(p, stage_u32, ks, vs, vph, metas, tails, qf, o, m_run, l_run, hsc, full, empty);
             stage = st[3] + 1; phase = ph[3];
             if (stage == nstages) { stage = 0; phase ^= 1u; }
         } else {
@@ -964,7 +1032,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             const int ks[1] = {stage}, vs[1] = {st1};
             const uint32_t vph[1] = {ph1};
             cnt += 1;
-            consume_pages<QT, KVI8, NT, 1>(p, stage_u32, ks, vs, vph, metas, tails, qf, o, m_run, l_run, hsc, full, empty);
+            consume_pages<QT, KVK, NT, 1>(p, stage_u32, ks, vs, vph, metas, tails, qf, o, m_run, l_run, hsc, full, empty);
             stage = st1 + 1; phase = ph1;
             if (stage == nstages) { stage = 0; phase ^= 1u; }
         }

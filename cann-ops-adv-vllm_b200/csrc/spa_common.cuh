@@ -219,10 +219,12 @@ template <> struct QTraits<__nv_bfloat16> {
     }
 };
 
-// Element type of the attention matmuls: the query dtype, except that int8 KV always runs in fp16
-// (exact and cheap int8 -> fp16 conversion; see attention_phase).
-template <typename QT, bool KVI8> struct MmaType { typedef QT type; };
-template <typename QT> struct MmaType<QT, true> { typedef __half type; };
+// KV kind of a chain-kernel instantiation: the query dtype (fp16 / bf16), int8 with antiquant, FP8 e4m3
+enum : int { kKvSame = 0, kKvI8 = 1, kKvF8 = 2 };
+// Element type of the attention matmuls: the query dtype, except that 8-bit KV always runs in fp16
+// (exact and cheap int8 / e4m3 -> fp16 conversion; see attention_phase).
+template <typename QT, int KVK> struct MmaType { typedef __half type; };
+template <typename QT> struct MmaType<QT, 0> { typedef QT type; };
 
 // ---- mbarrier / TMA (PTX ISA 8.x, sm_90+/sm_100a) -----------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
@@ -346,6 +348,13 @@ constexpr float kQDigit2 = 254.f;
 __device__ __forceinline__ void split_digits(float u, int &d1, int &d2) {
     d1 = __float2int_rn(u);
     d2 = __float2int_rn((u - (float)d1) * kQDigit2);
+}
+
+// two FP8 (e4m3) values in the low 16 bits of v -> f16x2 (exact: every e4m3 value is an fp16 value); low byte -> low half
+__device__ __forceinline__ uint32_t cvt_e4m3x2_f16x2(uint32_t v) {
+    uint32_t d;
+    asm("{\n.reg .b16 t;\ncvt.u16.u32 t, %1;\ncvt.rn.f16x2.e4m3x2 %0, t;\n}" : "=r"(d) : "r"(v));
+    return d;
 }
 
 // ---- int8 -> fp16/bf16 pairs (exact), for the fused KV antiquant ------------------------------

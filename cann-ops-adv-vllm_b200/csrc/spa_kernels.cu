@@ -74,7 +74,7 @@ __device__ __noinline__ void peer_exchange_flags(const ChainParams &p) {
     *reinterpret_cast<unsigned long long *>(p.sig_local + kSigWaitNs) += globaltimer_ns() - t_in;
 }
 
-template <typename QT, bool KVI8, int NT>
+template <typename QT, int KVK, int NT>
 __global__ void __launch_bounds__(kThreads, 1)
 spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmC) {
@@ -95,7 +95,7 @@ spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ 
         for (int item = blockIdx.x; item < p.items; item += gridDim.x) union_from_block_position(p, item, smem, &pub);
     trace_mark(p, 1);
     // ---- phase B + C: stream own prefixes and claimed chunks; the CTA completing an item combines it
-    attention_phase<QT, KVI8, NT>(p, &tmK, &tmV, smem, &pub);
+    attention_phase<QT, KVK, NT>(p, &tmK, &tmV, smem, &pub);
     trace_mark(p, 3);
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -158,7 +158,8 @@ struct spaExecutor {
     CUtensorMap tmK, tmV, tmC;
     int flags;            // selection flags
     int grid;
-    int q_bf16, kv_i8, nt_tiles;
+    int q_bf16, kv_i8, nt_tiles;       // kv_i8: 8-bit KV pages (int8 or FP8)
+    int kv_f8;                         // ... of which FP8 e4m3
     uint64_t ws_bytes;
     // workspace offsets (bytes)
     uint64_t off_ctrl, off_flat, off_desc, off_info, off_ippl, off_po, off_pml, off_xs;
@@ -193,6 +194,7 @@ static const char *dtype_name(int d) {
     switch (d) {
         case SPA_F16: return "float16"; case SPA_BF16: return "bfloat16"; case SPA_F32: return "float32";
         case SPA_I8: return "int8"; case SPA_I32: return "int32"; case SPA_I64: return "int64";
+        case SPA_F8E4M3: return "float8_e4m3";
     }
     return "?";
 }
@@ -338,7 +340,7 @@ static int make_kv_map(CUtensorMap *map, const spaTensor *t, const KvLayout &L, 
                        int *ax_row, int *ax_head, int *ax_blk, const char *name) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) return fail(SPA_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
-    const int esz = (t->dtype == SPA_I8) ? 1 : 2;
+    const int esz = (t->dtype == SPA_I8 || t->dtype == SPA_F8E4M3) ? 1 : 2;
     struct Ax { long long size, stride; int id; };
     Ax ax[3] = {{bs, L.s_row * esz, 0}, {Nkv, L.s_head * esz, 1}, {L.nblocks, L.s_blk * esz, 2}};
     // size-1 axes carry arbitrary strides: push them outermost and give them a consistent stride
@@ -362,7 +364,7 @@ static int make_kv_map(CUtensorMap *map, const spaTensor *t, const KvLayout &L, 
         if (ax[i].id == 2) *ax_blk = i + 1;
     }
     if (reinterpret_cast<uintptr_t>(t->data) & 15) return fail(SPA_ERR_SHAPE, "%s: must be 16-byte aligned", name);
-    CUtensorMapDataType dt = t->dtype == SPA_I8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+    CUtensorMapDataType dt = (t->dtype == SPA_I8 || t->dtype == SPA_F8E4M3) ? CU_TENSOR_MAP_DATA_TYPE_UINT8
                              : t->dtype == SPA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                     : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
     // L2 fetch granularity: a token row of one kv head is kD*esz contiguous bytes.  With int8 KV in the vLLM
@@ -397,11 +399,15 @@ static int make_cent_map(CUtensorMap *map, const void *cent, int rows, int bf16)
 // kernel dispatch tables
 // ---------------------------------------------------------------------------------------------
 typedef void (*ChainKernel)(const ChainParams, const CUtensorMap, const CUtensorMap, const CUtensorMap);
-static ChainKernel chain_kernel_for(int bf16, int kvi8, int nt) {
-    if (!bf16 && !kvi8) return nt == 1 ? spa_chain_kernel<__half, false, 1> : spa_chain_kernel<__half, false, 2>;
-    if (bf16 && !kvi8) return nt == 1 ? spa_chain_kernel<__nv_bfloat16, false, 1> : spa_chain_kernel<__nv_bfloat16, false, 2>;
-    if (!bf16 && kvi8) return nt == 1 ? spa_chain_kernel<__half, true, 1> : spa_chain_kernel<__half, true, 2>;
-    return nt == 1 ? spa_chain_kernel<__nv_bfloat16, true, 1> : spa_chain_kernel<__nv_bfloat16, true, 2>;
+static ChainKernel chain_kernel_for(int bf16, int kvk, int nt) {       // kvk: kKvSame / kKvI8 / kKvF8
+    if (!bf16) {
+        if (kvk == kKvSame) return nt == 1 ? spa_chain_kernel<__half, kKvSame, 1> : spa_chain_kernel<__half, kKvSame, 2>;
+        if (kvk == kKvI8) return nt == 1 ? spa_chain_kernel<__half, kKvI8, 1> : spa_chain_kernel<__half, kKvI8, 2>;
+        return nt == 1 ? spa_chain_kernel<__half, kKvF8, 1> : spa_chain_kernel<__half, kKvF8, 2>;
+    }
+    if (kvk == kKvSame) return nt == 1 ? spa_chain_kernel<__nv_bfloat16, kKvSame, 1> : spa_chain_kernel<__nv_bfloat16, kKvSame, 2>;
+    if (kvk == kKvI8) return nt == 1 ? spa_chain_kernel<__nv_bfloat16, kKvI8, 1> : spa_chain_kernel<__nv_bfloat16, kKvI8, 2>;
+    return nt == 1 ? spa_chain_kernel<__nv_bfloat16, kKvF8, 1> : spa_chain_kernel<__nv_bfloat16, kKvF8, 2>;
 }
 typedef void (*SelectKernel)(const ChainParams, const CUtensorMap);
 static SelectKernel select_kernel_for(int bf16, int flags) {
@@ -828,9 +834,10 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     p.bs = (int)blockSize;
     REQUIRE_PRESENT(key, "key"); REQUIRE_PRESENT(value, "value");
     if (key->dtype != value->dtype) return fail(SPA_ERR_DTYPE, "key/value dtypes differ");
-    e->kv_i8 = key->dtype == SPA_I8;
+    e->kv_f8 = key->dtype == SPA_F8E4M3;
+    e->kv_i8 = key->dtype == SPA_I8 || e->kv_f8;
     if (!e->kv_i8 && key->dtype != query->dtype)
-        return fail(SPA_ERR_DTYPE, "key dtype %s must equal query dtype %s or int8", dtype_name(key->dtype), dtype_name(query->dtype));
+        return fail(SPA_ERR_DTYPE, "key dtype %s must equal query dtype %s, int8 or float8_e4m3", dtype_name(key->dtype), dtype_name(query->dtype));
     KvLayout LK, LV;
     if ((rc = parse_kv(key, "key", p.Nkv, p.bs, &LK))) return rc;
     if ((rc = parse_kv(value, "value", p.Nkv, p.bs, &LV))) return rc;
@@ -841,7 +848,10 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     if (ar != vr || ah != vh || ab != vb) return fail(SPA_ERR_SHAPE, "key and value pools must share a layout");
     p.ax_row = ar; p.ax_head = ah; p.ax_blk = ab;
     // antiquant: non-empty <=> int8 KV
-    if (e->kv_i8) {
+    if (e->kv_f8 && absent(aqs)) {
+        // FP8 (e4m3) pages are numbers already: scale (and offset) are optional
+        if (!absent(aqo)) return fail(SPA_ERR_ARG, "antiquant_offset given without antiquant_scale");
+    } else if (e->kv_i8) {
         if (absent(aqs)) return fail(SPA_ERR_ARG, "int8 KV requires antiquant_scale");
         if (aqs->dtype != query->dtype) return fail(SPA_ERR_DTYPE, "antiquant_scale dtype must equal query dtype");
         const int64_t n = numel(aqs);
@@ -856,7 +866,7 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
             p.aq_offset = aqo->data;
         }
     } else if (!absent(aqs) || !absent(aqo)) {
-        return fail(SPA_ERR_ARG, "antiquant_scale/offset given but KV is not int8");
+        return fail(SPA_ERR_ARG, "antiquant_scale/offset given but KV is neither int8 nor float8_e4m3");
     }
     REQUIRE_PRESENT(blocktable, "blocktable"); REQUIRE_DTYPE(blocktable, SPA_I32, "blocktable");
     if (blocktable->ndim != 2 || blocktable->strides[1] != 1) return fail(SPA_ERR_SHAPE, "blocktable: expected [maxB,maxP]");
@@ -906,7 +916,7 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     // the producer stages every run's query rows (and the K scales) in shared memory ahead of the consumers
     // (bulk copies: 16-byte aligned rows); otherwise the consumers read them from global memory per segment
     p.q_stage = e->kv_i8 && (reinterpret_cast<uintptr_t>(p.q) % 16 == 0) && p.q_sb % 8 == 0 && p.q_sh % 8 == 0 &&
-                (p.aq_per_tensor || reinterpret_cast<uintptr_t>(p.aq_scale) % 16 == 0);      // (int8 KV kernels only)
+                (p.aq_per_tensor || reinterpret_cast<uintptr_t>(p.aq_scale) % 16 == 0);      // (8-bit KV kernels only)
     if (const char *s = getenv("SPA_Q_STAGE")) p.q_stage = p.q_stage && atoi(s) != 0;
     int nst = e->kv_i8 ? 12 : 6;
     for (; nst >= 2; --nst)
@@ -923,7 +933,7 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     }
     p.smem_bytes = std::max(attn_bytes, sel_bytes) + 1024;
     if (p.smem_bytes > d.smem_optin) return fail(SPA_ERR_UNSUPPORTED, "shared memory need %d > %d", p.smem_bytes, d.smem_optin);
-    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);
+    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_f8 ? kKvF8 : (e->kv_i8 ? kKvI8 : kKvSame), e->nt_tiles);
     if ((rc = raise_smem_limit((const void *)kern, d.smem_optin))) return rc;
     int occ = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, p.smem_bytes));
@@ -965,7 +975,7 @@ static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaSt
     p.item_ppl = (int *)(w + e->off_ippl);
     p.part_o = (float *)(w + e->off_po); p.part_ml = (float *)(w + e->off_pml);
     p.exact_scratch = (double *)(w + e->off_xs);
-    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_i8, e->nt_tiles);   // (smem limit raised once, in plan_attention)
+    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_f8 ? kKvF8 : (e->kv_i8 ? kKvI8 : kKvSame), e->nt_tiles);   // (smem limit raised once, in plan_attention)
     // queue words start at zero and the kernel leaves them at zero again, but the workspace is the
     // caller's scratch: clear it unless the caller vouches for it (spaExecutorSetPersistentWorkspace).
     // "Known clean" is only recorded for a clear that really executes: under stream capture the memset is

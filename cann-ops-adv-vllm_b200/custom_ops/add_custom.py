@@ -83,7 +83,8 @@ def sparse_paged_attention(query: torch.Tensor,
                            block_size: int,
                            inner_precise: int,
                            *, softmax_lse: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Paged flash-decode over the pages listed in `blockposition` (add_custom.py:41-75).
+    """Paged flash-decode over the pages listed in `blockposition` (add_custom.py:41-75).  key / value: the query
+    dtype, int8 with `antiquant_scale` (+ `antiquant_offset`), or torch.float8_e4m3fn (scales optional).
 
     `softmax_lse`: optional caller-allocated float32 [B, Nq], filled with ln(sum exp(scale * q.k)) per row
     (the reference kernels' softmaxLse output); fp16/bf16 and int8 KV."""

@@ -43,7 +43,8 @@ typedef enum {
 
 /* dtype codes (subset the reference binding converts, add_custom.cpp:43-70) */
 typedef enum {
-    SPA_F16 = 0, SPA_BF16 = 1, SPA_F32 = 2, SPA_I8 = 3, SPA_I32 = 4, SPA_I64 = 5
+    SPA_F16 = 0, SPA_BF16 = 1, SPA_F32 = 2, SPA_I8 = 3, SPA_I32 = 4, SPA_I64 = 5,
+    SPA_F8E4M3 = 6             /* FP8 e4m3 KV pages (attention ops only; no reference analogue) */
 } spaDtype;
 
 #define SPA_MAX_DIMS 8
@@ -150,6 +151,9 @@ SPA_API int spaCentSelect(void *workspace, uint64_t workspaceSize, spaExecutor *
  *      1-element tensor lists, add_custom.py:70-75).
  * actualSeqLengths: DEVICE int64 [B] or [1] (the reference copies it to the host,
  *      add_custom.cpp:105-118; here it is read on device, no sync).
+ * key / value dtype: the query dtype, int8 with antiquantScale (+ optional antiquantOffset) [2,Nkv,D] or [2] in the
+ *      query dtype (x = (x_i8 + offset) * scale; row 0 = K, row 1 = V), or SPA_F8E4M3 (FP8 e4m3 pages -- no
+ *      reference analogue; scale / offset optional with the same formula, absent = the stored numbers).
  * blockPosition [B, Nkv or Nq, MP] int32, 0x7fffffff-terminated.  A logical page listed more than once in a
  *      row is attended ONCE (the reference walks the slots and would weigh it twice; no reference test
  *      repeats a page).

@@ -47,8 +47,10 @@ def fused_chain(query, key, value, block_table, l1_cent, block_ids, seq_len, num
     ppl = ln.reshape(B, Nq, 1).expand(B, Nq, 8).to(torch.int32).contiguous()
     mppl = (ln.reshape(B, Nq).amax(dim=1) * bs).view(B, 1).expand(B, 8).to(torch.int64).contiguous()
     # ---- attention over the union of the group's pages, one (b, kv head) item at a time
-    i8 = key.dtype == torch.int8
-    if i8:
+    i8 = key.dtype in (torch.int8, torch.float8_e4m3fn)
+    if i8 and (antiquant_scale is None or antiquant_scale.numel() == 0):
+        sc, of = torch.ones(2, 1, 1), torch.zeros(2, 1, 1)                              # FP8 pages without scales
+    elif i8:
         sc = antiquant_scale.float().reshape(2, -1, D) if antiquant_scale.numel() > 2 else antiquant_scale.float().view(2, 1, 1)
         of = (antiquant_offset.float().reshape(2, -1, D) if antiquant_offset.numel() > 2 else antiquant_offset.float().view(2, 1, 1)) \
             if antiquant_offset is not None and antiquant_offset.numel() else torch.zeros_like(sc)

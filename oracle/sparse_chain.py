@@ -212,7 +212,9 @@ def attend_lists(
     K = _kv_view(key.detach().cpu(), Nkv, block_size, D)
     V = _kv_view(value.detach().cpu(), Nkv, block_size, D)
     bt = block_table.detach().cpu().to(torch.int64)
-    is_i8 = K.dtype == torch.int8
+    # 8-bit KV: int8 with antiquant (x = (x_i8 + offset) * scale), or FP8 e4m3 (no reference analogue: numbers
+    # already; scale / offset optional, same formula)
+    is_i8 = K.dtype in (torch.int8, torch.float8_e4m3fn)
     ft = torch.float64 if dtype64 else torch.float32
     if is_i8:
         sc, of = _antiquant(antiquant_scale, antiquant_offset, Nkv, D)

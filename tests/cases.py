@@ -6,7 +6,7 @@ import torch
 
 def make_case(seed, B, Nq, Nkv, C, S, kv_pages=None, maxP=None, maxB=None, D=128, bs=128,
               qdtype=torch.float16, kv_int8=False, cent_dist="rand", ragged=False, permute_table=False,
-              MP=256, device="cpu"):
+              MP=256, device="cpu", kv_fp8=False):
     """Shapes follow tests/cent_select.py:17-53 and fused_ifa_v5_case.py:21-78 of the reference:
     q ~ U[0,1), centroids ~ U[0,1) (or N(0,1)), block_ids ~ randint(0,C), block_table ~
     randint(0,kvPageLen) (collisions allowed) or a per-sequence permutation, K/V ~ U[1e-3,1)."""
@@ -36,6 +36,16 @@ def make_case(seed, B, Nq, Nkv, C, S, kv_pages=None, maxP=None, maxB=None, D=128
         value = torch.randint(-128, 128, (kv_pages, bs, Nkv, D), generator=g, dtype=torch.int8)
         aq_scale = (torch.rand(2, Nkv, D, generator=g) * 0.02 + 0.005).to(qdtype)
         aq_offset = torch.randn(2, Nkv, D, generator=g).to(qdtype)
+    elif kv_fp8:
+        # FP8 e4m3 pages: signed values over a few octaves; scales optional (kv_fp8 == "scaled")
+        key = (torch.randn(kv_pages, bs, Nkv, D, generator=g) * 2.0).to(torch.float8_e4m3fn)
+        value = (torch.randn(kv_pages, bs, Nkv, D, generator=g) * 2.0).to(torch.float8_e4m3fn)
+        if kv_fp8 == "scaled":
+            aq_scale = (torch.rand(2, Nkv, D, generator=g) * 0.5 + 0.25).to(qdtype)
+            aq_offset = (torch.randn(2, Nkv, D, generator=g) * 0.1).to(qdtype)
+        else:
+            aq_scale = torch.empty(0, dtype=qdtype)
+            aq_offset = torch.empty(0, dtype=qdtype)
     else:
         key = (torch.rand(kv_pages, bs, Nkv, D, generator=g) * (1 - eps) + eps).to(qdtype)
         value = (torch.rand(kv_pages, bs, Nkv, D, generator=g) * (1 - eps) + eps).to(qdtype)

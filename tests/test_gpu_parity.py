@@ -953,3 +953,44 @@ def test_block_sizes_below_128(ops, bs, int8):
     want_s = oc.sparse_paged_attention(c["q"], c["key"], c["value"], asl.cpu(), c["block_table"], pp.cpu(), Nq, c["scale"],
                                        Nkv, bs, *aq)
     assert_close(out_s, want_s, tol, f"separate, block_size {bs}")
+
+
+# ------------------------------------------------------------------------------------------
+# FP8 (e4m3) KV pages: SURVEY 8(f) F4's B200-native option (no reference analogue)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("qdtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("scaled", [False, "scaled"])
+@pytest.mark.parametrize("g16", [False, True])
+def test_fp8_kv_fused_and_separate(ops, qdtype, scaled, g16):
+    """float8_e4m3fn K/V pools through the same ops: x = (fp8 + offset) * scale with optional [2, Nkv, D] scale /
+    offset (absent: the stored numbers are the values).  Fused op and the separate chain against the oracle, which
+    dequantises in float32; tolerance of the 8-bit paths (2e-2).  Also the softmax LSE."""
+    B, Nq, Nkv, C, S, k = (2, 32, 2, 64, 6000, 8) if g16 else (3, 32, 8, 128, 9000, 16)
+    c = make_case(606, B, Nq, Nkv, C, S, kv_pages=B * 72 + 3, ragged=True, permute_table=True, qdtype=qdtype,
+                  kv_fp8=scaled or True)
+    c["scale"] = 0.02                                   # keeps the logits of N(0, 2) keys in a softmax-friendly range
+    g = to_device(c, DEV)
+    aq = (c["aq_scale"], c["aq_offset"]) if scaled else (None, None)
+    lse_w = torch.empty(B, Nq, dtype=torch.float32)
+    want = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"],
+                                            c["seq"], Nq, c["scale"], Nkv, 128, k, 256, *aq, lse_out=lse_w)
+    dev = g["q"].device
+    bp = torch.full((B, Nq, 256), 7, dtype=torch.int32, device=dev)
+    ppl = torch.full((B, Nq, 8), 7, dtype=torch.int32, device=dev)
+    mppl = torch.full((B, 8), 7, dtype=torch.int64, device=dev)
+    lse = torch.empty(B, Nq, dtype=torch.float32, device=dev)
+    e = torch.empty(0, dtype=qdtype, device=dev)
+    e64 = torch.empty(0, dtype=torch.int64, device=dev)
+    out, _, _ = ops.sparse_paged_fusion_attention(
+        g["q"], g["key"], g["value"], e, e, e64, e, e, e, e, e, g["aq_scale"], g["aq_offset"], g["block_table"], e64,
+        g["l1"], g["block_ids"], g["seq"], bp, ppl, mppl, Nq, c["scale"], "BNSD", Nkv, 128, 1, k=k, softmax_lse=lse)
+    assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2]) and torch.equal(mppl.cpu(), want[3])
+    assert_close(out, want[0], 2e-2, "fused, FP8 KV")
+    fin = torch.isfinite(lse_w)
+    assert torch.equal(torch.isfinite(lse.cpu()), fin)
+    assert bool(((lse.cpu()[fin] - lse_w[fin]).abs() < 2e-2).all()), "softmax LSE, FP8 KV"
+    asl = mppl[:, 0].contiguous()
+    out_s = attn_call(ops, g, bp, asl)
+    want_s = oc.sparse_paged_attention(c["q"], c["key"], c["value"], asl.cpu(), c["block_table"], bp.cpu(), Nq, c["scale"],
+                                       Nkv, 128, *aq)
+    assert_close(out_s, want_s, 2e-2, "separate, FP8 KV")
