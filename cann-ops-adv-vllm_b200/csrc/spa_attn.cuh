@@ -60,7 +60,7 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
     if (KVK != 0 && Lsum > 0.f) {
         // V dequant applied once to the normalised sum: (O + offset_v) * scale_v (…_Us2.h:3655-3670).  int8 pages
         // entered the matmul biased by 1152 (see consume_pages); FP8 pages need no scale at all (absent = 1)
-        const unsigned short *sv = p.aq_scale ? reinterpret_cast<const unsigned short *>(p.aq_scale) +
+        const unsigned short *sv = (KVK == kKvI8 || p.aq_scale) ? reinterpret_cast<const unsigned short *>(p.aq_scale) +
                                    (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD) : nullptr;
         const unsigned short *ov = p.aq_offset ? reinterpret_cast<const unsigned short *>(p.aq_offset) +
                                    (p.aq_per_tensor ? 1 : (size_t)(p.Nkv + n2) * kD) : nullptr;
@@ -68,7 +68,7 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
         for (int e = 0; e < NV; ++e) {
             const int d = p.aq_per_tensor ? 0 : d0 + e;
             const float off = ov ? QTraits<QT>::to_float(ov[d]) : 0.f;
-            const float scl = sv ? QTraits<QT>::to_float(sv[d]) : 1.f;
+            const float scl = (KVK == kKvI8 || sv) ? QTraits<QT>::to_float(sv[d]) : 1.f;
             r[e] = ((KVK == 1 ? r[e] - kI8Bias : r[e]) + off) * scl;             // int8: O'/l - 1152 = O/l
         }
     }
@@ -102,14 +102,14 @@ __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, i
     if (KVK != 0) {
         const unsigned short *qrow = reinterpret_cast<const unsigned short *>(p.q) + (size_t)b * p.q_sb +
                                      (size_t)(n2 * p.g + h) * p.q_sh + lane * 4;
-        const unsigned short *sk = p.aq_scale ? reinterpret_cast<const unsigned short *>(p.aq_scale) + (p.aq_per_tensor ? 0 : (size_t)n2 * kD + lane * 4) : nullptr;
+        const unsigned short *sk = (KVK == kKvI8 || p.aq_scale) ? reinterpret_cast<const unsigned short *>(p.aq_scale) + (p.aq_per_tensor ? 0 : (size_t)n2 * kD + lane * 4) : nullptr;
         const unsigned short *ok = p.aq_offset ? reinterpret_cast<const unsigned short *>(p.aq_offset) +
                                    (p.aq_per_tensor ? 0 : (size_t)n2 * kD + lane * 4) : nullptr;
         float f[4], off[4], amax = 0.f;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             const int j = p.aq_per_tensor ? 0 : e;
-            f[e] = QTraits<QT>::to_float(qrow[e]) * (sk ? QTraits<QT>::to_float(sk[j]) : 1.f);
+            f[e] = QTraits<QT>::to_float(qrow[e]) * ((KVK == kKvI8 || sk) ? QTraits<QT>::to_float(sk[j]) : 1.f);
             off[e] = ok ? QTraits<QT>::to_float(ok[j]) : 0.f;
             amax = fmaxf(amax, fabsf(f[e]));
         }
@@ -807,7 +807,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                         metaS[stage] = md;
                         uint32_t tx = (uint32_t)p.page_tx;
                         const bool with_q = stage_q && kv == 0;
-                        const bool with_s = with_q && !p.aq_per_tensor && p.aq_scale != nullptr;
+                        const bool with_s = with_q && !p.aq_per_tensor && (KVK == kKvI8 || p.aq_scale != nullptr);
                         if (with_q) {
                             // the rows of this run travel with its first K page and complete on the same barrier
                             if (2 * (pg - (qi ? qpg1 : qpg0)) <= nstages) mbar_wait(&empty[qi ? qstg1 : qstg0], qi ? qph1 : qph0);
@@ -930,14 +930,14 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                     // FP8 (e4m3) KV: the same folding, but K is converted to fp16 (exact) and Q enters as
                     // fp16(q * scale_k * 2^n) in the k-slot permutation of the converted fragments: b0 = Q[h][16ks +
                     // 4tig, +1], b1 = Q[h][16ks + 4tig + 2, +3].  Scales are optional for FP8 (absent = 1).
-                    const unsigned short *sk = (p.aq_scale == nullptr) ? nullptr
+                    const unsigned short *sk = (KVK == kKvF8 && p.aq_scale == nullptr) ? nullptr      // (int8: always present)
                                                : (sk_staged != nullptr && !p.aq_per_tensor) ? sk_staged
                                                : reinterpret_cast<const unsigned short *>(p.aq_scale) + (p.aq_per_tensor ? 0 : (size_t)n2 * kD);
                     auto qs4 = [&](int ks, float (&f)[4]) {
                         const int d0 = ks * 16 + tig * 4;
                         const uint2 qv = *reinterpret_cast<const uint2 *>(qrow + d0);
                         uint2 sv;
-                        if (sk == nullptr) sv.x = sv.y = (uint32_t)QTraits<QT>::from_float(1.f) * 0x10001u;
+                        if (KVK == kKvF8 && sk == nullptr) sv.x = sv.y = (uint32_t)QTraits<QT>::from_float(1.f) * 0x10001u;
                         else if (p.aq_per_tensor) sv.x = sv.y = (uint32_t)sk[0] * 0x10001u;
                         else sv = *reinterpret_cast<const uint2 *>(sk + d0);
                         f[0] = QTraits<QT>::to_float(qv.x & 0xffff) * QTraits<QT>::to_float(sv.x & 0xffff);
@@ -945,14 +945,15 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                         f[2] = QTraits<QT>::to_float(qv.y & 0xffff) * QTraits<QT>::to_float(sv.y & 0xffff);
                         f[3] = QTraits<QT>::to_float(qv.y >> 16) * QTraits<QT>::to_float(sv.y >> 16);
                     };
+                    // (q * scale_k is evaluated once and kept: the accumulators' registers are free at a segment start,
+                    // and this set-up is on the 8-bit stream's critical path -- every consumer warp runs it per segment)
+                    float fq[8][4];
                     float amax = 0.f;
-                    if (h < p.g) {
 #pragma unroll
-                        for (int ks = 0; ks < 8; ++ks) {
-                            float f[4];
-                            qs4(ks, f);
-                            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(f[0]), fabsf(f[1])), fmaxf(fabsf(f[2]), fabsf(f[3]))));
-                        }
+                    for (int ks = 0; ks < 8; ++ks) {
+                        fq[ks][0] = fq[ks][1] = fq[ks][2] = fq[ks][3] = 0.f;
+                        if (h < p.g) qs4(ks, fq[ks]);
+                        amax = fmaxf(amax, fmaxf(fmaxf(fabsf(fq[ks][0]), fabsf(fq[ks][1])), fmaxf(fabsf(fq[ks][2]), fabsf(fq[ks][3]))));
                     }
                     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
                     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
@@ -962,9 +963,8 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks) {
                         uint32_t v1 = 0, v2 = 0;
-                        if (h < p.g) {
-                            float f[4];
-                            qs4(ks, f);
+                        {
+                            const float (&f)[4] = fq[ks];
                             if (KVK == kKvI8) {
 #pragma unroll
                                 for (int e = 0; e < 4; ++e) {

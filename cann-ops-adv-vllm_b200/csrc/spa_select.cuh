@@ -414,12 +414,17 @@ __device__ __forceinline__ void topk_classify(const ChainParams &p, const float 
     // one bitmap word per head: ballots, no per-lane atomics.
 #pragma unroll 1
     for (int h0 = 0; h0 < p.g; h0 += 4) {
-        float lo[4], inv[4], band[4];
-        int bstar[4];
+        // sel_bin(x) > b*  <=>  x * inv + c0 >= b* + 1  (no bin above the last one);  sel_bin(x) >= b*  <=>  x * inv + c0 >= b*:
+        // float compares instead of a floor conversion per element.  The band is folded into the constants.
+        float inv[4], cin[4], ccd[4], tin[4], tcd[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int h = min(h0 + u, p.g - 1);
-            lo[u] = hd[h].lo; inv[u] = hd[h].inv; band[u] = hd[h].band; bstar[u] = hd[h].bstar;
+            inv[u] = hd[h].inv;
+            cin[u] = fmaf(-hd[h].band, hd[h].inv, hd[h].lo);          // (a - band) * inv + c0, up to one rounding: the
+            ccd[u] = fmaf(hd[h].band, hd[h].inv, hd[h].lo);           // band carries a 6 % safety factor for that
+            tin[u] = (hd[h].bstar >= kSelBins - 1) ? INFINITY : (float)(hd[h].bstar + 1);
+            tcd[u] = (float)hd[h].bstar;
         }
         const int nh = min(4, p.g - h0);
 #pragma unroll 1
@@ -432,8 +437,8 @@ __device__ __forceinline__ void topk_classify(const ChainParams &p, const float 
                 const float a = (c < p.C) ? sc[min(h0 + u, p.g - 1) * scs + c] : -INFINITY;
                 // above every score of the k-th score's bin even after the error band: certainly selected;
                 // able to reach that bin: candidate
-                const bool in = (c < p.C) && sel_bin(a - band[u], lo[u], inv[u]) > bstar[u];
-                cd[u] = (c < p.C) && !in && sel_bin(a + band[u], lo[u], inv[u]) >= bstar[u];
+                const bool in = (c < p.C) && fmaf(a, inv[u], cin[u]) >= tin[u];
+                cd[u] = (c < p.C) && !in && fmaf(a, inv[u], ccd[u]) >= tcd[u];
                 bin[u] = __ballot_sync(0xffffffffu, in);
                 bcd[u] = __ballot_sync(0xffffffffu, cd[u]);
             }

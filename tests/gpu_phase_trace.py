@@ -7,7 +7,7 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "cann-ops-adv-vllm_b200"))
+sys.path.insert(0, os.environ.get("SPA_PKG_DIR") or os.path.join(ROOT, "cann-ops-adv-vllm_b200"))
 import bench  # noqa: E402
 import custom_ops  # noqa: E402
 
