@@ -33,17 +33,29 @@ def _run(cmd):
 
 def build_kernels(force=False, verbose=False):
     import glob
-    main = os.path.join(CSRC, "spa_kernels.cu")
-    srcs = [main] + sorted(f for f in glob.glob(os.path.join(CSRC, "*.cu*")) if f != main)   # every header it includes
-    srcs.append(os.path.join(HERE, "..", "include", "spa_b200.h"))
-    if not force and not _newer(LIB, srcs):
+    units = [os.path.join(CSRC, "spa_kernels.cu"), os.path.join(CSRC, "spa_kernels_opt.cu")]
+    deps = sorted(glob.glob(os.path.join(CSRC, "*.cu*")))                  # every source and header
+    deps.append(os.path.join(HERE, "..", "include", "spa_b200.h"))
+    if not force and not _newer(LIB, deps):
         return LIB
-    cmd = [os.path.join(CUDA_HOME, "bin", "nvcc"), "-gencode", "arch=compute_100a,code=sm_100a", "-O3",
-           "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared"]
+    nvcc = [os.path.join(CUDA_HOME, "bin", "nvcc"), "-gencode", "arch=compute_100a,code=sm_100a", "-O3",
+            "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC,-fvisibility=hidden"]
     if verbose:
-        cmd += ["-Xptxas", "-v"]
-    cmd += ["-o", LIB, srcs[0]]
-    _run(cmd)
+        nvcc += ["-Xptxas", "-v"]
+    # the two translation units (plain / options build of the chain kernel, csrc/spa_chain.cuh) compile in parallel
+    objdir = os.path.join(HERE, "_obj")
+    os.makedirs(objdir, exist_ok=True)
+    objs, procs = [], []
+    for u in units:
+        o = os.path.join(objdir, os.path.basename(u) + ".o")
+        cmd = nvcc + ["-c", "-o", o, u]
+        print("+", " ".join(cmd), flush=True)
+        procs.append((cmd, subprocess.Popen(cmd)))
+        objs.append(o)
+    for cmd, pr in procs:
+        if pr.wait() != 0:
+            raise subprocess.CalledProcessError(pr.returncode, cmd)
+    _run(nvcc + ["-shared", "-o", LIB] + objs)
     return LIB
 
 

@@ -36,6 +36,8 @@ int to_spa_dtype(at::ScalarType t) {
         case at::kFloat8_e4m3fn: return SPA_F8E4M3;
         case at::kInt: return SPA_I32;
         case at::kLong: return SPA_I64;
+        case at::kByte: return SPA_U8;             // attention_mask
+        case at::kBool: return SPA_BOOL;
         default: TORCH_CHECK(false, "Unsupported tensor dtype");   // add_custom.cpp:69
     }
 }
@@ -237,7 +239,9 @@ at::Tensor sparse_paged_attention_ex(
     TORCH_CHECK(query.is_cuda(), "sparse_paged_attention: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(query.device());
     const at::Tensor &key = single(key_list, "key_list"), &value = single(value_list, "value_list");
-    at::Tensor out = at::empty(query.sizes(), query.options());                  // add_custom.cpp:559-560
+    // add_custom.cpp:559-560 allocates the query's dtype; with quant_scale2 the op's output is int8
+    // (sparse_paged_attention_tiling.cc:570-602), which the reference binding cannot express -- here it can
+    at::Tensor out = at::empty(query.sizes(), quant_scale2.defined() && quant_scale2.numel() ? query.options().dtype(at::kChar) : query.options());
     at::Tensor asl = seq_on_device(actual_seq_lengths, query);
     Desc q = desc(query, "query"), k = desc(key, "key"), v = desc(value, "value"), pse = desc(pse_shift, "pse_shift"),
          am = desc(attention_mask, "attention_mask"), sl = desc(asl, "actual_seq_lengths"),
@@ -344,7 +348,8 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> sparse_paged_fusion_attention_ex(
     c10::cuda::CUDAGuard guard(query.device());
     const at::Tensor &key = single(key_list, "key_list"), &value = single(value_list, "value_list");
     (void)actual_seq_lengths;    // ignored by the fused kernel (sparse_paged_fusion_attention.cpp:68)
-    at::Tensor out = at::empty(query.sizes(), query.options());                  // add_custom.cpp:800-801
+    // add_custom.cpp:800-801; int8 with quant_scale2 (see sparse_paged_attention_ex)
+    at::Tensor out = at::empty(query.sizes(), quant_scale2.defined() && quant_scale2.numel() ? query.options().dtype(at::kChar) : query.options());
     Desc q = desc(query, "query"), kk = desc(key, "key"), v = desc(value, "value"), pse = desc(pse_shift, "pse_shift"),
          am = desc(attention_mask, "attention_mask"), d1 = desc(dequant_scale1, "dequant_scale1"),
          q1 = desc(quant_scale1, "quant_scale1"), d2 = desc(dequant_scale2, "dequant_scale2"),
@@ -449,9 +454,9 @@ at::Tensor incre_flash_attention_v4(
 at::Tensor meta_attention(
     const at::Tensor &query, const std::vector<at::Tensor> &, const std::vector<at::Tensor> &, const at::Tensor &,
     const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
-    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &quant_scale2, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
     const at::Tensor &, const at::Tensor &, int64_t, double, std::string, int64_t, int64_t, int64_t) {
-    return at::empty(query.sizes(), query.options());
+    return at::empty(query.sizes(), quant_scale2.numel() ? query.options().dtype(at::kChar) : query.options());
 }
 at::Tensor meta_attention_v4(
     const at::Tensor &query, const std::vector<at::Tensor> &, const std::vector<at::Tensor> &, const at::Tensor &,
@@ -482,12 +487,12 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> meta_cent_select(const at::Tensor
 std::tuple<at::Tensor, at::Tensor, at::Tensor> meta_fusion(
     const at::Tensor &query, const std::vector<at::Tensor> &, const std::vector<at::Tensor> &, const at::Tensor &,
     const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
-    const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
+    const at::Tensor &quant_scale2, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &,
     const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &, const at::Tensor &block_position,
     const at::Tensor &, const at::Tensor &max_page_position_length, int64_t, double, std::string, int64_t, int64_t,
     int64_t) {
     // fresh tensors of the caller-allocated shapes (a functional schema must not return its inputs)
-    return std::make_tuple(at::empty(query.sizes(), query.options()),
+    return std::make_tuple(at::empty(query.sizes(), quant_scale2.numel() ? query.options().dtype(at::kChar) : query.options()),
                            at::empty(block_position.sizes(), block_position.options()),
                            at::empty(max_page_position_length.sizes(), max_page_position_length.options()));
 }

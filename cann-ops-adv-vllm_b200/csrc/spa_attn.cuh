@@ -22,6 +22,7 @@ namespace spa {
 constexpr int kMergeHalf = 64;                          // head dims merged per round
 constexpr int kMergeHeadStride = kMergeHalf + 4;        // floats; +4 padding keeps the 4 lanes of a quad on distinct banks
 constexpr int kMergeWarpFloats = 8 * kMergeHeadStride;
+constexpr float kMaskedLog2 = -1e12f * kLog2e;         // BOOL_ATTEN_MASK_SCALAR_VALUE (..._Us2.h:757) in the log2 domain
 constexpr int kMailSlots = 4;                           // flush -> post-warp messages in flight
 constexpr int kPostWarp = kConsumerWarps + 1;           // warp 8: TMA producer, warps 9..11: partial bookkeeping + combine
 
@@ -50,7 +51,7 @@ __device__ __forceinline__ int o_dim(int mt, int gid, int r) {
 }
 
 // normalise NV consecutive head dims d0.. of one output row, V antiquant, store
-template <typename QT, int KVK, int NV>
+template <typename QT, int KVK, int NV, int OPT>
 __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int n2, int h, int d0, const float (&acc)[NV],
                                                float Lsum) {
     const float inv = (Lsum > 0.f) ? 1.f / Lsum : 0.f;
@@ -73,6 +74,31 @@ __device__ __forceinline__ void write_out_vals(const ChainParams &p, int b, int 
         }
     }
     const size_t off = (size_t)b * p.out_sb + (size_t)(n2 * p.g + h) * p.out_sh + d0;
+    if (OPT && p.pq_scale != nullptr) {
+        // int8 post-quant (PostQuant, ..._Us2.h:3513-3600): q = sat_s8(rint(x * scale2 + offset2)), parameters per
+        // tensor or per output channel [Nq, D], fp32 or bf16; the row is stored as bytes
+        const size_t chn = (size_t)(n2 * p.g + h) * kD + d0;
+        auto param = [&](const void *base, int per_chn, int e) -> float {
+            const size_t i = per_chn ? chn + e : 0;
+            return p.pq_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16 *>(base)[i])
+                             : reinterpret_cast<const float *>(base)[i];
+        };
+        unsigned char *ob = reinterpret_cast<unsigned char *>(p.out) + off;
+#pragma unroll
+        for (int e = 0; e < NV; e += 2) {
+            unsigned short two = 0;
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const float x = r[e + u] * param(p.pq_scale, p.pq_scale_chn, e + u) +
+                                (p.pq_offset ? param(p.pq_offset, p.pq_offset_chn, e + u) : 0.f);
+                // (a row that attended to nothing is all zeros, like the rows of an item without pages)
+                const int q = (Lsum > 0.f) ? max(-128, min(127, __float2int_rn(fminf(fmaxf(x, -1e9f), 1e9f)))) : 0;
+                two |= (unsigned short)((unsigned)q & 0xffu) << (8 * u);
+            }
+            *reinterpret_cast<unsigned short *>(ob + e) = two;
+        }
+        return;
+    }
     unsigned short *op = reinterpret_cast<unsigned short *>(p.out) + off;
     uint32_t pk[NV / 2];
 #pragma unroll
@@ -142,7 +168,7 @@ __device__ __forceinline__ void write_lse(const ChainParams &p, int b, int n2, i
 // word that counts the item's finished pages also collects one bit per partial (see post_warp_loop), so the
 // last arriver knows the slots without searching.  Latency-bound (everything sits in L2): (m, l) of every
 // partial and head in one round of loads, then the O rows of two heads x all partials per round trip.
-template <typename QT, int KVK, int NT>
+template <typename QT, int KVK, int NT, int OPT>
 __device__ void combine_item_warp(const ChainParams &p, int item, unsigned bits) {
     constexpr int HP = NT * 8;
     constexpr int NB = 8;                                     // partials per round of O-row loads
@@ -208,7 +234,7 @@ __device__ void combine_item_warp(const ChainParams &p, int item, unsigned bits)
         }
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-            if (e < nh) write_out_vals<QT, KVK, 4>(p, b, n2, h0 + e, lane * 4, acc[e], Ls[e]);
+            if (e < nh) write_out_vals<QT, KVK, 4, OPT>(p, b, n2, h0 + e, lane * 4, acc[e], Ls[e]);
             if (e < nh && p.lse != nullptr) write_lse<QT, KVK>(p, b, n2, h0 + e, M[e], Ls[e]);
         }
     }
@@ -222,7 +248,7 @@ __device__ void combine_item_warp(const ChainParams &p, int item, unsigned bits)
 // the items' publishers leave 1 + their maximum in item_ppl (non-zero once written); post warp 0 of CTA
 // (b mod grid) waits for the Nkv words of b, reduces, writes, and returns the words to zero.  Nothing else in the
 // launch waits for this, and the waiting warp has nothing to do until its CTA's first partial.
-__device__ __noinline__ void max_ppl_poll(const ChainParams &p) {
+static __device__ __noinline__ void max_ppl_poll(const ChainParams &p) {
     const int lane = lane_id();
     for (int b = blockIdx.x; b < p.B; b += gridDim.x) {
         int m = 0;
@@ -242,7 +268,7 @@ __device__ __noinline__ void max_ppl_poll(const ChainParams &p) {
     }
 }
 
-template <typename QT, int KVK, int NT>
+template <typename QT, int KVK, int NT, int OPT>
 __device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t *mfull, uint64_t *mempty) {
     const int lane = lane_id();
     int mi = 0;
@@ -265,7 +291,7 @@ __device__ void post_warp_loop(const ChainParams &p, const int4 *mail, uint64_t 
         if ((old & 0xffff) + cnt == len) {
             __threadfence();
             const unsigned long long tc0 = (p.dbg && lane == 0) ? globaltimer_ns() : 0ull;
-            combine_item_warp<QT, KVK, NT>(p, item, ((unsigned)old >> 16) | (1u << pid));
+            combine_item_warp<QT, KVK, NT, OPT>(p, item, ((unsigned)old >> 16) | (1u << pid));
             if (p.dbg && lane == 0 && p.trace) {
                 p.trace[(size_t)blockIdx.x * kTraceSlots + 10] += 1;
                 p.trace[(size_t)blockIdx.x * kTraceSlots + 11] += globaltimer_ns() - tc0;
@@ -290,7 +316,7 @@ __device__ __forceinline__ void post_message(int4 *mail, uint64_t *mfull, uint64
 
 // ---- segment flush: merge the 8 warps' running states of `item`; either finish the item (all of its
 // pages were in this segment) or leave a partial and tell the post warp.  All consumers.
-template <typename QT, int KVK, int NT>
+template <typename QT, int KVK, int NT, int OPT>
 __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, int pid, int cnt,
                                               unsigned long long rec, float (&o)[NT][8][4],
                                               float (&m_run)[NT][2], float (&l_run)[NT][2], float *mbuf,
@@ -366,7 +392,7 @@ __device__ __forceinline__ void flush_segment(const ChainParams &p, int item, in
             }
             const int d0 = half * kMergeHalf + lane * 2;
             if (whole) {
-                if (h < p.g) write_out_vals<QT, KVK, 2>(p, b, n2, h, d0, acc, Ls);
+                if (h < p.g) write_out_vals<QT, KVK, 2, OPT>(p, b, n2, h, d0, acc, Ls);
             } else {
                 *reinterpret_cast<float2 *>(p.part_o + ((size_t)slot * HP + h) * kD + d0) = make_float2(acc[0], acc[1]);
             }
@@ -395,10 +421,11 @@ __device__ __forceinline__ unsigned long long take_entry(const ChainParams &p, i
 // O^T += V^T P^T.  With PP = 2 the two pages' chains are interleaved instruction by instruction, the
 // running max is reduced once over both and O is rescaled once (and only when some max moved).
 // ks/vs: ring stages of the K and V tiles (K full barriers already passed), vph: parities of the V stages.
-template <typename QT, int KVK, int NT, int PP>
+template <typename QT, int KVK, int NT, int PP, int OPT>
 __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t stage_u32, const int (&ks)[PP],
                                               const int (&vs)[PP], const uint32_t (&vph)[PP],
                                               const unsigned (&metas)[PP], const int (&tails)[PP],
+                                              const int (&lps)[PP], int item,
                                               const uint32_t (&qf)[NT][8][2], float (&o)[NT][8][4],
                                               float (&m_run)[NT][2], float (&l_run)[NT][2],
                                               const float (&hsc)[NT][2], uint64_t *full, uint64_t *empty) {
@@ -411,6 +438,36 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     const int v_row = t0 + (lane & 7) + ((lane >> 4) & 1) * 8;   // V tile as A^T operand (.trans)
     const int v_chk = (lane >> 3) & 1;
 
+    // options build (attenMask / pseShift, ..._Us2.h:2862-2899): the mask bytes and pse values of this thread's two
+    // tokens of each page (rows gid and gid + 8 of the warp's 16) at their LOGICAL positions page * bs + t; fetched
+    // here, used after the K matmuls
+    uint32_t mk[PP];                             // byte 0: row gid masked, byte 1: row gid + 8
+    uint32_t psv[PP][NT][2];                     // per head: pse of (row gid, row gid + 8), query dtype
+    if (OPT) {
+        const int b = item / p.Nkv, n2 = item % p.Nkv;
+#pragma unroll
+        for (int pp = 0; pp < PP; ++pp) {
+            const size_t pos = (size_t)lps[pp] * p.bs + t0 + gid;
+            const bool in0 = t0 + gid < tails[pp], in1 = t0 + gid + 8 < tails[pp];
+            mk[pp] = 0u;
+            if (p.mask != nullptr) {
+                const unsigned char *mrow = p.mask + (size_t)b * p.mask_sb + pos;
+                mk[pp] = (in0 ? (uint32_t)__ldg(mrow) : 0u) | (in1 ? (uint32_t)__ldg(mrow + 8) << 8 : 0u);
+            }
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int h = nt * 8 + tig * 2 + e;
+                    psv[pp][nt][e] = 0u;
+                    if (p.pse != nullptr && h < p.g) {
+                        const unsigned short *prow = reinterpret_cast<const unsigned short *>(p.pse) + (size_t)b * p.pse_sb +
+                                                     (size_t)(n2 * p.g + h) * p.pse_sh + pos;
+                        psv[pp][nt][e] = (in0 ? (uint32_t)__ldg(prow) : 0u) | (in1 ? (uint32_t)__ldg(prow + 8) << 16 : 0u);
+                    }
+                }
+        }
+    }
     // ------------------------------ K: S^T = K Q^T ------------------------------
     float s[PP][NT][4];
 #pragma unroll
@@ -512,6 +569,14 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
                 const int ntok = ((metas[pp] >> h) & 1u) ? tails[pp] : 0;
                 x[pp][0] = (t0 + gid < ntok) ? s[pp][nt][e] * sc2 : -INFINITY;
                 x[pp][1] = (t0 + gid + 8 < ntok) ? s[pp][nt][2 + e] * sc2 : -INFINITY;
+                if (OPT) {
+                    // pse is added to the scaled logit, a masked position is then SET to -1e12 (finite, as the reference's
+                    // SelectWithBytesMask does: a row whose tokens are all masked averages them)
+                    x[pp][0] += QTraits<QT>::to_float(psv[pp][nt][e] & 0xffffu) * kLog2e;
+                    x[pp][1] += QTraits<QT>::to_float(psv[pp][nt][e] >> 16) * kLog2e;
+                    if ((mk[pp] & 0xffu) && x[pp][0] != -INFINITY) x[pp][0] = kMaskedLog2;
+                    if ((mk[pp] >> 8) && x[pp][1] != -INFINITY) x[pp][1] = kMaskedLog2;
+                }
                 mx = fmaxf(mx, fmaxf(x[pp][0], x[pp][1]));
             }
             mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
@@ -635,7 +700,7 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     }
 }
 
-template <typename QT, int KVK, int NT>
+template <typename QT, int KVK, int NT, int OPT>
 __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, const CUtensorMap *tmV,
                                 unsigned char *smem, PubState *pub) {
     // query staging is compiled into the int8 kernels only: the fp16 stream gains nothing from it (its pages are
@@ -679,7 +744,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     if (warp >= kPostWarp) {
         const int pw = warp - kPostWarp;
         if (pw == 0 && p.mode == kModeFused && p.max_ppl != nullptr) max_ppl_poll(p);
-        post_warp_loop<QT, KVK, NT>(p, mail + pw * kMailSlots * 2, mfull + pw * kMailSlots, mempty + pw * kMailSlots);
+        post_warp_loop<QT, KVK, NT, OPT>(p, mail + pw * kMailSlots * 2, mfull + pw * kMailSlots, mempty + pw * kMailSlots);
         return;
     }
     if (warp == kConsumerWarps) {
@@ -778,25 +843,31 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             int ok2 = next_chunk(cf2, cn2, cpid2, rstart2, last2, false);
             unsigned long long ent2 = (ok2 == 1 && lane < cn2) ? ld_relaxed_u64(p.flat + cf2 + lane) : 0ull;
             if (lane < cn) ent = take_entry(p, cf + lane, ent);
+            // options build: an entry names the LOGICAL page (mask / pse positions); every lane looks up the block of
+            // its own entry -- one round trip per 32 pages, in front of the stores that wait for a free stage anyway
+            int lph = 0;
+            if (OPT && lane < cn)
+                lph = __ldg(p.block_table + (size_t)((int)((ent >> 48) & (kMaxItems - 1)) / p.Nkv) * p.bt_stride + (int)((unsigned)ent & 0xffffffu));
             t_pages += cn;
             bool second = false;                                           // this entry closes a pair
             for (int j = 0; j < cn; ++j) {
                 if (last) advance_claim(cn - j);
                 const unsigned long long e = __shfl_sync(0xffffffffu, ent, j);
                 const unsigned long long en = __shfl_sync(0xffffffffu, ent, min(j + 1, cn - 1));
+                const int ph_opt = OPT ? __shfl_sync(0xffffffffu, lph, j) : 0;
                 // two consecutive pages of one item (inside a chunk) are handed to the consumers as a pair
                 const bool first = p.pair_pages && !second && j + 1 < cn && (((e ^ en) >> 48) & (kMaxItems - 1)) == 0;
                 second = first;
                 if (lane == 0) {
                     const unsigned hi = (unsigned)(e >> 32), lo = (unsigned)e;
-                    const int ph = (int)(lo & 0xffffffu), item = (int)((hi >> 16) & (kMaxItems - 1));
+                    const int ph = OPT ? ph_opt : (int)(lo & 0xffffffu), item = (int)((hi >> 16) & (kMaxItems - 1));
                     const int n2 = item % p.Nkv;
                     // stage header: head mask | tail flag << 16 | pair flag << 17 | query buffer << 18, item, partial id
                     // of the run, tokens on a tail page
                     const bool stage_q = q_stage && rstart && j == 0;
                     const int qi = qrun & 1;
                     const int4 md = make_int4((int)(hi & 0xffffu) | (int)(((hi >> 30) & 1u) << 16) | (first ? (1 << 17) : 0) | (qi << 18),
-                                              item, cpid, (int)((lo >> 24) & 0x7fu) + 1);
+                                              item, cpid, ((int)((lo >> 24) & 0x7fu) + 1) | (OPT ? (int)(lo & 0xffffffu) << 8 : 0));
                     int c[4];
                     c[1] = (p.ax_head == 1) ? n2 : (p.ax_blk == 1 ? ph : 0);
                     c[2] = (p.ax_head == 2) ? n2 : (p.ax_blk == 2 ? ph : 0);
@@ -882,10 +953,10 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
         const int4 md = metaS[stage];
         const unsigned meta = (unsigned)md.x & 0xffffu;      // head mask of the page
         const bool tail_page = (md.x >> 16) & 1;
-        const int tail_cnt = md.w;
+        const int tail_cnt = OPT ? (md.w & 0xff) : md.w;     // options build: logical page << 8 rides along
         if (md.y != cur) {
             if (p.dbg && tid == 0 && md.y < 0) { trace_put(p, 10, 0); trace_put(p, 11, 0); trace_put(p, 8, globaltimer_ns()); }
-            if (cur >= 0) flush_segment<QT, KVK, NT>(p, cur, pid, cnt, rec, o, m_run, l_run, mbuf, wml, mail, mfull, mempty, mi, mph);
+            if (cur >= 0) flush_segment<QT, KVK, NT, OPT>(p, cur, pid, cnt, rec, o, m_run, l_run, mbuf, wml, mail, mfull, mempty, mi, mph);
             if (p.dbg && tid == 0 && md.y < 0) trace_put(p, 9, globaltimer_ns());
             if (md.y < 0) break;
             cur = md.y; cnt = 0; pid = md.z;
@@ -1017,11 +1088,12 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             mbar_wait(&full[st[2]], ph[2]);
             const int4 md1 = metaS[st[2]];
             const unsigned metas[2] = {meta, (unsigned)md1.x & 0xffffu};
-            const int tails[2] = {tail_page ? tail_cnt : p.bs, ((md1.x >> 16) & 1) ? md1.w : p.bs};
+            const int tails[2] = {tail_page ? tail_cnt : p.bs, ((md1.x >> 16) & 1) ? (OPT ? (md1.w & 0xff) : md1.w) : p.bs};
+            const int lps[2] = {OPT ? md.w >> 8 : 0, OPT ? md1.w >> 8 : 0};
             const int ks[2] = {st[0], st[2]}, vs[2] = {st[1], st[3]};
             const uint32_t vph[2] = {ph[1], ph[3]};
             cnt += 2;
-            consume_pages<QT, KVK, NT, 2>(p, stage_u32, ks, vs, vph, metas, tails, qf, o, m_run, l_run, hsc, full, empty);
+            consume_pages<QT, KVK, NT, 2, OPT>(p, stage_u32, ks, vs, vph, metas, tails, lps, cur, qf, o, m_run, l_run, hsc, full, empty);
             stage = st[3] + 1; phase = ph[3];
             if (stage == nstages) { stage = 0; phase ^= 1u; }
         } else {
@@ -1029,10 +1101,11 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             if (st1 == nstages) { st1 = 0; ph1 ^= 1u; }
             const unsigned metas[1] = {meta};
             const int tails[1] = {tail_page ? tail_cnt : p.bs};
+            const int lps[1] = {OPT ? md.w >> 8 : 0};
             const int ks[1] = {stage}, vs[1] = {st1};
             const uint32_t vph[1] = {ph1};
             cnt += 1;
-            consume_pages<QT, KVK, NT, 1>(p, stage_u32, ks, vs, vph, metas, tails, qf, o, m_run, l_run, hsc, full, empty);
+            consume_pages<QT, KVK, NT, 1, OPT>(p, stage_u32, ks, vs, vph, metas, tails, lps, cur, qf, o, m_run, l_run, hsc, full, empty);
             stage = st1 + 1; phase = ph1;
             if (stage == nstages) { stage = 0; phase ^= 1u; }
         }

@@ -64,6 +64,13 @@ struct ChainParams {
     unsigned *sig_local;                                  // own signal block: [rank] = launch count flagged by that rank,
                                                           // [kSigEpoch] = own launch count, [kSigError] = time-out marker
     int n_peer, tp_rank;
+    // ---- options build only (OPT = 1 kernels, spa_chain.cuh).  Positions are LOGICAL token positions
+    // page * bs + t; page entries then carry the logical page and the producer looks the block up
+    int opt;
+    const unsigned char *mask; long long mask_sb;        // attenMask [B, >= maxP*bs] bytes, non-zero = masked (..._Us2.h:2876-2899)
+    const void *pse; long long pse_sb, pse_sh;           // pseShift [B or 1, Nq, 1, >= maxP*bs] in the query dtype; pse_sb = 0: shared (:2862-2874)
+    const void *pq_scale, *pq_offset;                    // int8 post-quant of the output (:3513-3600): [1] or [Nq, D]; `out` is int8 then
+    int pq_scale_chn, pq_offset_chn, pq_bf16;            // per-channel flags; parameter dtype bf16 (else fp32)
     float scale_log2;                                    // scale_value * log2(e)
     int ax_row, ax_head, ax_blk;                         // TMA coordinate slots (1..3)
     int num_blocks;

@@ -18,6 +18,7 @@
 #include "../../include/spa_b200.h"
 #include "spa_assign.cuh"
 #include "spa_attn.cuh"
+#include "spa_chain.cuh"
 #include "spa_common.cuh"
 #include "spa_select.cuh"
 
@@ -27,89 +28,6 @@ using namespace spa;
 // =============================================================================================
 // kernels
 // =============================================================================================
-// 1 KiB-aligned start of the dynamic shared memory (TMA 128B-swizzled tiles).  Plain pointer + offset:
-// going through an integer would hide the address space from the compiler, and every access below
-// would become a generic LD/ST/ATOM instead of LDS/STS/ATOMS.
-__device__ __forceinline__ unsigned char *aligned_smem(unsigned char *raw) {
-    return raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u);
-}
-
-// The whole chain in one persistent launch (SparsePagedFusionAttention,
-// sparse_paged_fusion_attention.cpp:56-76: InitCentSelect -> ProcessCentSelect -> SyncAll ->
-// Init/Process attention), or, with mode == kModeAttnOnly, SparsePagedAttention.  The reference's
-// SyncAll between selection and attention becomes a producer/consumer page queue: CTAs only wait
-// for entries that are not published yet, so the launch is cooperative (co-residency) but has no
-// grid-wide barrier.
-// End of a tensor-parallel launch (last CTA, one thread).  Every CTA fenced its peer stores at system scope
-// before it reported, so after one more fence the flag stores below order behind ALL output rows of this
-// rank.  Then wait until every peer has flagged the same launch count: from there on the local gathered
-// buffer is complete and the stream may go on to its consumer.  The count lives in the signal words, not
-// in the parameters, so a captured CUDA graph replays correctly.
-__device__ __noinline__ void peer_exchange_flags(const ChainParams &p) {
-    const unsigned long long t_in = globaltimer_ns();
-    const unsigned e = p.sig_local[kSigEpoch] + 1u;
-    p.sig_local[kSigEpoch] = e;
-    asm volatile("fence.acq_rel.sys;" ::: "memory");        // one release fence, then relaxed flag stores
-    for (int i = 0; i < p.n_peer; ++i)
-        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p.sig_peer[i] + p.tp_rank), "r"(e) : "memory");
-    const unsigned long long t0 = globaltimer_ns();
-    *reinterpret_cast<unsigned long long *>(p.sig_local + kSigWaitNs + 2) += t0 - t_in;    // fence + flag stores alone
-    for (int i = 0; i < p.n_peer; ++i) {
-        for (;;) {
-            unsigned v;
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p.sig_local + p.peer_rank[i]) : "memory");
-            if ((int)(v - e) >= 0) break;
-            if (globaltimer_ns() - t0 > 2000000000ull) {
-                // a peer did not launch within 2 s: the gathered buffer is incomplete and the lock-step that makes
-                // the double buffer safe is broken.  Fail LOUDLY: leave the marker for the host, then trap -- the
-                // stream's next synchronisation returns an error instead of a consumer reading stale rows.
-                p.sig_local[kSigError] = e;
-                asm volatile("fence.acq_rel.sys;" ::: "memory");
-                __trap();
-            }
-            __nanosleep(64);
-        }
-    }
-    // statistics: total ns this rank spent in the exchange (fence + flag stores + waiting for the peers)
-    *reinterpret_cast<unsigned long long *>(p.sig_local + kSigWaitNs) += globaltimer_ns() - t_in;
-}
-
-template <typename QT, int KVK, int NT>
-__global__ void __launch_bounds__(kThreads, 1)
-spa_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ CUtensorMap tmK,
-                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmC) {
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char *smem = aligned_smem(smem_raw);
-    __shared__ PubState pub;
-
-    trace_mark(p, 0);
-    if (threadIdx.x == 0) {
-        pub.n_own = 0; pub.priv_used = 0;
-        pub.req_seq[0] = pub.req_seq[1] = 0u; pub.ack_seq[0] = pub.ack_seq[1] = 0u;
-    }
-    // ---- phase A: selection (or union building) per (b, kv head); every item ends by publishing its
-    // pages (both branches start with a __syncthreads: the publisher state above is visible)
-    if (p.mode == kModeFused)
-        select_phase<QT, kSelScores | kSelSelect | kSelUnion>(p, &tmC, smem, &pub);
-    else
-        for (int item = blockIdx.x; item < p.items; item += gridDim.x) union_from_block_position(p, item, smem, &pub);
-    trace_mark(p, 1);
-    // ---- phase B + C: stream own prefixes and claimed chunks; the CTA completing an item combines it
-    attention_phase<QT, KVK, NT>(p, &tmK, &tmV, smem, &pub);
-    trace_mark(p, 3);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        // the last CTA to leave returns the queue counters to zero for the next launch
-        if (p.n_peer) asm volatile("fence.acq_rel.sys;" ::: "memory"); else __threadfence();
-        if (atomicAdd(p.ctrl + Ctrl::kFinished, 1) == (int)gridDim.x - 1) {
-            p.ctrl[Ctrl::kHead] = 0; p.ctrl[Ctrl::kTail] = 0;
-            p.ctrl[Ctrl::kItemsDone] = 0; p.ctrl[Ctrl::kPool] = 0; p.ctrl[Ctrl::kFinished] = 0;
-            if (p.n_peer) peer_exchange_flags(p);
-        }
-    }
-    trace_mark(p, 5);
-}
-
 // Stand-alone selection ops (ComputeCent / SelectPosition / CentSelect share the device code).
 template <typename QT, int FLAGS>
 __global__ void __launch_bounds__(kThreads, 1) spa_select_kernel(const __grid_constant__ ChainParams p,
@@ -160,6 +78,7 @@ struct spaExecutor {
     int grid;
     int q_bf16, kv_i8, nt_tiles;       // kv_i8: 8-bit KV pages (int8 or FP8)
     int kv_f8;                         // ... of which FP8 e4m3
+    int opt;                           // options build of the chain kernel (attenMask / pseShift / post-quant), spa_chain.cuh
     uint64_t ws_bytes;
     // workspace offsets (bytes)
     uint64_t off_ctrl, off_flat, off_desc, off_info, off_ippl, off_po, off_pml, off_xs;
@@ -194,7 +113,7 @@ static const char *dtype_name(int d) {
     switch (d) {
         case SPA_F16: return "float16"; case SPA_BF16: return "bfloat16"; case SPA_F32: return "float32";
         case SPA_I8: return "int8"; case SPA_I32: return "int32"; case SPA_I64: return "int64";
-        case SPA_F8E4M3: return "float8_e4m3";
+        case SPA_F8E4M3: return "float8_e4m3"; case SPA_U8: return "uint8"; case SPA_BOOL: return "bool";
     }
     return "?";
 }
@@ -398,16 +317,8 @@ static int make_cent_map(CUtensorMap *map, const void *cent, int rows, int bf16)
 // ---------------------------------------------------------------------------------------------
 // kernel dispatch tables
 // ---------------------------------------------------------------------------------------------
-typedef void (*ChainKernel)(const ChainParams, const CUtensorMap, const CUtensorMap, const CUtensorMap);
-static ChainKernel chain_kernel_for(int bf16, int kvk, int nt) {       // kvk: kKvSame / kKvI8 / kKvF8
-    if (!bf16) {
-        if (kvk == kKvSame) return nt == 1 ? spa_chain_kernel<__half, kKvSame, 1> : spa_chain_kernel<__half, kKvSame, 2>;
-        if (kvk == kKvI8) return nt == 1 ? spa_chain_kernel<__half, kKvI8, 1> : spa_chain_kernel<__half, kKvI8, 2>;
-        return nt == 1 ? spa_chain_kernel<__half, kKvF8, 1> : spa_chain_kernel<__half, kKvF8, 2>;
-    }
-    if (kvk == kKvSame) return nt == 1 ? spa_chain_kernel<__nv_bfloat16, kKvSame, 1> : spa_chain_kernel<__nv_bfloat16, kKvSame, 2>;
-    if (kvk == kKvI8) return nt == 1 ? spa_chain_kernel<__nv_bfloat16, kKvI8, 1> : spa_chain_kernel<__nv_bfloat16, kKvI8, 2>;
-    return nt == 1 ? spa_chain_kernel<__nv_bfloat16, kKvF8, 1> : spa_chain_kernel<__nv_bfloat16, kKvF8, 2>;
+static ChainKernel chain_kernel_for(int bf16, int kvk, int nt, int opt) {
+    return opt ? opt_chain_kernel_for(bf16, kvk, nt) : chain_kernel_table<0>(bf16, kvk, nt);
 }
 typedef void (*SelectKernel)(const ChainParams, const CUtensorMap);
 static SelectKernel select_kernel_for(int bf16, int flags) {
@@ -505,6 +416,7 @@ int spaExecutorSetPeerOutput(spaExecutor *e, int rank, int world, void *const *g
     for (int i = 0; i < kMaxPeers; ++i) { p.out_peer[i] = nullptr; p.sig_peer[i] = nullptr; p.peer_rank[i] = 0; }
     if (world <= 1 || !gatheredOut) return SPA_OK;
     if (e->op != OP_FUSION && e->op != OP_ATTENTION) return fail(SPA_ERR_UNSUPPORTED, "peer output: only the attention ops write attentionOut");
+    if (e->p.pq_scale != nullptr) return fail(SPA_ERR_UNSUPPORTED, "peer output: not with an int8 (post-quant) attentionOut");
     if (world > kMaxPeers || rank < 0 || rank >= world || !signals) return fail(SPA_ERR_ARG, "peer output: rank %d of world %d (max %d)", rank, world, kMaxPeers);
     for (int r = 0; r < world; ++r)
         if (!gatheredOut[r] || !signals[r]) return fail(SPA_ERR_ARG, "peer output: null buffer for rank %d", r);
@@ -802,20 +714,68 @@ int spaCentSelect(void *workspace, uint64_t wsSize, spaExecutor *e, spaStream st
 // ---------------------------------------------------------------------------------------------
 // attention ops
 // ---------------------------------------------------------------------------------------------
-static int reject_unsupported(const spaTensor *pse, const spaTensor *mask, const spaTensor *dq1,
-                              const spaTensor *q1, const spaTensor *dq2, const spaTensor *q2,
-                              const spaTensor *qo2, const spaTensor *kvpad) {
-    // Never non-empty in any reference sparse test (tests/ifa_v5_case.py:133-146)
-    if (!absent(pse)) return fail(SPA_ERR_UNSUPPORTED, "pse_shift is not supported in the sparse path");
-    if (!absent(mask)) return fail(SPA_ERR_UNSUPPORTED, "attention_mask is not supported in the sparse path");
-    if (!absent(dq1) || !absent(q1) || !absent(dq2) || !absent(q2) || !absent(qo2))
-        return fail(SPA_ERR_UNSUPPORTED, "quant/dequant scales (int8 in/out) are not supported in the sparse path");
-    if (!absent(kvpad)) return fail(SPA_ERR_UNSUPPORTED, "kv_padding_size is not supported in the sparse path");
+// The optional tensors of the aclnn prototypes between `value` and `antiquantScale` (+ kvPaddingSize).  None of
+// them is non-empty in any reference sparse test (tests/ifa_v5_case.py:133-146 pass empty tensors).
+struct AttnOptions { const spaTensor *pse, *mask, *dq1, *q1, *dq2, *q2, *qo2, *kvpad; };
+
+// pseShift / attenMask / quantScale2 / quantOffset2 -> the options build of the chain kernel.  Shapes
+// and dtypes as the reference tiling checks them (sparse_paged_attention_tiling_check.cc:737-850,
+// sparse_paged_attention_tiling.cc:566-647).  Called once B, Nq, maxP and bs are known.
+static int parse_attn_options(spaExecutor *e, const AttnOptions &o, const spaTensor *query) {
+    ChainParams &p = e->p;
+    // int8 QUERY (full-quant IFA) does not exist on the sparse path: the query is f16 / bf16
+    if (!absent(o.dq1) || !absent(o.q1) || !absent(o.dq2))
+        return fail(SPA_ERR_UNSUPPORTED, "dequant_scale1 / quant_scale1 / dequant_scale2 belong to int8 queries, which the sparse path does not take");
+    if (!absent(o.kvpad)) return fail(SPA_ERR_UNSUPPORTED, "kv_padding_size (left padding) is not defined for paged KV");
+    const long long smax = (long long)p.maxP * p.bs;
+    if (!absent(o.pse)) {
+        const spaTensor *t = o.pse;
+        if (t->dtype != query->dtype) return fail(SPA_ERR_DTYPE, "pse_shift dtype %s must equal the query dtype %s", dtype_name(t->dtype), dtype_name(query->dtype));
+        if (t->ndim != 4 || (t->sizes[0] != 1 && t->sizes[0] < p.B) || t->sizes[1] != p.Nq || t->sizes[2] != 1)
+            return fail(SPA_ERR_SHAPE, "pse_shift: expected [B or 1, Nq, 1, S]");
+        if (t->sizes[3] < smax) return fail(SPA_ERR_SHAPE, "pse_shift: S=%lld < maxBlocksPerBatch * blockSize = %lld", (long long)t->sizes[3], smax);
+        if (t->strides[3] != 1) return fail(SPA_ERR_SHAPE, "pse_shift rows must be contiguous");
+        p.pse = t->data; p.pse_sb = t->sizes[0] == 1 ? 0 : t->strides[0]; p.pse_sh = t->strides[1];
+        e->opt = 1;
+    }
+    if (!absent(o.mask)) {
+        const spaTensor *t = o.mask;
+        if (t->dtype != SPA_BOOL && t->dtype != SPA_I8 && t->dtype != SPA_U8)
+            return fail(SPA_ERR_DTYPE, "attention_mask: bool, int8 or uint8 (got %s)", dtype_name(t->dtype));
+        if (t->ndim < 2 || t->sizes[0] < p.B) return fail(SPA_ERR_SHAPE, "attention_mask: expected [B, (1, (1,)) S]");
+        for (int i = 1; i + 1 < t->ndim; ++i)
+            if (t->sizes[i] != 1) return fail(SPA_ERR_SHAPE, "attention_mask: expected [B, (1, (1,)) S]");
+        if (t->sizes[t->ndim - 1] < smax)
+            return fail(SPA_ERR_SHAPE, "attention_mask: S=%lld < maxBlocksPerBatch * blockSize = %lld", (long long)t->sizes[t->ndim - 1], smax);
+        if (t->strides[t->ndim - 1] != 1) return fail(SPA_ERR_SHAPE, "attention_mask rows must be contiguous");
+        p.mask = (const unsigned char *)t->data; p.mask_sb = t->strides[0];
+        e->opt = 1;
+    }
+    if (!absent(o.q2)) {
+        const spaTensor *t = o.q2;
+        if (t->dtype != SPA_F32 && !(t->dtype == SPA_BF16 && query->dtype == SPA_BF16))
+            return fail(SPA_ERR_DTYPE, "quant_scale2: float32, or bfloat16 with a bfloat16 query");
+        const int64_t n = numel(t);
+        if (n != 1 && n != (int64_t)p.Nq * kD) return fail(SPA_ERR_SHAPE, "quant_scale2: expected 1 or Nq*D = %lld elements", (long long)p.Nq * kD);
+        REQUIRE_CONTIG(t, "quant_scale2");
+        p.pq_scale = t->data; p.pq_scale_chn = n != 1; p.pq_bf16 = t->dtype == SPA_BF16;
+        if (!absent(o.qo2)) {
+            if (o.qo2->dtype != t->dtype) return fail(SPA_ERR_DTYPE, "quant_offset2 dtype must equal quant_scale2's");
+            const int64_t m = numel(o.qo2);
+            if (m != 1 && m != (int64_t)p.Nq * kD) return fail(SPA_ERR_SHAPE, "quant_offset2: expected 1 or Nq*D elements");
+            REQUIRE_CONTIG(o.qo2, "quant_offset2");
+            p.pq_offset = o.qo2->data; p.pq_offset_chn = m != 1;
+        }
+        e->opt = 1;
+    } else if (!absent(o.qo2)) {
+        return fail(SPA_ERR_ARG, "quant_offset2 given without quant_scale2");
+    }
+    p.opt = e->opt;
     return SPA_OK;
 }
 
 static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTensor *key, const spaTensor *value,
-                          const spaTensor *aqs, const spaTensor *aqo, const spaTensor *blocktable,
+                          const AttnOptions &opts, const spaTensor *aqs, const spaTensor *aqo, const spaTensor *blocktable,
                           int64_t numHeads, double scaleValue, const char *inputLayout, int64_t numKV,
                           int64_t blockSize, const spaTensor *out, uint64_t *ws) {
     ChainParams &p = e->p;
@@ -832,6 +792,28 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     if (blockSize != 16 && blockSize != 32 && blockSize != 64 && blockSize != kBS)
         return fail(SPA_ERR_UNSUPPORTED, "block_size %lld: this build supports 16, 32, 64 and %d", (long long)blockSize, kBS);
     p.bs = (int)blockSize;
+    REQUIRE_PRESENT(blocktable, "blocktable"); REQUIRE_DTYPE(blocktable, SPA_I32, "blocktable");
+    if (blocktable->ndim != 2 || blocktable->strides[1] != 1) return fail(SPA_ERR_SHAPE, "blocktable: expected [maxB,maxP]");
+    if (blocktable->sizes[0] < p.B) return fail(SPA_ERR_SHAPE, "blocktable rows %lld < batch %d", (long long)blocktable->sizes[0], p.B);
+    p.block_table = (const int *)blocktable->data; p.bt_stride = blocktable->strides[0]; p.maxP = (int)blocktable->sizes[1];
+    if ((rc = parse_attn_options(e, opts, query))) return rc;
+    // output: same shape as query (add_custom.cpp:559-560); its dtype, or int8 exactly when quant_scale2 is given
+    // (sparse_paged_attention_tiling.cc:570-602)
+    REQUIRE_PRESENT(out, "attention_out");
+    if (p.pq_scale != nullptr) {
+        if (out->dtype != SPA_I8) return fail(SPA_ERR_DTYPE, "quant_scale2 is given: attention_out must be int8 (got %s)", dtype_name(out->dtype));
+    } else if (out->dtype == SPA_I8) {
+        return fail(SPA_ERR_ARG, "attention_out is int8 but quant_scale2 is absent");
+    } else {
+        REQUIRE_DTYPE(out, query->dtype, "attention_out");
+    }
+    if (out->ndim != query->ndim) return fail(SPA_ERR_SHAPE, "attention_out must have the query's shape");
+    for (int i = 0; i < out->ndim; ++i)
+        if (out->sizes[i] != query->sizes[i] && !(i == 0 && out->sizes[0] >= p.B))
+            return fail(SPA_ERR_SHAPE, "attention_out must have the query's shape");
+    if (out->strides[out->ndim - 1] != 1 || (out->strides[0] & 3) || (out->strides[1] & 3) ||
+        (reinterpret_cast<uintptr_t>(out->data) & 7))
+        return fail(SPA_ERR_SHAPE, "attention_out rows must be contiguous and 8-byte aligned");
     REQUIRE_PRESENT(key, "key"); REQUIRE_PRESENT(value, "value");
     if (key->dtype != value->dtype) return fail(SPA_ERR_DTYPE, "key/value dtypes differ");
     e->kv_f8 = key->dtype == SPA_F8E4M3;
@@ -868,19 +850,6 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     } else if (!absent(aqs) || !absent(aqo)) {
         return fail(SPA_ERR_ARG, "antiquant_scale/offset given but KV is neither int8 nor float8_e4m3");
     }
-    REQUIRE_PRESENT(blocktable, "blocktable"); REQUIRE_DTYPE(blocktable, SPA_I32, "blocktable");
-    if (blocktable->ndim != 2 || blocktable->strides[1] != 1) return fail(SPA_ERR_SHAPE, "blocktable: expected [maxB,maxP]");
-    if (blocktable->sizes[0] < p.B) return fail(SPA_ERR_SHAPE, "blocktable rows %lld < batch %d", (long long)blocktable->sizes[0], p.B);
-    p.block_table = (const int *)blocktable->data; p.bt_stride = blocktable->strides[0]; p.maxP = (int)blocktable->sizes[1];
-    // output: same shape/dtype as query (add_custom.cpp:559-560)
-    REQUIRE_PRESENT(out, "attention_out"); REQUIRE_DTYPE(out, query->dtype, "attention_out");
-    if (out->ndim != query->ndim) return fail(SPA_ERR_SHAPE, "attention_out must have the query's shape");
-    for (int i = 0; i < out->ndim; ++i)
-        if (out->sizes[i] != query->sizes[i] && !(i == 0 && out->sizes[0] >= p.B))
-            return fail(SPA_ERR_SHAPE, "attention_out must have the query's shape");
-    if (out->strides[out->ndim - 1] != 1 || (out->strides[0] & 3) || (out->strides[1] & 3) ||
-        (reinterpret_cast<uintptr_t>(out->data) & 7))
-        return fail(SPA_ERR_SHAPE, "attention_out rows must be contiguous and 8-byte aligned");
     p.out = out->data; p.out_sb = out->strides[0]; p.out_sh = out->strides[1];
     p.q = query->data;
     p.scale_log2 = (float)scaleValue * kLog2e;
@@ -923,7 +892,7 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
         if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.q_stage ? p.g : 0).total <= budget) break;
     if (nst < 2) return fail(SPA_ERR_UNSUPPORTED, "attention working set exceeds shared memory");
     p.nstages = nst;
-    p.pair_pages = nst >= 4;
+    p.pair_pages = nst >= 4 && !e->opt;      // options build: one page per step (registers for the mask / pse values)
     if (const char *s = getenv("SPA_PAIR")) p.pair_pages = p.pair_pages && atoi(s) != 0;
     int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.q_stage ? p.g : 0).total;
     int sel_bytes = p.maxP * 4;
@@ -933,7 +902,7 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     }
     p.smem_bytes = std::max(attn_bytes, sel_bytes) + 1024;
     if (p.smem_bytes > d.smem_optin) return fail(SPA_ERR_UNSUPPORTED, "shared memory need %d > %d", p.smem_bytes, d.smem_optin);
-    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_f8 ? kKvF8 : (e->kv_i8 ? kKvI8 : kKvSame), e->nt_tiles);
+    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_f8 ? kKvF8 : (e->kv_i8 ? kKvI8 : kKvSame), e->nt_tiles, e->opt);
     if ((rc = raise_smem_limit((const void *)kern, d.smem_optin))) return rc;
     int occ = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, p.smem_bytes));
@@ -975,7 +944,7 @@ static int launch_chain(void *workspace, uint64_t wsSize, spaExecutor *e, cudaSt
     p.item_ppl = (int *)(w + e->off_ippl);
     p.part_o = (float *)(w + e->off_po); p.part_ml = (float *)(w + e->off_pml);
     p.exact_scratch = (double *)(w + e->off_xs);
-    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_f8 ? kKvF8 : (e->kv_i8 ? kKvI8 : kKvSame), e->nt_tiles);   // (smem limit raised once, in plan_attention)
+    ChainKernel kern = chain_kernel_for(e->q_bf16, e->kv_f8 ? kKvF8 : (e->kv_i8 ? kKvI8 : kKvSame), e->nt_tiles, e->opt);   // (smem limit raised once, in plan_attention)
     // queue words start at zero and the kernel leaves them at zero again, but the workspace is the
     // caller's scratch: clear it unless the caller vouches for it (spaExecutorSetPersistentWorkspace).
     // "Known clean" is only recorded for a clear that really executes: under stream capture the memset is
@@ -1018,14 +987,14 @@ int spaSparsePagedAttentionGetWorkspaceSize(
     memset(e, 0, sizeof(*e));
     ChainParams &p = e->p;
     int rc;
-    BAIL(reject_unsupported(pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize));
+    const AttnOptions opts = {pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize};
     BAIL(parse_query(query, "query", &p.B, &p.Nq, &p.q_sb, &p.q_sh, &e->q_bf16));
     p.mode = kModeAttnOnly;
     if (absent(blockPosition)) { delete e; return fail(SPA_ERR_ARG, "blockposition: required tensor is absent"); }
     if (blockPosition->dtype != SPA_I32) { delete e; return fail(SPA_ERR_DTYPE, "blockposition: expected int32"); }
     if (absent(actualSeqLengths)) { delete e; return fail(SPA_ERR_ARG, "actual_seq_lengths: required tensor is absent"); }
     if (actualSeqLengths->dtype != SPA_I64) { delete e; return fail(SPA_ERR_DTYPE, "actual_seq_lengths: expected int64"); }
-    BAIL(plan_attention(e, query, key, value, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
+    BAIL(plan_attention(e, query, key, value, opts, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
                         inputLayout, numKeyValueHeads, blockSize, attentionOut, ws));
     if (blockPosition->ndim != 3 || blockPosition->sizes[0] < p.B || blockPosition->strides[2] != 1 ||
         (blockPosition->sizes[1] != p.Nkv && blockPosition->sizes[1] != p.Nq)) {
@@ -1064,12 +1033,12 @@ int spaSparsePagedFusionAttentionGetWorkspaceSize(
     memset(e, 0, sizeof(*e));
     ChainParams &p = e->p;
     int rc;
-    BAIL(reject_unsupported(pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize));
+    const AttnOptions opts = {pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize};
     p.mode = kModeFused;
     BAIL(parse_cent_select_common(e, query, l1Cent, blockIds, blocktable, totalSeqLen, topK, blockSize,
                                   blockPosition, pagePositionLength, maxPagePositionLength));
     if (numKeyValueHeads > 0 && numKeyValueHeads != p.Nkv) { delete e; return fail(SPA_ERR_SHAPE, "num_key_value_heads=%lld disagrees with l1_cent heads %d", (long long)numKeyValueHeads, p.Nkv); }
-    BAIL(plan_attention(e, query, key, value, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
+    BAIL(plan_attention(e, query, key, value, opts, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
                         inputLayout, p.Nkv, blockSize, attentionOut, ws));
     e->op = OP_FUSION;
     *executor = e;
@@ -1138,14 +1107,14 @@ int spaSparsePagedFusionAttentionStatic(
     spaExecutor *e = &plan;
     ChainParams &p = e->p;
     int rc;
-    if ((rc = reject_unsupported(pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize))) return rc;
+    const AttnOptions opts = {pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2, kvPaddingSize};
     p.mode = kModeFused;
     if ((rc = parse_cent_select_common(e, query, l1Cent, blockIds, blocktable, totalSeqLen, topK, blockSize,
                                        blockPosition, pagePositionLength, maxPagePositionLength))) return rc;
     if (numKeyValueHeads > 0 && numKeyValueHeads != p.Nkv)
         return fail(SPA_ERR_SHAPE, "num_key_value_heads=%lld disagrees with l1_cent heads %d", (long long)numKeyValueHeads, p.Nkv);
     uint64_t need = 0;
-    if ((rc = plan_attention(e, query, key, value, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
+    if ((rc = plan_attention(e, query, key, value, opts, antiquantScale, antiquantOffset, blocktable, numHeads, scaleValue,
                              inputLayout, p.Nkv, blockSize, attentionOut, &need))) return rc;
     e->op = OP_FUSION;
     if (need > SPA_STATIC_SCRATCH_BYTES)

@@ -300,7 +300,7 @@ __device__ __forceinline__ double exact_partial(uint2 v, const double (&qd)[4]) 
 
 // exact scores of list[0..n) -> xs[0..n)   (one warp; rows come from L2, 4 in flight)
 template <typename QT>
-__device__ __noinline__ void exact_scores(const CentSrc cent_rows, const unsigned short *qrow, const int *list32,
+static __device__ __noinline__ void exact_scores(const CentSrc cent_rows, const unsigned short *qrow, const int *list32,
                                           const unsigned short *list16, int n, double *xs) {
     const int lane = lane_id();
     double qd[4];
@@ -554,7 +554,7 @@ __device__ __forceinline__ void emit_sorted(const ChainParams &p, const unsigned
 // One warp.  Writes out[0..min(count, cap)) = ascending i with (pm[i] >> bit) & 1, pads with the
 // sentinel up to cap, clears the bit of entries beyond cap (so the union agrees with the
 // truncated list), returns the kept count.
-__device__ __noinline__ int warp_compact_bit(unsigned *pm, int pl, int bit, int *out, int cap) {
+static __device__ __noinline__ int warp_compact_bit(unsigned *pm, int pl, int bit, int *out, int cap) {
     const int lane = lane_id();
     int base = 0;
     for (int i0 = 0; i0 < pl; i0 += 32) {
@@ -594,7 +594,7 @@ __device__ __noinline__ int warp_compact_bit(unsigned *pm, int pl, int bit, int 
 //   * little work (own items adding up to <= small_pages pages): the item stays whole and private -- no
 //     partial, no combine (five dependent L2 round trips after the item's last page).
 // One thread.  m >= 0: also report the item's longest per-head page list (max_page_position_length).
-__device__ __noinline__ void publish_item(const ChainParams &p, PubState *pub, int item, int ulen, int tail_cnt, int m) {
+static __device__ __noinline__ void publish_item(const ChainParams &p, PubState *pub, int item, int ulen, int tail_cnt, int m) {
     if (m >= 0) p.item_ppl[item] = m + 1;                             // picked up by a post warp (max_ppl_poll)
     int nch = 0;
     if (ulen > 0) {
@@ -658,10 +658,12 @@ __device__ __forceinline__ void publisher_loop(const ChainParams &p, PubState *p
 }
 // attention_out rows of an item without any page (seq 0 / nothing selected): zeros, as the combine of
 // an empty sum gives.  nthreads threads, tid in [0, nthreads).
-__device__ __noinline__ void zero_item_output(const ChainParams &p, int b, int n2, int tid, int nthreads) {
+static __device__ __noinline__ void zero_item_output(const ChainParams &p, int b, int n2, int tid, int nthreads) {
+    const bool i8out = p.pq_scale != nullptr;              // post-quant: int8 rows (InitAllZeroInt8Output, ..._Us2.h:996)
     for (int i = tid; i < p.g * (kD / 4); i += nthreads) {
         const int h = i / (kD / 4), d4 = i % (kD / 4);
         const size_t off = (size_t)b * p.out_sb + (size_t)(n2 * p.g + h) * p.out_sh + d4 * 4;
+        if (i8out) { *reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(p.out) + off) = 0u; continue; }
         *reinterpret_cast<uint2 *>(reinterpret_cast<unsigned short *>(p.out) + off) = make_uint2(0u, 0u);
         for (int r = 0; r < p.n_peer; ++r)                 // tensor parallel: the peers' gathered buffers too
             *reinterpret_cast<uint2 *>(reinterpret_cast<unsigned short *>(p.out_peer[r]) + off) = make_uint2(0u, 0u);
@@ -673,7 +675,7 @@ __device__ __noinline__ void zero_item_output(const ChainParams &p, int b, int n
 // logical page i; writes the ascending pages with a non-zero mask to the item's place in `flat`.  An entry has
 // ONE tail flag: a page that is the tail page of some heads and a full page of others (possible only with
 // per-head block_position lists) is listed twice, once per head subset.  Returns the number of entries.
-__device__ __noinline__ int warp_emit_union(const ChainParams &p, int item, const int *phys, const unsigned *pm, int pl,
+static __device__ __noinline__ int warp_emit_union(const ChainParams &p, int item, const int *phys, const unsigned *pm, int pl,
                                             int tail_cnt) {
     const int lane = lane_id();
     const unsigned lt = (1u << lane) - 1u;
@@ -685,8 +687,9 @@ __device__ __noinline__ int warp_emit_union(const ChainParams &p, int item, cons
         if (m != 0u && (unsigned)phys[i] >= (unsigned)p.num_blocks) m = 0u;      // block id outside the pool: skipped
         const unsigned mt = (m >> 16) & m & 0xffffu, mf = m & 0xffffu & ~mt;
         const unsigned bf = __ballot_sync(0xffffffffu, mf != 0u), bt = __ballot_sync(0xffffffffu, mt != 0u);
-        if (mf) st_relaxed_u64(q + base + __popc(bf & lt), queue_entry(phys[i], mf, false, item, p.bs));
-        if (mt) st_relaxed_u64(q + base + __popc(bf) + __popc(bt & lt), queue_entry(phys[i], mt, true, item, max(1, tail_cnt)));
+        const int id = (m != 0u) ? (p.opt ? i : phys[i]) : 0;                     // options build: the LOGICAL page travels
+        if (mf) st_relaxed_u64(q + base + __popc(bf & lt), queue_entry(id, mf, false, item, p.bs));
+        if (mt) st_relaxed_u64(q + base + __popc(bf) + __popc(bt & lt), queue_entry(id, mt, true, item, max(1, tail_cnt)));
         base += __popc(bf) + __popc(bt);
     }
     __syncwarp();
@@ -940,7 +943,7 @@ __device__ void select_item(const ChainParams &p, const CUtensorMap *tmC, int it
             if (FLAGS & kSelUnion) {
                 const bool on = (m & 0xffffu) != 0u && (unsigned)physS[i < pl ? i : 0] < (unsigned)p.num_blocks;
                 const unsigned bal = __ballot_sync(0xffffffffu, on);
-                if (on) st_relaxed_u64(qent + cnt[ch * KG1 + g] + __popc(bal & lt), queue_entry(physS[i], m, (m >> 16) != 0u, item, max(1, tail_cnt)));
+                if (on) st_relaxed_u64(qent + cnt[ch * KG1 + g] + __popc(bal & lt), queue_entry(p.opt ? i : physS[i], m, (m >> 16) != 0u, item, max(1, tail_cnt)));
             }
         }
         if (p.page_position_length)

@@ -44,7 +44,8 @@ typedef enum {
 /* dtype codes (subset the reference binding converts, add_custom.cpp:43-70) */
 typedef enum {
     SPA_F16 = 0, SPA_BF16 = 1, SPA_F32 = 2, SPA_I8 = 3, SPA_I32 = 4, SPA_I64 = 5,
-    SPA_F8E4M3 = 6             /* FP8 e4m3 KV pages (attention ops only; no reference analogue) */
+    SPA_F8E4M3 = 6,            /* FP8 e4m3 KV pages (attention ops only; no reference analogue) */
+    SPA_U8 = 7, SPA_BOOL = 8   /* attenMask (one byte per position; the reference takes bool / int8 / uint8)       */
 } spaDtype;
 
 #define SPA_MAX_DIMS 8
@@ -162,8 +163,30 @@ SPA_API int spaCentSelect(void *workspace, uint64_t workspaceSize, spaExecutor *
  *      softmax; it is never read.  blockPosition / pagePositionLength of the fused op still list it, as the
  *      reference golden does (tests/utils.py:57-80 clamps the table value for the block_ids lookup only).
  *      At most 2^24 blocks per pool.
- * pseShift, attenMask, dequantScale1, quantScale1, dequantScale2, quantScale2, quantOffset2,
- * kvPaddingSize must be absent (SPA_ERR_UNSUPPORTED otherwise).                                 */
+ * Optional inputs of the op definition (sparse_paged_attention_def.cpp:70-190; both attention ops, every KV dtype,
+ * layout and block size; they select the "options build" of the kernel, csrc/spa_chain.cuh -- absent, the plain
+ * build runs).  No reference test passes any of them (tests/ifa_v5_case.py:133-146):
+ *   pseShift   [B or 1, Nq, 1, S] in the query dtype, S >= maxBlocksPerBatch * blockSize
+ *              (sparse_paged_attention_tiling_check.cc:737-803): added to the scaled logits
+ *              (sparse_paged_attention_split_Bbn2s2_Us2.h:2862-2874).
+ *   attenMask  [B, (1, (1,)) S] bool / int8 / uint8, same S (tiling_check.cc:805-847): a non-zero byte SETS the
+ *              logit to -1e12 after pseShift (:2876-2899, :757) -- finite, so a row whose tokens are all masked
+ *              averages them.
+ *     Both are indexed by the LOGICAL token position  page * blockSize + t  of the KV sequence.  The reference
+ *     kernel, whose code is inherited from the dense op, indexes them by the position in the WALKED sequence
+ *     (slot j of blockPosition -> positions j*blockSize ..): the same thing for a dense walk, but for a sparse walk
+ *     it would make a mask or an ALiBi-style bias refer to compacted positions that differ from head to head;
+ *     its own sources mark blockPosition support of such per-position inputs as unfinished (:1912 "TODO").
+ *   quantScale2 (+ quantOffset2)  float32, or bfloat16 with a bfloat16 query; 1 element or [Nq, D]
+ *              (sparse_paged_attention_tiling.cc:566-647): attentionOut must then be int8 and receives
+ *              sat_s8(rint(o * scale2 + offset2)) (PostQuant, :3513-3600); rows that attended to nothing are 0.
+ *              Not together with peer output (tensor parallelism).
+ * dequantScale1, quantScale1, dequantScale2 (int8 QUERY: the sparse path takes f16 / bf16 queries only) and
+ * kvPaddingSize (left padding, undefined for paged KV) must be absent (SPA_ERR_UNSUPPORTED otherwise).
+ * Per-token antiquant (antiquant modes 1-5 of the tiling, sparse_paged_attention_tiling.cc:940-987) cannot be
+ * requested through this op in the reference either: its definition has no antiquant_mode attribute and no
+ * key/value_antiquant_scale inputs (sparse_paged_attention_def.cpp:200-310), ConvertContext leaves antiquantMode
+ * null (tiling.cc:2035-2052, :2156), so the mode is always 0 = per channel / per tensor -- which is built.      */
 SPA_API int spaSparsePagedAttentionGetWorkspaceSize(
     const spaTensor *query, const spaTensor *key, const spaTensor *value,
     const spaTensor *pseShift, const spaTensor *attenMask, const spaTensor *actualSeqLengths,

@@ -187,8 +187,17 @@ def attend_lists(
     num_key_value_heads: int, scale_value: float, block_size: int,
     antiquant_scale: Optional[torch.Tensor] = None, antiquant_offset: Optional[torch.Tensor] = None,
     round_p: bool = True, dtype64: bool = False, lse_out: Optional[torch.Tensor] = None,
+    pse_shift: Optional[torch.Tensor] = None, attention_mask: Optional[torch.Tensor] = None,
+    quant_scale2: Optional[torch.Tensor] = None, quant_offset2: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
     """Attention over explicit per-(b, q-head) page lists.
+
+    pse_shift [B or 1, Nq, 1, S] is added to the scaled logits, then attention_mask [B, (1, 1,) S] (non-zero =
+      masked) SETS a logit to -1e12 (..._Us2.h:2862-2899, :757).  Both are indexed by the LOGICAL token position
+      page * block_size + t (include/spa_b200.h: the reference, whose code is inherited from the dense op, indexes
+      them by the position in the walked sequence -- the same thing for a dense walk).
+    quant_scale2 (+ quant_offset2), [1] or [Nq, D]: int8 output sat(rint(o * scale2 + offset2)) (:3513-3600);
+      rows that attended to nothing are zeros.
 
     lse_out: optional float32 [B, Nq], filled with the softmax log-sum-exp ln(sum_i exp(s_i)) = ln(l) + m
       (the reference's softmaxLse output, ..._Us2.h:2601-2623); -inf for an empty list.
@@ -222,6 +231,11 @@ def attend_lists(
     if lse_out is not None:
         lse_out.fill_(-float("inf"))
     nblk = K.shape[0]
+    pse = pse_shift.detach().cpu() if pse_shift is not None and pse_shift.numel() else None
+    msk = attention_mask.detach().cpu() if attention_mask is not None and attention_mask.numel() else None
+    if msk is not None:
+        msk = msk.reshape(msk.shape[0], msk.shape[-1]) != 0
+    attended = torch.zeros(B, Nq, dtype=torch.bool)
     for b in range(len(lists)):
         for hq in range(Nq):
             ent = lists[b][hq]
@@ -242,10 +256,17 @@ def attend_lists(
             Kf = Kp.reshape(-1, D)
             Vf = Vp.reshape(-1, D)
             s = (Kf @ q[b, hq].to(ft)) * float(scale_value)
+            if pse is not None or msk is not None:
+                pos = (pages.view(-1, 1) * block_size + torch.arange(block_size).view(1, -1)).reshape(-1)
+                if pse is not None:
+                    s = s + pse[b if pse.shape[0] > 1 else 0, hq, 0, pos].to(ft)
+                if msk is not None:
+                    s = torch.where(msk[b, pos], torch.full_like(s, -1e12), s)
             s = torch.where(tokmask.reshape(-1), s, torch.full_like(s, -float("inf")))
             m = s.max()
             if not torch.isfinite(m):
                 continue
+            attended[b, hq] = True
             p = torch.exp(s - m)
             l = p.sum()
             if lse_out is not None:
@@ -254,6 +275,14 @@ def attend_lists(
                 p = p.to(qd if is_i8 else K.dtype).to(ft)
             o = (p @ Vf) / l
             out[b, hq] = o
+    if quant_scale2 is not None and quant_scale2.numel():
+        sc2 = quant_scale2.detach().cpu().to(ft).reshape(-1)
+        of2 = quant_offset2.detach().cpu().to(ft).reshape(-1) if quant_offset2 is not None and quant_offset2.numel() else torch.zeros(1, dtype=ft)
+        sc2 = sc2.view(1, Nq, D) if sc2.numel() > 1 else sc2.view(1, 1, 1)
+        of2 = of2.view(1, Nq, D) if of2.numel() > 1 else of2.view(1, 1, 1)
+        qv = torch.round(out * sc2 + of2).clamp(-128, 127)
+        qv = torch.where(attended.view(B, Nq, 1), qv, torch.zeros_like(qv))
+        return qv.to(torch.int8).reshape(shape)
     if dtype64:
         return out.reshape(shape)
     return out.to(qd).reshape(shape)
@@ -299,12 +328,14 @@ def lists_from_block_position(block_position: torch.Tensor, actual_seq_lengths, 
 def sparse_paged_attention(query, key, value, actual_seq_lengths, block_table, block_position,
                            num_heads: int, scale_value: float, num_key_value_heads: int,
                            block_size: int, antiquant_scale=None, antiquant_offset=None,
-                           round_p: bool = True, dtype64: bool = False, lse_out=None) -> torch.Tensor:
+                           round_p: bool = True, dtype64: bool = False, lse_out=None, pse_shift=None,
+                           attention_mask=None, quant_scale2=None, quant_offset2=None) -> torch.Tensor:
     """custom_ops.sparse_paged_attention (add_custom.py:41-75)."""
     lists = lists_from_block_position(block_position, actual_seq_lengths, num_heads,
                                       num_key_value_heads, block_size, block_table.shape[1])
     return attend_lists(query, key, value, block_table, lists, num_key_value_heads, scale_value,
-                        block_size, antiquant_scale, antiquant_offset, round_p, dtype64, lse_out)
+                        block_size, antiquant_scale, antiquant_offset, round_p, dtype64, lse_out,
+                        pse_shift, attention_mask, quant_scale2, quant_offset2)
 
 
 def lists_from_selection(page_position: torch.Tensor, page_position_length: torch.Tensor,
@@ -339,7 +370,8 @@ def sparse_paged_fusion_attention(query, key, value, block_table, l1_cent, block
                                   block_size: int = 128, k: int = 64, max_page_num: int = 256,
                                   antiquant_scale=None, antiquant_offset=None,
                                   round_p: bool = True, dtype64: bool = False, sink_pages: int = 0,
-                                  recent_pages: int = 0, max_fraction_den: int = 0, lse_out=None):
+                                  recent_pages: int = 0, max_fraction_den: int = 0, lse_out=None,
+                                  pse_shift=None, attention_mask=None, quant_scale2=None, quant_offset2=None):
     """custom_ops.sparse_paged_fusion_attention (add_custom.py:96-135): cent_select followed by the
     attention over the selected pages (sparse_paged_fusion_attention.cpp:56-76).  Returns
     (attention_out, block_position, page_position_length, max_page_position_length)."""
@@ -348,7 +380,8 @@ def sparse_paged_fusion_attention(query, key, value, block_table, l1_cent, block
                                 block_size, max_page_num, sink_pages, recent_pages, max_fraction_den)
     lists = lists_from_selection(pos, plen, total_seq_len, block_size)
     out = attend_lists(query[:B], key, value, block_table, lists, num_key_value_heads, scale_value,
-                       block_size, antiquant_scale, antiquant_offset, round_p, dtype64, lse_out)
+                       block_size, antiquant_scale, antiquant_offset, round_p, dtype64, lse_out,
+                       pse_shift, attention_mask, quant_scale2, quant_offset2)
     return out, pos, plen, mx
 
 

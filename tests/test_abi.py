@@ -122,9 +122,10 @@ def test_select_position_validation_needs_no_gpu(lib):
     assert f(*args(idx=tensor([4, 30, 64], SPA_I32))) == SPA_ERR_SHAPE
 
 
-def test_attention_rejects_unsupported_ifa_features_without_gpu(lib):
-    """pse_shift / attention_mask / quant scales / kv_padding are never non-empty in any reference
-    sparse test (tests/ifa_v5_case.py:133-146): the boundary refuses them instead of ignoring them."""
+def test_attention_validates_ifa_options_without_gpu(lib):
+    """pse_shift / attention_mask / quant_scale2 (+ offset) are checked as the reference tiling checks them
+    (sparse_paged_attention_tiling_check.cc:737-850, sparse_paged_attention_tiling.cc:566-647) before anything touches
+    the device; the int8-query scales and kv_padding_size stay refused."""
     ws = ctypes.c_uint64(0)
     ex = ctypes.c_void_p(0)
     q = tensor([2, 32, 128], SPA_F16)
@@ -133,20 +134,36 @@ def test_attention_rejects_unsupported_ifa_features_without_gpu(lib):
     bt = tensor([2, 32], SPA_I32)
     bp = tensor([2, 8, 256], SPA_I32)
     out = tensor([2, 32, 128], SPA_F16)
+    out8 = tensor([2, 32, 128], SPA_I8)
     extra = tensor([1], SPA_F16)
+    SPA_F32, SPA_I8_, SPA_U8, SPA_BOOL = 2, 3, 7, 8
+    S = 32 * 128
     f = lib.spaSparsePagedAttentionGetWorkspaceSize
     f.argtypes = [ctypes.c_void_p] * 16 + [ctypes.c_int64, ctypes.c_double, ctypes.c_char_p, ctypes.c_int64,
                                            ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p,
                                            ctypes.c_void_p]
 
-    def call(pse=None, mask=None, dq1=None, kvpad=None, heads=32, layout=b"BNSD", bs=128, kvh=8):
+    def call(pse=None, mask=None, dq1=None, q2=None, qo2=None, kvpad=None, heads=32, layout=b"BNSD", bs=128, kvh=8, o=out):
         p = lambda t: ctypes.cast(ctypes.pointer(t), ctypes.c_void_p) if t is not None else None
-        return f(p(q), p(kv), p(kv), p(pse), p(mask), p(asl), p(dq1), None, None, None, None, None, None, p(bt),
-                 p(kvpad), p(bp), heads, 0.088, layout, kvh, bs, 1, p(out), ctypes.addressof(ws),
+        return f(p(q), p(kv), p(kv), p(pse), p(mask), p(asl), p(dq1), None, None, p(q2), p(qo2), None, None, p(bt),
+                 p(kvpad), p(bp), heads, 0.088, layout, kvh, bs, 1, p(o), ctypes.addressof(ws),
                  ctypes.addressof(ex))
 
-    assert call(pse=extra) == SPA_ERR_UNSUPPORTED and b"pse_shift" in lib.spaGetLastError()
-    assert call(mask=extra) == SPA_ERR_UNSUPPORTED and b"attention_mask" in lib.spaGetLastError()
+    err = lambda: lib.spaGetLastError()
+    assert call(pse=extra) == SPA_ERR_SHAPE and b"pse_shift" in err()                       # not [B or 1, Nq, 1, S]
+    assert call(pse=tensor([2, 32, 1, S], SPA_BF16)) == SPA_ERR_DTYPE and b"pse_shift" in err()
+    assert call(pse=tensor([2, 32, 1, S - 1], SPA_F16)) == SPA_ERR_SHAPE and b"pse_shift" in err()
+    assert call(pse=tensor([3, 16, 1, S], SPA_F16)) == SPA_ERR_SHAPE
+    assert call(mask=extra) == SPA_ERR_DTYPE and b"attention_mask" in err()                 # bool / int8 / uint8 only
+    assert call(mask=tensor([2, 1, 1, S - 1], SPA_BOOL)) == SPA_ERR_SHAPE and b"attention_mask" in err()
+    assert call(mask=tensor([1, S], SPA_U8)) == SPA_ERR_SHAPE                               # batch of the mask < B
+    assert call(mask=tensor([2, 2, S], SPA_I8_)) == SPA_ERR_SHAPE                           # middle dims must be 1
+    assert call(q2=tensor([1], SPA_F32)) == SPA_ERR_DTYPE and b"int8" in err()              # post-quant needs an int8 output
+    assert call(o=out8) == SPA_ERR_ARG and b"quant_scale2" in err()                         # and the other way round
+    assert call(q2=tensor([1], SPA_F16), o=out8) == SPA_ERR_DTYPE
+    assert call(q2=tensor([7], SPA_F32), o=out8) == SPA_ERR_SHAPE
+    assert call(q2=tensor([1], SPA_F32), qo2=tensor([32 * 128], SPA_BF16), o=out8) == SPA_ERR_DTYPE
+    assert call(qo2=tensor([1], SPA_F32)) == SPA_ERR_ARG
     assert call(dq1=extra) == SPA_ERR_UNSUPPORTED
     assert call(kvpad=extra) == SPA_ERR_UNSUPPORTED
     assert call(heads=16) == SPA_ERR_SHAPE and b"num_heads" in lib.spaGetLastError()
