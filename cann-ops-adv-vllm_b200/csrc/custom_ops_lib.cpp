@@ -81,7 +81,7 @@ std::list<CachedExec> &plan_cache() {
 }
 bool plan_cache_enabled() {
     // off while any scheduling knob is set from the environment (they are read when an executor is planned)
-    for (const char *v : {"SPA_SMALL_PAGES", "SPA_STATIC_PCT", "SPA_DYN_RUNS", "SPA_DYN_MIN", "SPA_SEL_GW", "SPA_PAIR", "SPA_COOP"})
+    for (const char *v : {"SPA_SMALL_PAGES", "SPA_STATIC_PCT", "SPA_DYN_RUNS", "SPA_DYN_MIN", "SPA_SEL_GW", "SPA_PAIR", "SPA_COOP", "SPA_AUX_STAGE"})
         if (getenv(v)) return false;
     const char *s = getenv("SPA_PLAN_CACHE");
     return !(s && s[0] == '0');

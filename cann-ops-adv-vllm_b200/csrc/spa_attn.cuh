@@ -26,12 +26,15 @@ constexpr float kMaskedLog2 = -1e12f * kLog2e;         // BOOL_ATTEN_MASK_SCALAR
 constexpr int kMailSlots = 4;                           // flush -> post-warp messages in flight
 constexpr int kPostWarp = kConsumerWarps + 1;           // warp 8: TMA producer, warps 9..11: partial bookkeeping + combine
 
+constexpr int kAuxMask = 128;                           // bytes reserved for a page's mask in its stage's aux block
 struct AttnSmem {
-    int stages, mbuf, wml, meta, bars, mail, qst, total;
+    int stages, mbuf, wml, meta, bars, mail, qst, aux, total;
     __host__ __device__ static inline int align(int x, int a) { return (x + a - 1) / a * a; }
     // one of the two query staging buffers: g rows of kQStageStride halves + the kv head's K antiquant scales
     __host__ __device__ static inline int qstage_bytes(int g) { return g * kQStageStride * 2 + kD * 2; }
-    __host__ __device__ AttnSmem(int nstages, int stage_bytes, int nt_tiles, int g_staged) {
+    // options build: per stage, the page's attenMask bytes (kAuxMask reserved) and its g pseShift rows of bs values
+    __host__ __device__ static inline int aux_bytes(int g_pse, int bs) { return align(kAuxMask + g_pse * bs * 2, 16); }
+    __host__ __device__ AttnSmem(int nstages, int stage_bytes, int nt_tiles, int g_staged, int aux_per_stage = 0) {
         int o = 0;
         stages = o;   o = align(o + nstages * stage_bytes, 1024);
         mbuf = o;     o = align(o + kConsumerWarps * kMergeWarpFloats * 4, 16);   // 8 heads x 64 dims per warp
@@ -40,6 +43,7 @@ struct AttnSmem {
         bars = o;     o = align(o + (nstages * 2 + kPostWarps * kMailSlots * 2) * 8, 16);
         mail = o;     o = align(o + kPostWarps * kMailSlots * 32, 16);
         qst = o;      o = align(o + 2 * qstage_bytes(g_staged), 16);      // g_staged == 0: no staging
+        aux = o;      o = align(o + nstages * aux_per_stage, 16);
         total = o;
     }
 };
@@ -425,7 +429,7 @@ template <typename QT, int KVK, int NT, int PP, int OPT>
 __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t stage_u32, const int (&ks)[PP],
                                               const int (&vs)[PP], const uint32_t (&vph)[PP],
                                               const unsigned (&metas)[PP], const int (&tails)[PP],
-                                              const int (&lps)[PP], int item,
+                                              const int (&lps)[PP], int item, const unsigned char *aux,
                                               const uint32_t (&qf)[NT][8][2], float (&o)[NT][8][4],
                                               float (&m_run)[NT][2], float (&l_run)[NT][2],
                                               const float (&hsc)[NT][2], uint64_t *full, uint64_t *empty) {
@@ -443,7 +447,8 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
     // here, used after the K matmuls
     uint32_t mk[PP];                             // byte 0: row gid masked, byte 1: row gid + 8
     uint32_t psv[PP][NT][2];                     // per head: pse of (row gid, row gid + 8), query dtype
-    if (OPT) {
+    if (OPT && !p.aux_stage) {
+        // (fallback for tensors whose rows are not 16-byte aligned: read from global memory -- a round trip per page)
         const int b = item / p.Nkv, n2 = item % p.Nkv;
 #pragma unroll
         for (int pp = 0; pp < PP; ++pp) {
@@ -544,6 +549,27 @@ __device__ __forceinline__ void consume_pages(const ChainParams &p, uint32_t sta
             for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
                 for (int i = 0; i < 4; ++i) s[pp][nt][i] = (float)(s1[pp][nt][i] * 254 + s2[pp][nt][i]);
+    }
+    if (OPT && p.aux_stage) {
+        // the producer staged the page's mask bytes and pse rows next to its K image (same barrier); they are read
+        // before the K stage is released
+#pragma unroll
+        for (int pp = 0; pp < PP; ++pp) {
+            const unsigned char *ax = aux + (size_t)ks[pp] * p.aux_bytes;
+            const bool in0 = t0 + gid < tails[pp], in1 = t0 + gid + 8 < tails[pp];
+            mk[pp] = 0u;
+            if (p.mask != nullptr) mk[pp] = (in0 ? (uint32_t)ax[t0 + gid] : 0u) | (in1 ? (uint32_t)ax[t0 + gid + 8] << 8 : 0u);
+            const unsigned short *px = reinterpret_cast<const unsigned short *>(ax + kAuxMask);
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int h = nt * 8 + tig * 2 + e;
+                    psv[pp][nt][e] = 0u;
+                    if (p.pse != nullptr && h < p.g)
+                        psv[pp][nt][e] = (in0 ? (uint32_t)px[h * p.bs + t0 + gid] : 0u) | (in1 ? (uint32_t)px[h * p.bs + t0 + gid + 8] << 16 : 0u);
+                }
+        }
     }
     __syncwarp();
     if (lane == 0) {
@@ -706,7 +732,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
     // query staging is compiled into the int8 kernels only: the fp16 stream gains nothing from it (its pages are
     // twice as long) and the extra live state cost the fp16 kernels 1-2 us (same-box A/B, c2 / c4)
     const bool q_stage = KVK != kKvSame && p.q_stage;
-    AttnSmem L(p.nstages, p.stage_bytes, NT, q_stage ? p.g : 0);
+    AttnSmem L(p.nstages, p.stage_bytes, NT, q_stage ? p.g : 0, (OPT && p.aux_stage) ? p.aux_bytes : 0);
     unsigned char *stage_base = smem + L.stages;
     float *mbuf = reinterpret_cast<float *>(smem + L.mbuf);
     float *wml = reinterpret_cast<float *>(smem + L.wml);
@@ -884,6 +910,8 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                             if (2 * (pg - (qi ? qpg1 : qpg0)) <= nstages) mbar_wait(&empty[qi ? qstg1 : qstg0], qi ? qph1 : qph0);
                             tx += (uint32_t)(p.g * kD * 2) + (with_s ? (uint32_t)(kD * 2) : 0u);
                         }
+                        const bool with_aux = OPT && p.aux_stage && kv == 0;
+                        if (with_aux) tx += (p.mask != nullptr ? (uint32_t)p.bs : 0u) + (p.pse != nullptr ? (uint32_t)(p.g * p.bs * 2) : 0u);
                         mbar_expect_tx(&full[stage], tx);
                         unsigned char *dst = stage_base + (size_t)stage * p.stage_bytes;
                         const CUtensorMap *tm = kv ? tmV : tmK;
@@ -892,6 +920,17 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
                         } else {
                             tma_load_4d(dst, tm, &full[stage], 0, c[1], c[2], c[3]);
                             tma_load_4d(dst + p.stage_bytes / 2, tm, &full[stage], 64, c[1], c[2], c[3]);
+                        }
+                        if (with_aux) {
+                            // the page's mask bytes and the group's pse rows at its logical position (16-byte aligned rows)
+                            unsigned char *ax = smem + L.aux + (size_t)stage * p.aux_bytes;
+                            const size_t b = (size_t)(item / p.Nkv), pos = (size_t)(lo & 0xffffffu) * p.bs;
+                            if (p.mask != nullptr) bulk_load(ax, p.mask + b * p.mask_sb + pos, p.bs, &full[stage]);
+                            if (p.pse != nullptr)
+                                for (int h = 0; h < p.g; ++h)
+                                    bulk_load(ax + kAuxMask + (size_t)h * p.bs * 2,
+                                              reinterpret_cast<const unsigned short *>(p.pse) + b * p.pse_sb + (size_t)(n2 * p.g + h) * p.pse_sh + pos,
+                                              p.bs * 2, &full[stage]);
                         }
                         if (with_q) {
                             unsigned char *qd = qst_base + (size_t)qi * qst_bytes;
@@ -1093,7 +1132,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             const int ks[2] = {st[0], st[2]}, vs[2] = {st[1], st[3]};
             const uint32_t vph[2] = {ph[1], ph[3]};
             cnt += 2;
-            consume_pages<QT, KVK, NT, 2, OPT>(p, stage_u32, ks, vs, vph, metas, tails, lps, cur, qf, o, m_run, l_run, hsc, full, empty);
+            consume_pages<QT, KVK, NT, 2, OPT>(p, stage_u32, ks, vs, vph, metas, tails, lps, cur, smem + L.aux, qf, o, m_run, l_run, hsc, full, empty);
             stage = st[3] + 1; phase = ph[3];
             if (stage == nstages) { stage = 0; phase ^= 1u; }
         } else {
@@ -1105,7 +1144,7 @@ __device__ void attention_phase(const ChainParams &p, const CUtensorMap *tmK, co
             const int ks[1] = {stage}, vs[1] = {st1};
             const uint32_t vph[1] = {ph1};
             cnt += 1;
-            consume_pages<QT, KVK, NT, 1, OPT>(p, stage_u32, ks, vs, vph, metas, tails, lps, cur, qf, o, m_run, l_run, hsc, full, empty);
+            consume_pages<QT, KVK, NT, 1, OPT>(p, stage_u32, ks, vs, vph, metas, tails, lps, cur, smem + L.aux, qf, o, m_run, l_run, hsc, full, empty);
             stage = st1 + 1; phase = ph1;
             if (stage == nstages) { stage = 0; phase ^= 1u; }
         }

@@ -71,6 +71,7 @@ struct ChainParams {
     const void *pse; long long pse_sb, pse_sh;           // pseShift [B or 1, Nq, 1, >= maxP*bs] in the query dtype; pse_sb = 0: shared (:2862-2874)
     const void *pq_scale, *pq_offset;                    // int8 post-quant of the output (:3513-3600): [1] or [Nq, D]; `out` is int8 then
     int pq_scale_chn, pq_offset_chn, pq_bf16;            // per-channel flags; parameter dtype bf16 (else fp32)
+    int aux_stage, aux_bytes;                            // the producer stages mask / pse slices next to each K page (AttnSmem::aux)
     float scale_log2;                                    // scale_value * log2(e)
     int ax_row, ax_head, ax_blk;                         // TMA coordinate slots (1..3)
     int num_blocks;

@@ -887,14 +887,24 @@ static int plan_attention(spaExecutor *e, const spaTensor *query, const spaTenso
     p.q_stage = e->kv_i8 && (reinterpret_cast<uintptr_t>(p.q) % 16 == 0) && p.q_sb % 8 == 0 && p.q_sh % 8 == 0 &&
                 (p.aq_per_tensor || reinterpret_cast<uintptr_t>(p.aq_scale) % 16 == 0);      // (8-bit KV kernels only)
     if (const char *s = getenv("SPA_Q_STAGE")) p.q_stage = p.q_stage && atoi(s) != 0;
+    // options build: the producer stages each page's mask bytes and pse rows next to its K image (bulk copies:
+    // 16-byte aligned rows); otherwise the consumers read them from global memory, one page per step
+    p.aux_stage = 0; p.aux_bytes = 0;
+    if (p.mask != nullptr || p.pse != nullptr) {
+        const bool mask_ok = p.mask == nullptr || (reinterpret_cast<uintptr_t>(p.mask) % 16 == 0 && p.mask_sb % 16 == 0);
+        const bool pse_ok = p.pse == nullptr || (reinterpret_cast<uintptr_t>(p.pse) % 16 == 0 && p.pse_sb % 8 == 0 && p.pse_sh % 8 == 0);
+        p.aux_stage = mask_ok && pse_ok;
+        if (const char *s = getenv("SPA_AUX_STAGE")) p.aux_stage = p.aux_stage && atoi(s) != 0;
+        if (p.aux_stage) p.aux_bytes = AttnSmem::aux_bytes(p.pse != nullptr ? p.g : 0, p.bs);
+    }
     int nst = e->kv_i8 ? 12 : 6;
     for (; nst >= 2; --nst)
-        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.q_stage ? p.g : 0).total <= budget) break;
+        if (AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.q_stage ? p.g : 0, p.aux_bytes).total <= budget) break;
     if (nst < 2) return fail(SPA_ERR_UNSUPPORTED, "attention working set exceeds shared memory");
     p.nstages = nst;
-    p.pair_pages = nst >= 4 && !e->opt;      // options build: one page per step (registers for the mask / pse values)
+    p.pair_pages = nst >= 4 && (p.aux_stage || (p.mask == nullptr && p.pse == nullptr));   // (mask / pse from global memory: one page per step)
     if (const char *s = getenv("SPA_PAIR")) p.pair_pages = p.pair_pages && atoi(s) != 0;
-    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.q_stage ? p.g : 0).total;
+    int attn_bytes = AttnSmem(nst, p.stage_bytes, e->nt_tiles, p.q_stage ? p.g : 0, p.aux_bytes).total;
     int sel_bytes = p.maxP * 4;
     if (p.mode == kModeFused) {
         if ((rc = plan_select_smem(&p, kSelScores | kSelSelect | kSelUnion, d.sms, budget - 1024, &sel_bytes))) return rc;

@@ -63,11 +63,12 @@ def separate(ops, g, bp, asl, pse=None, mask=None, q2=None, qo2=None):
         g["block_table"], e64, bp, g["Nq"], g["scale"], "BNSD", g["Nkv"], g["bs"], 1)
 
 
-def make_mask_pse(c, seed, mask_dtype, pse_batch, frac=0.3):
-    """mask [B, 1, 1, S] (non-zero = masked, `frac` of the positions) and pse [B or 1, Nq, 1, S] ~ N(0, 1)."""
+def make_mask_pse(c, seed, mask_dtype, pse_batch, frac=0.3, pad=0):
+    """mask [B, 1, 1, S] (non-zero = masked, `frac` of the positions) and pse [B or 1, Nq, 1, S] ~ N(0, 1);
+    S = maxBlocksPerBatch * blockSize + pad."""
     gen = torch.Generator().manual_seed(seed)
     B, Nq = c["seq"].shape[0], c["Nq"]
-    smax = c["block_table"].shape[1] * c["bs"]
+    smax = c["block_table"].shape[1] * c["bs"] + pad
     mask = (torch.rand(B, 1, 1, smax, generator=gen) < frac).to(mask_dtype)
     pse = torch.randn(pse_batch if pse_batch else B, Nq, 1, smax, generator=gen).to(c["q"].dtype)
     return mask, pse
@@ -146,6 +147,20 @@ def test_mask_and_pse_fused_and_separate_vs_oracle(ops, kind, mask_dtype, pse_ba
                                              c["seq"], Nq, c["scale"], Nkv, 128, k, 256, *aq)
     assert torch.equal(bp0.cpu(), want0[1])
     assert_close(plain, want0[0], tol, f"plain build next to the options build, {kind}")
+
+
+def test_mask_and_pse_rows_not_16_byte_aligned(ops):
+    """S = maxBlocksPerBatch * blockSize + 3: the rows of both tensors start at odd offsets, the producer cannot stage
+    them with bulk copies, and the consumers read them from global memory instead (one page per step)."""
+    B, Nq, Nkv, C, S, k = 3, 32, 8, 128, 9000, 16
+    c = make_case(747, B, Nq, Nkv, C, S, kv_pages=B * 72 + 3, ragged=True, permute_table=True)
+    g = to_device(c, DEV)
+    mask, pse = make_mask_pse(c, 19, torch.uint8, 0, pad=3)
+    want = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"],
+                                            c["seq"], Nq, c["scale"], Nkv, 128, k, 256, pse_shift=pse, attention_mask=mask)
+    out, bp, ppl, _ = fused(ops, g, k, pse=pse.to(DEV), mask=mask.to(DEV))
+    assert torch.equal(bp.cpu(), want[1]) and torch.equal(ppl.cpu(), want[2])
+    assert_close(out, want[0], 1e-3, "unaligned mask / pse rows")
 
 
 @pytest.mark.parametrize("bs", [16, 64])
