@@ -86,6 +86,12 @@ def sparse_paged_attention(query: torch.Tensor,
     """Paged flash-decode over the pages listed in `blockposition` (add_custom.py:41-75).  key / value: the query
     dtype, int8 with `antiquant_scale` (+ `antiquant_offset`), or torch.float8_e4m3fn (scales optional).
 
+    `pse_shift` [B or 1, Nq, 1, S] (query dtype) is added to the scaled logits, `attention_mask` [B, (1, 1,) S]
+    (bool / int8 / uint8, non-zero = masked) sets them to -1e12, both at the LOGICAL token position
+    page * block_size + t (S >= blocktable.shape[1] * block_size); `quant_scale2` (+ `quant_offset2`), float32 or
+    bfloat16, 1 element or [Nq, D]: the result is int8 = sat(rint(o * scale2 + offset2)).  Empty tensors = absent,
+    as in the reference's calls.  (include/spa_b200.h has the reference citations.)
+
     `softmax_lse`: optional caller-allocated float32 [B, Nq], filled with ln(sum exp(scale * q.k)) per row
     (the reference kernels' softmaxLse output); fp16/bf16 and int8 KV."""
     actual_seq_lengths = _tensor(actual_seq_lengths, torch.int64, query.device)
