@@ -25,7 +25,8 @@ on the selected-KV bytes).  Prints ONE JSON line on rank 0.
             else a bounded sample); cpu_baseline_vectorised = the same chain with batched torch ops
             (oracle/fast_chain.py), the "fair CPU" number of BASELINE.md section 3.
   extra_workloads (N=1, default run)  the same measurement for BASELINE configs[2] (c3: int8 KV),
-            configs[3] (c4: 70B shape) and c2 with randn centroids (independent heads: larger union).
+            configs[3] (c4: 70B shape), c2 with randn centroids (independent heads: larger union), c3 with
+            contiguous page-head slices / FP8 pages, and c2 with attention_mask + pse_shift (options build).
   strong_c4 (N>1)  STRONG scaling of configs[3] (c4, B=32 fixed, KV heads split over the ranks):
             ms/step at N, at N=1 (rank 0 alone, same run), speed-up and efficiency.
   gather_verified (N>1)  the fused peer-store all-gather compared, outside the timed region, bit for
@@ -98,6 +99,10 @@ WORKLOADS = {
                desc="Llama-3-8B decode, int8 KV (antiquant), bf16 query: B=64 seq 32k C=512 top-k=64, fused"),
     "c3_fp8": dict(B=64, Nq=32, Nkv=8, S=32768, C=512, k=64, q="bf16", kv="f8",
                    desc="c3 with FP8 (e4m3) KV pages instead of int8 + antiquant: B=64 seq 32k C=512 top-k=64, bf16 query, fused"),
+    # the inherited IFA options: attention_mask (30 % of the positions) + pse_shift [B, Nq, 1, S] on c2;
+    # runs the options build of the chain kernel (csrc/spa_kernels_opt.cu)
+    "c2_mask_pse": dict(B=16, Nq=32, Nkv=8, S=32768, C=512, k=64, q="f16", kv="f16", opts="mask_pse",
+                        desc="c2 with attention_mask + pse_shift (options build): B=16 32Q/8KV D=128 seq 32k C=512 top-k=64 fp16 KV, fused"),
     "c4": dict(B=32, Nq=64, Nkv=8, S=131072, C=2048, k=128, q="f16", kv="f16",
                desc="Llama-3-70B decode: B=32 64Q/8KV D=128 seq 128k C=2048 top-k=128 fp16 KV, fused"),
     # corners of the configs[4] sweep (tools/sweep.py), for traces
@@ -358,6 +363,13 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
     i8 = w["kv"] == "i8"
     peer = world > 1 and args.gather == "peer"
     aq = dict(antiquant_scale=inp["aq_scale"] if i8 else None, antiquant_offset=inp["aq_offset"] if i8 else None)
+    opt_mask = opt_pse = None
+    if w.get("opts") == "mask_pse":
+        assert world == 1, "the options workloads are single-GPU lines"
+        g_opt = torch.Generator(device=dev).manual_seed(77)
+        smax = inp["P"] * BS
+        opt_mask = torch.rand(B, 1, 1, smax, generator=g_opt, device=dev) < 0.3
+        opt_pse = torch.randn(B, nq, 1, smax, generator=g_opt, device=dev).to(qd)
     if world > 1:
         from kvhead_tp import HeadGather, head_shard
         gather = HeadGather(out.shape, qd, dev)                      # NCCL all-gather of the output shards
@@ -371,7 +383,7 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
     else:
         plan = custom_ops.FusedDecodePlan(inp["q"], inp["key"], inp["value"], inp["block_table"], inp["l1"],
                                           inp["block_ids"], inp["seq"], bp, ppl, mppl, out, nq, inp["scale"], nkv, BS,
-                                          k=inp["k"], **aq)
+                                          k=inp["k"], pse_shift=opt_pse, attention_mask=opt_mask, **aq)
     flush = None if args.no_flush else L2Flush(dev)
 
     def step():
@@ -441,6 +453,9 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
 
     # ---------------- device-resident timing ----------------
     ab = algorithmic_bytes(inp, bp, ppl)
+    if opt_mask is not None:
+        # + one mask byte and g pse values (2 bytes) per position of every union page
+        ab["bytes_alg"] += ab["union_pages"] * BS * (1 + 2 * (nq // nkv))
     sampler = ClockSampler(ctx["local_rank"]) if (rank == 0 and sample_clocks) else None
     if sampler:
         sampler.start()
@@ -488,7 +503,8 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
                 hout.copy_(dshard, non_blocking=True)
                 return
             o, _, _ = custom_ops.sparse_paged_fusion_attention(
-                sq, inp["key"], inp["value"], e, e, e64, e, e, e, e, e, inp["aq_scale"], inp["aq_offset"], sbt, e64,
+                sq, inp["key"], inp["value"], e if opt_pse is None else opt_pse, e if opt_mask is None else opt_mask,
+                e64, e, e, e, e, e, inp["aq_scale"], inp["aq_offset"], sbt, e64,
                 inp["l1"], inp["block_ids"], sseq, bp, ppl, mppl, nq, inp["scale"], "BNSD", nkv, BS, 1, k=inp["k"])
             if world > 1 and args.gather == "nccl":
                 gather(o, out_full)
@@ -525,7 +541,7 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
     rec = None
     if rank == 0:
         achieved = ab["bytes_alg"] / (ms_per_step * 1e-3) / 1e9      # per-GPU kernel (rank 0's launch)
-        traffic, traffic_src = measured_traffic(name) if (world == 1 and cent_dist == "rand") else (None, "not captured for this configuration")
+        traffic, traffic_src = measured_traffic(name) if (world == 1 and cent_dist == "rand" and not w.get("opts")) else (None, "not captured for this configuration")
         rec = {
             "workload": name, "B": B, "ms_per_step": ms_per_step, "value": B / (ms_per_step * 1e-3),
             "achieved_hbm_gbs_selected_kv": agg[1].item() / (ms_per_step * 1e-3) / 1e9,
@@ -630,7 +646,7 @@ def main():
         xs = max(10, min(args.steps, 30))
         # (c3_bnsd: int8 KV with contiguous page-head slices -- in the vLLM layout an int8 row is 128 B at a 1 KiB stride)
         for nm, cd, lay in (("c3", "rand", None), ("c4", "rand", None), ("c2", "randn", None), ("c3", "rand", "bnsd"),
-                            ("c3_fp8", "rand", None)):
+                            ("c3_fp8", "rand", None), ("c2_mask_pse", "rand", None)):
             r = bench_workload(args, nm, ctx, xs, args.warmup, cent_dist=cd, kv_layout=lay)
             extra[nm + ("" if cd == "rand" else f"_{cd}") + (f"_{lay}" if lay else "")] = dict(brief(r), steps=xs)
             del r

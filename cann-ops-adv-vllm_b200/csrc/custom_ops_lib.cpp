@@ -295,10 +295,15 @@ std::shared_ptr<FusionPlan> make_fusion_plan(
     const at::Tensor &page_position_length, const at::Tensor &max_page_position_length,
     const at::Tensor &attention_out, int64_t num_heads, double scale_value, const std::string &input_layout,
     int64_t num_key_value_heads, int64_t block_size, int64_t inner_precise, int64_t k, int64_t sink_pages,
-    int64_t recent_pages, int64_t max_fraction_den, const c10::optional<at::Tensor> &softmax_lse) {
+    int64_t recent_pages, int64_t max_fraction_den, const c10::optional<at::Tensor> &softmax_lse,
+    const c10::optional<at::Tensor> &pse_shift, const c10::optional<at::Tensor> &attention_mask,
+    const c10::optional<at::Tensor> &quant_scale2, const c10::optional<at::Tensor> &quant_offset2) {
     TORCH_CHECK(query.is_cuda(), "sparse_paged_fusion_attention: the CUDA extension only runs on CUDA tensors");
     c10::cuda::CUDAGuard guard(query.device());
     auto plan = std::make_shared<FusionPlan>();
+    auto opt = [](const c10::optional<at::Tensor> &t) { return t.has_value() ? *t : at::Tensor(); };
+    Desc pse = desc(opt(pse_shift), "pse_shift"), am = desc(opt(attention_mask), "attention_mask"),
+         q2 = desc(opt(quant_scale2), "quant_scale2"), qo2 = desc(opt(quant_offset2), "quant_offset2");
     Desc q = desc(query, "query"), kk = desc(key, "key"), v = desc(value, "value"),
          as = desc(antiquant_scale, "antiquant_scale"), ao = desc(antiquant_offset, "antiquant_offset"),
          bt = desc(blocktable, "blocktable"), lc = desc(l1_cent, "l1_cent"), bi = desc(block_ids, "block_ids"),
@@ -307,7 +312,7 @@ std::shared_ptr<FusionPlan> make_fusion_plan(
          mp = desc(max_page_position_length, "max_page_position_length", true),
          o = desc(attention_out, "attention_out", true);
     check(spaSparsePagedFusionAttentionGetWorkspaceSize(
-              q.ptr(), kk.ptr(), v.ptr(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+              q.ptr(), kk.ptr(), v.ptr(), pse.ptr(), am.ptr(), nullptr, nullptr, nullptr, nullptr, q2.ptr(), qo2.ptr(),
               as.ptr(), ao.ptr(), bt.ptr(), nullptr, lc.ptr(), bi.ptr(), ts.ptr(), num_heads, scale_value,
               input_layout.c_str(), num_key_value_heads, block_size, inner_precise, k, bp.ptr(), pl.ptr(), mp.ptr(),
               o.ptr(), &plan->ws_bytes, &plan->exec),
@@ -317,6 +322,8 @@ std::shared_ptr<FusionPlan> make_fusion_plan(
               "sparse_paged_fusion_attention");
     set_lse(plan->exec, softmax_lse, "sparse_paged_fusion_attention");
     if (softmax_lse.has_value() && softmax_lse->defined()) plan->keep.push_back(*softmax_lse);
+    for (const auto *t : {&pse_shift, &attention_mask, &quant_scale2, &quant_offset2})
+        if (t->has_value() && (*t)->defined()) plan->keep.push_back(**t);
     plan->workspace = alloc_ws(plan->ws_bytes, query);
     // the plan owns its workspace and nothing else writes to it: the queue words need clearing only once
     check(spaExecutorSetPersistentWorkspace(plan->exec, 1), "spaExecutorSetPersistentWorkspace");

@@ -202,7 +202,8 @@ class FusedDecodePlan:
                  block_position, page_position_length, max_page_position_length, attention_out,
                  num_heads, scale_value, num_key_value_heads, block_size=128, *, k=64,
                  antiquant_scale=None, antiquant_offset=None, input_layout="BNSD", inner_precise=1,
-                 sink_pages=0, recent_pages=0, max_fraction_den=0, softmax_lse=None):
+                 sink_pages=0, recent_pages=0, max_fraction_den=0, softmax_lse=None,
+                 pse_shift=None, attention_mask=None, quant_scale2=None, quant_offset2=None):
         empty = torch.empty(0, dtype=query.dtype, device=query.device)
         self.attention_out = attention_out
         self._plan = custom_ops_lib.make_fusion_plan(
@@ -211,7 +212,8 @@ class FusedDecodePlan:
             total_seq_len, block_position, page_position_length, max_page_position_length,
             attention_out, int(num_heads), float(scale_value), input_layout,
             int(num_key_value_heads), int(block_size), int(inner_precise), int(k), int(sink_pages),
-            int(recent_pages), int(max_fraction_den), softmax_lse)
+            int(recent_pages), int(max_fraction_den), softmax_lse, pse_shift, attention_mask, quant_scale2,
+            quant_offset2)
 
     @property
     def workspace_bytes(self) -> int:
