@@ -541,7 +541,7 @@ def bench_workload(args, name, ctx, steps, warmup, scaling="weak", cent_dist="ra
     rec = None
     if rank == 0:
         achieved = ab["bytes_alg"] / (ms_per_step * 1e-3) / 1e9      # per-GPU kernel (rank 0's launch)
-        traffic, traffic_src = measured_traffic(name) if (world == 1 and cent_dist == "rand" and not w.get("opts")) else (None, "not captured for this configuration")
+        traffic, traffic_src = measured_traffic(name) if (world == 1 and cent_dist == "rand" and kv_layout == "bsnd" and not w.get("opts")) else (None, "not captured for this configuration")
         rec = {
             "workload": name, "B": B, "ms_per_step": ms_per_step, "value": B / (ms_per_step * 1e-3),
             "achieved_hbm_gbs_selected_kv": agg[1].item() / (ms_per_step * 1e-3) / 1e9,
