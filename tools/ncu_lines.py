@@ -21,8 +21,9 @@ def main():
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
     tmp = tempfile.mkdtemp()
     subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, check=True, stdout=subprocess.DEVNULL)
-    cubin = [os.path.join(tmp, f) for f in os.listdir(tmp) if f.endswith(".cubin")][0]
-    dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout.splitlines()
+    dis = []                                                   # (one cubin per translation unit)
+    for cubin in sorted(os.path.join(tmp, f) for f in os.listdir(tmp) if f.endswith(".cubin")):
+        dis += subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout.splitlines()
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     kname = rows[0][1]
@@ -72,6 +73,15 @@ def main():
             if v:
                 per[key][1][hdr[i]] += v
     print(f"kernel: {kname}\ntotal samples {total}")
+    # per source file: samples and the stall reasons behind them
+    byfile = defaultdict(lambda: [0, defaultdict(int)])
+    for (f, l), (sm, st) in per.items():
+        byfile[f][0] += sm
+        for k, v in st.items():
+            byfile[f][1][k] += v
+    for f, (sm, st) in sorted(byfile.items(), key=lambda kv: -kv[1][0]):
+        tops = ", ".join(f"{k[6:]} {v}" for k, v in sorted(st.items(), key=lambda kv: -kv[1])[:8])
+        print(f"  {f:18s} {sm:6d} samples ({100 * sm / max(total, 1):4.1f} %): {tops}")
     srcs = {}
     for (f, l), (s, st) in sorted(per.items(), key=lambda kv: -kv[1][0])[:top]:
         if f not in srcs:
