@@ -54,6 +54,7 @@ class SparseDecodeBackend:
         self.max_page_position_length = torch.empty(max_batch, 8, dtype=torch.int64, device=dev)
         self.attention_out = torch.empty(max_batch, self.num_heads, head_dim, dtype=dtype, device=dev)
         self._cache = None
+        self._bias = (None, None)
         self._plans: Dict[int, object] = {}
         self._graphs: Dict[int, tuple] = {}
 
@@ -65,6 +66,24 @@ class SparseDecodeBackend:
         [Nkv, C, D] and the per-page cluster ids [Nkv, blocks] of this layer (this rank's heads).  The
         tensors are cache STATE: they are bound once and updated in place by the engine."""
         self._cache = (key_cache, value_cache, l1_cent, block_ids, antiquant_scale, antiquant_offset)
+        self._close_plans()
+
+    def bind_bias(self, pse_shift: Optional[torch.Tensor] = None, attention_mask: Optional[torch.Tensor] = None) -> None:
+        """Optional per-position inputs of the attention (the reference op's pse_shift / attention_mask,
+        include/spa_b200.h): pse_shift [max_batch or 1, Nq, 1, >= max_blocks_per_seq * block_size] in the query dtype
+        (added to the scaled logits, e.g. a relative-position bias), attention_mask [max_batch, 1, 1, same S] bool /
+        int8 / uint8 (non-zero = the position is not attended).  Positions are LOGICAL token positions of each
+        sequence.  Like the caches they are state: bound once, updated in place by the engine; rows [:B] are used by a
+        step of batch size B.  They select the options build of the kernel; None switches them off again."""
+        if self.world > 1 and (pse_shift is not None or attention_mask is not None):
+            raise NotImplementedError("pse_shift / attention_mask are not wired through the tensor-parallel plan")
+        smin = self.max_blocks * self.block_size
+        if pse_shift is not None and (pse_shift.dim() != 4 or pse_shift.shape[0] not in (1, self.max_batch) or
+                                      pse_shift.shape[1] != self.num_heads or pse_shift.shape[3] < smin):
+            raise ValueError(f"pse_shift: expected [{self.max_batch} or 1, {self.num_heads}, 1, >= {smin}]")
+        if attention_mask is not None and (attention_mask.shape[0] != self.max_batch or attention_mask.shape[-1] < smin):
+            raise ValueError(f"attention_mask: expected [{self.max_batch}, 1, 1, >= {smin}]")
+        self._bias = (pse_shift, attention_mask)
         self._close_plans()
 
     def _close_plans(self):
@@ -91,8 +110,11 @@ class SparseDecodeBackend:
             plan = TPFusedDecode(self.shard, self.num_heads_total, *args, self.scale, self.block_size, k=self.top_k,
                                  antiquant_scale=aqs, antiquant_offset=aqo, group=self.tp_group)
         else:
+            pse, mask = self._bias
             plan = FusedDecodePlan(*args, self.attention_out[:B], self.num_heads, self.scale, self.num_kv_heads,
-                                   self.block_size, k=self.top_k, antiquant_scale=aqs, antiquant_offset=aqo)
+                                   self.block_size, k=self.top_k, antiquant_scale=aqs, antiquant_offset=aqo,
+                                   pse_shift=None if pse is None else (pse if pse.shape[0] == 1 else pse[:B]),
+                                   attention_mask=None if mask is None else mask[:B])
         self._plans[B] = plan
         return plan
 

@@ -236,3 +236,31 @@ def test_post_quant_with_mask_and_pse_and_empty_rows(ops):
     assert int(out[1].cpu().int().abs().max()) == 0, "rows of an empty sequence must be zeros"
     d = (out.cpu().int() - want[0].int()).abs()
     assert int(d.max()) <= 1 and float((d == 0).float().mean()) > 0.9
+
+
+def test_decode_backend_with_bias_and_mask_and_graph_replay(ops):
+    """SparseDecodeBackend.bind_bias: the persistent pse_shift / attention_mask of a layer go into every step's launch
+    (eager and CUDA-graph replay, two batch sizes), and unbinding returns to the plain kernel."""
+    from decode_backend import SparseDecodeBackend
+    B, Nq, Nkv, C, S, k = 4, 16, 4, 64, 5000, 8
+    c = make_case(757, B, Nq, Nkv, C, S, kv_pages=B * 40 + 3, ragged=True, permute_table=True)
+    g = to_device(c, DEV)
+    P = c["block_table"].shape[1]
+    be = SparseDecodeBackend(Nq, Nkv, 128, 128, k, max_batch=B, max_blocks_per_seq=P, dtype=torch.float16, device=DEV,
+                             scale=c["scale"], max_page_num=256)
+    be.bind_cache(g["key"], g["value"], g["l1"], g["block_ids"])
+    mask, pse = make_mask_pse(c, 23, torch.bool, 1)
+    be.bind_bias(pse.to(DEV), mask.to(DEV))
+    for nb, graph in ((B, False), (2, False), (B, True), (B, True)):
+        out = be.forward_decode(g["q"][:nb], g["block_table"][:nb], g["seq"][:nb], use_graph=graph)
+        want = oc.sparse_paged_fusion_attention(c["q"][:nb], c["key"], c["value"], c["block_table"][:nb], c["l1"], c["block_ids"],
+                                                c["seq"][:nb], Nq, c["scale"], Nkv, 128, k, 256, pse_shift=pse,
+                                                attention_mask=mask[:nb])
+        assert torch.equal(be.selection(nb)[0].cpu(), want[1])
+        assert_close(out, want[0], 1e-3, f"backend with bias + mask, batch {nb}, graph={graph}")
+    be.bind_bias(None, None)
+    out = be.forward_decode(g["q"], g["block_table"], g["seq"])
+    want = oc.sparse_paged_fusion_attention(c["q"], c["key"], c["value"], c["block_table"], c["l1"], c["block_ids"],
+                                            c["seq"], Nq, c["scale"], Nkv, 128, k, 256)
+    assert_close(out, want[0], 1e-3, "backend after unbinding the bias")
+    be.close()
